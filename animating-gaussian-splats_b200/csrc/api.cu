@@ -1,0 +1,248 @@
+// api.cu -- the extern "C" surface of libgsb200.so (see include/gsb200.h) and the host orchestration
+// that replaces CudaRasterizer::Rasterizer::forward/backward (cr/rasterizer_impl.cu:198-436).
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include "common.cuh"
+
+namespace gsb {
+
+static thread_local char g_err[512] = "";
+void set_last_error(const char* what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+}
+
+// Small per-thread pinned staging block: per-camera scalars go up, num_rendered + error flag come down.
+struct HostStage {
+  void* pinned = nullptr;      // [0..63]: downloads; [64..]: CamParams upload area
+  size_t bytes = 0;
+  cudaEvent_t ev = nullptr;    // guards re-use of the upload area by a later call
+  bool ev_pending = false;
+};
+static thread_local HostStage g_stage;
+
+static int stage_reserve(size_t bytes) {
+  if (g_stage.bytes >= bytes) return GSB_OK;
+  if (g_stage.ev_pending) { GSB_CUDA_CHECK(cudaEventSynchronize(g_stage.ev)); g_stage.ev_pending = false; }
+  if (g_stage.pinned) GSB_CUDA_CHECK(cudaFreeHost(g_stage.pinned));
+  g_stage.pinned = nullptr;
+  g_stage.bytes = 0;
+  GSB_CUDA_CHECK(cudaMallocHost(&g_stage.pinned, bytes));
+  g_stage.bytes = bytes;
+  if (!g_stage.ev) GSB_CUDA_CHECK(cudaEventCreateWithFlags(&g_stage.ev, cudaEventDisableTiming));
+  return GSB_OK;
+}
+
+// Bump-pointer carve-up of a byte buffer, 256-B aligned (the reference aligns to 128 B,
+// cr/rasterizer_impl.h:21-29).
+struct Carver {
+  char* p;
+  size_t off = 0;
+  explicit Carver(char* base) : p(base) {}
+  template <typename T>
+  T* take(size_t count) {
+    off = align_up(off, 256);
+    T* r = reinterpret_cast<T*>(p ? p + off : nullptr);
+    off += count * sizeof(T);
+    return r;
+  }
+};
+
+struct GeomLayout {
+  static size_t carve(char* base, int64_t P, int n_cams, gsb_raster_ctx* c, CamParams** cams, int** err,
+                      void** scan_scratch) {
+    Carver k(base);
+    const size_t n = (size_t)P * n_cams;
+    float* depths = k.take<float>(n);
+    int32_t* radii = k.take<int32_t>(n);
+    float* means2D = k.take<float>(2 * n);
+    float* cov3D = k.take<float>(6 * n);
+    float* conic = k.take<float>(4 * n);
+    uint32_t* tt = k.take<uint32_t>(n);
+    uint32_t* po = k.take<uint32_t>(n);
+    CamParams* cp = k.take<CamParams>(n_cams);
+    int* e = k.take<int>(4);
+    void* ss = k.take<char>(scan_scratch_bytes((int64_t)n));
+    if (c) {
+      c->depths = depths; c->radii = radii; c->means2D = means2D; c->cov3D = cov3D; c->conic_opacity = conic;
+      c->tiles_touched = tt; c->point_offsets = po;
+    }
+    if (cams) *cams = cp;
+    if (err) *err = e;
+    if (scan_scratch) *scan_scratch = ss;
+    return align_up(k.off, 256);
+  }
+};
+
+static size_t carve_image(char* base, int W, int H, int n_cams, int tiles_total, gsb_raster_ctx* c) {
+  Carver k(base);
+  const size_t n = (size_t)W * H * n_cams;
+  float* ft = k.take<float>(n);
+  uint32_t* nc = k.take<uint32_t>(n);
+  uint32_t* rg = k.take<uint32_t>(2 * (size_t)tiles_total);
+  if (c) { c->final_T = ft; c->n_contrib = nc; c->ranges = rg; }
+  return align_up(k.off, 256);
+}
+
+static size_t carve_binning(char* base, int64_t R, gsb_raster_ctx* c) {
+  Carver k(base);
+  const size_t n = (size_t)(R > 0 ? R : 1);
+  uint32_t* pl = k.take<uint32_t>(n);
+  uint32_t* plu = k.take<uint32_t>(n);
+  uint64_t* keys = k.take<uint64_t>(n);
+  uint64_t* keysu = k.take<uint64_t>(n);
+  void* tmp = k.take<char>(sort_temp_bytes(R));
+  if (c) {
+    c->point_list = pl; c->point_list_unsorted = plu; c->point_list_keys = keys; c->point_list_keys_unsorted = keysu;
+    c->sort_temp = tmp;
+  }
+  return align_up(k.off, 256);
+}
+
+static uint32_t higher_msb(uint32_t n) {  // getHigherMsb, cr/rasterizer_impl.cu:35-50
+  uint32_t msb = sizeof(n) * 4, step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+
+}  // namespace gsb
+
+using namespace gsb;
+
+extern "C" {
+
+const char* gsb_version(void) { return "gsb200 0.1 (sm_100a)"; }
+const char* gsb_last_error(void) { return g_err; }
+
+size_t gsb_geom_bytes(int32_t P, int32_t n_cams) {
+  return GeomLayout::carve(nullptr, P, n_cams, nullptr, nullptr, nullptr, nullptr);
+}
+size_t gsb_image_bytes(int32_t width, int32_t height, int32_t n_cams) {
+  const int tiles = ((width + GSB_TILE - 1) / GSB_TILE) * ((height + GSB_TILE - 1) / GSB_TILE) * n_cams;
+  return carve_image(nullptr, width, height, n_cams, tiles, nullptr);
+}
+size_t gsb_binning_bytes(int64_t num_rendered, int32_t n_tiles_total) {
+  (void)n_tiles_total;
+  return carve_binning(nullptr, num_rendered, nullptr);
+}
+uint32_t gsb_higher_msb(uint32_t n) { return higher_msb(n); }
+
+int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_alloc_fn binning_alloc,
+                       gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth, int32_t* radii,
+                       gsb_raster_ctx* ctx, void* stream) {
+  if (!a || !ctx || !geom_alloc || !binning_alloc || !image_alloc) return GSB_EINVAL;
+  if (a->P < 0 || a->n_cams <= 0 || a->width <= 0 || a->height <= 0) return GSB_EINVAL;
+  if (!a->tanfovx_host || !a->tanfovy_host) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  memset(ctx, 0, sizeof(*ctx));
+  ctx->P = a->P; ctx->n_cams = a->n_cams; ctx->width = a->width; ctx->height = a->height;
+  ctx->tiles_x = (a->width + GSB_TILE - 1) / GSB_TILE;
+  ctx->tiles_y = (a->height + GSB_TILE - 1) / GSB_TILE;
+  const int tiles_total = ctx->tiles_x * ctx->tiles_y * a->n_cams;
+  ctx->sort_bits = 32 + (int)higher_msb((uint32_t)tiles_total);
+  if (a->P == 0) return GSB_OK;  // the glue returns zero images, like DGR/rasterize_points.cu:81
+  if (!a->means3D || !a->colors || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->background ||
+      !out_color || !out_depth)
+    return GSB_EINVAL;
+  if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSB_EINVAL;
+
+  // geometry + image state
+  char* geom = geom_alloc(user, gsb_geom_bytes(a->P, a->n_cams));
+  char* img = image_alloc(user, gsb_image_bytes(a->width, a->height, a->n_cams));
+  if (!geom || !img) return GSB_ENOMEM;
+  CamParams* cams_dev; int* err_dev; void* scan_scratch;
+  GeomLayout::carve(geom, a->P, a->n_cams, ctx, &cams_dev, &err_dev, &scan_scratch);
+  carve_image(img, a->width, a->height, a->n_cams, tiles_total, ctx);
+
+  // per-camera scalars: focal = dim / (2 tanfov) (cr/rasterizer_impl.cu:222-223)
+  int rc = stage_reserve(64 + sizeof(CamParams) * (size_t)a->n_cams);
+  if (rc) return rc;
+  if (g_stage.ev_pending) { GSB_CUDA_CHECK(cudaEventSynchronize(g_stage.ev)); g_stage.ev_pending = false; }
+  CamParams* cams_host = reinterpret_cast<CamParams*>(reinterpret_cast<char*>(g_stage.pinned) + 64);
+  for (int i = 0; i < a->n_cams; i++) {
+    cams_host[i].tanfovx = a->tanfovx_host[i];
+    cams_host[i].tanfovy = a->tanfovy_host[i];
+    cams_host[i].focal_y = (float)a->height / (2.0f * a->tanfovy_host[i]);
+    cams_host[i].focal_x = (float)a->width / (2.0f * a->tanfovx_host[i]);
+  }
+  GSB_CUDA_CHECK(cudaMemcpyAsync(cams_dev, cams_host, sizeof(CamParams) * (size_t)a->n_cams, cudaMemcpyHostToDevice, st));
+  GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
+
+  if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, err_dev, st))) return rc;
+  const int64_t n_slots = (int64_t)a->P * a->n_cams;
+  if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st))) return rc;
+
+  // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
+  uint32_t* down = reinterpret_cast<uint32_t*>(g_stage.pinned);
+  GSB_CUDA_CHECK(cudaMemcpyAsync(down, ctx->point_offsets + n_slots - 1, 4, cudaMemcpyDeviceToHost, st));
+  GSB_CUDA_CHECK(cudaMemcpyAsync(down + 1, err_dev, 4, cudaMemcpyDeviceToHost, st));
+  GSB_CUDA_CHECK(cudaStreamSynchronize(st));
+  if ((int)down[1] != 0) return (int)down[1];
+  ctx->num_rendered = (int64_t)down[0];
+
+  char* bin = binning_alloc(user, gsb_binning_bytes(ctx->num_rendered, tiles_total));
+  if (!bin) return GSB_ENOMEM;
+  carve_binning(bin, ctx->num_rendered, ctx);
+
+  if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
+  if ((rc = launch_sort_pairs(ctx->num_rendered, ctx->point_list_keys_unsorted, ctx->point_list_keys,
+                              ctx->point_list_unsorted, ctx->point_list, ctx->sort_bits, ctx->sort_temp, st)))
+    return rc;
+  if ((rc = launch_tile_ranges(*ctx, st))) return rc;
+  if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
+  return GSB_OK;
+}
+
+int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                        float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                        float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot, void* stream) {
+  if (!a || !ctx) return GSB_EINVAL;
+  if (a->P == 0) return GSB_OK;
+  if (!dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor || !dL_dmean3D) return GSB_EINVAL;
+  if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height)
+    return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t n = (size_t)a->P * a->n_cams;
+  GSB_CUDA_CHECK(cudaMemsetAsync(dL_dmean2D, 0, n * 3 * sizeof(float), st));
+  GSB_CUDA_CHECK(cudaMemsetAsync(dL_dconic, 0, n * 4 * sizeof(float), st));
+  GSB_CUDA_CHECK(cudaMemsetAsync(dL_dopacity, 0, (size_t)a->P * sizeof(float), st));
+  const size_t ncol = a->color_cam_stride ? ((size_t)(a->n_cams - 1) * a->color_cam_stride + (size_t)a->P * 3)
+                                          : (size_t)a->P * 3;
+  GSB_CUDA_CHECK(cudaMemsetAsync(dL_dcolor, 0, ncol * sizeof(float), st));
+  int rc;
+  if (ctx->num_rendered > 0)
+    if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, st))) return rc;
+  // the per-camera scalar table still sits in the geometry buffer next to the state arrays
+  CamParams* cams_dev;
+  GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &cams_dev, nullptr, nullptr);
+  if ((rc = launch_preprocess_bwd(*a, cams_dev, *ctx, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcov3D, dL_dscale,
+                                  dL_drot, st)))
+    return rc;
+  return GSB_OK;
+}
+
+int gsb_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream) {
+  (void)projmatrix;
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return GSB_EINVAL;
+  return launch_mark_visible(P, means3D, viewmatrix, present, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t gsb_scan_scratch_bytes(int32_t n) { return scan_scratch_bytes(n); }
+int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream) {
+  if (n < 0 || (n > 0 && (!in || !out || !scratch))) return GSB_EINVAL;
+  return launch_inclusive_scan_u32(n, in, out, scratch, reinterpret_cast<cudaStream_t>(stream));
+}
+size_t gsb_sort_temp_bytes(int64_t n) { return sort_temp_bytes(n); }
+int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
+                   uint32_t* vals_out, int32_t end_bit, void* temp, void* stream) {
+  if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !temp))) return GSB_EINVAL;
+  return launch_sort_pairs(n, keys_in, keys_out, vals_in, vals_out, end_bit, temp,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

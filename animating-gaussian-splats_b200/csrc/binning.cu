@@ -1,0 +1,476 @@
+// binning.cu -- inclusive scan, (tile|depth) key emission, hand-written onesweep radix sort, tile ranges.
+//
+// Replaces cub::DeviceScan::InclusiveSum (cr/rasterizer_impl.cu:277-278), duplicateWithKeys (:70-111),
+// cub::DeviceRadixSort::SortPairs (:304-309) and identifyTileRanges (:116-138).  No CUB/Thrust.
+// All integer work: results are bit-identical to the reference by construction (inclusive prefix
+// sum; *stable* ascending LSD sort on bits [0, end_bit)).
+#include <algorithm>
+#include "common.cuh"
+
+namespace gsb {
+
+// ------------------------------------------------------------------------------------------------
+// Single-pass inclusive scan with decoupled look-back (one read + one write of the data).
+// Tile = 256 threads x 8 items.  Tile status word: (flag << 32) | value, flag 1 = aggregate,
+// 2 = inclusive prefix.  Tiles take their index from an atomic ticket, so a tile can only wait on
+// tiles that already started (forward-progress safe).
+// ------------------------------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+size_t scan_scratch_bytes(int64_t n) {
+  const int64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  return align_up(16 + (size_t)(tiles > 0 ? tiles : 1) * sizeof(unsigned long long), 256);
+}
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
+                unsigned int* __restrict__ ticket, unsigned long long* __restrict__ status) {
+  __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+  __shared__ uint32_t s_tile, s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const long long base = (long long)tile * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
+
+  uint32_t v[SCAN_ITEMS];
+  if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0)) {
+    const uint4 a = *reinterpret_cast<const uint4*>(in + base);
+    const uint4 b = *reinterpret_cast<const uint4*>(in + base + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) v[k] = (base + k < n) ? in[base + k] : 0u;
+  }
+  uint32_t run = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { run += v[k]; v[k] = run; }
+
+  // block exclusive scan of the per-thread totals
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t inc = run;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  uint32_t warp_off = 0, block_total = 0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; w++) {
+    const uint32_t t = s_warp[w];
+    if (w < warp) warp_off += t;
+    block_total += t;
+  }
+  const uint32_t thread_excl = warp_off + inc - run;
+
+  // decoupled look-back by thread 0 (tiles are few: n / 2048)
+  if (threadIdx.x == 0) {
+    uint32_t prefix = 0;
+    if (tile == 0) {
+      st_relaxed_u64(status, (2ull << 32) | block_total);
+    } else {
+      st_relaxed_u64(status + tile, (1ull << 32) | block_total);
+      long long p = (long long)tile - 1;
+      while (true) {
+        unsigned long long s = ld_relaxed_u64(status + p);
+        while ((s >> 32) == 0) s = ld_relaxed_u64(status + p);
+        prefix += (uint32_t)s;
+        if ((s >> 32) == 2) break;
+        p--;
+      }
+      st_relaxed_u64(status + tile, (2ull << 32) | (uint32_t)(prefix + block_total));
+    }
+    s_prefix = prefix;
+  }
+  __syncthreads();
+  const uint32_t add = s_prefix + thread_excl;
+  if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0)) {
+    *reinterpret_cast<uint4*>(out + base) = make_uint4(v[0] + add, v[1] + add, v[2] + add, v[3] + add);
+    *reinterpret_cast<uint4*>(out + base + 4) = make_uint4(v[4] + add, v[5] + add, v[6] + add, v[7] + add);
+  } else {
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++)
+      if (base + k < n) out[base + k] = v[k] + add;
+  }
+}
+
+int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st) {
+  if (n <= 0) return GSB_OK;
+  const int64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, scan_scratch_bytes(n), st));
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  unsigned long long* status = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(scratch) + 16);
+  scan_u32_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(n, in, out, ticket, status);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// duplicateWithKeys (cr/rasterizer_impl.cu:70-111), warp-cooperative: a warp owns 32 consecutive
+// (camera, Gaussian) slots, and its lanes walk the warp's contiguous instance range together, so the
+// key/value stores are coalesced (the reference runs a divergent serial loop per thread).
+// key = (camera*tiles + y*grid.x + x) << 32 | bits(depth);  value = Gaussian index in its camera.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tile_rect_dup(float px, float py, int rad, int gx, int gy, uint32_t& x0, uint32_t& y0,
+                                              uint32_t& x1, uint32_t& y1) {
+  const float rf = (float)rad;
+  const int ix0 = __float2int_rz(MUL(SUB(px, rf), 0.0625f));
+  const int iy0 = __float2int_rz(MUL(SUB(py, rf), 0.0625f));
+  const int ix1 = __float2int_rz(MUL(ADD(ADD(ADD(px, rf), 16.0f), -1.0f), 0.0625f));
+  const int iy1 = __float2int_rz(MUL(ADD(ADD(ADD(py, rf), 16.0f), -1.0f), 0.0625f));
+  x0 = min((uint32_t)max(ix0, 0), (uint32_t)gx);
+  y0 = min((uint32_t)max(iy0, 0), (uint32_t)gy);
+  x1 = min((uint32_t)max(ix1, 0), (uint32_t)gx);
+  y1 = min((uint32_t)max(iy1, 0), (uint32_t)gy);
+}
+
+__global__ void __launch_bounds__(256)
+duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const float2* __restrict__ means2D,
+                           const float* __restrict__ depths, const int32_t* __restrict__ radii,
+                           const uint32_t* __restrict__ offsets, unsigned long long* __restrict__ keys,
+                           uint32_t* __restrict__ vals) {
+  const long long slot = (long long)blockIdx.x * 256 + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31u;
+  uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, depth_bits = 0, tile_base = 0, gidx = 0;
+  const long long warp_first = slot - lane;
+  if (warp_first >= total) return;
+  if (slot < total) {
+    end = offsets[slot];
+    const int rad = radii[slot];
+    const uint32_t cam = (uint32_t)(slot / P);
+    gidx = (uint32_t)(slot - (long long)cam * P);
+    tile_base = cam * (uint32_t)(gx * gy);
+    start = end;
+    if (rad > 0) {
+      const float2 xy = means2D[slot];
+      uint32_t x1, y1;
+      tile_rect_dup(xy.x, xy.y, rad, gx, gy, x0, y0, x1, y1);
+      w = x1 - x0;
+      start = end - w * (y1 - y0);
+      depth_bits = __float_as_uint(depths[slot]);
+      if (w == 0) w = 1;
+    }
+  }
+  // slots past `total` inherit the last valid end so that the search below stays monotone
+  uint32_t last_end = __shfl_sync(0xffffffffu, end, (unsigned)min(31ll, total - 1 - warp_first));
+  if (slot >= total) { end = last_end; start = last_end; }
+  const uint32_t warp_start = __shfl_sync(0xffffffffu, start, 0);
+  // lane 0's start may be stale if it is culled (start == end == previous end): that is exactly the first instance
+  const uint32_t warp_end = last_end;
+  for (uint32_t b = warp_start; b < warp_end; b += 32) {
+    const uint32_t i = b + lane;
+    // owner = number of lanes whose `end` <= i  (ends are non-decreasing)
+    unsigned j = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+      const uint32_t e = __shfl_sync(0xffffffffu, end, (j + step - 1) & 31u);
+      if (e <= i) j += step;
+    }
+    j &= 31u;
+    const uint32_t s = __shfl_sync(0xffffffffu, start, j);
+    const uint32_t ox = __shfl_sync(0xffffffffu, x0, j);
+    const uint32_t oy = __shfl_sync(0xffffffffu, y0, j);
+    const uint32_t ow = __shfl_sync(0xffffffffu, w, j);
+    const uint32_t od = __shfl_sync(0xffffffffu, depth_bits, j);
+    const uint32_t ot = __shfl_sync(0xffffffffu, tile_base, j);
+    const uint32_t og = __shfl_sync(0xffffffffu, gidx, j);
+    if (i < warp_end) {
+      const uint32_t k = i - s;
+      const uint32_t ry = k / ow, rx = k - ry * ow;
+      const uint32_t tile = ot + (oy + ry) * (uint32_t)gx + (ox + rx);
+      keys[i] = ((unsigned long long)tile << 32) | od;
+      vals[i] = og;
+    }
+  }
+}
+
+int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st) {
+  const long long total = (long long)c.n_cams * c.P;
+  if (total <= 0 || c.num_rendered <= 0) return GSB_OK;
+  duplicate_with_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
+      total, c.P, c.tiles_x, c.tiles_y, reinterpret_cast<const float2*>(c.means2D), c.depths, c.radii,
+      c.point_offsets, reinterpret_cast<unsigned long long*>(c.point_list_keys_unsorted), c.point_list_unsorted);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Onesweep LSD radix sort, 8-bit digits, 64-bit keys + 32-bit payloads, stable.
+//   kernel 1: all per-pass digit histograms in one read of the keys;
+//   kernel 2 (per pass): each tile ranks its keys (warp match), publishes its digit counts and
+//     resolves its global offsets with a decoupled look-back over earlier tiles, then scatters
+//     through shared memory so that global stores are in runs.
+// Temp layout: hist[8][256] u32 | ticket[8] u32 (padded) | status[passes][tiles][256] u32.
+// Status word: top 2 bits flag (1 = tile aggregate, 2 = inclusive prefix), low 30 bits value.
+// ------------------------------------------------------------------------------------------------
+constexpr int RS_BITS = 8;
+constexpr int RS_RADIX = 1 << RS_BITS;
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 keys
+constexpr int RS_MAX_PASSES = 8;
+constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INC = 2u << 30, RS_VAL_MASK = (1u << 30) - 1;
+constexpr size_t RS_HEADER = (size_t)RS_MAX_PASSES * RS_RADIX * 4 + 256;
+
+size_t sort_temp_bytes(int64_t n) {
+  const int64_t tiles = (n + RS_TILE - 1) / RS_TILE;
+  const size_t t = (size_t)(tiles > 0 ? tiles : 1);
+  return RS_HEADER + align_up((size_t)RS_MAX_PASSES * t * RS_RADIX * 4, 256) + align_up((size_t)(n > 0 ? n : 1) * 12, 256);
+}
+
+__global__ void __launch_bounds__(256)
+rs_histogram_kernel(long long n, const unsigned long long* __restrict__ keys, int end_bit, int passes,
+                    uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
+  for (int i = threadIdx.x; i < passes * RS_RADIX; i += 256) s_hist[i] = 0;
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+    const unsigned long long k = keys[i];
+    for (int p = 0; p < passes; p++) {
+      const int shift = p * RS_BITS;
+      const int nb = min(RS_BITS, end_bit - shift);
+      const uint32_t d = (uint32_t)(k >> shift) & ((1u << nb) - 1u);
+      atomicAdd(&s_hist[p * RS_RADIX + d], 1u);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * RS_RADIX; i += 256) {
+    const uint32_t c = s_hist[i];
+    if (c) atomicAdd(&ghist[i], c);
+  }
+}
+
+struct RsSmem {
+  unsigned long long keys[RS_TILE];
+  uint32_t vals[RS_TILE];
+  uint32_t warp_cnt[RS_WARPS][RS_RADIX];
+  uint32_t digit_start[RS_RADIX];   // exclusive prefix of this tile's digit counts
+  uint32_t digit_gbase[RS_RADIX];   // global position of the tile's first key of digit d, minus digit_start[d]
+  uint32_t warp_tot[RS_WARPS];
+  uint32_t tile;
+};
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsigned long long* __restrict__ kout,
+                   const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout, int shift, int nbits,
+                   const uint32_t* __restrict__ ghist, uint32_t* __restrict__ ticket,
+                   uint32_t* __restrict__ status) {
+  extern __shared__ __align__(16) unsigned char rs_smem_raw[];
+  RsSmem& S = *reinterpret_cast<RsSmem*>(rs_smem_raw);
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  if (tid == 0) S.tile = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int w = 0; w < RS_WARPS; w++) S.warp_cnt[w][tid] = 0;
+  __syncthreads();
+  const uint32_t tile = S.tile;
+  const long long tile_base = (long long)tile * RS_TILE;
+  const int n_valid = (int)min((long long)RS_TILE, n - tile_base);
+  const uint32_t dmask = (1u << nbits) - 1u;
+
+  // load (warp-striped: item i of lane l is element warp*512 + i*32 + l of the tile)
+  unsigned long long key[RS_ITEMS];
+  uint32_t val[RS_ITEMS];
+  uint32_t rank[RS_ITEMS];
+  const int wbase = warp * (32 * RS_ITEMS);
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const int e = wbase + i * 32 + lane;
+    if (e < n_valid) {
+      key[i] = kin[tile_base + e];
+      val[i] = vin[tile_base + e];
+    } else {
+      key[i] = ~0ull;
+      val[i] = 0;
+    }
+  }
+  // rank within the warp, in (item, lane) order == memory order => stable
+  const unsigned lt = lanemask_lt();
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const int e = wbase + i * 32 + lane;
+    const uint32_t d = (e < n_valid) ? ((uint32_t)(key[i] >> shift) & dmask) : (RS_RADIX - 1);
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t before = 0;
+    if ((int)lane == leader) {
+      before = S.warp_cnt[warp][d];
+      S.warp_cnt[warp][d] = before + __popc(peers);
+    }
+    before = __shfl_sync(0xffffffffu, before, leader);
+    rank[i] = before + __popc(peers & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // thread d: per-warp exclusive offsets of digit d, tile count, look-back
+  {
+    const uint32_t d = tid;
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) {
+      const uint32_t c = S.warp_cnt[w][d];
+      S.warp_cnt[w][d] = run;
+      run += c;
+    }
+    const uint32_t cnt = run;  // tile's count of digit d (the last tile's digit 255 also counts its padding)
+    uint32_t* my_status = status + (size_t)tile * RS_RADIX + d;
+    if (tile == 0) st_relaxed_u32(my_status, RS_FLAG_INC | cnt);
+    else st_relaxed_u32(my_status, RS_FLAG_AGG | cnt);
+
+    // exclusive scans over the 256 digits: tile counts and global histogram
+    const uint32_t g = ghist[d];
+    uint32_t inc_c = cnt, inc_g = g;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t tc = __shfl_up_sync(0xffffffffu, inc_c, s);
+      const uint32_t tg = __shfl_up_sync(0xffffffffu, inc_g, s);
+      if (lane >= (unsigned)s) { inc_c += tc; inc_g += tg; }
+    }
+    if (lane == 31) { S.warp_tot[warp] = inc_c; S.digit_start[warp] = inc_g; }  // digit_start reused as scratch
+    __syncthreads();
+    uint32_t off_c = 0, off_g = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++)
+      if (w < (int)warp) { off_c += S.warp_tot[w]; off_g += S.digit_start[w]; }
+    __syncthreads();
+    const uint32_t excl_c = off_c + inc_c - cnt;
+    const uint32_t excl_g = off_g + inc_g - g;
+
+    uint32_t prefix = 0;
+    if (tile > 0) {
+      long long p = (long long)tile - 1;
+      while (true) {
+        const uint32_t* ps = status + (size_t)p * RS_RADIX + d;
+        uint32_t s = ld_relaxed_u32(ps);
+        while ((s & ~RS_VAL_MASK) == 0) s = ld_relaxed_u32(ps);
+        prefix += s & RS_VAL_MASK;
+        if (s & RS_FLAG_INC) break;
+        p--;
+      }
+      st_relaxed_u32(my_status, RS_FLAG_INC | ((prefix + cnt) & RS_VAL_MASK));
+    }
+    S.digit_start[d] = excl_c;
+    S.digit_gbase[d] = excl_g + prefix - excl_c;
+  }
+  __syncthreads();
+
+  // scatter into tile-sorted order in shared memory
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const int e = wbase + i * 32 + lane;
+    const uint32_t d = (e < n_valid) ? ((uint32_t)(key[i] >> shift) & dmask) : (RS_RADIX - 1);
+    const uint32_t pos = S.digit_start[d] + S.warp_cnt[warp][d] + rank[i];
+    S.keys[pos] = key[i];
+    S.vals[pos] = val[i];
+  }
+  __syncthreads();
+  // write out in runs; padding sits at the very end of the tile-sorted order
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const int p = i * RS_THREADS + tid;
+    if (p < n_valid) {
+      const unsigned long long k = S.keys[p];
+      const uint32_t d = (uint32_t)(k >> shift) & dmask;
+      const uint32_t dst = S.digit_gbase[d] + (uint32_t)p;
+      kout[dst] = k;
+      vout[dst] = S.vals[p];
+    }
+  }
+}
+
+int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
+                      int end_bit, void* temp, cudaStream_t st) {
+  if (n <= 0) return GSB_OK;
+  if (n >= (1ll << 30) || end_bit <= 0 || end_bit > 64) return GSB_EINVAL;
+  const int passes = (end_bit + RS_BITS - 1) / RS_BITS;
+  const int64_t tiles = (n + RS_TILE - 1) / RS_TILE;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(RsSmem)));
+    attr_set = true;
+  }
+  GSB_CUDA_CHECK(cudaMemsetAsync(temp, 0, RS_HEADER + (size_t)passes * tiles * RS_RADIX * 4, st));
+  uint32_t* ghist = reinterpret_cast<uint32_t*>(temp);
+  uint32_t* tickets = ghist + RS_MAX_PASSES * RS_RADIX;
+  uint32_t* status = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(temp) + RS_HEADER);
+  const int hist_blocks = (int)std::min<int64_t>((n + 256 * 16 - 1) / (256 * 16), 148 * 8);
+  rs_histogram_kernel<<<hist_blocks, 256, 0, st>>>(n, reinterpret_cast<const unsigned long long*>(kin), end_bit,
+                                                   passes, ghist);
+  GSB_LAUNCH_CHECK();
+  // ping-pong between the outputs and an alternate pair inside `temp`, arranged so that the last pass
+  // lands in (kout, vout) and the caller's input is never written (like CUB's non-DoubleBuffer API).
+  const size_t status_bytes = align_up((size_t)RS_MAX_PASSES * tiles * RS_RADIX * 4, 256);
+  unsigned long long* alt_k = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(temp) + RS_HEADER + status_bytes);
+  uint32_t* alt_v = reinterpret_cast<uint32_t*>(alt_k + n);
+  const unsigned long long* a = reinterpret_cast<const unsigned long long*>(kin);
+  const uint32_t* va = vin;
+  for (int p = 0; p < passes; p++) {
+    const int shift = p * RS_BITS;
+    const int nb = (end_bit - shift < RS_BITS) ? end_bit - shift : RS_BITS;
+    const bool to_out = ((passes - 1 - p) % 2 == 0);
+    unsigned long long* b = to_out ? reinterpret_cast<unsigned long long*>(kout) : alt_k;
+    uint32_t* vb = to_out ? vout : alt_v;
+    rs_onesweep_kernel<<<(unsigned)tiles, RS_THREADS, sizeof(RsSmem), st>>>(
+        n, a, b, va, vb, shift, nb, ghist + p * RS_RADIX, tickets + p, status + (size_t)p * tiles * RS_RADIX);
+    GSB_LAUNCH_CHECK();
+    a = b;
+    va = vb;
+  }
+  return GSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// identifyTileRanges (cr/rasterizer_impl.cu:116-138); ranges pre-zeroed by the caller (:311).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(long long R, const unsigned long long* __restrict__ keys, uint2* __restrict__ ranges) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= R) return;
+  const uint32_t cur = (uint32_t)(keys[i] >> 32);
+  if (i == 0) {
+    ranges[cur].x = 0;
+  } else {
+    const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+    if (cur != prev) {
+      ranges[prev].y = (uint32_t)i;
+      ranges[cur].x = (uint32_t)i;
+    }
+  }
+  if (i == R - 1) ranges[cur].y = (uint32_t)R;
+}
+
+int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st) {
+  const size_t tiles = (size_t)c.n_cams * c.tiles_x * c.tiles_y;
+  GSB_CUDA_CHECK(cudaMemsetAsync(c.ranges, 0, tiles * 8, st));
+  if (c.num_rendered <= 0) return GSB_OK;
+  tile_ranges_kernel<<<(unsigned)((c.num_rendered + 255) / 256), 256, 0, st>>>(
+      c.num_rendered, reinterpret_cast<const unsigned long long*>(c.point_list_keys),
+      reinterpret_cast<uint2*>(c.ranges));
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+}  // namespace gsb

@@ -1,0 +1,294 @@
+// blend.cu -- per-tile alpha blending, forward and backward.
+//
+// Forward replaces renderCUDA (cr/forward.cu:261-393): a 16x16 block per tile walks the tile's depth-
+// sorted instance list in batches staged into shared memory (position, conic+opacity and colour+depth
+// packed as float2/float4/float4, so the inner loop never touches global memory -- the reference
+// gathers the colour from global per blended pair), front to back, with per-pixel early termination.
+// The power/alpha/T arithmetic is pinned with round-to-nearest intrinsics in the reference's rounding
+// order so every threshold decision (power > 0, alpha < 1/255, T < 1e-4, median depth) and therefore
+// n_contrib is identical.
+//
+// Backward replaces renderCUDA (cr/backward.cu:399-557): same lists back to front.  The nine
+// per-Gaussian partial gradients are first summed over the 32 pixels of the warp with a butterfly
+// multi-value shuffle reduction (14 SHFL for 9 values) and only the per-warp sums go to global
+// atomics in one RED instruction (the reference issues 9 global atomics per pixel-Gaussian pair).
+// Warps skip list entries behind their deepest contributor, and whole batches behind the tile's.
+#include "common.cuh"
+
+namespace gsb {
+
+// power = -0.5 (A dx^2 + C dy^2) - B dx dy with the reference's contraction (SASS of renderCUDA):
+//   fma(fma(dx, dx*A, dy*(dy*C)), -0.5, -(dy*(dx*B)))
+__device__ __forceinline__ float blend_power(float dx, float dy, float A, float B, float C) {
+  const float q = FMA(dx, MUL(dx, A), MUL(dy, MUL(dy, C)));
+  return FMA(q, -0.5f, -MUL(dy, MUL(dx, B)));
+}
+
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
+                  const float2* __restrict__ means2D, const float* __restrict__ colors, int color_cam_stride,
+                  const float4* __restrict__ conic_opacity, const float* __restrict__ depths,
+                  const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                  float* __restrict__ out_color, float* __restrict__ out_depth) {
+  __shared__ float2 s_xy[GSB_BLOCK_SIZE];
+  __shared__ float4 s_co[GSB_BLOCK_SIZE];
+  __shared__ float4 s_cd[GSB_BLOCK_SIZE];  // r, g, b, depth
+
+  const int cam = blockIdx.z;
+  const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
+  const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const unsigned tid = threadIdx.y * GSB_BLOCK_X + threadIdx.x;
+  const uint32_t px = blockIdx.x * GSB_BLOCK_X + threadIdx.x;
+  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
+  const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+  const float pfx = (float)px, pfy = (float)py;
+  bool done = !inside;
+
+  const uint2 range = ranges[(size_t)cam * tiles_per_cam + tile];
+  const int total = (int)(range.y - range.x);
+  const int rounds = (total + GSB_BLOCK_SIZE - 1) / GSB_BLOCK_SIZE;
+  const size_t cam_off = (size_t)cam * P;
+  const float* col_tab = colors + (size_t)cam * color_cam_stride;
+
+  float T = 1.0f;
+  uint32_t last_contributor = 0;
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  float D = 15.0f;  // median depth default (cr/forward.cu:308)
+
+  int toDo = total;
+  for (int i = 0; i < rounds; i++, toDo -= GSB_BLOCK_SIZE) {
+    if (__syncthreads_count(done) == GSB_BLOCK_SIZE) break;
+    const int progress = i * GSB_BLOCK_SIZE + tid;
+    if (progress < total) {
+      const uint32_t id = point_list[range.x + progress];
+      s_xy[tid] = means2D[cam_off + id];
+      s_co[tid] = conic_opacity[cam_off + id];
+      s_cd[tid] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
+                              depths[cam_off + id]);
+    }
+    __syncthreads();
+    const int n = min(GSB_BLOCK_SIZE, toDo);
+    for (int j = 0; !done && j < n; j++) {
+      const float2 xy = s_xy[j];
+      const float4 co = s_co[j];
+      const float dx = SUB(xy.x, pfx), dy = SUB(xy.y, pfy);
+      const float power = blend_power(dx, dy, co.x, co.y, co.z);
+      if (power > 0.0f) continue;
+      const float alpha = fminf(0.99f, MUL(co.w, expf(power)));
+      if (alpha < 1.0f / 255.0f) continue;
+      const float test_T = MUL(T, SUB(1.0f, alpha));
+      if (test_T < 0.0001f) { done = true; continue; }
+      const float4 cd = s_cd[j];
+      C0 = FMA(T, MUL(alpha, cd.x), C0);
+      C1 = FMA(T, MUL(alpha, cd.y), C1);
+      C2 = FMA(T, MUL(alpha, cd.z), C2);
+      if (T > 0.5f && test_T < 0.5f) D = cd.w;
+      T = test_T;
+      last_contributor = (uint32_t)(i * GSB_BLOCK_SIZE + j + 1);
+    }
+  }
+
+  if (inside) {
+    const size_t HW = (size_t)H * W;
+    const size_t pid = (size_t)py * W + px;
+    final_T[cam * HW + pid] = T;
+    n_contrib[cam * HW + pid] = last_contributor;
+    float* oc = out_color + (size_t)cam * 3 * HW;
+    oc[pid] = FMA(bg[0], T, C0);
+    oc[HW + pid] = FMA(bg[1], T, C1);
+    oc[2 * HW + pid] = FMA(bg[2], T, C2);
+    out_depth[cam * HW + pid] = D;
+  }
+}
+
+int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,
+                      cudaStream_t st) {
+  dim3 grid(c.tiles_x, c.tiles_y, a.n_cams), block(GSB_BLOCK_X, GSB_BLOCK_Y);
+  render_fwd_kernel<<<grid, block, 0, st>>>(
+      reinterpret_cast<const uint2*>(c.ranges), c.point_list, a.width, a.height, a.P,
+      reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
+      reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, c.final_T, c.n_contrib, out_color,
+      out_depth);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward
+// ------------------------------------------------------------------------------------------------
+
+// Sum 8 values over the 32 lanes with 9 shuffles.  Afterwards lane L (L % 4 == 0) holds in v[0] the
+// full warp sum of component L / 4.
+__device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
+  const unsigned full = 0xffffffffu;
+  {
+    const bool up = lane & 16u;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float send = up ? v[i] : v[i + 4];
+      const float keep = up ? v[i + 4] : v[i];
+      v[i] = keep + __shfl_xor_sync(full, send, 16);
+    }
+  }
+  {
+    const bool up = lane & 8u;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float send = up ? v[i] : v[i + 2];
+      const float keep = up ? v[i + 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(full, send, 8);
+    }
+  }
+  {
+    const bool up = lane & 4u;
+    const float send = up ? v[0] : v[1];
+    const float keep = up ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(full, send, 4);
+  }
+  v[0] += __shfl_xor_sync(full, v[0], 2);
+  v[0] += __shfl_xor_sync(full, v[0], 1);
+}
+
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE)
+render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
+                  const float* __restrict__ bg, const float2* __restrict__ means2D,
+                  const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,
+                  const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                  const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
+                  float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
+  __shared__ float2 s_xy[GSB_BLOCK_SIZE];
+  __shared__ float4 s_co[GSB_BLOCK_SIZE];
+  __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
+  __shared__ int s_block_last;
+
+  const int cam = blockIdx.z;
+  const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
+  const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const unsigned tid = threadIdx.y * GSB_BLOCK_X + threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const uint32_t px = blockIdx.x * GSB_BLOCK_X + threadIdx.x;
+  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
+  const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+  const float pfx = (float)px, pfy = (float)py;
+  const size_t HW = (size_t)H * W;
+  const size_t pid = (size_t)py * W + px;
+
+  const uint2 range = ranges[(size_t)cam * tiles_per_cam + tile];
+  const size_t cam_off = (size_t)cam * P;
+  const float* col_tab = colors + (size_t)cam * color_cam_stride;
+  float* dcol_tab = dL_dcolor + (size_t)cam * color_cam_stride;
+
+  const float T_final = inside ? final_Ts[cam * HW + pid] : 0.f;
+  float T = T_final;
+  const int last_contributor = inside ? (int)n_contrib[cam * HW + pid] : 0;
+  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f;
+  if (inside) {
+    const float* dp = dL_dpixels + (size_t)cam * 3 * HW;
+    dpx0 = dp[pid]; dpx1 = dp[HW + pid]; dpx2 = dp[2 * HW + pid];
+  }
+  float bg_dot = 0.f;
+  bg_dot += bg[0] * dpx0; bg_dot += bg[1] * dpx1; bg_dot += bg[2] * dpx2;
+  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // accum_rec
+  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;       // last_color
+  float last_alpha = 0.f;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+  // deepest contributor of the warp / of the tile: entries at list positions >= that are dead
+  int warp_last = last_contributor;
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, s));
+  if (tid == 0) s_block_last = 0;
+  __syncthreads();
+  if (lane == 0 && warp_last > 0) atomicMax(&s_block_last, warp_last);
+  __syncthreads();
+  const int block_last = s_block_last;   // list positions [0, block_last) matter
+  if (block_last == 0) return;
+
+  // walk positions block_last-1 ... 0 in batches of 256 (back to front)
+  const int rounds = (block_last + GSB_BLOCK_SIZE - 1) / GSB_BLOCK_SIZE;
+  for (int i = 0; i < rounds; i++) {
+    if (i > 0) __syncthreads();
+    const int batch_top = block_last - 1 - i * GSB_BLOCK_SIZE;  // list position of batch entry 0
+    const int n = min(GSB_BLOCK_SIZE, batch_top + 1);
+    if ((int)tid < n) {
+      const uint32_t id = point_list[range.x + (uint32_t)(batch_top - (int)tid)];
+      s_xy[tid] = means2D[cam_off + id];
+      s_co[tid] = conic_opacity[cam_off + id];
+      s_ci[tid] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
+                              __uint_as_float(id));
+    }
+    __syncthreads();
+    // entry j has list position batch_top - j; this warp needs position < warp_last
+    const int j0 = max(0, batch_top - warp_last + 1);
+    for (int j = j0; j < n; j++) {
+      const int pos = batch_top - j;
+      const float2 xy = s_xy[j];
+      const float4 co = s_co[j];
+      const float dx = SUB(xy.x, pfx), dy = SUB(xy.y, pfy);
+      const float power = blend_power(dx, dy, co.x, co.y, co.z);
+      const float G = expf(power);
+      const float alpha = fminf(0.99f, MUL(co.w, G));
+      const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+      if (!__any_sync(0xffffffffu, valid)) continue;
+
+      float v[8];
+      float g_op = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; k++) v[k] = 0.f;
+      const float4 ci = s_ci[j];
+      if (valid) {
+        T = T / (1.f - alpha);
+        const float dchannel_dcolor = alpha * T;
+        float dL_dalpha = 0.0f;
+        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = ci.x;
+        dL_dalpha += (ci.x - ar0) * dpx0;
+        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = ci.y;
+        dL_dalpha += (ci.y - ar1) * dpx1;
+        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = ci.z;
+        dL_dalpha += (ci.z - ar2) * dpx2;
+        v[0] = dchannel_dcolor * dpx0;
+        v[1] = dchannel_dcolor * dpx1;
+        v[2] = dchannel_dcolor * dpx2;
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+        const float dL_dG = co.w * dL_dalpha;
+        const float gdx = G * dx, gdy = G * dy;
+        const float dG_ddelx = -gdx * co.x - gdy * co.y;
+        const float dG_ddely = -gdy * co.z - gdx * co.y;
+        v[3] = dL_dG * dG_ddelx * ddelx_dx;
+        v[4] = dL_dG * dG_ddely * ddely_dy;
+        v[5] = -0.5f * gdx * dx * dL_dG;
+        v[6] = -0.5f * gdx * dy * dL_dG;
+        v[7] = -0.5f * gdy * dy * dL_dG;
+        g_op = G * dL_dalpha;
+      }
+      warp_reduce8(v, lane);
+#pragma unroll
+      for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
+
+      const uint32_t id = __float_as_uint(ci.w);
+      const unsigned comp = lane >> 2;
+      float* dst;
+      float val = v[0];
+      if (lane == 1) { dst = dL_dopacity + id; val = g_op; }
+      else if (comp < 3) dst = dcol_tab + 3 * (size_t)id + comp;
+      else if (comp < 5) dst = dL_dmean2D + 3 * (cam_off + id) + (comp - 3);
+      else dst = dL_dconic + 4 * (cam_off + id) + (comp == 7 ? 3 : comp - 5);
+      if (((lane & 3u) == 0 || lane == 1) && val != 0.f) atomicAdd(dst, val);
+    }
+  }
+}
+
+int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
+                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st) {
+  dim3 grid(c.tiles_x, c.tiles_y, a.n_cams), block(GSB_BLOCK_X, GSB_BLOCK_Y);
+  render_bwd_kernel<<<grid, block, 0, st>>>(
+      reinterpret_cast<const uint2*>(c.ranges), c.point_list, a.width, a.height, a.P, a.background,
+      reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
+      a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+}  // namespace gsb

@@ -1,0 +1,73 @@
+// common.cuh -- shared device helpers for libgsb200 (sm_100a only).
+//
+// Bit-exactness note: radii / tiles_touched / depth key bits / means2D must match the reference
+// rasterizer bit for bit (SURVEY.md section 7 "hard parts" #1).  The reference is compiled without
+// fast-math, and nvcc's FMA contraction decides the rounding sequence.  Every FP32 operation on
+// such a path is therefore written with an explicit round-to-nearest intrinsic below, which nvcc
+// neither contracts nor reassociates.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/gsb200.h"
+
+#define GSB_BLOCK_X 16
+#define GSB_BLOCK_Y 16
+#define GSB_BLOCK_SIZE (GSB_BLOCK_X * GSB_BLOCK_Y)
+#define GSB_NCH 3
+
+namespace gsb {
+
+__device__ __forceinline__ float FMA(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float MUL(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float ADD(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float SUB(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float DIV(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float SQRT(float a) { return __fsqrt_rn(a); }
+
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// Error plumbing shared by the host side of every translation unit.
+void set_last_error(const char* what, cudaError_t e);
+#define GSB_CUDA_CHECK(expr)                                  \
+  do {                                                        \
+    cudaError_t _e = (expr);                                  \
+    if (_e != cudaSuccess) {                                  \
+      gsb::set_last_error(#expr, _e);                         \
+      return GSB_ECUDA;                                       \
+    }                                                         \
+  } while (0)
+#define GSB_LAUNCH_CHECK() GSB_CUDA_CHECK(cudaGetLastError())
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Host launchers implemented across the .cu files (all asynchronous on `st`).
+struct CamParams {  // per-camera scalars that live in a small device table
+  float tanfovx, tanfovy, focal_x, focal_y;
+};
+
+int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
+                      int32_t* radii_out, int* err_flag_dev, cudaStream_t st);
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
+                          const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
+                          float* dL_dscale, float* dL_drot, cudaStream_t st);
+
+size_t scan_scratch_bytes(int64_t n);
+int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st);
+int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st);
+size_t sort_temp_bytes(int64_t n);
+int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
+                      int end_bit, void* temp, cudaStream_t st);
+int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st);
+
+int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,
+                      cudaStream_t st);
+int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
+                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st);
+
+}  // namespace gsb

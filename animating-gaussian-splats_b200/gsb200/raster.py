@@ -1,0 +1,179 @@
+"""Tensor-level wrappers of gsb_raster_forward / gsb_raster_backward / gsb_mark_visible.
+
+Mirrors the torch glue of the reference (RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA /
+markVisible, DGR/rasterize_points.cu:35-215): allocate outputs, hand raw pointers to the C ABI, keep the
+three state buffers alive for backward.  `n_cams > 1` is the additional batched entry point: all
+cameras of a timestep in one call (one preprocess launch, ONE sort over (camera, tile, depth) keys,
+one blend launch), gradients summed over the cameras.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+class RasterState:
+    """What the reference returns to Python as (num_rendered, geomBuffer, binningBuffer, imgBuffer)."""
+
+    __slots__ = ("ctx", "args", "geom", "binning", "img", "keep", "tan_x", "tan_y")
+
+    @property
+    def num_rendered(self):
+        return int(self.ctx.num_rendered)
+
+    # ---- debug accessors for the bit-exact tests: views into the state buffers ------------------
+    def _view(self, addr, base_t, dtype, shape):
+        off = addr - base_t.data_ptr()
+        n = 1
+        for s in shape:
+            n *= s
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return base_t[off:off + nbytes].view(dtype).view(*shape)
+
+    def tensors(self):
+        c = self.ctx
+        n, P = c.n_cams, c.P
+        R = int(c.num_rendered)
+        tiles = c.tiles_x * c.tiles_y * n
+        hw = c.width * c.height
+        out = {
+            "depths": self._view(c.depths, self.geom, torch.float32, (n, P)),
+            "radii": self._view(c.radii, self.geom, torch.int32, (n, P)),
+            "means2D": self._view(c.means2D, self.geom, torch.float32, (n, P, 2)),
+            "cov3D": self._view(c.cov3D, self.geom, torch.float32, (n, P, 6)),
+            "conic_opacity": self._view(c.conic_opacity, self.geom, torch.float32, (n, P, 4)),
+            "tiles_touched": self._view(c.tiles_touched, self.geom, torch.int32, (n, P)),
+            "point_offsets": self._view(c.point_offsets, self.geom, torch.int32, (n, P)),
+            "final_T": self._view(c.final_T, self.img, torch.float32, (n, c.height, c.width)),
+            "n_contrib": self._view(c.n_contrib, self.img, torch.int32, (n, c.height, c.width)),
+            "ranges": self._view(c.ranges, self.img, torch.int32, (tiles, 2)),
+        }
+        if R > 0:
+            out.update({
+                "point_list": self._view(c.point_list, self.binning, torch.int32, (R,)),
+                "point_list_keys": self._view(c.point_list_keys, self.binning, torch.int64, (R,)),
+                "point_list_unsorted": self._view(c.point_list_unsorted, self.binning, torch.int32, (R,)),
+                "point_list_keys_unsorted": self._view(c.point_list_keys_unsorted, self.binning, torch.int64, (R,)),
+            })
+        return out
+
+
+def _f32c(t, name):
+    if t is None or t.numel() == 0:
+        return None
+    L.require_cuda(t, name)
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32")
+    return t.contiguous()
+
+
+def _as_list(x, n):
+    if isinstance(x, (list, tuple)):
+        assert len(x) == n
+        return [float(v) for v in x]
+    return [float(x)] * n
+
+
+def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, scale_modifier, viewmatrix,
+            projmatrix, tanfovx, tanfovy, image_height, image_width, prefiltered=False, n_cams=1,
+            colors_per_camera=False):
+    """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim."""
+    if means3D.ndim != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # DGR/rasterize_points.cu:56-58
+    L.require_cuda(means3D, "means3D")
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = int(image_height), int(image_width)
+    st = RasterState()
+    st.keep = [_f32c(means3D, "means3D"), _f32c(colors, "colors_precomp"), _f32c(opacities, "opacities"),
+               _f32c(scales, "scales"), _f32c(rotations, "rotations"), _f32c(cov3D_precomp, "cov3D_precomp"),
+               _f32c(bg, "bg"), _f32c(viewmatrix, "viewmatrix"), _f32c(projmatrix, "projmatrix")]
+    m3, col, opa, sca, rot, cov, bgc, vm, pm = st.keep
+    st.tan_x = (C.c_float * n_cams)(*_as_list(tanfovx, n_cams))
+    st.tan_y = (C.c_float * n_cams)(*_as_list(tanfovy, n_cams))
+    a = L.RasterArgs()
+    a.P, a.n_cams, a.width, a.height = P, n_cams, W, H
+    a.prefiltered = 1 if prefiltered else 0
+    a.color_cam_stride = 3 * P if colors_per_camera else 0
+    a.scale_modifier = float(scale_modifier)
+    a.tanfovx_host = C.cast(st.tan_x, C.POINTER(C.c_float))
+    a.tanfovy_host = C.cast(st.tan_y, C.POINTER(C.c_float))
+    a.background, a.means3D, a.colors, a.opacities = L.ptr(bgc), L.ptr(m3), L.ptr(col), L.ptr(opa)
+    a.scales, a.rotations, a.cov3D_precomp = L.ptr(sca), L.ptr(rot), L.ptr(cov)
+    a.viewmatrix, a.projmatrix = L.ptr(vm), L.ptr(pm)
+    st.args = a
+    st.ctx = L.RasterCtx()
+
+    # outputs (DGR/rasterize_points.cu:67-69); every pixel / slot is written by the kernels
+    color = torch.empty((n_cams, 3, H, W), dtype=torch.float32, device=dev)
+    depth = torch.empty((n_cams, 1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((n_cams, P), dtype=torch.int32, device=dev)
+    st.geom = st.binning = st.img = None
+    if P == 0:
+        color.zero_(); depth.zero_()
+        st.ctx.P, st.ctx.n_cams, st.ctx.width, st.ctx.height = 0, n_cams, W, H
+    else:
+        bufs = {}
+
+        def make_cb(slot):
+            def cb(_user, nbytes):
+                t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=dev)
+                bufs[slot] = t
+                return t.data_ptr()
+            return L.ALLOC_FN(cb)
+
+        cbs = [make_cb("geom"), make_cb("binning"), make_cb("img")]
+        with torch.cuda.device(dev):
+            rc = L.lib().gsb_raster_forward(C.byref(a), cbs[0], cbs[1], cbs[2], None, L.ptr(color), L.ptr(depth),
+                                            L.ptr(radii), C.byref(st.ctx), L.stream_ptr())
+        L.check(rc, "gsb_raster_forward")
+        st.geom, st.binning, st.img = bufs.get("geom"), bufs.get("binning"), bufs.get("img")
+    if n_cams == 1:
+        return color[0], depth[0], radii[0], st
+    return color, depth, radii, st
+
+
+def backward(st, dL_dpix, need_cov3D_grad=True):
+    """-> dict of gradients (summed over the cameras of the batch where the parameter is shared)."""
+    a, c = st.args, st.ctx
+    P, n = a.P, a.n_cams
+    dev = dL_dpix.device
+    f = dict(dtype=torch.float32, device=dev)
+    g = {
+        "means2D": torch.empty((n, P, 3), **f), "conic": torch.empty((n, P, 4), **f),
+        "opacities": torch.empty((P, 1), **f),
+        "colors": torch.empty((n, P, 3) if a.color_cam_stride else (P, 3), **f),
+        "means3D": torch.empty((P, 3), **f),
+        "cov3D": torch.empty((P, 6), **f) if need_cov3D_grad else None,
+        "scales": torch.empty((P, 3), **f), "rotations": torch.empty((P, 4), **f),
+    }
+    if P > 0:
+        dpix = dL_dpix.contiguous()
+        if dpix.dtype != torch.float32:
+            dpix = dpix.float()
+        with torch.cuda.device(dev):
+            rc = L.lib().gsb_raster_backward(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(g["means2D"]), L.ptr(g["conic"]),
+                                             L.ptr(g["opacities"]), L.ptr(g["colors"]), L.ptr(g["means3D"]),
+                                             L.ptr(g["cov3D"]), L.ptr(g["scales"]), L.ptr(g["rotations"]),
+                                             L.stream_ptr())
+        L.check(rc, "gsb_raster_backward")
+    if n == 1:
+        g["means2D"] = g["means2D"][0]
+        g["conic"] = g["conic"][0]
+    return g
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """bool[P]: p_view.z > 0.2 (DGR/rasterize_points.cu:196-215)."""
+    L.require_cuda(means3D, "means3D")
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P > 0:
+        m = means3D.contiguous().float()
+        v = viewmatrix.contiguous().float()
+        p = projmatrix.contiguous().float()
+        with torch.cuda.device(means3D.device):
+            rc = L.lib().gsb_mark_visible(P, L.ptr(m), L.ptr(v), L.ptr(p), L.ptr(present), L.stream_ptr())
+        L.check(rc, "gsb_mark_visible")
+    return present

@@ -1,0 +1,143 @@
+/*
+ * gsb200.h -- C ABI of the B200-native Gaussian-splat hot path (libgsb200.so).
+ *
+ * Plain pointers and sizes only: no torch, no C++ types.  Every pointer is a DEVICE pointer unless
+ * the parameter name ends in `_host`.  Every entry point takes the CUDA stream it must run on as a
+ * `void*` (a cudaStream_t) and returns 0 on success or a negative GSB_E* code; nothing here
+ * synchronises the device except where stated.
+ *
+ * Each entry point cites the reference interface it replaces.  "DGR/" is
+ * /root/reference/diff-gaussian-rasterization-w-depth/ ; "cr/" is DGR/cuda_rasterizer/.
+ */
+#ifndef GSB200_H
+#define GSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_OK 0
+#define GSB_EINVAL (-1)   /* bad argument (null pointer, non-positive size, unsupported channel count) */
+#define GSB_ECUDA (-2)    /* a CUDA runtime call or launch failed; see gsb_last_error() */
+#define GSB_ENOMEM (-3)   /* a buffer callback returned NULL / capacity exceeded */
+#define GSB_EPREFILTER (-4) /* prefiltered=1 was promised but a Gaussian was culled (cr/auxiliary.h:154-161) */
+
+#define GSB_TILE 16       /* cr/config.h:16-17 BLOCK_X = BLOCK_Y = 16 */
+#define GSB_MAX_CHANNELS 3 /* cr/config.h:15 NUM_CHANNELS */
+
+/* Growable byte buffer callback: replaces std::function<char*(size_t)> of
+ * Rasterizer::forward (cr/rasterizer.h:32-34) / resizeFunctional (DGR/rasterize_points.cu:27-33).
+ * Must return a device pointer to at least `bytes` bytes (256-B aligned), valid until backward. */
+typedef char* (*gsb_alloc_fn)(void* user, size_t bytes);
+
+/* One camera (or a batch of n_cams cameras that share W, H, bg).  Replaces the argument list of
+ * Rasterizer::forward (cr/rasterizer.h:31-54).  Matrices are the reference's transposed (column-major
+ * flat) 4x4s, `n_cams` of them back to back. */
+typedef struct gsb_raster_args {
+  int32_t P;               /* Gaussians */
+  int32_t n_cams;          /* 1 for the drop-in path */
+  int32_t width, height;
+  int32_t prefiltered;
+  int32_t color_cam_stride; /* 0: one colour table [P][3] shared by all cameras; else floats between tables */
+  float scale_modifier;
+  const float* tanfovx_host; /* HOST [n_cams] */
+  const float* tanfovy_host; /* HOST [n_cams] */
+  const float* background;   /* [3] */
+  const float* means3D;      /* [P][3] */
+  const float* colors;       /* [P][3] colors_precomp (SH path is dead code in the reference repo: shared.py:32,121) */
+  const float* opacities;    /* [P] */
+  const float* scales;       /* [P][3] or NULL when cov3D_precomp is given */
+  const float* rotations;    /* [P][4] (r,x,y,z) or NULL */
+  const float* cov3D_precomp;/* [P][6] or NULL */
+  const float* viewmatrix;   /* [n_cams][16] */
+  const float* projmatrix;   /* [n_cams][16] */
+} gsb_raster_args;
+
+/* Saved state of one forward call: replaces the (geomBuffer, binningBuffer, imgBuffer, num_rendered)
+ * tuple the reference hands back to Python (DGR/rasterize_points.cu:114) and re-decodes with
+ * fromChunk (cr/rasterizer_impl.cu:155-194, 373-375).  POD; pointers point into the three buffers. */
+typedef struct gsb_raster_ctx {
+  int64_t num_rendered;      /* R: total (Gaussian, tile) instances over all cameras */
+  int32_t P, n_cams, width, height, tiles_x, tiles_y, sort_bits, _pad;
+  /* geometry state, [n_cams][P] each (cr/rasterizer_impl.h:31-45) */
+  float* depths; int32_t* radii; float* means2D; float* cov3D; float* conic_opacity;
+  uint32_t* tiles_touched; uint32_t* point_offsets;
+  /* image state (cr/rasterizer_impl.h:47-54) */
+  float* final_T; uint32_t* n_contrib; uint32_t* ranges; /* ranges: [n_cams*tiles][2] */
+  /* binning state (cr/rasterizer_impl.h:56-66) */
+  uint32_t* point_list; uint64_t* point_list_keys; uint32_t* point_list_unsorted; uint64_t* point_list_keys_unsorted;
+  void* sort_temp;
+} gsb_raster_ctx;
+
+/* Library / build identification. */
+const char* gsb_version(void);
+const char* gsb_last_error(void);            /* text of the last CUDA error seen by this thread */
+
+/* Byte sizes of the three state buffers: replaces required<GeometryState/ImageState/BinningState>
+ * (cr/rasterizer_impl.h:68-73). */
+size_t gsb_geom_bytes(int32_t P, int32_t n_cams);
+size_t gsb_image_bytes(int32_t width, int32_t height, int32_t n_cams);
+size_t gsb_binning_bytes(int64_t num_rendered, int32_t n_tiles_total);
+
+/* getHigherMsb (cr/rasterizer_impl.cu:35-50). */
+uint32_t gsb_higher_msb(uint32_t n);
+
+/* Rasterizer::forward (cr/rasterizer.h:31-54, cr/rasterizer_impl.cu:198-339).
+ * out_color [n_cams][3][H][W], out_depth [n_cams][1][H][W], radii [n_cams][P] (may be NULL).
+ * Blocks the host once (4-byte D2H of num_rendered, like cr/rasterizer_impl.cu:281-282).
+ * Returns num_rendered in ctx->num_rendered. */
+int gsb_raster_forward(const gsb_raster_args* args, gsb_alloc_fn geom_alloc, gsb_alloc_fn binning_alloc,
+                       gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth,
+                       int32_t* radii, gsb_raster_ctx* ctx, void* stream);
+
+/* Rasterizer::backward (cr/rasterizer.h:56-83, cr/rasterizer_impl.cu:343-436).
+ * dL_dpix [n_cams][3][H][W].  Outputs (all written in full, no pre-zeroing required):
+ *   dL_dmean2D [n_cams][P][3] (z = 0), dL_dconic [n_cams][P][4] (slot 2 = 0),
+ *   dL_dopacity [P], dL_dcolor [P][3] (or [n_cams][P][3] if color_cam_stride != 0),
+ *   dL_dmean3D [P][3], dL_dcov3D [P][6] (n_cams==1 only, else may be NULL), dL_dscale [P][3], dL_drot [P][4]
+ * summed over the cameras of the batch. */
+int gsb_raster_backward(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                        float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                        float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot, void* stream);
+
+/* Rasterizer::markVisible (cr/rasterizer.h:24-29, cr/rasterizer_impl.cu:141-153). present: uint8 [P]. */
+int gsb_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* Fused L1 + SSIM loss (replaces external.calc_ssim, external.py:49-110, torch l1_loss and the
+ * 0.8/0.2 mix of densify.py:127-129 / train.py:362-364).  img, target: [n][3][H][W].
+ * loss_out: float [n][3] = (l1 mean, ssim mean, w_l1*l1 + w_ssim*(1-ssim)) per image.
+ * If dL_dimg != NULL it receives grad_scale * d loss/d img.  scratch: gsb_ssim_scratch_bytes(). */
+size_t gsb_ssim_scratch_bytes(int32_t n, int32_t height, int32_t width);
+int gsb_ssim_l1(int32_t n, int32_t height, int32_t width, const float* img, const float* target,
+                float w_l1, float w_ssim, float grad_scale, float* loss_out, float* dL_dimg,
+                void* scratch, void* stream);
+
+/* Densification statistics: update_max_2d_radii_and_visibility_mask (densify.py:154-162) fused with
+ * accumulate_mean_2d_gradients (external.py:113-124).  radii [P], grad_means2D [P][3]. */
+int gsb_densify_accumulate(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_2d_radii,
+                           float* grad_accum, float* vis_count, uint8_t* visible, void* stream);
+
+/* Stable stream compaction of row tables: replaces the boolean-mask indexing of
+ * remove_points / cat_params_to_optimizer (external.py:127-204).
+ *   gsb_mask_scan: keep[P] (uint8) -> dst_index[P] (exclusive rank of kept rows), count_out (device int32[1]).
+ *   gsb_gather_rows: dst[dst_index[i]] = src[i] for kept rows, `row_floats` floats per row. */
+size_t gsb_scan_scratch_bytes(int32_t n);
+int gsb_mask_scan(int32_t P, const uint8_t* keep, int32_t* dst_index, int32_t* count_out, void* scratch, void* stream);
+int gsb_gather_rows(int32_t P, const uint8_t* keep, const int32_t* dst_index, const float* src, float* dst,
+                    int32_t row_floats, void* stream);
+
+/* Debug / test accessors: the individual stages, so that tests can compare every intermediate
+ * bit-for-bit. */
+int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream);
+size_t gsb_sort_temp_bytes(int64_t n);
+int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
+                   uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSB200_H */

@@ -1,0 +1,49 @@
+"""Shared helpers for the parity tests."""
+import numpy as np
+import torch
+
+from gsb200 import scene
+
+
+def scene_inputs(P, W, H, seed=0, n_cams=1, device="cpu", scale_override=None, extent=1.5):
+    g = scene.make_gaussians(P, seed=seed, scale_override=scale_override, extent=extent)
+    a = {k: v.to(device).contiguous() for k, v in scene.activate(g).items()}
+    cams = scene.make_cameras(n_cams, W, H, seed=seed)
+    return g, a, cams
+
+
+def ref_forward(refdgr, a, cam, bg, device, cov3D_precomp=None, scale_modifier=1.0):
+    """Call the unmodified reference extension the way DGR/diff_gaussian_rasterization/__init__.py:55-79 does."""
+    e = torch.Tensor([])
+    args = (bg, a["means3D"], a["colors_precomp"], a["opacities"],
+            a["scales"] if cov3D_precomp is None else e, a["rotations"] if cov3D_precomp is None else e,
+            scale_modifier, cov3D_precomp if cov3D_precomp is not None else e,
+            cam["viewmatrix"].to(device), cam["projmatrix"].to(device), cam["tanfovx"], cam["tanfovy"],
+            cam["image_height"], cam["image_width"], e, 0, cam["campos"].to(device), False)
+    num_rendered, color, radii, geom, binning, img, depth = refdgr.rasterize_gaussians(*args)
+    return dict(num_rendered=num_rendered, color=color, radii=radii, geom=geom, binning=binning, img=img, depth=depth)
+
+
+def ref_backward(refdgr, a, cam, bg, device, fw, dL_dpix, cov3D_precomp=None, scale_modifier=1.0):
+    e = torch.Tensor([])
+    args = (bg, a["means3D"], fw["radii"], a["colors_precomp"],
+            a["scales"] if cov3D_precomp is None else e, a["rotations"] if cov3D_precomp is None else e,
+            scale_modifier, cov3D_precomp if cov3D_precomp is not None else e,
+            cam["viewmatrix"].to(device), cam["projmatrix"].to(device), cam["tanfovx"], cam["tanfovy"], dL_dpix, e, 0,
+            cam["campos"].to(device), fw["geom"], fw["num_rendered"], fw["binning"], fw["img"])
+    dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = refdgr.rasterize_gaussians_backward(*args)
+    return {"means2D": dm2, "colors": dcol, "opacities": dop, "means3D": dm3, "cov3D": dcov, "scales": dsc,
+            "rotations": drot}
+
+
+def grad_close(a, b, rel=1e-4, floor=1e-6):
+    """north_star tolerance for parameter gradients: 1e-4 relative (atomic order differs), with an
+    absolute floor of `floor` x the tensor's largest magnitude for entries that are sums of cancelling terms."""
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    tol = rel * np.maximum(np.abs(a), np.abs(b)) + floor * max(np.abs(b).max(), 1e-30)
+    bad = np.abs(a - b) > tol
+    return int(bad.sum()), float(np.abs(a - b).max())
+
+
+def to_np(t):
+    return t.detach().cpu().numpy()
