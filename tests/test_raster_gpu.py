@@ -75,12 +75,14 @@ def test_backward_vs_reference_ext(refdgr, name, P, W, H, seed, bgv, so):
     dL = torch.randn((3, H, W), generator=gen).to(dev)
     fw = helpers.ref_forward(refdgr, a, cam, bg, dev)
     gr = helpers.ref_backward(refdgr, a, cam, bg, dev, fw, dL)
+    gr2 = helpers.ref_backward(refdgr, a, cam, bg, dev, fw, dL)   # the reference's own atomic-order spread
     color, depth, radii, st = run_mine(a, cam, bg)
     gm = raster.backward(st, dL)
     torch.cuda.synchronize()
     for k in ("means2D", "colors", "opacities", "means3D", "scales", "rotations"):
-        nbad, maxerr = helpers.grad_close(helpers.to_np(gm[k]), helpers.to_np(gr[k]))
-        assert nbad == 0, (k, nbad, maxerr)
+        spread = float((gr[k] - gr2[k]).abs().max())
+        nbad, maxerr = helpers.grad_close(helpers.to_np(gm[k]), helpers.to_np(gr[k]), spread=spread)
+        assert nbad == 0, (k, nbad, maxerr, spread)
 
 
 def test_cov3d_precomp_path(refdgr):
