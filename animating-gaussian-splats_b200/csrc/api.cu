@@ -33,6 +33,19 @@ static int stage_reserve(size_t bytes) {
   return GSB_OK;
 }
 
+// Optional per-stage CUDA-event timing (gsb_profile_enable / gsb_profile_read), used by bench.py to time
+// each kernel live on the launching stream.
+enum { PF_FWD_BEGIN = 0, PF_PREPROCESS, PF_SCAN, PF_D2H, PF_DUPKEYS, PF_SORT, PF_RANGES, PF_RENDER_FWD,
+       PF_BWD_BEGIN, PF_BWD_ZERO, PF_RENDER_BWD, PF_PREPROCESS_BWD, PF_COUNT };
+static bool g_prof_on = false;
+static cudaEvent_t g_prof_ev[PF_COUNT];
+static bool g_prof_seen[PF_COUNT];
+static inline void prof_mark(int i, cudaStream_t st) {
+  if (!g_prof_on) return;
+  cudaEventRecord(g_prof_ev[i], st);
+  g_prof_seen[i] = true;
+}
+
 // Bump-pointer carve-up of a byte buffer, 256-B aligned (the reference aligns to 128 B,
 // cr/rasterizer_impl.h:21-29).
 struct Carver {
@@ -172,9 +185,12 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   GSB_CUDA_CHECK(cudaMemcpyAsync(cams_dev, cams_host, sizeof(CamParams) * (size_t)a->n_cams, cudaMemcpyHostToDevice, st));
   GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
 
+  prof_mark(PF_FWD_BEGIN, st);
   if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, err_dev, st))) return rc;
+  prof_mark(PF_PREPROCESS, st);
   const int64_t n_slots = (int64_t)a->P * a->n_cams;
   if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st))) return rc;
+  prof_mark(PF_SCAN, st);
 
   // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
   uint32_t* down = reinterpret_cast<uint32_t*>(g_stage.pinned);
@@ -188,12 +204,17 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   if (!bin) return GSB_ENOMEM;
   carve_binning(bin, ctx->num_rendered, ctx);
 
+  prof_mark(PF_D2H, st);
   if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
+  prof_mark(PF_DUPKEYS, st);
   if ((rc = launch_sort_pairs(ctx->num_rendered, ctx->point_list_keys_unsorted, ctx->point_list_keys,
                               ctx->point_list_unsorted, ctx->point_list, ctx->sort_bits, ctx->sort_temp, st)))
     return rc;
+  prof_mark(PF_SORT, st);
   if ((rc = launch_tile_ranges(*ctx, st))) return rc;
+  prof_mark(PF_RANGES, st);
   if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
+  prof_mark(PF_RENDER_FWD, st);
   return GSB_OK;
 }
 
@@ -207,6 +228,7 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
     return GSB_EINVAL;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const size_t n = (size_t)a->P * a->n_cams;
+  prof_mark(PF_BWD_BEGIN, st);
   GSB_CUDA_CHECK(cudaMemsetAsync(dL_dmean2D, 0, n * 3 * sizeof(float), st));
   GSB_CUDA_CHECK(cudaMemsetAsync(dL_dconic, 0, n * 4 * sizeof(float), st));
   GSB_CUDA_CHECK(cudaMemsetAsync(dL_dopacity, 0, (size_t)a->P * sizeof(float), st));
@@ -214,14 +236,38 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
                                           : (size_t)a->P * 3;
   GSB_CUDA_CHECK(cudaMemsetAsync(dL_dcolor, 0, ncol * sizeof(float), st));
   int rc;
+  prof_mark(PF_BWD_ZERO, st);
   if (ctx->num_rendered > 0)
     if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, st))) return rc;
+  prof_mark(PF_RENDER_BWD, st);
   // the per-camera scalar table still sits in the geometry buffer next to the state arrays
   CamParams* cams_dev;
   GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &cams_dev, nullptr, nullptr);
   if ((rc = launch_preprocess_bwd(*a, cams_dev, *ctx, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcov3D, dL_dscale,
                                   dL_drot, st)))
     return rc;
+  prof_mark(PF_PREPROCESS_BWD, st);
+  return GSB_OK;
+}
+
+int gsb_profile_enable(int on) {
+  if (on && !g_prof_ev[0]) {
+    for (int i = 0; i < PF_COUNT; i++) GSB_CUDA_CHECK(cudaEventCreate(&g_prof_ev[i]));
+  }
+  for (int i = 0; i < PF_COUNT; i++) g_prof_seen[i] = false;
+  g_prof_on = on != 0;
+  return GSB_OK;
+}
+
+int gsb_profile_read(float* ms_out, int32_t n) {
+  // ms_out[i] = elapsed between stage event i-1 and i of the LAST forward / backward (0 for the two begins)
+  if (!ms_out || n < PF_COUNT) return GSB_EINVAL;
+  for (int i = 0; i < PF_COUNT; i++) {
+    ms_out[i] = 0.f;
+    if (i == PF_FWD_BEGIN || i == PF_BWD_BEGIN || !g_prof_seen[i] || !g_prof_seen[i - 1]) continue;
+    GSB_CUDA_CHECK(cudaEventSynchronize(g_prof_ev[i]));
+    GSB_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i], g_prof_ev[i - 1], g_prof_ev[i]));
+  }
   return GSB_OK;
 }
 

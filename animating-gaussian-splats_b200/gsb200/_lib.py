@@ -66,7 +66,11 @@ SYMBOLS = {
     "gsb_sort_temp_bytes": (C.c_size_t, [C.c_int64]),
     "gsb_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                  C.c_void_p]),
+    "gsb_profile_enable": (C.c_int, [C.c_int]),
+    "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }
+PROFILE_STAGES = ["fwd_begin", "preprocess", "scan", "d2h_sync", "duplicate_keys", "sort", "tile_ranges",
+                  "render_fwd", "bwd_begin", "bwd_zero", "render_bwd", "preprocess_bwd"]
 
 _lib = None
 

@@ -1,0 +1,451 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the rasterizer + L1/SSIM + densify-statistics hot path.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference ...                     (the CPU arm: C oracle on the host cores)
+    python bench.py --impl reference_cuda ...                (extra: the unmodified reference CUDA extension)
+
+Workload (BASELINE.json configs[1] / configs[2]): one Panoptic-shaped synthetic timestep, 300 000
+Gaussians, 27 cameras 640x360.  One STEP = one pass of the hot path over all 27 cameras:
+    rasterize forward (batched over the rank's cameras) -> fused L1+SSIM loss and dL/dimage ->
+    rasterize backward (gradients summed over cameras) -> densification statistics per camera
+and, for N > 1, ONE NCCL allreduce of the flat gradient + statistics buffer (cameras are sharded
+c -> rank c % N; total work is fixed, so scaling is "strong").
+metric = train iters/sec, one iteration = one camera's fwd + loss + bwd (the unit of densify.py:218-247),
+so value = 27 / step time, whole job.  Gaussian-pixel blends/sec (fwd+bwd) is reported beside it.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "animating-gaussian-splats_b200")
+for p in (ROOT, PKG, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+
+# ------------------------------------------------------------------------------------------------
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference_cuda"])
+    ap.add_argument("--gaussians", type=int, default=300_000)
+    ap.add_argument("--cams", type=int, default=27)
+    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--height", type=int, default=360)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-cuda", action="store_true")
+    ap.add_argument("--profile-only", action="store_true", help="one warm step + 2 steps, for ncu")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), float(p.get("sm_max_mhz", 1965.0)), "measured"
+    except Exception:
+        return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def build_workload(args):
+    """Seeded synthetic timestep (CPU tensors): raw parameters, cameras, and the raw parameters of the
+    perturbed copy whose renders are the target images."""
+    from gsb200 import scene
+    g = scene.make_gaussians(args.gaussians, seed=0)
+    cams = scene.make_cameras(args.cams, args.width, args.height, seed=0)
+    rng = np.random.default_rng(7)
+    tgt = {k: v.clone() for k, v in g.items()}
+    tgt["means"] = tgt["means"] + torch.from_numpy(rng.normal(0, 0.01, size=tuple(g["means"].shape)).astype(np.float32))
+    tgt["colors"] = (tgt["colors"] + torch.from_numpy(rng.normal(0, 0.1, size=tuple(g["colors"].shape)).astype(np.float32))).clamp(0, 1)
+    return g, tgt, cams
+
+
+def render_targets(tgt_raw, cams_stacked, n, bg, dev):
+    from gsb200 import raster, scene
+    a = {k: v.to(dev).contiguous() for k, v in scene.activate(tgt_raw).items()}
+    color, _, _, _ = raster.forward(a["means3D"], a["colors_precomp"], a["opacities"], a["scales"], a["rotations"], None,
+                                    bg, 1.0, cams_stacked["viewmatrix"], cams_stacked["projmatrix"],
+                                    cams_stacked["tanfovx"], cams_stacked["tanfovy"], cams_stacked["image_height"],
+                                    cams_stacked["image_width"], n_cams=n)
+    return (color if n > 1 else color[None]).clone()
+
+
+def sort_passes(tiles_total):
+    bits = 32 + int(np.ceil(np.log2(max(tiles_total, 2))) if tiles_total & (tiles_total - 1) else int(np.log2(tiles_total)) + 1)
+    return (bits + 7) // 8
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from gsb200 import _lib, scene, step as step_mod
+    import ctypes as C
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl ours needs a CUDA device (no CPU fallback exists)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.lib()
+
+    g_raw, tgt_raw, cams = build_workload(args)
+    my_cam_ids = list(range(rank, args.cams, world))
+    my_cams = [cams[i] for i in my_cam_ids]
+    n_my = len(my_cams)
+    sc = scene.stack_cameras(my_cams, dev)
+    bg = torch.zeros(3, device=dev)
+    targets = render_targets(tgt_raw, sc, n_my, bg, dev)
+    P = args.gaussians
+
+    # host (pinned) copies for the end-to-end leg
+    raw_keys = ["means", "colors", "rotation_quaternions", "opacity_logits", "log_scales"]
+    host_raw = {k: g_raw[k].contiguous().pin_memory() for k in raw_keys}
+    host_targets = targets.cpu().pin_memory()
+    dev_raw = {k: torch.empty_like(v, device=dev) for k, v in host_raw.items()}
+    dev_targets = torch.empty_like(targets)
+    loss_host = torch.empty((n_my, 3), dtype=torch.float32).pin_memory()
+
+    stats = step_mod.DensifyStats(P, dev)
+    # flat buffer for the one allreduce: 17 gradient floats + 2 summed statistics per Gaussian
+    flat = torch.zeros((P, 19), dtype=torch.float32, device=dev) if world > 1 else None
+
+    def activate():
+        return {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}
+
+    def one_step(act):
+        loss_stats, grads, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, stats)
+        if world > 1:
+            flat[:, 0:3] = grads["means3D"]; flat[:, 3:6] = grads["colors"]; flat[:, 6:10] = grads["rotations"]
+            flat[:, 10:11] = grads["opacities"]; flat[:, 11:14] = grads["scales"]
+            flat[:, 14] = stats.mean_2d_gradients_accumulated; flat[:, 15] = stats.visibility_count
+            dist.all_reduce(flat)
+        return loss_stats, grads, st
+
+    for k in raw_keys:
+        dev_raw[k].copy_(host_raw[k])
+    dev_targets.copy_(host_targets)
+    act = activate()
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if args.profile_only:
+        for _ in range(3):
+            one_step(act)
+        torch.cuda.synchronize()
+        return
+
+    # ---- device-resident timing -------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        loss_stats, grads, st = one_step(act)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss_stats, grads, st = one_step(act)
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+
+    # ---- end to end: host buffers in, loss out, every step ------------------------------------
+    def e2e_step():
+        for k in raw_keys:
+            dev_raw[k].copy_(host_raw[k], non_blocking=True)
+        dev_targets.copy_(host_targets, non_blocking=True)
+        a = activate()
+        ls, _, _ = one_step(a)
+        loss_host.copy_(ls, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    e2e_step()
+    sync_all()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    sync_all()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_e2e = float(t.item()) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    h2d = sum(v.numel() * 4 for v in host_raw.values()) + host_targets.numel() * 4
+    d2h = loss_host.numel() * 4
+
+    # ---- per-stage timing of one step (CUDA events inside the library, on the launching stream) --
+    lib.gsb_profile_enable(1)
+    stage_acc = np.zeros(len(_lib.PROFILE_STAGES))
+    reps = 3
+    buf = (C.c_float * len(_lib.PROFILE_STAGES))()
+    for _ in range(reps):
+        loss_stats, grads, st = one_step(act)
+        torch.cuda.synchronize()
+        lib.gsb_profile_read(buf, len(_lib.PROFILE_STAGES))
+        stage_acc += np.array(list(buf))
+    lib.gsb_profile_enable(0)
+    stages = {k: float(v / reps) for k, v in zip(_lib.PROFILE_STAGES, stage_acc) if not k.endswith("_begin")}
+
+    # ---- workload statistics ---------------------------------------------------------------------
+    tt = st.tensors()
+    walked = int(tt["n_contrib"].long().sum().item())             # sum over pixels of n_contrib
+    R = st.num_rendered
+    cnt = torch.tensor([walked, R], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(cnt)
+    walked_all, R_all = int(cnt[0].item()), int(cnt[1].item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_peak, sm_max_mhz, peak_src = peaks()
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    fp32_peak_tflops = n_sm * 128 * 2 * sm_max_mhz * 1e6 / 1e12
+    # dominant kernel: backward blend.  Algorithmic work: 70 FP32 flop per walked pair.
+    bwd_ms = stages["render_bwd"]
+    achieved = (walked * 70.0) / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else 0.0
+    roofline = {"kernel": "render_bwd_kernel", "bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops,
+                "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": None,
+                "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
+                "ms": bwd_ms, "pairs": walked}
+    # the HBM-bound kernel with the most bytes: the onesweep sort (152 B / instance at 6 passes)
+    tiles_total = ((args.width + 15) // 16) * ((args.height + 15) // 16) * n_my
+    passes = (st.ctx.sort_bits + 7) // 8
+    sort_bytes = R * (8 + 24 * passes)
+    sort_ms = stages["sort"]
+    roofline_hbm = {"kernel": "rs_histogram_kernel + rs_onesweep_kernel x%d" % passes, "bound": "hbm",
+                    "achieved": sort_bytes / (sort_ms * 1e-3) / 1e9 if sort_ms > 0 else 0.0, "peak": hbm_peak,
+                    "unit": "GB/s", "traffic": None, "ms": sort_ms, "instances": R}
+    roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
+    launches = 1 + 1 + 1 + 1 + passes + 1 + 1 + 3 + 1 + 1 + n_my  # see DESIGN.md "launch list"
+
+    out = {
+        "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",
+        "value": args.cams / (ms_step * 1e-3), "unit": "iters/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"Panoptic-shaped timestep: {P} gaussians, {args.cams} cameras {args.width}x{args.height}, "
+                               "fwd + L1/SSIM + bwd + densify stats (BASELINE.json configs[1])",
+                   "cameras_per_rank": n_my, "parallelism": f"camera-sharded dp{world}",
+                   "l2": "per-step working set (state + instance lists) is several hundred MB > 126 MB L2; no explicit flush"},
+        "blends_per_sec": 2.0 * walked_all / (ms_step * 1e-3), "walked_pairs_per_step": walked_all,
+        "num_rendered_per_step": R_all,
+        "e2e": {"value": args.cams / (ms_e2e * 1e-3), "unit": "iters/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches * args.steps,
+        "stage_ms": stages, "roofline": roofline, "roofline_hbm": roofline_hbm, "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(args, g_raw, cams, host_targets)
+    if world == 1 and not args.no_reference_cuda:
+        out["reference_cuda"] = reference_cuda(args, act, my_cams, dev_targets, bg, dev)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_step(o, act_np, cam, target_np, H, W):
+    """One camera of the workload on the CPU oracle: forward, L1+SSIM (+ gradient), backward."""
+    r = o.forward(act_np["means3D"], act_np["colors_precomp"], act_np["opacities"], act_np["scales"],
+                  act_np["rotations"], np.zeros(3, np.float32), cam["viewmatrix"].numpy(), cam["projmatrix"].numpy(),
+                  cam["tanfovx"], cam["tanfovy"], H, W)
+    _, dL = o.ssim_l1(r["color"], target_np, 0.8, 0.2, grad=True)
+    o.backward(r, dL)
+    return r
+
+
+def cpu_baseline(args, g_raw, cams, host_targets, steps=1):
+    import oracle_lib
+    from gsb200 import scene
+    o = oracle_lib.load()
+    act_np = {k: v.numpy() for k, v in scene.activate(g_raw).items()}
+    tgt = host_targets[0].numpy()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(o, act_np, cams[0], tgt, args.height, args.width)
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": 1.0 / dt, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"camera 0 of the workload ({args.gaussians} gaussians, {args.width}x{args.height}): "
+                      f"fwd + L1/SSIM + bwd on the C oracle (OpenMP), {steps} pass(es), {dt:.2f} s each"}
+
+
+def run_reference(args):
+    """--impl reference: the CPU arm.  The reference ships no CPU implementation of this path, so the
+    C restatement under oracle/ (OpenMP, all host threads) is what is timed; each step is a bounded
+    sample of the workload: ONE camera (fwd + L1/SSIM + bwd)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle_lib
+    from gsb200 import scene
+    o = oracle_lib.load()
+    g_raw, tgt_raw, cams = build_workload(args)
+    act_np = {k: v.numpy() for k, v in scene.activate(g_raw).items()}
+    tgt_np = {k: v.numpy() for k, v in scene.activate(tgt_raw).items()}
+    H, W = args.height, args.width
+    tr = o.forward(tgt_np["means3D"], tgt_np["colors_precomp"], tgt_np["opacities"], tgt_np["scales"], tgt_np["rotations"],
+                   np.zeros(3, np.float32), cams[0]["viewmatrix"].numpy(), cams[0]["projmatrix"].numpy(),
+                   cams[0]["tanfovx"], cams[0]["tanfovy"], H, W)
+    target = tr["color"]
+    for _ in range(min(args.warmup, 1)):
+        cpu_step(o, act_np, cams[0], target, H, W)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_step(o, act_np, cams[0], target, H, W)
+    dt = (time.perf_counter() - t0) / args.steps
+    v = 1.0 / dt
+    sample = (f"camera 0 of the workload ({args.gaussians} gaussians, {W}x{H}) per step: fwd + L1/SSIM + bwd on the "
+              f"C oracle (OpenMP); the reference has no CPU path for the rasterizer")
+    print(json.dumps({
+        "impl": "reference", "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",
+        "value": v, "unit": "iters/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"Panoptic-shaped timestep: {args.gaussians} gaussians, {args.cams} cameras "
+                               f"{W}x{H}, fwd + L1/SSIM + bwd + densify stats (BASELINE.json configs[1])",
+                   "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+def torch_ssim_l1(img, target):
+    """Restatement of external.calc_ssim + the 0.8/0.2 mix (external.py:49-110, densify.py:127-129) in
+    stock PyTorch ops -- what the reference runs next to its CUDA rasterizer."""
+    import torch.nn.functional as F
+    g = torch.tensor([np.exp(-((x - 5) ** 2) / (2 * 1.5 ** 2)) for x in range(11)], dtype=torch.float32)
+    g = (g / g.sum()).unsqueeze(1)
+    w = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0).expand(3, 1, 11, 11).contiguous().to(img.device)
+    mu1 = F.conv2d(img, w, padding=5, groups=3); mu2 = F.conv2d(target, w, padding=5, groups=3)
+    mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(img * img, w, padding=5, groups=3) - mu1_sq
+    s2 = F.conv2d(target * target, w, padding=5, groups=3) - mu2_sq
+    s12 = F.conv2d(img * target, w, padding=5, groups=3) - mu12
+    c1, c2 = 0.01 ** 2, 0.03 ** 2
+    ssim = (((2 * mu12 + c1) * (2 * s12 + c2)) / ((mu1_sq + mu2_sq + c1) * (s1 + s2 + c2))).mean()
+    return 0.8 * (img - target).abs().mean() + 0.2 * (1.0 - ssim)
+
+
+def reference_cuda(args, act, cams, targets, bg, dev, passes=2):
+    """The unmodified reference CUDA extension (oracle/_ref) on the same GPU, same inputs, its own
+    per-camera call pattern: forward -> torch L1/SSIM -> autograd -> backward, camera by camera."""
+    import oracle_lib
+    import helpers
+    ref = oracle_lib.load_reference_ext()
+    if ref is None:
+        return {"unavailable": "oracle/_ref/refdgr/_C.so not built"}
+
+    def one_pass():
+        for i, cam in enumerate(cams):
+            fw = helpers.ref_forward(ref, act, cam, bg, dev)
+            img = fw["color"].detach().requires_grad_(True)
+            loss = torch_ssim_l1(img, targets[i])
+            loss.backward()
+            helpers.ref_backward(ref, act, cam, bg, dev, fw, img.grad)
+
+    one_pass()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(passes):
+        one_pass()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / passes
+    return {"value": len(cams) / (ms * 1e-3), "unit": "iters/s", "ms_per_step": ms,
+            "what": "unmodified reference extension (sm_100a build, CUB sort) + stock torch L1/SSIM, camera by camera"}
+
+
+def run_reference_cuda(args):
+    from gsb200 import scene
+    dev = torch.device("cuda", 0)
+    g_raw, tgt_raw, cams = build_workload(args)
+    sc = scene.stack_cameras(cams, dev)
+    bg = torch.zeros(3, device=dev)
+    targets = render_targets(tgt_raw, sc, args.cams, bg, dev)
+    act = {k: v.to(dev).contiguous() for k, v in scene.activate(g_raw).items()}
+    r = reference_cuda(args, act, cams, targets, bg, dev, passes=max(args.steps, 1))
+    r["impl"] = "reference_cuda"
+    print(json.dumps(r))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    elif a.impl == "reference_cuda":
+        run_reference_cuda(a)
+    else:
+        run_ours(a)

@@ -137,6 +137,13 @@ size_t gsb_sort_temp_bytes(int64_t n);
 int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
                    uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
 
+/* Per-stage CUDA-event timing of the last forward/backward on this thread's library instance (bench
+ * instrumentation; off by default).  Stage order: fwd_begin, preprocess, scan, d2h_sync, duplicate_keys,
+ * sort, tile_ranges, render_fwd, bwd_begin, bwd_zero, render_bwd, preprocess_bwd (GSB_PROFILE_STAGES). */
+#define GSB_PROFILE_STAGES 12
+int gsb_profile_enable(int on);
+int gsb_profile_read(float* ms_out_host, int32_t n);
+
 #ifdef __cplusplus
 }
 #endif
