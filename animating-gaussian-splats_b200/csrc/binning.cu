@@ -272,7 +272,7 @@ struct RsSmem {
   uint32_t tile;
 };
 
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 3)
 rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsigned long long* __restrict__ kout,
                    const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout, int shift, int nbits,
                    const uint32_t* __restrict__ ghist, uint32_t* __restrict__ ticket,
@@ -410,6 +410,8 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
   if (!attr_set) {
     GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(RsSmem)));
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
   GSB_CUDA_CHECK(cudaMemsetAsync(temp, 0, RS_HEADER + (size_t)passes * tiles * RS_RADIX * 4, st));

@@ -24,15 +24,74 @@ __device__ __forceinline__ float blend_power(float dx, float dy, float A, float 
   return FMA(q, -0.5f, -MUL(dy, MUL(dx, B)));
 }
 
-__global__ void __launch_bounds__(GSB_BLOCK_SIZE)
+// ------------------------------------------------------------------------------------------------
+// Exact-conservative tile culling, done by the thread that stages a list entry.
+//
+// The reference's lists hold every Gaussian whose 3-sigma bounding SQUARE touches the tile; most of
+// them cannot reach alpha >= 1/255 at any pixel of the tile.  An entry may be dropped from the staged
+// batch iff for every pixel of the tile the reference would `continue` (cr/forward.cu:342-351), i.e.
+//   opacity < 1/255                      (alpha = min(.99, o*exp(power)) <= o, power <= 0), or
+//   max over the tile of power < -ln(255 o)   with a slack that covers every rounding difference.
+// max power = -0.5 * min q, q = A dx^2 + 2 B dx dy + C dy^2 (convex): 0 if the centre lies in the tile,
+// else attained on one of the four edges (a clamped 1-D quadratic each).  Dropping such entries leaves
+// colour, depth, final_T and n_contrib (= original list position of the last blended entry) unchanged.
+// `thr` (returned) is the per-entry power below which a pixel certainly has alpha < 1/255, so the inner
+// loop can skip it before paying for expf.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool tile_cull_keep(float cx, float cy, float4 co, float tx0, float ty0, float& thr) {
+  const float A = co.x, B = co.y, C = co.z, o = co.w;
+  thr = -3.0e38f;
+  if (o < 1.0f / 255.0f) return false;
+  if (!(o >= 1.0f / 255.0f)) return true;                 // NaN opacity: keep, no early threshold
+  const float L = logf(255.0f * o);                        // >= 0
+  thr = -(L + 2.0e-3f + 1.0e-3f * L);
+  if (!(A > 0.f && C > 0.f && A * C > B * B)) return true;  // not positive definite: no claim
+  const float dxlo = cx - (tx0 + 15.0f), dxhi = cx - tx0;  // d = centre - pixel over the tile
+  const float dylo = cy - (ty0 + 15.0f), dyhi = cy - ty0;
+  if (dxlo <= 0.f && dxhi >= 0.f && dylo <= 0.f && dyhi >= 0.f) return true;
+  const float iA = __fdividef(1.0f, A), iC = __fdividef(1.0f, C);
+  float qmin = 3.0e38f;
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const float e = k ? dxhi : dxlo;                       // vertical edges: dx = e
+    const float dy = fminf(fmaxf(-B * e * iC, dylo), dyhi);
+    qmin = fminf(qmin, A * e * e + 2.f * B * e * dy + C * dy * dy);
+    const float f = k ? dyhi : dylo;                       // horizontal edges: dy = f
+    const float dx = fminf(fmaxf(-B * f * iA, dxlo), dxhi);
+    qmin = fminf(qmin, A * dx * dx + 2.f * B * dx * f + C * f * f);
+  }
+  if (!(qmin < 3.0e38f)) return true;                      // NaN geometry: no claim
+  const float DX = fmaxf(fabsf(dxlo), fabsf(dxhi)), DY = fmaxf(fabsf(dylo), fabsf(dyhi));
+  const float Mmax = A * DX * DX + 2.f * fabsf(B) * DX * DY + C * DY * DY;  // bounds every rounding error
+  return !(0.5f * qmin > L + 2.0e-3f + 1.0e-3f * L + 1.0e-5f * Mmax);
+}
+
+// Block-wide stable compaction slot for `keep`; returns the number of kept entries of the batch.
+__device__ __forceinline__ int compact_slot(bool keep, unsigned tid, int* s_wcnt, int& slot) {
+  const unsigned bal = __ballot_sync(0xffffffffu, keep);
+  if ((tid & 31u) == 0) s_wcnt[tid >> 5] = __popc(bal);
+  __syncthreads();
+  int before = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < GSB_BLOCK_SIZE / 32; w++) {
+    const int c = s_wcnt[w];
+    if (w < (int)(tid >> 5)) before += c;
+    total += c;
+  }
+  slot = before + __popc(bal & lanemask_lt());
+  return total;
+}
+
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE, 6)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
                   const float2* __restrict__ means2D, const float* __restrict__ colors, int color_cam_stride,
                   const float4* __restrict__ conic_opacity, const float* __restrict__ depths,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth) {
-  __shared__ float2 s_xy[GSB_BLOCK_SIZE];
-  __shared__ float4 s_co[GSB_BLOCK_SIZE];
+  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position + 1)
+  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_cd[GSB_BLOCK_SIZE];  // r, g, b, depth
+  __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
 
   const int cam = blockIdx.z;
   const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
@@ -42,6 +101,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pfx = (float)px, pfy = (float)py;
+  const float tx0 = (float)(blockIdx.x * GSB_BLOCK_X), ty0 = (float)(blockIdx.y * GSB_BLOCK_Y);
   bool done = !inside;
 
   const uint2 range = ranges[(size_t)cam * tiles_per_cam + tile];
@@ -55,26 +115,36 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float C0 = 0.f, C1 = 0.f, C2 = 0.f;
   float D = 15.0f;  // median depth default (cr/forward.cu:308)
 
-  int toDo = total;
-  for (int i = 0; i < rounds; i++, toDo -= GSB_BLOCK_SIZE) {
+  for (int i = 0; i < rounds; i++) {
     if (__syncthreads_count(done) == GSB_BLOCK_SIZE) break;
     const int progress = i * GSB_BLOCK_SIZE + tid;
+    bool keep = false;
+    uint32_t id = 0;
+    float2 xy = make_float2(0.f, 0.f);
+    float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+    float thr = 0.f;
     if (progress < total) {
-      const uint32_t id = point_list[range.x + progress];
-      s_xy[tid] = means2D[cam_off + id];
-      s_co[tid] = conic_opacity[cam_off + id];
-      s_cd[tid] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
-                              depths[cam_off + id]);
+      id = point_list[range.x + progress];
+      xy = means2D[cam_off + id];
+      co = conic_opacity[cam_off + id];
+      keep = tile_cull_keep(xy.x, xy.y, co, tx0, ty0, thr);
+    }
+    int slot;
+    const int n = compact_slot(keep, tid, s_wcnt, slot);
+    if (keep) {
+      s_a[slot] = make_float4(xy.x, xy.y, thr, __uint_as_float((uint32_t)progress + 1u));
+      s_co[slot] = co;
+      s_cd[slot] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
+                               depths[cam_off + id]);
     }
     __syncthreads();
-    const int n = min(GSB_BLOCK_SIZE, toDo);
     for (int j = 0; !done && j < n; j++) {
-      const float2 xy = s_xy[j];
-      const float4 co = s_co[j];
-      const float dx = SUB(xy.x, pfx), dy = SUB(xy.y, pfy);
-      const float power = blend_power(dx, dy, co.x, co.y, co.z);
-      if (power > 0.0f) continue;
-      const float alpha = fminf(0.99f, MUL(co.w, expf(power)));
+      const float4 a = s_a[j];
+      const float4 co2 = s_co[j];
+      const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
+      const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
+      if (power > 0.0f || power < a.z) continue;   // below a.z: certainly alpha < 1/255
+      const float alpha = fminf(0.99f, MUL(co2.w, expf(power)));
       if (alpha < 1.0f / 255.0f) continue;
       const float test_T = MUL(T, SUB(1.0f, alpha));
       if (test_T < 0.0001f) { done = true; continue; }
@@ -84,7 +154,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       C2 = FMA(T, MUL(alpha, cd.z), C2);
       if (T > 0.5f && test_T < 0.5f) D = cd.w;
       T = test_T;
-      last_contributor = (uint32_t)(i * GSB_BLOCK_SIZE + j + 1);
+      last_contributor = __float_as_uint(a.w);
     }
   }
 
@@ -149,16 +219,17 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
   v[0] += __shfl_xor_sync(full, v[0], 1);
 }
 
-__global__ void __launch_bounds__(GSB_BLOCK_SIZE)
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE, 4)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
                   const float* __restrict__ bg, const float2* __restrict__ means2D,
                   const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
                   float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
-  __shared__ float2 s_xy[GSB_BLOCK_SIZE];
-  __shared__ float4 s_co[GSB_BLOCK_SIZE];
+  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position)
+  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
+  __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
   __shared__ int s_block_last;
 
   const int cam = blockIdx.z;
@@ -170,6 +241,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pfx = (float)px, pfy = (float)py;
+  const float tx0 = (float)(blockIdx.x * GSB_BLOCK_X), ty0 = (float)(blockIdx.y * GSB_BLOCK_Y);
   const size_t HW = (size_t)H * W;
   const size_t pid = (size_t)py * W + px;
 
@@ -208,27 +280,39 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int rounds = (block_last + GSB_BLOCK_SIZE - 1) / GSB_BLOCK_SIZE;
   for (int i = 0; i < rounds; i++) {
     if (i > 0) __syncthreads();
-    const int batch_top = block_last - 1 - i * GSB_BLOCK_SIZE;  // list position of batch entry 0
-    const int n = min(GSB_BLOCK_SIZE, batch_top + 1);
-    if ((int)tid < n) {
-      const uint32_t id = point_list[range.x + (uint32_t)(batch_top - (int)tid)];
-      s_xy[tid] = means2D[cam_off + id];
-      s_co[tid] = conic_opacity[cam_off + id];
-      s_ci[tid] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
-                              __uint_as_float(id));
+    const int pos_mine = block_last - 1 - i * GSB_BLOCK_SIZE - (int)tid;  // list position staged by this thread
+    bool keep = false;
+    uint32_t id = 0;
+    float2 xy = make_float2(0.f, 0.f);
+    float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+    float thr = 0.f;
+    if (pos_mine >= 0) {
+      id = point_list[range.x + (uint32_t)pos_mine];
+      xy = means2D[cam_off + id];
+      co = conic_opacity[cam_off + id];
+      keep = tile_cull_keep(xy.x, xy.y, co, tx0, ty0, thr);
+    }
+    int slot;
+    const int n = compact_slot(keep, tid, s_wcnt, slot);
+    if (keep) {
+      s_a[slot] = make_float4(xy.x, xy.y, thr, __int_as_float(pos_mine));
+      s_co[slot] = co;
+      s_ci[slot] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
+                               __uint_as_float(id));
     }
     __syncthreads();
-    // entry j has list position batch_top - j; this warp needs position < warp_last
-    const int j0 = max(0, batch_top - warp_last + 1);
-    for (int j = j0; j < n; j++) {
-      const int pos = batch_top - j;
-      const float2 xy = s_xy[j];
-      const float4 co = s_co[j];
-      const float dx = SUB(xy.x, pfx), dy = SUB(xy.y, pfy);
-      const float power = blend_power(dx, dy, co.x, co.y, co.z);
+    for (int j = 0; j < n; j++) {
+      const float4 a = s_a[j];
+      const int pos = __float_as_int(a.w);
+      if (pos >= warp_last) continue;            // warp-uniform: behind this warp's deepest contributor
+      const float4 co2 = s_co[j];
+      const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
+      const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
+      const bool pre = (pos < last_contributor) && !(power > 0.0f) && !(power < a.z);
+      if (!__any_sync(0xffffffffu, pre)) continue;
       const float G = expf(power);
-      const float alpha = fminf(0.99f, MUL(co.w, G));
-      const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+      const float alpha = fminf(0.99f, MUL(co2.w, G));
+      const bool valid = pre && !(alpha < 1.0f / 255.0f);
       if (!__any_sync(0xffffffffu, valid)) continue;
 
       float v[8];
@@ -252,10 +336,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         dL_dalpha *= T;
         last_alpha = alpha;
         dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-        const float dL_dG = co.w * dL_dalpha;
+        const float dL_dG = co2.w * dL_dalpha;
         const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * co.x - gdy * co.y;
-        const float dG_ddely = -gdy * co.z - gdx * co.y;
+        const float dG_ddelx = -gdx * co2.x - gdy * co2.y;
+        const float dG_ddely = -gdy * co2.z - gdx * co2.y;
         v[3] = dL_dG * dG_ddelx * ddelx_dx;
         v[4] = dL_dG * dG_ddely * ddely_dy;
         v[5] = -0.5f * gdx * dx * dL_dG;
@@ -267,14 +351,14 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #pragma unroll
       for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
 
-      const uint32_t id = __float_as_uint(ci.w);
+      const uint32_t id2 = __float_as_uint(ci.w);
       const unsigned comp = lane >> 2;
       float* dst;
       float val = v[0];
-      if (lane == 1) { dst = dL_dopacity + id; val = g_op; }
-      else if (comp < 3) dst = dcol_tab + 3 * (size_t)id + comp;
-      else if (comp < 5) dst = dL_dmean2D + 3 * (cam_off + id) + (comp - 3);
-      else dst = dL_dconic + 4 * (cam_off + id) + (comp == 7 ? 3 : comp - 5);
+      if (lane == 1) { dst = dL_dopacity + id2; val = g_op; }
+      else if (comp < 3) dst = dcol_tab + 3 * (size_t)id2 + comp;
+      else if (comp < 5) dst = dL_dmean2D + 3 * (cam_off + id2) + (comp - 3);
+      else dst = dL_dconic + 4 * (cam_off + id2) + (comp == 7 ? 3 : comp - 5);
       if (((lane & 3u) == 0 || lane == 1) && val != 0.f) atomicAdd(dst, val);
     }
   }
