@@ -35,7 +35,7 @@ static int stage_reserve(size_t bytes) {
 
 // Optional per-stage CUDA-event timing (gsb_profile_enable / gsb_profile_read), used by bench.py to time
 // each kernel live on the launching stream.
-enum { PF_FWD_BEGIN = 0, PF_PREPROCESS, PF_SCAN, PF_D2H, PF_DUPKEYS, PF_SORT, PF_RANGES, PF_RENDER_FWD,
+enum { PF_FWD_BEGIN = 0, PF_PREPROCESS, PF_DEPTH_SORT, PF_SCAN, PF_D2H, PF_DUPKEYS, PF_SORT, PF_RANGES, PF_RENDER_FWD,
        PF_BWD_BEGIN, PF_BWD_ZERO, PF_RENDER_BWD, PF_PREPROCESS_BWD, PF_COUNT };
 static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[PF_COUNT];
@@ -61,9 +61,17 @@ struct Carver {
   }
 };
 
+struct GeomExtras {
+  CamParams* cams = nullptr;
+  int* err = nullptr;
+  void* scan_scratch = nullptr;
+  uint64_t* gkeys_in = nullptr;   // unsorted (camera << 32 | depth) keys, written by preprocess
+  uint32_t* gvals_in = nullptr;   // iota
+  void* gsort_temp = nullptr;
+};
+
 struct GeomLayout {
-  static size_t carve(char* base, int64_t P, int n_cams, gsb_raster_ctx* c, CamParams** cams, int** err,
-                      void** scan_scratch) {
+  static size_t carve(char* base, int64_t P, int n_cams, gsb_raster_ctx* c, GeomExtras* x) {
     Carver k(base);
     const size_t n = (size_t)P * n_cams;
     float* depths = k.take<float>(n);
@@ -72,17 +80,20 @@ struct GeomLayout {
     float* cov3D = k.take<float>(6 * n);
     float* conic = k.take<float>(4 * n);
     uint32_t* tt = k.take<uint32_t>(n);
+    uint64_t* gk = k.take<uint64_t>(n);
+    uint32_t* go = k.take<uint32_t>(n);
     uint32_t* po = k.take<uint32_t>(n);
     CamParams* cp = k.take<CamParams>(n_cams);
     int* e = k.take<int>(4);
     void* ss = k.take<char>(scan_scratch_bytes((int64_t)n));
+    uint64_t* gki = k.take<uint64_t>(n);
+    uint32_t* gvi = k.take<uint32_t>(n);
+    void* gt = k.take<char>(sort_temp_bytes((int64_t)n));
     if (c) {
       c->depths = depths; c->radii = radii; c->means2D = means2D; c->cov3D = cov3D; c->conic_opacity = conic;
-      c->tiles_touched = tt; c->point_offsets = po;
+      c->tiles_touched = tt; c->gauss_keys = gk; c->gauss_order = go; c->point_offsets = po;
     }
-    if (cams) *cams = cp;
-    if (err) *err = e;
-    if (scan_scratch) *scan_scratch = ss;
+    if (x) { x->cams = cp; x->err = e; x->scan_scratch = ss; x->gkeys_in = gki; x->gvals_in = gvi; x->gsort_temp = gt; }
     return align_up(k.off, 256);
   }
 };
@@ -102,11 +113,11 @@ static size_t carve_binning(char* base, int64_t R, gsb_raster_ctx* c) {
   const size_t n = (size_t)(R > 0 ? R : 1);
   uint32_t* pl = k.take<uint32_t>(n);
   uint32_t* plu = k.take<uint32_t>(n);
-  uint64_t* keys = k.take<uint64_t>(n);
-  uint64_t* keysu = k.take<uint64_t>(n);
+  uint32_t* tl = k.take<uint32_t>(n);
+  uint32_t* tlu = k.take<uint32_t>(n);
   void* tmp = k.take<char>(sort_temp_bytes(R));
   if (c) {
-    c->point_list = pl; c->point_list_unsorted = plu; c->point_list_keys = keys; c->point_list_keys_unsorted = keysu;
+    c->point_list = pl; c->point_list_unsorted = plu; c->point_list_tiles = tl; c->point_list_tiles_unsorted = tlu;
     c->sort_temp = tmp;
   }
   return align_up(k.off, 256);
@@ -132,7 +143,7 @@ const char* gsb_version(void) { return "gsb200 0.1 (sm_100a)"; }
 const char* gsb_last_error(void) { return g_err; }
 
 size_t gsb_geom_bytes(int32_t P, int32_t n_cams) {
-  return GeomLayout::carve(nullptr, P, n_cams, nullptr, nullptr, nullptr, nullptr);
+  return GeomLayout::carve(nullptr, P, n_cams, nullptr, nullptr);
 }
 size_t gsb_image_bytes(int32_t width, int32_t height, int32_t n_cams) {
   const int tiles = ((width + GSB_TILE - 1) / GSB_TILE) * ((height + GSB_TILE - 1) / GSB_TILE) * n_cams;
@@ -156,7 +167,8 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   ctx->tiles_x = (a->width + GSB_TILE - 1) / GSB_TILE;
   ctx->tiles_y = (a->height + GSB_TILE - 1) / GSB_TILE;
   const int tiles_total = ctx->tiles_x * ctx->tiles_y * a->n_cams;
-  ctx->sort_bits = 32 + (int)higher_msb((uint32_t)tiles_total);
+  ctx->tile_bits = (int)higher_msb((uint32_t)tiles_total);
+  ctx->sort_bits = 32 + ctx->tile_bits;
   if (a->P == 0) return GSB_OK;  // the glue returns zero images, like DGR/rasterize_points.cu:81
   if (!a->means3D || !a->colors || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->background ||
       !out_color || !out_depth)
@@ -167,8 +179,9 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   char* geom = geom_alloc(user, gsb_geom_bytes(a->P, a->n_cams));
   char* img = image_alloc(user, gsb_image_bytes(a->width, a->height, a->n_cams));
   if (!geom || !img) return GSB_ENOMEM;
-  CamParams* cams_dev; int* err_dev; void* scan_scratch;
-  GeomLayout::carve(geom, a->P, a->n_cams, ctx, &cams_dev, &err_dev, &scan_scratch);
+  GeomExtras gx;
+  GeomLayout::carve(geom, a->P, a->n_cams, ctx, &gx);
+  CamParams* cams_dev = gx.cams; int* err_dev = gx.err; void* scan_scratch = gx.scan_scratch;
   carve_image(img, a->width, a->height, a->n_cams, tiles_total, ctx);
 
   // per-camera scalars: focal = dim / (2 tanfov) (cr/rasterizer_impl.cu:222-223)
@@ -186,10 +199,18 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
 
   prof_mark(PF_FWD_BEGIN, st);
-  if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, err_dev, st))) return rc;
+  if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, gx.gkeys_in, gx.gvals_in, err_dev, st))) return rc;
   prof_mark(PF_PREPROCESS, st);
   const int64_t n_slots = (int64_t)a->P * a->n_cams;
-  if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st))) return rc;
+  // the depth digits (and the camera id) are sorted here, on Gaussians, before duplication
+  const int depth_bits = 32 + (a->n_cams > 1 ? (int)higher_msb((uint32_t)a->n_cams) : 0);
+  if ((rc = launch_sort_pairs(n_slots, gx.gkeys_in, ctx->gauss_keys, gx.gvals_in, ctx->gauss_order, depth_bits,
+                              gx.gsort_temp, st)))
+    return rc;
+  prof_mark(PF_DEPTH_SORT, st);
+  if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st,
+                                      ctx->gauss_order, a->P)))
+    return rc;
   prof_mark(PF_SCAN, st);
 
   // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
@@ -207,8 +228,8 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   prof_mark(PF_D2H, st);
   if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
   prof_mark(PF_DUPKEYS, st);
-  if ((rc = launch_sort_pairs(ctx->num_rendered, ctx->point_list_keys_unsorted, ctx->point_list_keys,
-                              ctx->point_list_unsorted, ctx->point_list, ctx->sort_bits, ctx->sort_temp, st)))
+  if ((rc = launch_sort_pairs_u32(ctx->num_rendered, ctx->point_list_tiles_unsorted, ctx->point_list_tiles,
+                                  ctx->point_list_unsorted, ctx->point_list, ctx->tile_bits, ctx->sort_temp, st)))
     return rc;
   prof_mark(PF_SORT, st);
   if ((rc = launch_tile_ranges(*ctx, st))) return rc;
@@ -241,8 +262,9 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
     if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, st))) return rc;
   prof_mark(PF_RENDER_BWD, st);
   // the per-camera scalar table still sits in the geometry buffer next to the state arrays
-  CamParams* cams_dev;
-  GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &cams_dev, nullptr, nullptr);
+  GeomExtras gx;
+  GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
+  CamParams* cams_dev = gx.cams;
   if ((rc = launch_preprocess_bwd(*a, cams_dev, *ctx, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcov3D, dL_dscale,
                                   dL_drot, st)))
     return rc;
@@ -289,6 +311,12 @@ int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const
   if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !temp))) return GSB_EINVAL;
   return launch_sort_pairs(n, keys_in, keys_out, vals_in, vals_out, end_bit, temp,
                            reinterpret_cast<cudaStream_t>(stream));
+}
+int gsb_sort_pairs_u32(int64_t n, const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
+                       uint32_t* vals_out, int32_t end_bit, void* temp, void* stream) {
+  if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !temp))) return GSB_EINVAL;
+  return launch_sort_pairs_u32(n, keys_in, keys_out, vals_in, vals_out, end_bit, temp,
+                               reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -43,7 +43,8 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
 
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
-                unsigned int* __restrict__ ticket, unsigned long long* __restrict__ status) {
+                unsigned int* __restrict__ ticket, unsigned long long* __restrict__ status,
+                const uint32_t* __restrict__ perm, int perm_block) {
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_tile, s_prefix;
   if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
@@ -52,7 +53,14 @@ scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
   const long long base = (long long)tile * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0)) {
+  if (perm) {
+    // element i is in[(i / perm_block) * perm_block + perm[i]]: the scan runs in a permuted order
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+      const long long i = base + k;
+      v[k] = (i < n) ? in[(i / perm_block) * perm_block + perm[i]] : 0u;
+    }
+  } else if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0)) {
     const uint4 a = *reinterpret_cast<const uint4*>(in + base);
     const uint4 b = *reinterpret_cast<const uint4*>(in + base + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -114,13 +122,14 @@ scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
   }
 }
 
-int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st) {
+int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st,
+                              const uint32_t* perm, int perm_block) {
   if (n <= 0) return GSB_OK;
   const int64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, scan_scratch_bytes(n), st));
   unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
   unsigned long long* status = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(scratch) + 16);
-  scan_u32_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(n, in, out, ticket, status);
+  scan_u32_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(n, in, out, ticket, status, perm, perm_block);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -145,29 +154,29 @@ __device__ __forceinline__ void tile_rect_dup(float px, float py, int rad, int g
 }
 
 __global__ void __launch_bounds__(256)
-duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const float2* __restrict__ means2D,
-                           const float* __restrict__ depths, const int32_t* __restrict__ radii,
-                           const uint32_t* __restrict__ offsets, unsigned long long* __restrict__ keys,
+duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_t* __restrict__ gauss_order,
+                           const float2* __restrict__ means2D, const int32_t* __restrict__ radii,
+                           const uint32_t* __restrict__ offsets, uint32_t* __restrict__ tile_keys,
                            uint32_t* __restrict__ vals) {
   const long long slot = (long long)blockIdx.x * 256 + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
-  uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, depth_bits = 0, tile_base = 0, gidx = 0;
+  uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, tile_base = 0, gidx = 0;
   const long long warp_first = slot - lane;
   if (warp_first >= total) return;
   if (slot < total) {
     end = offsets[slot];
-    const int rad = radii[slot];
     const uint32_t cam = (uint32_t)(slot / P);
-    gidx = (uint32_t)(slot - (long long)cam * P);
+    gidx = gauss_order[slot];
+    const size_t o = (size_t)cam * P + gidx;
+    const int rad = radii[o];
     tile_base = cam * (uint32_t)(gx * gy);
     start = end;
     if (rad > 0) {
-      const float2 xy = means2D[slot];
+      const float2 xy = means2D[o];
       uint32_t x1, y1;
       tile_rect_dup(xy.x, xy.y, rad, gx, gy, x0, y0, x1, y1);
       w = x1 - x0;
       start = end - w * (y1 - y0);
-      depth_bits = __float_as_uint(depths[slot]);
       if (w == 0) w = 1;
     }
   }
@@ -175,7 +184,6 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const float2*
   uint32_t last_end = __shfl_sync(0xffffffffu, end, (unsigned)min(31ll, total - 1 - warp_first));
   if (slot >= total) { end = last_end; start = last_end; }
   const uint32_t warp_start = __shfl_sync(0xffffffffu, start, 0);
-  // lane 0's start may be stale if it is culled (start == end == previous end): that is exactly the first instance
   const uint32_t warp_end = last_end;
   for (uint32_t b = warp_start; b < warp_end; b += 32) {
     const uint32_t i = b + lane;
@@ -191,14 +199,12 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const float2*
     const uint32_t ox = __shfl_sync(0xffffffffu, x0, j);
     const uint32_t oy = __shfl_sync(0xffffffffu, y0, j);
     const uint32_t ow = __shfl_sync(0xffffffffu, w, j);
-    const uint32_t od = __shfl_sync(0xffffffffu, depth_bits, j);
     const uint32_t ot = __shfl_sync(0xffffffffu, tile_base, j);
     const uint32_t og = __shfl_sync(0xffffffffu, gidx, j);
     if (i < warp_end) {
       const uint32_t k = i - s;
       const uint32_t ry = k / ow, rx = k - ry * ow;
-      const uint32_t tile = ot + (oy + ry) * (uint32_t)gx + (ox + rx);
-      keys[i] = ((unsigned long long)tile << 32) | od;
+      tile_keys[i] = ot + (oy + ry) * (uint32_t)gx + (ox + rx);
       vals[i] = og;
     }
   }
@@ -208,8 +214,8 @@ int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st) {
   const long long total = (long long)c.n_cams * c.P;
   if (total <= 0 || c.num_rendered <= 0) return GSB_OK;
   duplicate_with_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
-      total, c.P, c.tiles_x, c.tiles_y, reinterpret_cast<const float2*>(c.means2D), c.depths, c.radii,
-      c.point_offsets, reinterpret_cast<unsigned long long*>(c.point_list_keys_unsorted), c.point_list_unsorted);
+      total, c.P, c.tiles_x, c.tiles_y, c.gauss_order, reinterpret_cast<const float2*>(c.means2D), c.radii,
+      c.point_offsets, c.point_list_tiles_unsorted, c.point_list_unsorted);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -236,18 +242,20 @@ constexpr size_t RS_HEADER = (size_t)RS_MAX_PASSES * RS_RADIX * 4 + 256;
 size_t sort_temp_bytes(int64_t n) {
   const int64_t tiles = (n + RS_TILE - 1) / RS_TILE;
   const size_t t = (size_t)(tiles > 0 ? tiles : 1);
-  return RS_HEADER + align_up((size_t)RS_MAX_PASSES * t * RS_RADIX * 4, 256) + align_up((size_t)(n > 0 ? n : 1) * 12, 256);
+  const size_t nn = (size_t)(n > 0 ? n : 1);  // sized for 64-bit keys; 32-bit keys use less
+  return RS_HEADER + align_up((size_t)RS_MAX_PASSES * t * RS_RADIX * 4, 256) + align_up(nn * 8, 256) + align_up(nn * 4, 256);
 }
 
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-rs_histogram_kernel(long long n, const unsigned long long* __restrict__ keys, int end_bit, int passes,
+rs_histogram_kernel(long long n, const KeyT* __restrict__ keys, int end_bit, int passes,
                     uint32_t* __restrict__ ghist) {
   __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
   for (int i = threadIdx.x; i < passes * RS_RADIX; i += 256) s_hist[i] = 0;
   __syncthreads();
   const long long stride = (long long)gridDim.x * 256;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
-    const unsigned long long k = keys[i];
+    const KeyT k = keys[i];
     for (int p = 0; p < passes; p++) {
       const int shift = p * RS_BITS;
       const int nb = min(RS_BITS, end_bit - shift);
@@ -262,8 +270,9 @@ rs_histogram_kernel(long long n, const unsigned long long* __restrict__ keys, in
   }
 }
 
+template <typename KeyT>
 struct RsSmem {
-  unsigned long long keys[RS_TILE];
+  KeyT keys[RS_TILE];
   uint32_t vals[RS_TILE];
   uint32_t warp_cnt[RS_WARPS][RS_RADIX];
   uint32_t digit_start[RS_RADIX];   // exclusive prefix of this tile's digit counts
@@ -272,13 +281,14 @@ struct RsSmem {
   uint32_t tile;
 };
 
+template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS, 3)
-rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsigned long long* __restrict__ kout,
+rs_onesweep_kernel(long long n, const KeyT* __restrict__ kin, KeyT* __restrict__ kout,
                    const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout, int shift, int nbits,
                    const uint32_t* __restrict__ ghist, uint32_t* __restrict__ ticket,
                    uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) unsigned char rs_smem_raw[];
-  RsSmem& S = *reinterpret_cast<RsSmem*>(rs_smem_raw);
+  RsSmem<KeyT>& S = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
@@ -290,7 +300,7 @@ rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsi
   const uint32_t dmask = (1u << nbits) - 1u;
 
   // load (warp-striped: item i of lane l is element warp*512 + i*32 + l of the tile)
-  unsigned long long key[RS_ITEMS];
+  KeyT key[RS_ITEMS];
   uint32_t val[RS_ITEMS];
   uint32_t rank[RS_ITEMS];
   const int wbase = warp * (32 * RS_ITEMS);
@@ -301,7 +311,7 @@ rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsi
       key[i] = kin[tile_base + e];
       val[i] = vin[tile_base + e];
     } else {
-      key[i] = ~0ull;
+      key[i] = (KeyT)~(KeyT)0;
       val[i] = 0;
     }
   }
@@ -391,7 +401,7 @@ rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsi
   for (int i = 0; i < RS_ITEMS; i++) {
     const int p = i * RS_THREADS + tid;
     if (p < n_valid) {
-      const unsigned long long k = S.keys[p];
+      const KeyT k = S.keys[p];
       const uint32_t d = (uint32_t)(k >> shift) & dmask;
       const uint32_t dst = S.digit_gbase[d] + (uint32_t)p;
       kout[dst] = k;
@@ -400,17 +410,18 @@ rs_onesweep_kernel(long long n, const unsigned long long* __restrict__ kin, unsi
   }
 }
 
-int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
-                      int end_bit, void* temp, cudaStream_t st) {
+template <typename KeyT>
+static int sort_pairs_impl(int64_t n, const KeyT* kin, KeyT* kout, const uint32_t* vin, uint32_t* vout,
+                           int end_bit, void* temp, cudaStream_t st) {
   if (n <= 0) return GSB_OK;
-  if (n >= (1ll << 30) || end_bit <= 0 || end_bit > 64) return GSB_EINVAL;
+  if (n >= (1ll << 30) || end_bit <= 0 || end_bit > (int)sizeof(KeyT) * 8) return GSB_EINVAL;
   const int passes = (end_bit + RS_BITS - 1) / RS_BITS;
   const int64_t tiles = (n + RS_TILE - 1) / RS_TILE;
   static bool attr_set = false;
   if (!attr_set) {
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)sizeof(RsSmem)));
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(RsSmem<KeyT>)));
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(rs_onesweep_kernel<KeyT>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
@@ -419,23 +430,22 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
   uint32_t* tickets = ghist + RS_MAX_PASSES * RS_RADIX;
   uint32_t* status = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(temp) + RS_HEADER);
   const int hist_blocks = (int)std::min<int64_t>((n + 256 * 16 - 1) / (256 * 16), 148 * 8);
-  rs_histogram_kernel<<<hist_blocks, 256, 0, st>>>(n, reinterpret_cast<const unsigned long long*>(kin), end_bit,
-                                                   passes, ghist);
+  rs_histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(n, kin, end_bit, passes, ghist);
   GSB_LAUNCH_CHECK();
   // ping-pong between the outputs and an alternate pair inside `temp`, arranged so that the last pass
   // lands in (kout, vout) and the caller's input is never written (like CUB's non-DoubleBuffer API).
   const size_t status_bytes = align_up((size_t)RS_MAX_PASSES * tiles * RS_RADIX * 4, 256);
-  unsigned long long* alt_k = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(temp) + RS_HEADER + status_bytes);
-  uint32_t* alt_v = reinterpret_cast<uint32_t*>(alt_k + n);
-  const unsigned long long* a = reinterpret_cast<const unsigned long long*>(kin);
+  KeyT* alt_k = reinterpret_cast<KeyT*>(reinterpret_cast<char*>(temp) + RS_HEADER + status_bytes);
+  uint32_t* alt_v = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(alt_k) + align_up((size_t)n * sizeof(KeyT), 256));
+  const KeyT* a = kin;
   const uint32_t* va = vin;
   for (int p = 0; p < passes; p++) {
     const int shift = p * RS_BITS;
     const int nb = (end_bit - shift < RS_BITS) ? end_bit - shift : RS_BITS;
     const bool to_out = ((passes - 1 - p) % 2 == 0);
-    unsigned long long* b = to_out ? reinterpret_cast<unsigned long long*>(kout) : alt_k;
+    KeyT* b = to_out ? kout : alt_k;
     uint32_t* vb = to_out ? vout : alt_v;
-    rs_onesweep_kernel<<<(unsigned)tiles, RS_THREADS, sizeof(RsSmem), st>>>(
+    rs_onesweep_kernel<KeyT><<<(unsigned)tiles, RS_THREADS, sizeof(RsSmem<KeyT>), st>>>(
         n, a, b, va, vb, shift, nb, ghist + p * RS_RADIX, tickets + p, status + (size_t)p * tiles * RS_RADIX);
     GSB_LAUNCH_CHECK();
     a = b;
@@ -444,18 +454,28 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
   return GSB_OK;
 }
 
+int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
+                      int end_bit, void* temp, cudaStream_t st) {
+  return sort_pairs_impl<unsigned long long>(n, reinterpret_cast<const unsigned long long*>(kin),
+                                             reinterpret_cast<unsigned long long*>(kout), vin, vout, end_bit, temp, st);
+}
+int launch_sort_pairs_u32(int64_t n, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
+                          int end_bit, void* temp, cudaStream_t st) {
+  return sort_pairs_impl<uint32_t>(n, kin, kout, vin, vout, end_bit, temp, st);
+}
+
 // ------------------------------------------------------------------------------------------------
 // identifyTileRanges (cr/rasterizer_impl.cu:116-138); ranges pre-zeroed by the caller (:311).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(long long R, const unsigned long long* __restrict__ keys, uint2* __restrict__ ranges) {
+tile_ranges_kernel(long long R, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= R) return;
-  const uint32_t cur = (uint32_t)(keys[i] >> 32);
+  const uint32_t cur = keys[i];
   if (i == 0) {
     ranges[cur].x = 0;
   } else {
-    const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+    const uint32_t prev = keys[i - 1];
     if (cur != prev) {
       ranges[prev].y = (uint32_t)i;
       ranges[cur].x = (uint32_t)i;
@@ -469,8 +489,7 @@ int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st) {
   GSB_CUDA_CHECK(cudaMemsetAsync(c.ranges, 0, tiles * 8, st));
   if (c.num_rendered <= 0) return GSB_OK;
   tile_ranges_kernel<<<(unsigned)((c.num_rendered + 255) / 256), 256, 0, st>>>(
-      c.num_rendered, reinterpret_cast<const unsigned long long*>(c.point_list_keys),
-      reinterpret_cast<uint2*>(c.ranges));
+      c.num_rendered, c.point_list_tiles, reinterpret_cast<uint2*>(c.ranges));
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -51,18 +51,22 @@ struct CamParams {  // per-camera scalars that live in a small device table
 };
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                      int32_t* radii_out, int* err_flag_dev, cudaStream_t st);
+                      int32_t* radii_out, uint64_t* gauss_keys_in, uint32_t* gauss_vals_in, int* err_flag_dev,
+                      cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st);
 
 size_t scan_scratch_bytes(int64_t n);
-int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st);
+int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st,
+                              const uint32_t* perm = nullptr, int perm_block = 0);
 int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st);
 size_t sort_temp_bytes(int64_t n);
 int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
                       int end_bit, void* temp, cudaStream_t st);
+int launch_sort_pairs_u32(int64_t n, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
+                          int end_bit, void* temp, cudaStream_t st);
 int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st);
 
 int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,

@@ -106,7 +106,8 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
                       const float* __restrict__ projmatrix, const CamParams* __restrict__ cams,
                       float* __restrict__ depths, int32_t* __restrict__ radii_state, int32_t* __restrict__ radii_out,
                       float2* __restrict__ means2D, float* __restrict__ cov3D, float4* __restrict__ conic_opacity,
-                      uint32_t* __restrict__ tiles_touched, int* __restrict__ err_flag) {
+                      uint32_t* __restrict__ tiles_touched, unsigned long long* __restrict__ gauss_keys,
+                      uint32_t* __restrict__ gauss_vals, int* __restrict__ err_flag) {
   __shared__ __align__(16) float s_mean[768];
   __shared__ __align__(16) float s_scale[768];
   __shared__ float s_V[16], s_Pm[16];
@@ -124,6 +125,7 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
   // Culled Gaussians: radii = tiles_touched = 0, nothing else written (cr/forward.cu:179-194).
   int rad_w = 0;
   uint32_t tt_w = 0;
+  uint32_t depth_key = 0xFFFFFFFFu;  // culled Gaussians sort behind every visible one of their camera
   do {
     const float mx = s_mean[3 * threadIdx.x], my = s_mean[3 * threadIdx.x + 1], mz = s_mean[3 * threadIdx.x + 2];
     const float* V = s_V;
@@ -216,21 +218,25 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
     conic_opacity[o] = make_float4(con_x, con_y, con_z, __ldg(opacities + idx));
     rad_w = rad;
     tt_w = area;
+    depth_key = __float_as_uint(tz);
   } while (false);
+  gauss_keys[o] = ((unsigned long long)(uint32_t)cam << 32) | depth_key;
+  gauss_vals[o] = (uint32_t)idx;
   radii_state[o] = rad_w;
   if (radii_out) radii_out[o] = rad_w;
   tiles_touched[o] = tt_w;
 }
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                      int32_t* radii_out, int* err_flag_dev, cudaStream_t st) {
+                      int32_t* radii_out, uint64_t* gauss_keys_in, uint32_t* gauss_vals_in, int* err_flag_dev,
+                      cudaStream_t st) {
   if (a.P <= 0) return GSB_OK;
   dim3 grid((a.P + 255) / 256, a.n_cams);
   preprocess_fwd_kernel<<<grid, 256, 0, st>>>(
       a.P, a.width, a.height, c.tiles_x, c.tiles_y, a.scale_modifier, a.prefiltered, a.means3D, a.scales,
       a.rotations, a.opacities, a.cov3D_precomp, a.viewmatrix, a.projmatrix, cams_dev, c.depths, c.radii,
       radii_out, reinterpret_cast<float2*>(c.means2D), c.cov3D, reinterpret_cast<float4*>(c.conic_opacity),
-      c.tiles_touched, err_flag_dev);
+      c.tiles_touched, reinterpret_cast<unsigned long long*>(gauss_keys_in), gauss_vals_in, err_flag_dev);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

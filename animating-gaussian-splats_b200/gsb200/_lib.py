@@ -34,12 +34,13 @@ class RasterCtx(C.Structure):
     _fields_ = [
         ("num_rendered", C.c_int64),
         ("P", C.c_int32), ("n_cams", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
-        ("tiles_x", C.c_int32), ("tiles_y", C.c_int32), ("sort_bits", C.c_int32), ("_pad", C.c_int32),
+        ("tiles_x", C.c_int32), ("tiles_y", C.c_int32), ("sort_bits", C.c_int32), ("tile_bits", C.c_int32),
         ("depths", C.c_void_p), ("radii", C.c_void_p), ("means2D", C.c_void_p), ("cov3D", C.c_void_p),
-        ("conic_opacity", C.c_void_p), ("tiles_touched", C.c_void_p), ("point_offsets", C.c_void_p),
+        ("conic_opacity", C.c_void_p), ("tiles_touched", C.c_void_p), ("gauss_keys", C.c_void_p),
+        ("gauss_order", C.c_void_p), ("point_offsets", C.c_void_p),
         ("final_T", C.c_void_p), ("n_contrib", C.c_void_p), ("ranges", C.c_void_p),
-        ("point_list", C.c_void_p), ("point_list_keys", C.c_void_p), ("point_list_unsorted", C.c_void_p),
-        ("point_list_keys_unsorted", C.c_void_p), ("sort_temp", C.c_void_p),
+        ("point_list", C.c_void_p), ("point_list_tiles", C.c_void_p), ("point_list_unsorted", C.c_void_p),
+        ("point_list_tiles_unsorted", C.c_void_p), ("sort_temp", C.c_void_p),
     ]
 
 
@@ -66,10 +67,12 @@ SYMBOLS = {
     "gsb_sort_temp_bytes": (C.c_size_t, [C.c_int64]),
     "gsb_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                  C.c_void_p]),
+    "gsb_sort_pairs_u32": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                     C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),
     "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }
-PROFILE_STAGES = ["fwd_begin", "preprocess", "scan", "d2h_sync", "duplicate_keys", "sort", "tile_ranges",
+PROFILE_STAGES = ["fwd_begin", "preprocess", "depth_sort", "scan", "d2h_sync", "duplicate_keys", "sort", "tile_ranges",
                   "render_fwd", "bwd_begin", "bwd_zero", "render_bwd", "preprocess_bwd"]
 
 _lib = None

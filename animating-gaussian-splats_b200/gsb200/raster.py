@@ -45,6 +45,8 @@ class RasterState:
             "conic_opacity": self._view(c.conic_opacity, self.geom, torch.float32, (n, P, 4)),
             "tiles_touched": self._view(c.tiles_touched, self.geom, torch.int32, (n, P)),
             "point_offsets": self._view(c.point_offsets, self.geom, torch.int32, (n, P)),
+            "gauss_order": self._view(c.gauss_order, self.geom, torch.int32, (n, P)),
+            "gauss_keys": self._view(c.gauss_keys, self.geom, torch.int64, (n, P)),
             "final_T": self._view(c.final_T, self.img, torch.float32, (n, c.height, c.width)),
             "n_contrib": self._view(c.n_contrib, self.img, torch.int32, (n, c.height, c.width)),
             "ranges": self._view(c.ranges, self.img, torch.int32, (tiles, 2)),
@@ -52,10 +54,14 @@ class RasterState:
         if R > 0:
             out.update({
                 "point_list": self._view(c.point_list, self.binning, torch.int32, (R,)),
-                "point_list_keys": self._view(c.point_list_keys, self.binning, torch.int64, (R,)),
-                "point_list_unsorted": self._view(c.point_list_unsorted, self.binning, torch.int32, (R,)),
-                "point_list_keys_unsorted": self._view(c.point_list_keys_unsorted, self.binning, torch.int64, (R,)),
+                "point_list_tiles": self._view(c.point_list_tiles, self.binning, torch.int32, (R,)),
             })
+            # the reference's sorted 64-bit keys, reassembled: (tile << 32) | bits(depth of the Gaussian)
+            pl = out["point_list"].long()
+            tiles_per_cam = c.tiles_x * c.tiles_y
+            cam = out["point_list_tiles"].long() // tiles_per_cam
+            dbits = out["depths"].view(torch.int32).view(-1)[cam * P + pl].long() & 0xFFFFFFFF
+            out["point_list_keys"] = (out["point_list_tiles"].long() << 32) | dbits
         return out
 
 

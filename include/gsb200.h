@@ -58,17 +58,31 @@ typedef struct gsb_raster_args {
 
 /* Saved state of one forward call: replaces the (geomBuffer, binningBuffer, imgBuffer, num_rendered)
  * tuple the reference hands back to Python (DGR/rasterize_points.cu:114) and re-decodes with
- * fromChunk (cr/rasterizer_impl.cu:155-194, 373-375).  POD; pointers point into the three buffers. */
+ * fromChunk (cr/rasterizer_impl.cu:155-194, 373-375).  POD; pointers point into the three buffers.
+ *
+ * Binning layout.  The reference sorts R instances on 64-bit (tile << 32 | depth) keys, 6 radix passes
+ * over 12 B records.  The low 32 key bits are the same for all instances of a Gaussian, so the LSD
+ * passes over them are done BEFORE duplication, on the n_cams*P Gaussians (camera << 32 | depth keys),
+ * instances are emitted in that order, and only the tile-id bits are sorted at instance granularity
+ * (32-bit keys, 2 passes over 8 B records).  A stable LSD sort is digit-separable, so point_list and
+ * ranges are bit-identical to the reference's. */
 typedef struct gsb_raster_ctx {
   int64_t num_rendered;      /* R: total (Gaussian, tile) instances over all cameras */
-  int32_t P, n_cams, width, height, tiles_x, tiles_y, sort_bits, _pad;
+  int32_t P, n_cams, width, height, tiles_x, tiles_y;
+  int32_t sort_bits;         /* 32 + getHigherMsb(tiles): what the reference passes to SortPairs */
+  int32_t tile_bits;         /* bits sorted at instance granularity */
   /* geometry state, [n_cams][P] each (cr/rasterizer_impl.h:31-45) */
   float* depths; int32_t* radii; float* means2D; float* cov3D; float* conic_opacity;
-  uint32_t* tiles_touched; uint32_t* point_offsets;
+  uint32_t* tiles_touched;
+  uint64_t* gauss_keys;      /* sorted (camera << 32 | bits(depth)); culled Gaussians carry depth bits 0xFFFFFFFF */
+  uint32_t* gauss_order;     /* Gaussian index per sorted slot: camera-major, depth-ascending, stable */
+  uint32_t* point_offsets;   /* inclusive scan of tiles_touched taken in gauss_order */
   /* image state (cr/rasterizer_impl.h:47-54) */
   float* final_T; uint32_t* n_contrib; uint32_t* ranges; /* ranges: [n_cams*tiles][2] */
   /* binning state (cr/rasterizer_impl.h:56-66) */
-  uint32_t* point_list; uint64_t* point_list_keys; uint32_t* point_list_unsorted; uint64_t* point_list_keys_unsorted;
+  uint32_t* point_list;               /* sorted Gaussian indices == the reference's point_list */
+  uint32_t* point_list_tiles;         /* sorted tile ids == high words of the reference's point_list_keys */
+  uint32_t* point_list_unsorted; uint32_t* point_list_tiles_unsorted;
   void* sort_temp;
 } gsb_raster_ctx;
 
@@ -136,11 +150,13 @@ int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* s
 size_t gsb_sort_temp_bytes(int64_t n);
 int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
                    uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
+int gsb_sort_pairs_u32(int64_t n, const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
+                       uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
 
 /* Per-stage CUDA-event timing of the last forward/backward on this thread's library instance (bench
- * instrumentation; off by default).  Stage order: fwd_begin, preprocess, scan, d2h_sync, duplicate_keys,
+ * instrumentation; off by default).  Stage order: fwd_begin, preprocess, depth_sort, scan, d2h_sync, duplicate_keys,
  * sort, tile_ranges, render_fwd, bwd_begin, bwd_zero, render_bwd, preprocess_bwd (GSB_PROFILE_STAGES). */
-#define GSB_PROFILE_STAGES 12
+#define GSB_PROFILE_STAGES 13
 int gsb_profile_enable(int on);
 int gsb_profile_read(float* ms_out_host, int32_t n);
 

@@ -49,13 +49,16 @@ def test_forward_vs_reference_ext(refdgr, name, P, W, H, seed, bgv, so):
     assert torch.equal(radii, fw["radii"])
     vis = fw["radii"] > 0
     assert torch.equal(mine["tiles_touched"][0], ref["tiles_touched"])
-    assert torch.equal(mine["point_offsets"][0], torch.cumsum(ref["tiles_touched"], 0).int())
+    # our scan runs in depth order (gauss_order): a stable sort of the visible Gaussians by depth bits
+    order = mine["gauss_order"][0].long()
+    assert torch.equal(torch.sort(order).values, torch.arange(P, device=dev))
+    assert torch.equal(mine["point_offsets"][0], torch.cumsum(ref["tiles_touched"][order], 0).int())
+    dkey = torch.where(vis, ref["depths"].view(torch.int32).long() & 0xFFFFFFFF, torch.full_like(vis, 0xFFFFFFFF, dtype=torch.long))
+    assert torch.equal(order, torch.sort(dkey, stable=True).indices)
     for k in ("depths", "means2D", "conic_opacity", "cov3D"):
         m, r = mine[k][0][vis], ref[k][vis]
         assert torch.equal(m.view(torch.int32), r.view(torch.int32)), k
     if R > 0:
-        assert torch.equal(mine["point_list_keys_unsorted"], ref["point_list_keys_unsorted"])
-        assert torch.equal(mine["point_list_unsorted"], ref["point_list_unsorted"])
         assert torch.equal(mine["point_list_keys"], ref["point_list_keys"])
         assert torch.equal(mine["point_list"], ref["point_list"])
     assert torch.equal(mine["ranges"], ref["ranges"])
@@ -122,7 +125,8 @@ def test_forward_backward_vs_c_oracle(oracle, name, P, W, H, seed, bgv, so):
     assert np.array_equal(helpers.to_np(radii), o["radii"])
     vis = o["radii"] > 0
     assert np.array_equal(helpers.to_np(mine["tiles_touched"][0]).view(np.uint32), o["tiles_touched"])
-    assert np.array_equal(helpers.to_np(mine["point_offsets"][0]).view(np.uint32), o["point_offsets"])
+    order = helpers.to_np(mine["gauss_order"][0])
+    assert np.array_equal(helpers.to_np(mine["point_offsets"][0]).view(np.uint32), np.cumsum(o["tiles_touched"][order], dtype=np.uint32))
     for k in ("depths", "means2D", "conic_opacity", "cov3D"):
         assert np.array_equal(helpers.to_np(mine[k][0])[vis].view(np.uint32), o[k][vis].view(np.uint32)), k
     if o["num_rendered"]:
