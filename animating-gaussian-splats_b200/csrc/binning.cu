@@ -469,26 +469,39 @@ int launch_sort_pairs_u32(int64_t n, const uint32_t* kin, uint32_t* kout, const 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(long long R, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
-  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (i >= R) return;
-  const uint32_t cur = keys[i];
-  if (i == 0) {
-    ranges[cur].x = 0;
+  // 4 consecutive sorted instances per thread (one 16-byte load + the predecessor)
+  const long long i0 = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i0 >= R) return;
+  uint32_t k[4];
+  if (i0 + 4 <= R) {
+    const uint4 v = *reinterpret_cast<const uint4*>(keys + i0);
+    k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
   } else {
-    const uint32_t prev = keys[i - 1];
-    if (cur != prev) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) k[j] = (i0 + j < R) ? keys[i0 + j] : 0u;
+  }
+  uint32_t prev = (i0 > 0) ? keys[i0 - 1] : 0u;
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const long long i = i0 + j;
+    if (i >= R) break;
+    const uint32_t cur = k[j];
+    if (i == 0) {
+      ranges[cur].x = 0;
+    } else if (cur != prev) {
       ranges[prev].y = (uint32_t)i;
       ranges[cur].x = (uint32_t)i;
     }
+    if (i == R - 1) ranges[cur].y = (uint32_t)R;
+    prev = cur;
   }
-  if (i == R - 1) ranges[cur].y = (uint32_t)R;
 }
 
 int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st) {
   const size_t tiles = (size_t)c.n_cams * c.tiles_x * c.tiles_y;
   GSB_CUDA_CHECK(cudaMemsetAsync(c.ranges, 0, tiles * 8, st));
   if (c.num_rendered <= 0) return GSB_OK;
-  tile_ranges_kernel<<<(unsigned)((c.num_rendered + 255) / 256), 256, 0, st>>>(
+  tile_ranges_kernel<<<(unsigned)((c.num_rendered + 1023) / 1024), 256, 0, st>>>(
       c.num_rendered, c.point_list_tiles, reinterpret_cast<uint2*>(c.ranges));
   GSB_LAUNCH_CHECK();
   return GSB_OK;

@@ -97,8 +97,10 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
   const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
   const unsigned tid = threadIdx.y * GSB_BLOCK_X + threadIdx.x;
-  const uint32_t px = blockIdx.x * GSB_BLOCK_X + threadIdx.x;
-  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
+  // a warp owns an 8x4 pixel patch (not the reference's 16x2 strip): a splat's footprint then meets fewer
+  // warps, and the warps it meets have more live lanes.  Per-pixel results do not depend on the mapping.
+  const uint32_t px = blockIdx.x * GSB_BLOCK_X + ((tid >> 5) & 1u) * 8u + (tid & 7u);
+  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + (tid >> 6) * 4u + ((tid >> 3) & 3u);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pfx = (float)px, pfy = (float)py;
   const float tx0 = (float)(blockIdx.x * GSB_BLOCK_X), ty0 = (float)(blockIdx.y * GSB_BLOCK_Y);
@@ -237,8 +239,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
   const unsigned tid = threadIdx.y * GSB_BLOCK_X + threadIdx.x;
   const unsigned lane = tid & 31u;
-  const uint32_t px = blockIdx.x * GSB_BLOCK_X + threadIdx.x;
-  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + threadIdx.y;
+  const uint32_t px = blockIdx.x * GSB_BLOCK_X + ((tid >> 5) & 1u) * 8u + (tid & 7u);   // 8x4 patch per warp
+  const uint32_t py = blockIdx.y * GSB_BLOCK_Y + (tid >> 6) * 4u + ((tid >> 3) & 3u);
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pfx = (float)px, pfy = (float)py;
   const float tx0 = (float)(blockIdx.x * GSB_BLOCK_X), ty0 = (float)(blockIdx.y * GSB_BLOCK_Y);
@@ -321,7 +323,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       for (int k = 0; k < 8; k++) v[k] = 0.f;
       const float4 ci = s_ci[j];
       if (valid) {
-        T = T / (1.f - alpha);
+        // 1 / (1 - alpha): MUFU.RCP + one Newton step (the reference divides twice, cr/backward.cu:503,534)
+        const float om = 1.f - alpha;
+        float rcp;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(om));
+        rcp = fmaf(rcp, fmaf(-om, rcp, 1.f), rcp);
+        T = T * rcp;
         const float dchannel_dcolor = alpha * T;
         float dL_dalpha = 0.0f;
         ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = ci.x;
@@ -335,7 +342,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         v[2] = dchannel_dcolor * dpx2;
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+        dL_dalpha += (-T_final * rcp) * bg_dot;
         const float dL_dG = co2.w * dL_dalpha;
         const float gdx = G * dx, gdy = G * dy;
         const float dG_ddelx = -gdx * co2.x - gdy * co2.y;
