@@ -55,6 +55,50 @@ gather_rows_kernel(long long total, int row_floats, const uint8_t* __restrict__ 
   dst[(long long)dst_index[row] * row_floats + k] = src[e];
 }
 
+// accumulate_mean_2d_gradients (external.py:113-124) with the visibility mask as the reference passes it
+__global__ void __launch_bounds__(256)
+densify_accumulate_masked_kernel(int P, const uint8_t* __restrict__ visible, const float* __restrict__ grad_means2D,
+                                 float* __restrict__ grad_accum, float* __restrict__ vis_count) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P || !visible[i]) return;
+  const float gx = grad_means2D[3 * (size_t)i], gy = grad_means2D[3 * (size_t)i + 1];
+  grad_accum[i] += sqrtf(gx * gx + gy * gy);
+  vis_count[i] += 1.0f;
+}
+
+// Split (external.py:251-271): selected row i with rank r produces rows r and S + r ([sel; sel], repeat(2,1)):
+//   mean' = mean + R(normalize(q)) * sample,   log_scale' = log(exp(log_scale) / 1.6)
+__global__ void __launch_bounds__(256)
+split_rows_kernel(int P, int S, const uint8_t* __restrict__ sel, const int32_t* __restrict__ rank,
+                  const float* __restrict__ means, const float* __restrict__ quats,
+                  const float* __restrict__ log_scales, const float* __restrict__ samples,
+                  float* __restrict__ out_means, float* __restrict__ out_log_scales) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P || !sel[i]) return;
+  const int r = rank[i];
+  float4 q = reinterpret_cast<const float4*>(quats)[i];
+  const float norm = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);  // build_rotation, external.py:27-46
+  q.x /= norm; q.y /= norm; q.z /= norm; q.w /= norm;
+  const float rr = q.x, x = q.y, y = q.z, z = q.w;
+  const float R00 = 1.f - 2.f * (y * y + z * z), R01 = 2.f * (x * y - rr * z), R02 = 2.f * (x * z + rr * y);
+  const float R10 = 2.f * (x * y + rr * z), R11 = 1.f - 2.f * (x * x + z * z), R12 = 2.f * (y * z - rr * x);
+  const float R20 = 2.f * (x * z - rr * y), R21 = 2.f * (y * z + rr * x), R22 = 1.f - 2.f * (x * x + y * y);
+  const float mx = means[3 * (size_t)i], my = means[3 * (size_t)i + 1], mz = means[3 * (size_t)i + 2];
+  float ls[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) ls[k] = logf(expf(log_scales[3 * (size_t)i + k]) * (1.0f / 1.6f));
+#pragma unroll
+  for (int rep = 0; rep < 2; rep++) {
+    const size_t j = (size_t)rep * S + r;
+    const float sx = samples[3 * j], sy = samples[3 * j + 1], sz = samples[3 * j + 2];
+    out_means[3 * j] = mx + (R00 * sx + R01 * sy + R02 * sz);
+    out_means[3 * j + 1] = my + (R10 * sx + R11 * sy + R12 * sz);
+    out_means[3 * j + 2] = mz + (R20 * sx + R21 * sy + R22 * sz);
+#pragma unroll
+    for (int k = 0; k < 3; k++) out_log_scales[3 * j + k] = ls[k];
+  }
+}
+
 }  // namespace gsb
 
 using namespace gsb;
@@ -68,6 +112,29 @@ int gsb_densify_accumulate(int32_t P, const int32_t* radii, const float* grad_me
   if (!radii || !grad_means2D || !grad_accum || !vis_count) return GSB_EINVAL;
   densify_accumulate_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       P, radii, grad_means2D, max_2d_radii, grad_accum, vis_count, visible);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_densify_accumulate_masked(int32_t P, const uint8_t* visible, const float* grad_means2D, float* grad_accum,
+                                  float* vis_count, void* stream) {
+  if (P < 0) return GSB_EINVAL;
+  if (P == 0) return GSB_OK;
+  if (!visible || !grad_means2D || !grad_accum || !vis_count) return GSB_EINVAL;
+  densify_accumulate_masked_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, visible, grad_means2D, grad_accum, vis_count);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_split_rows(int32_t P, int32_t S, const uint8_t* sel, const int32_t* rank, const float* means,
+                   const float* quats, const float* log_scales, const float* samples, float* out_means,
+                   float* out_log_scales, void* stream) {
+  if (P < 0 || S < 0) return GSB_EINVAL;
+  if (P == 0 || S == 0) return GSB_OK;
+  if (!sel || !rank || !means || !quats || !log_scales || !samples || !out_means || !out_log_scales) return GSB_EINVAL;
+  split_rows_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, S, sel, rank, means, quats, log_scales, samples, out_means, out_log_scales);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -1,0 +1,52 @@
+"""Camera-sharded data parallelism (the reference has no multi-GPU code).
+
+One process per GPU.  The cameras of a timestep are dealt round-robin (camera c -> rank c % world); every
+rank rasterizes its cameras against the replicated Gaussian set; parameter gradients and the summed
+densification statistics are packed into ONE flat [P, 16] buffer and summed with ONE allreduce (NCCL over
+NVLink on GPUs, gloo in the CPU tests); max_2d_radii takes a MAX allreduce.  The densification
+statistic is the per-camera norm of the means2D gradient, so norms are taken BEFORE the reduction
+(external.py:113-124).  After the reduction every rank holds identical gradients and statistics, so
+the replicated parameters stay bit-identical without a broadcast.
+"""
+import torch
+import torch.distributed as dist
+
+# column layout of the flat buffer
+COLS = {"means3D": (0, 3), "colors": (3, 6), "rotations": (6, 10), "opacities": (10, 11), "scales": (11, 14),
+        "mean_2d_gradients_accumulated": (14, 15), "visibility_count": (15, 16)}
+WIDTH = 16
+
+
+def shard_cameras(n_cams, rank, world):
+    """Indices of the cameras rank `rank` renders."""
+    return list(range(rank, n_cams, world))
+
+
+def pack(flat, grads, stats_delta=None):
+    """Write this rank's camera-summed gradients (and statistic increments) into flat [P, 16]."""
+    for k in ("means3D", "colors", "rotations", "opacities", "scales"):
+        a, b = COLS[k]
+        flat[:, a:b] = grads[k].reshape(flat.shape[0], b - a)
+    if stats_delta is not None:
+        flat[:, 14] = stats_delta["mean_2d_gradients_accumulated"]
+        flat[:, 15] = stats_delta["visibility_count"]
+    else:
+        flat[:, 14:16] = 0
+    return flat
+
+
+def unpack(flat):
+    out = {}
+    for k, (a, b) in COLS.items():
+        v = flat[:, a:b]
+        out[k] = v[:, 0] if k in ("mean_2d_gradients_accumulated", "visibility_count") else v
+    return out
+
+
+def allreduce(flat, max_2d_radii=None, group=None):
+    """The step's exchange: one SUM allreduce of the flat buffer (+ one MAX for max_2d_radii)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        if max_2d_radii is not None:
+            dist.all_reduce(max_2d_radii, op=dist.ReduceOp.MAX, group=group)
+    return flat

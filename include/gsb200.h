@@ -135,6 +135,17 @@ int gsb_ssim_l1(int32_t n, int32_t height, int32_t width, const float* img, cons
 int gsb_densify_accumulate(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_2d_radii,
                            float* grad_accum, float* vis_count, uint8_t* visible, void* stream);
 
+/* accumulate_mean_2d_gradients (external.py:113-124) taking the visibility mask (uint8 [P]) like the reference. */
+int gsb_densify_accumulate_masked(int32_t P, const uint8_t* visible, const float* grad_means2D, float* grad_accum,
+                                  float* vis_count, void* stream);
+
+/* Split step of densify_gaussians (external.py:251-271).  sel uint8 [P], rank = gsb_mask_scan(sel), S selected rows,
+ * samples [2S][3] (the torch.normal draw of external.py:261).  Row rank r yields output rows r and S + r:
+ * out_means = mean + R(normalize(q)) * sample,  out_log_scales = log(exp(log_scale) / 1.6). */
+int gsb_split_rows(int32_t P, int32_t S, const uint8_t* sel, const int32_t* rank, const float* means,
+                   const float* quats, const float* log_scales, const float* samples, float* out_means,
+                   float* out_log_scales, void* stream);
+
 /* Stable stream compaction of row tables: replaces the boolean-mask indexing of
  * remove_points / cat_params_to_optimizer (external.py:127-204).
  *   gsb_mask_scan: keep[P] (uint8) -> dst_index[P] (exclusive rank of kept rows), count_out (device int32[1]).

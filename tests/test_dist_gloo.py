@@ -1,0 +1,69 @@
+"""N > 1 host logic on CPU: world_size-2 gloo ranks shard the cameras, pack per-rank gradients and
+statistic increments into the flat buffer, run the one allreduce and must all end with the single-rank sum."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def fake_camera_grads(cam, P):
+    g = torch.Generator().manual_seed(1000 + cam)
+    r = lambda *s: torch.randn(*s, generator=g)
+    vis = torch.rand(P, generator=g) > 0.3
+    grads = {"means3D": r(P, 3), "colors": r(P, 3), "rotations": r(P, 4), "opacities": r(P, 1), "scales": r(P, 3)}
+    stats = {"mean_2d_gradients_accumulated": r(P).abs() * vis, "visibility_count": vis.float()}
+    radii = (torch.rand(P, generator=g) * 30).floor() * vis
+    return grads, stats, radii
+
+
+def worker(rank, world, port, n_cams, P, out_dir):
+    sys.path.insert(0, os.path.join(ROOT, "animating-gaussian-splats_b200"))
+    from gsb200 import dist as gd
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mine = gd.shard_cameras(n_cams, rank, world)
+    acc = {k: torch.zeros(P, b - a) for k, (a, b) in gd.COLS.items() if b - a > 1 or k == "opacities"}
+    st = {"mean_2d_gradients_accumulated": torch.zeros(P), "visibility_count": torch.zeros(P)}
+    maxr = torch.zeros(P)
+    for c in mine:
+        g, s, r = fake_camera_grads(c, P)
+        for k in g:
+            acc[k] += g[k]
+        for k in s:
+            st[k] += s[k]
+        maxr = torch.maximum(maxr, r)
+    flat = gd.pack(torch.zeros(P, gd.WIDTH), acc, st)
+    gd.allreduce(flat, maxr)
+    out = gd.unpack(flat)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), maxr=maxr.numpy(), cams=np.array(mine),
+             **{k: v.numpy() for k, v in out.items()})
+    dist.destroy_process_group()
+
+
+def test_two_rank_camera_sharding_allreduce(tmp_path):
+    world, n_cams, P = 2, 5, 257
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(worker, args=(world, port, n_cams, P, str(tmp_path)), nprocs=world, join=True)
+    r0, r1 = np.load(tmp_path / "rank0.npz"), np.load(tmp_path / "rank1.npz")
+    assert sorted(list(r0["cams"]) + list(r1["cams"])) == list(range(n_cams))
+    # single-rank sum over all cameras
+    want = None
+    maxr = torch.zeros(P)
+    for c in range(n_cams):
+        g, s, r = fake_camera_grads(c, P)
+        cur = {**{k: v.reshape(P, -1) for k, v in g.items()}, **{k: v.reshape(P, 1) for k, v in s.items()}}
+        want = cur if want is None else {k: want[k] + cur[k] for k in cur}
+        maxr = torch.maximum(maxr, r)
+    for k, v in want.items():
+        for rk in (r0, r1):
+            assert np.allclose(rk[k].reshape(P, -1), v.numpy(), rtol=1e-5, atol=1e-6), k
+    assert np.array_equal(r0["maxr"], maxr.numpy()) and np.array_equal(r1["maxr"], maxr.numpy())
+    # replicas end bit-identical
+    for k in want:
+        assert np.array_equal(r0[k], r1[k])
