@@ -28,6 +28,33 @@ densify_accumulate_kernel(int P, const int32_t* __restrict__ radii, const float*
   vis_count[i] += 1.0f;
 }
 
+// The same over all cameras of a batch in one launch: thread per Gaussian, cameras in order (so the
+// float accumulation order equals n_cams successive single-camera calls).
+__global__ void __launch_bounds__(256)
+densify_accumulate_batch_kernel(int P, int n_cams, const int32_t* __restrict__ radii,
+                                const float* __restrict__ grad_means2D, float* __restrict__ max_2d_radii,
+                                float* __restrict__ grad_accum, float* __restrict__ vis_count,
+                                uint8_t* __restrict__ visible) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  float mr = max_2d_radii ? max_2d_radii[i] : 0.f, acc = grad_accum[i], cnt = vis_count[i];
+  bool vis = false;
+  for (int c = 0; c < n_cams; c++) {
+    const size_t o = (size_t)c * P + i;
+    const int r = radii[o];
+    vis = r > 0;
+    if (!vis) continue;
+    mr = fmaxf((float)r, mr);
+    const float gx = grad_means2D[3 * o], gy = grad_means2D[3 * o + 1];
+    acc += sqrtf(gx * gx + gy * gy);
+    cnt += 1.0f;
+  }
+  if (max_2d_radii) max_2d_radii[i] = mr;
+  grad_accum[i] = acc;
+  vis_count[i] = cnt;
+  if (visible) visible[i] = vis ? 1 : 0;  // mask of the last camera, like repeated single-camera calls
+}
+
 __global__ void __launch_bounds__(256)
 mask_to_u32_kernel(int P, const uint8_t* __restrict__ keep, uint32_t* __restrict__ out) {
   const int i = blockIdx.x * 256 + threadIdx.x;
@@ -112,6 +139,18 @@ int gsb_densify_accumulate(int32_t P, const int32_t* radii, const float* grad_me
   if (!radii || !grad_means2D || !grad_accum || !vis_count) return GSB_EINVAL;
   densify_accumulate_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       P, radii, grad_means2D, max_2d_radii, grad_accum, vis_count, visible);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii, const float* grad_means2D,
+                                 float* max_2d_radii, float* grad_accum, float* vis_count, uint8_t* visible,
+                                 void* stream) {
+  if (P < 0 || n_cams < 0) return GSB_EINVAL;
+  if (P == 0 || n_cams == 0) return GSB_OK;
+  if (!radii || !grad_means2D || !grad_accum || !vis_count) return GSB_EINVAL;
+  densify_accumulate_batch_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, n_cams, radii, grad_means2D, max_2d_radii, grad_accum, vis_count, visible);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -33,6 +33,16 @@ class DensifyStats:
                                                 L.stream_ptr())
         L.check(rc, "gsb_densify_accumulate")
 
+    def accumulate_batch(self, radii, grad_means2D):
+        """radii [n,P], grad_means2D [n,P,3]: all cameras of the batch in one launch."""
+        n, P = radii.shape
+        with torch.cuda.device(radii.device):
+            rc = L.lib().gsb_densify_accumulate_batch(P, n, L.ptr(radii), L.ptr(grad_means2D), L.ptr(self.max_2d_radii),
+                                                      L.ptr(self.mean_2d_gradients_accumulated),
+                                                      L.ptr(self.visibility_count),
+                                                      L.ptr(self.gaussian_is_visible_mask), L.stream_ptr())
+        L.check(rc, "gsb_densify_accumulate_batch")
+
 
 def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2):
     """act: activated parameters (means3D, colors_precomp, opacities, scales, rotations) on the GPU;
@@ -49,6 +59,5 @@ def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2):
     grads = raster.backward(st, dL, need_cov3D_grad=False)
     if stats is not None:
         g2 = grads["means2D"] if n > 1 else grads["means2D"][None]
-        for i in range(n):
-            stats.accumulate(radii[i], g2[i])
+        stats.accumulate_batch(radii.contiguous(), g2.contiguous())
     return loss_stats, grads, radii, st

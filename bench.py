@@ -126,15 +126,10 @@ def render_targets(tgt_raw, cams_stacked, n, bg, dev):
     return (color if n > 1 else color[None]).clone()
 
 
-def sort_passes(tiles_total):
-    bits = 32 + int(np.ceil(np.log2(max(tiles_total, 2))) if tiles_total & (tiles_total - 1) else int(np.log2(tiles_total)) + 1)
-    return (bits + 7) // 8
-
-
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
     import torch.distributed as dist
-    from gsb200 import _lib, scene, step as step_mod
+    from gsb200 import _lib, scene, step as step_mod, dist as gd
     import ctypes as C
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -167,7 +162,7 @@ def run_ours(args):
 
     stats = step_mod.DensifyStats(P, dev)
     # flat buffer for the one allreduce: 17 gradient floats + 2 summed statistics per Gaussian
-    flat = torch.zeros((P, 19), dtype=torch.float32, device=dev) if world > 1 else None
+    flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev) if world > 1 else None
 
     def activate():
         return {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}
@@ -175,10 +170,9 @@ def run_ours(args):
     def one_step(act):
         loss_stats, grads, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, stats)
         if world > 1:
-            flat[:, 0:3] = grads["means3D"]; flat[:, 3:6] = grads["colors"]; flat[:, 6:10] = grads["rotations"]
-            flat[:, 10:11] = grads["opacities"]; flat[:, 11:14] = grads["scales"]
-            flat[:, 14] = stats.mean_2d_gradients_accumulated; flat[:, 15] = stats.visibility_count
-            dist.all_reduce(flat)
+            gd.pack(flat, grads, {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
+                                  "visibility_count": stats.visibility_count})
+            gd.allreduce(flat, stats.max_2d_radii)
         return loss_stats, grads, st
 
     for k in raw_keys:
@@ -279,15 +273,17 @@ def run_ours(args):
                 "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
                 "ms": bwd_ms, "pairs": walked}
     # the HBM-bound kernel with the most bytes: the onesweep sort (152 B / instance at 6 passes)
-    tiles_total = ((args.width + 15) // 16) * ((args.height + 15) // 16) * n_my
-    passes = (st.ctx.sort_bits + 7) // 8
-    sort_bytes = R * (8 + 24 * passes)
+    passes = (st.ctx.tile_bits + 7) // 8
+    gpasses = (32 + (int(n_my).bit_length() if n_my > 1 else 0) + 7) // 8
+    sort_bytes = R * (4 + 16 * passes)     # 32-bit tile keys + 32-bit payloads
     sort_ms = stages["sort"]
-    roofline_hbm = {"kernel": "rs_histogram_kernel + rs_onesweep_kernel x%d" % passes, "bound": "hbm",
+    roofline_hbm = {"kernel": "rs_histogram_kernel<u32> + rs_onesweep_kernel<u32> x%d (instance sort on tile ids)" % passes, "bound": "hbm",
                     "achieved": sort_bytes / (sort_ms * 1e-3) / 1e9 if sort_ms > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "traffic": None, "ms": sort_ms, "instances": R}
     roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
-    launches = 1 + 1 + 1 + 1 + passes + 1 + 1 + 3 + 1 + 1 + n_my  # see DESIGN.md "launch list"
+    # preprocess, depth sort (hist + passes), scan, key emission, instance sort (hist + passes), ranges,
+    # blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
+    launches = 1 + (1 + gpasses) + 1 + 1 + (1 + passes) + 1 + 1 + 3 + 1 + 1 + 1
 
     out = {
         "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",

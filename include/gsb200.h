@@ -135,6 +135,12 @@ int gsb_ssim_l1(int32_t n, int32_t height, int32_t width, const float* img, cons
 int gsb_densify_accumulate(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_2d_radii,
                            float* grad_accum, float* vis_count, uint8_t* visible, void* stream);
 
+/* The same for the n_cams cameras of a batch in one launch: radii [n_cams][P], grad_means2D [n_cams][P][3];
+ * equals n_cams successive gsb_densify_accumulate calls (same accumulation order). */
+int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii, const float* grad_means2D,
+                                 float* max_2d_radii, float* grad_accum, float* vis_count, uint8_t* visible,
+                                 void* stream);
+
 /* accumulate_mean_2d_gradients (external.py:113-124) taking the visibility mask (uint8 [P]) like the reference. */
 int gsb_densify_accumulate_masked(int32_t P, const uint8_t* visible, const float* grad_means2D, float* grad_accum,
                                   float* vis_count, void* stream);

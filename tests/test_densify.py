@@ -106,3 +106,18 @@ def test_accumulate_matches_oracle(oracle):
     assert np.array_equal(st.max_2d_radii.cpu().numpy(), mr)
     assert np.allclose(st.mean_2d_gradients_accumulated.cpu().numpy(), acc, rtol=1e-6)
     assert np.array_equal(st.visibility_count.cpu().numpy(), cnt)
+
+
+@pytest.mark.gpu
+def test_accumulate_batch_equals_sequential():
+    from gsb200 import step
+    P, n = 7001, 5
+    g = torch.Generator().manual_seed(3)
+    radii = (torch.rand(n, P, generator=g) * 20 - 6).int().clamp(min=0).cuda()
+    grad = torch.randn(n, P, 3, generator=g).cuda()
+    a, b = step.DensifyStats(P, "cuda"), step.DensifyStats(P, "cuda")
+    for i in range(n):
+        a.accumulate(radii[i], grad[i])
+    b.accumulate_batch(radii, grad)
+    for k in ("visibility_count", "mean_2d_gradients_accumulated", "max_2d_radii", "gaussian_is_visible_mask"):
+        assert torch.equal(getattr(a, k), getattr(b, k)), k
