@@ -38,16 +38,47 @@ __device__ __forceinline__ float blend_power(float dx, float dy, float A, float 
 // `thr` (returned) is the per-entry power below which a pixel certainly has alpha < 1/255, so the inner
 // loop can skip it before paying for expf.
 // ------------------------------------------------------------------------------------------------
+// Packs the 8-bit patch mask into the low mantissa bits of the threshold (a 3e-5 relative change of a
+// value that carries a 2e-3 slack).
+__device__ __forceinline__ float pack_thr(float thr, unsigned mask) {
+  return __uint_as_float((__float_as_uint(thr) & ~0xFFu) | (mask & 0xFFu));
+}
+
 __device__ __forceinline__ bool tile_cull_keep(float cx, float cy, float4 co, float tx0, float ty0, float& thr) {
   const float A = co.x, B = co.y, C = co.z, o = co.w;
-  thr = -3.0e38f;
+  thr = pack_thr(-3.0e38f, 0xFFu);
   if (o < 1.0f / 255.0f) return false;
   if (!(o >= 1.0f / 255.0f)) return true;                 // NaN opacity: keep, no early threshold
   const float L = logf(255.0f * o);                        // >= 0
-  thr = -(L + 2.0e-3f + 1.0e-3f * L);
-  if (!(A > 0.f && C > 0.f && A * C > B * B)) return true;  // not positive definite: no claim
+  thr = pack_thr(-(L + 2.0e-3f + 1.0e-3f * L), 0xFFu);
+  const float det = A * C - B * B;
+  if (!(A > 0.f && C > 0.f && det > 0.f)) return true;      // not positive definite: no claim
   const float dxlo = cx - (tx0 + 15.0f), dxhi = cx - tx0;  // d = centre - pixel over the tile
   const float dylo = cy - (ty0 + 15.0f), dyhi = cy - ty0;
+  const float DX = fmaxf(fabsf(dxlo), fabsf(dxhi)), DY = fmaxf(fabsf(dylo), fabsf(dyhi));
+  const float Mmax = A * DX * DX + 2.f * fabsf(B) * DX * DY + C * DY * DY;  // bounds every rounding error
+  const float lim = L + 2.0e-3f + 1.0e-3f * L + 1.0e-5f * Mmax;              // a pixel contributes only if q/2 <= lim
+  {
+    // Patch mask: the axis-aligned bounding box of the ellipse q <= 2 lim has half-widths
+    // sqrt(2 lim C / det), sqrt(2 lim A / det); warp w owns the 8x4 patch (column w & 1, row w >> 1).
+    const float idet = __fdividef(1.0f, det);
+    const float hx = sqrtf(2.f * lim * C * idet) * 1.0001f + 1.0e-3f;
+    const float hy = sqrtf(2.f * lim * A * idet) * 1.0001f + 1.0e-3f;
+    unsigned cols = 0, rows = 0;
+#pragma unroll
+    for (int j = 0; j < 2; j++)
+      if (cx + hx >= tx0 + 8.f * j && cx - hx <= tx0 + 8.f * j + 7.f) cols |= 1u << j;
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+      if (cy + hy >= ty0 + 4.f * r && cy - hy <= ty0 + 4.f * r + 3.f) rows |= 1u << r;
+    unsigned mask = 0;
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+      if (rows & (1u << r)) mask |= cols << (2 * r);
+    if (!(hx == hx && hy == hy)) mask = 0xFFu;             // NaN: no claim
+    thr = pack_thr(thr, mask);
+    if (mask == 0) return false;
+  }
   if (dxlo <= 0.f && dxhi >= 0.f && dylo <= 0.f && dyhi >= 0.f) return true;
   const float iA = __fdividef(1.0f, A), iC = __fdividef(1.0f, C);
   float qmin = 3.0e38f;
@@ -61,9 +92,7 @@ __device__ __forceinline__ bool tile_cull_keep(float cx, float cy, float4 co, fl
     qmin = fminf(qmin, A * dx * dx + 2.f * B * dx * f + C * f * f);
   }
   if (!(qmin < 3.0e38f)) return true;                      // NaN geometry: no claim
-  const float DX = fmaxf(fabsf(dxlo), fabsf(dxhi)), DY = fmaxf(fabsf(dylo), fabsf(dyhi));
-  const float Mmax = A * DX * DX + 2.f * fabsf(B) * DX * DY + C * DY * DY;  // bounds every rounding error
-  return !(0.5f * qmin > L + 2.0e-3f + 1.0e-3f * L + 1.0e-5f * Mmax);
+  return !(0.5f * qmin > lim);
 }
 
 // Block-wide stable compaction slot for `keep`; returns the number of kept entries of the batch.
@@ -142,6 +171,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
     for (int j = 0; !done && j < n; j++) {
       const float4 a = s_a[j];
+      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;   // cannot reach this warp's 8x4 patch
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
       const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
@@ -267,6 +297,18 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float last_alpha = 0.f;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
+  // this lane's gradient slot: lanes 0,4,..,28 own the 8 reduced components, lane 1 the opacity gradient
+  float* lane_base;
+  unsigned lane_stride;
+  {
+    const unsigned comp = lane >> 2;
+    if (lane == 1) { lane_base = dL_dopacity; lane_stride = 1; }
+    else if (comp < 3) { lane_base = dcol_tab + comp; lane_stride = 3; }
+    else if (comp < 5) { lane_base = dL_dmean2D + 3 * cam_off + (comp - 3); lane_stride = 3; }
+    else { lane_base = dL_dconic + 4 * cam_off + (comp == 7 ? 3 : comp - 5); lane_stride = 4; }
+  }
+  const bool lane_writes = ((lane & 3u) == 0) || lane == 1;
+
   // deepest contributor of the warp / of the tile: entries at list positions >= that are dead
   int warp_last = last_contributor;
 #pragma unroll
@@ -307,6 +349,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const float4 a = s_a[j];
       const int pos = __float_as_int(a.w);
       if (pos >= warp_last) continue;            // warp-uniform: behind this warp's deepest contributor
+      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;   // cannot reach this warp's 8x4 patch
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
       const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
@@ -359,14 +402,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
 
       const uint32_t id2 = __float_as_uint(ci.w);
-      const unsigned comp = lane >> 2;
-      float* dst;
-      float val = v[0];
-      if (lane == 1) { dst = dL_dopacity + id2; val = g_op; }
-      else if (comp < 3) dst = dcol_tab + 3 * (size_t)id2 + comp;
-      else if (comp < 5) dst = dL_dmean2D + 3 * (cam_off + id2) + (comp - 3);
-      else dst = dL_dconic + 4 * (cam_off + id2) + (comp == 7 ? 3 : comp - 5);
-      if (((lane & 3u) == 0 || lane == 1) && val != 0.f) atomicAdd(dst, val);
+      const float val = (lane == 1) ? g_op : v[0];
+      if (lane_writes && val != 0.f) atomicAdd(lane_base + (size_t)id2 * lane_stride, val);
     }
   }
 }

@@ -2,6 +2,6 @@
 set -x
 CMD="python bench.py --profile-only"
 $CMD > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"gsb" -s 23 -c 23 --csv --log-file gpurun_out/r1_launches.csv $CMD > gpurun_out/ncu_l.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"gsb" -s 23 -c 23 -o gpurun_out/r1_prof $CMD > gpurun_out/ncu_f.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^(preprocess|rs_|scan_u32|duplicate_with|tile_ranges|render_|ssim_|densify_)" -s 21 -c 21 --csv --log-file gpurun_out/r1_launches.csv $CMD > gpurun_out/ncu_l.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"^(preprocess|rs_|scan_u32|duplicate_with|tile_ranges|render_|ssim_|densify_)" -s 21 -c 21 -o gpurun_out/r1_prof $CMD > gpurun_out/ncu_f.log 2>&1
 tail -3 gpurun_out/ncu_f.log
