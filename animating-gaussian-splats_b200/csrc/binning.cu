@@ -278,6 +278,7 @@ struct RsSmem {
   uint32_t digit_start[RS_RADIX];   // exclusive prefix of this tile's digit counts
   uint32_t digit_gbase[RS_RADIX];   // global position of the tile's first key of digit d, minus digit_start[d]
   uint32_t warp_tot[RS_WARPS];
+  uint32_t block_cnt[RS_RADIX];     // early digit counts of the tile (published before ranking)
   uint32_t tile;
 };
 
@@ -293,6 +294,7 @@ rs_onesweep_kernel(long long n, const KeyT* __restrict__ kin, KeyT* __restrict__
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
   for (int w = 0; w < RS_WARPS; w++) S.warp_cnt[w][tid] = 0;
+  S.block_cnt[tid] = 0;
   __syncthreads();
   const uint32_t tile = S.tile;
   const long long tile_base = (long long)tile * RS_TILE;
@@ -315,13 +317,35 @@ rs_onesweep_kernel(long long n, const KeyT* __restrict__ kin, KeyT* __restrict__
       val[i] = 0;
     }
   }
-  // rank within the warp, in (item, lane) order == memory order => stable
+  // early counts: the tile's digit histogram via shared atomics, published as the tile's aggregate BEFORE
+  // the (long) ranking phase, so that by the time this tile looks back its predecessors have published too
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; i++) {
+    const int e = wbase + i * 32 + lane;
+    const uint32_t d = (e < n_valid) ? ((uint32_t)(key[i] >> shift) & dmask) : (RS_RADIX - 1);
+    atomicAdd(&S.block_cnt[d], 1u);
+  }
+  __syncthreads();
+  {
+    const uint32_t c = S.block_cnt[tid];
+    uint32_t* my_status = status + (size_t)tile * RS_RADIX + tid;
+    st_relaxed_u32(my_status, (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | c);
+  }
+  // rank within the warp, in (item, lane) order == memory order => stable.  Peers (lanes holding the same
+  // digit) come from 8 ballots, one per digit bit: independent across items, unlike match.any whose
+  // latency serialised the loop.
   const unsigned lt = lanemask_lt();
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; i++) {
     const int e = wbase + i * 32 + lane;
     const uint32_t d = (e < n_valid) ? ((uint32_t)(key[i] >> shift) & dmask) : (RS_RADIX - 1);
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    unsigned peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < RS_BITS; b++) {
+      const bool bit = (d >> b) & 1u;
+      const unsigned bal = __ballot_sync(0xffffffffu, bit);
+      peers &= bit ? bal : ~bal;
+    }
     const int leader = __ffs(peers) - 1;
     uint32_t before = 0;
     if ((int)lane == leader) {
@@ -346,8 +370,6 @@ rs_onesweep_kernel(long long n, const KeyT* __restrict__ kin, KeyT* __restrict__
     }
     const uint32_t cnt = run;  // tile's count of digit d (the last tile's digit 255 also counts its padding)
     uint32_t* my_status = status + (size_t)tile * RS_RADIX + d;
-    if (tile == 0) st_relaxed_u32(my_status, RS_FLAG_INC | cnt);
-    else st_relaxed_u32(my_status, RS_FLAG_AGG | cnt);
 
     // exclusive scans over the 256 digits: tile counts and global histogram
     const uint32_t g = ghist[d];

@@ -44,6 +44,7 @@ __device__ __forceinline__ float pack_thr(float thr, unsigned mask) {
   return __uint_as_float((__float_as_uint(thr) & ~0xFFu) | (mask & 0xFFu));
 }
 
+template <bool WITH_MASK>
 __device__ __forceinline__ bool tile_cull_keep(float cx, float cy, float4 co, float tx0, float ty0, float& thr) {
   const float A = co.x, B = co.y, C = co.z, o = co.w;
   thr = pack_thr(-3.0e38f, 0xFFu);
@@ -58,7 +59,7 @@ __device__ __forceinline__ bool tile_cull_keep(float cx, float cy, float4 co, fl
   const float DX = fmaxf(fabsf(dxlo), fabsf(dxhi)), DY = fmaxf(fabsf(dylo), fabsf(dyhi));
   const float Mmax = A * DX * DX + 2.f * fabsf(B) * DX * DY + C * DY * DY;  // bounds every rounding error
   const float lim = L + 2.0e-3f + 1.0e-3f * L + 1.0e-5f * Mmax;              // a pixel contributes only if q/2 <= lim
-  {
+  if (WITH_MASK) {
     // Patch mask: the axis-aligned bounding box of the ellipse q <= 2 lim has half-widths
     // sqrt(2 lim C / det), sqrt(2 lim A / det); warp w owns the 8x4 patch (column w & 1, row w >> 1).
     const float idet = __fdividef(1.0f, det);
@@ -158,7 +159,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       id = point_list[range.x + progress];
       xy = means2D[cam_off + id];
       co = conic_opacity[cam_off + id];
-      keep = tile_cull_keep(xy.x, xy.y, co, tx0, ty0, thr);
+      keep = tile_cull_keep<false>(xy.x, xy.y, co, tx0, ty0, thr);
     }
     int slot;
     const int n = compact_slot(keep, tid, s_wcnt, slot);
@@ -171,7 +172,6 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
     for (int j = 0; !done && j < n; j++) {
       const float4 a = s_a[j];
-      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;   // cannot reach this warp's 8x4 patch
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
       const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
@@ -334,7 +334,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       id = point_list[range.x + (uint32_t)pos_mine];
       xy = means2D[cam_off + id];
       co = conic_opacity[cam_off + id];
-      keep = tile_cull_keep(xy.x, xy.y, co, tx0, ty0, thr);
+      keep = tile_cull_keep<true>(xy.x, xy.y, co, tx0, ty0, thr);
     }
     int slot;
     const int n = compact_slot(keep, tid, s_wcnt, slot);
