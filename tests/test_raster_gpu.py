@@ -212,3 +212,32 @@ def test_camera_batch_matches_single(refdgr):
     for k in acc:
         nbad, maxerr = helpers.grad_close(helpers.to_np(gb[k]), helpers.to_np(acc[k]), rel=2e-4)
         assert nbad == 0, (k, nbad, maxerr)
+
+
+def test_c4_full_size_forward_only(refdgr):
+    """BASELINE.json configs[3]: 1 M Gaussians at 1920x1080, forward only (sort / tile-range stress: 8160
+    tiles, 45 sort bits in the reference).  One of the eight cameras, full size, against the reference."""
+    dev = "cuda"
+    P, W, H = 1_000_000, 1920, 1080
+    g = helpers.scene.make_gaussians(P, seed=40, scale_override=0.012)
+    a = {k: v.to(dev).contiguous() for k, v in helpers.scene.activate(g).items()}
+    cam = helpers.scene.make_cameras(8, W, H, seed=40)[3]
+    bg = torch.zeros(3, device=dev)
+    fw = helpers.ref_forward(refdgr, a, cam, bg, dev)
+    color, depth, radii, st = run_mine(a, cam, bg)
+    R = fw["num_rendered"]
+    assert st.num_rendered == R and R > 5_000_000
+    assert st.ctx.sort_bits == 45
+    ref = oracle_lib.decode_reference_buffers(P, H, W, R, fw["geom"], fw["binning"], fw["img"])
+    mine = st.tensors()
+    assert torch.equal(radii, fw["radii"])
+    assert torch.equal(mine["point_list_keys"], ref["point_list_keys"])
+    assert torch.equal(mine["point_list"], ref["point_list"])
+    assert torch.equal(mine["ranges"], ref["ranges"])
+    assert torch.equal(mine["n_contrib"][0], ref["n_contrib"])
+    assert (color - fw["color"]).abs().max().item() <= 1e-5
+    assert (depth - fw["depth"]).abs().max().item() <= 1e-5
+    # size-independent properties at full size: ranges tile the list; keys ascending
+    rg = mine["ranges"].long()
+    assert int((rg[:, 1] - rg[:, 0]).sum()) == R
+    assert bool((mine["point_list_keys"][1:] >= mine["point_list_keys"][:-1]).all())
