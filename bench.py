@@ -263,13 +263,21 @@ def run_ours(args):
         return
 
     hbm_peak, sm_max_mhz, peak_src = peaks()
+    traffic = {}
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+        if (args.gaussians, args.cams, args.width, args.height, world) == (300_000, 27, 640, 360, 1):
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                traffic = json.load(f)["kernels"]
+    except Exception:
+        traffic = {}
+    tr = lambda name: (traffic.get(name, {}).get("dram_bytes_per_launch") if traffic else None)
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
     fp32_peak_tflops = n_sm * 128 * 2 * sm_max_mhz * 1e6 / 1e12
     # dominant kernel: backward blend.  Algorithmic work: 70 FP32 flop per walked pair.
     bwd_ms = stages["render_bwd"]
     achieved = (walked * 70.0) / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else 0.0
     roofline = {"kernel": "render_bwd_kernel", "bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops,
-                "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": tr("render_bwd_kernel"),
                 "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
                 "ms": bwd_ms, "pairs": walked}
     # the HBM-bound kernel with the most bytes: the onesweep sort (152 B / instance at 6 passes)
@@ -279,7 +287,10 @@ def run_ours(args):
     sort_ms = stages["sort"]
     roofline_hbm = {"kernel": "rs_histogram_kernel<u32> + rs_onesweep_kernel<u32> x%d (instance sort on tile ids)" % passes, "bound": "hbm",
                     "achieved": sort_bytes / (sort_ms * 1e-3) / 1e9 if sort_ms > 0 else 0.0, "peak": hbm_peak,
-                    "unit": "GB/s", "traffic": None, "ms": sort_ms, "instances": R}
+                    "unit": "GB/s", "ms": sort_ms, "instances": R,
+                    "traffic": (None if tr("rs_onesweep_kernel<unsigned int>") is None else
+                                passes * tr("rs_onesweep_kernel<unsigned int>") + tr("rs_histogram_kernel<unsigned int>")),
+                    "algorithmic_bytes": sort_bytes}
     roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
     # preprocess, depth sort (hist + passes), scan, key emission, instance sort (hist + passes), ranges,
     # blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
@@ -305,6 +316,14 @@ def run_ours(args):
         out["cpu_baseline"] = cpu_baseline(args, g_raw, cams, host_targets)
     if world == 1 and not args.no_reference_cuda:
         out["reference_cuda"] = reference_cuda(args, act, my_cams, dev_targets, bg, dev)
+        try:
+            out["densify_loop_shape"] = {
+                "what": "densify.py:201-248 shape: 1 camera/iteration, colour + segmentation render, 2x L1/SSIM, "
+                        "backward, densify statistics, torch Adam; through the drop-in Python surface",
+                "unit": "iters/s", "ours": densify_shaped(args, "ours"),
+                "reference_cuda": densify_shaped(args, "reference_cuda")}
+        except Exception as ex:  # never lose the headline line to the extra measurement
+            out["densify_loop_shape"] = {"error": repr(ex)[:300]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -422,6 +441,84 @@ def reference_cuda(args, act, cams, targets, bg, dev, passes=2):
     ms = e0.elapsed_time(e1) / passes
     return {"value": len(cams) / (ms * 1e-3), "unit": "iters/s", "ms_per_step": ms,
             "what": "unmodified reference extension (sm_100a build, CUB sort) + stock torch L1/SSIM, camera by camera"}
+
+
+def densify_shaped(args, impl, iters=30, warm=5):
+    """The reference's first-frame loop shape (densify.py:201-248): ONE camera per iteration, two renders
+    (colour + segmentation colours), 0.8 L1 + 0.2 (1-SSIM) each, total = image + 3 segmentation, backward,
+    densification statistics, Adam.  impl = "ours" (drop-in GaussianRasterizer + fused loss + statistics
+    kernels) or "reference_cuda" (unmodified extension through its autograd node + stock torch loss and
+    masked-index statistics).  Returns iterations / second (CUDA events)."""
+    from gsb200 import scene, loss as gloss, densify as gdens
+    import helpers
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g_raw, tgt_raw, cams = build_workload(args)
+    sc = scene.stack_cameras(cams, dev)
+    bg = torch.zeros(3, device=dev)
+    targets = render_targets(tgt_raw, sc, args.cams, bg, dev)
+    seg_targets = (targets > 0.5).float()
+    params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in g_raw.items()}
+    opt = torch.optim.Adam([{"params": [v], "name": k, "lr": 1e-4} for k, v in params.items()], lr=0.0, eps=1e-15)
+    P = args.gaussians
+    dv = gdens.DensificationVariables(visibility_count=torch.zeros(P, device=dev),
+                                      mean_2d_gradients_accumulated=torch.zeros(P, device=dev),
+                                      max_2d_radii=torch.zeros(P, device=dev))
+    if impl == "ours":
+        from diff_gaussian_rasterization import GaussianRasterizer as Renderer
+        settings = [scene.settings_for(c, dev) for c in cams]
+    else:
+        import oracle_lib
+        ref = oracle_lib.load_reference_ext()
+        if ref is None:
+            return None
+
+    def render(i, colors):
+        a = {"means3D": params["means"], "colors_precomp": colors,
+             "rotations": torch.nn.functional.normalize(params["rotation_quaternions"]),
+             "opacities": torch.sigmoid(params["opacity_logits"]), "scales": torch.exp(params["log_scales"]),
+             "means2D": torch.zeros_like(params["means"], requires_grad=True) + 0}
+        a["means2D"].retain_grad()
+        if impl == "ours":
+            im, radii, _ = Renderer(raster_settings=settings[i])(**a)
+        else:
+            im, radii, _ = helpers.RefRasterize.apply(ref, a["means3D"], a["means2D"], a["colors_precomp"], a["opacities"],
+                                                      a["scales"], a["rotations"], cams[i], bg)
+        return im, radii, a["means2D"]
+
+    def loss_fn(im, tgt):
+        return gloss.l1_ssim_loss(im, tgt) if impl == "ours" else torch_ssim_l1(im, tgt)
+
+    def one(it):
+        i = it % args.cams
+        im, radii, m2d = render(i, params["colors"])
+        l_img = loss_fn(im, targets[i])
+        seg, _, _ = render(i, params["segmentation_masks"])
+        total = l_img + 3 * loss_fn(seg, seg_targets[i])
+        total.backward()
+        with torch.no_grad():
+            dv.means_2d = m2d
+            if impl == "ours":
+                gdens.update_max_2d_radii_and_visibility_mask(radii, dv)
+                gdens.accumulate_mean_2d_gradients(dv)
+            else:  # densify.py:154-162 + external.py:113-124 as the reference writes them
+                pos = radii > 0
+                dv.max_2d_radii[pos] = torch.max(radii[pos], dv.max_2d_radii[pos])
+                dv.gaussian_is_visible_mask = pos
+                dv.mean_2d_gradients_accumulated[pos] += torch.norm(m2d.grad[pos, :2], dim=-1)
+                dv.visibility_count[pos] += 1
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+
+    for it in range(warm):
+        one(it)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for it in range(iters):
+        one(warm + it)
+    e1.record()
+    torch.cuda.synchronize()
+    return iters / (e0.elapsed_time(e1) * 1e-3)
 
 
 def run_reference_cuda(args):

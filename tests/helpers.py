@@ -49,3 +49,32 @@ def grad_close(a, b, rel=1e-4, floor=1e-6, spread=0.0):
 
 def to_np(t):
     return t.detach().cpu().numpy()
+
+
+class RefRasterize(torch.autograd.Function):
+    """The reference's autograd node (DGR/diff_gaussian_rasterization/__init__.py:40-132) around the
+    unmodified extension module `refdgr` -- used to time / check the reference through its own call pattern."""
+
+    @staticmethod
+    def forward(ctx, refdgr, means3D, means2D, colors, opacities, scales, rotations, cam, bg):
+        e = torch.Tensor([])
+        dev = means3D.device
+        args = (bg, means3D, colors, opacities, scales, rotations, 1.0, e, cam["viewmatrix"].to(dev),
+                cam["projmatrix"].to(dev), cam["tanfovx"], cam["tanfovy"], cam["image_height"], cam["image_width"], e, 0,
+                cam["campos"].to(dev), False)
+        n, color, radii, geom, binning, img, depth = refdgr.rasterize_gaussians(*args)
+        ctx.refdgr, ctx.cam, ctx.n, ctx.bg = refdgr, cam, n, bg
+        ctx.save_for_backward(colors, means3D, scales, rotations, radii, geom, binning, img)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, g_color, _r, _d):
+        colors, means3D, scales, rotations, radii, geom, binning, img = ctx.saved_tensors
+        e = torch.Tensor([])
+        cam, dev = ctx.cam, means3D.device
+        args = (ctx.bg, means3D, radii, colors, scales, rotations, 1.0, e, cam["viewmatrix"].to(dev),
+                cam["projmatrix"].to(dev), cam["tanfovx"], cam["tanfovy"], g_color.contiguous(), e, 0,
+                cam["campos"].to(dev), geom, ctx.n, binning, img)
+        dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = ctx.refdgr.rasterize_gaussians_backward(*args)
+        return None, dm3, dm2, dcol, dop, dsc, drot, None, None
