@@ -126,6 +126,22 @@ split_rows_kernel(int P, int S, const uint8_t* __restrict__ sel, const int32_t* 
   }
 }
 
+// Packs the step's exchange buffer [P][16] in one pass: means3D(3) colours(3) rotations(4) opacity(1)
+// scales(3) grad-norm accumulator(1) visibility count(1)  (gsb200/dist.py COLS).
+__global__ void __launch_bounds__(256)
+pack_flat_kernel(int P, const float* __restrict__ g_means, const float* __restrict__ g_colors,
+                 const float* __restrict__ g_rot, const float* __restrict__ g_opac, const float* __restrict__ g_scales,
+                 const float* __restrict__ accum, const float* __restrict__ count, float4* __restrict__ flat) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  const size_t j = (size_t)i;
+  const float4 q = reinterpret_cast<const float4*>(g_rot)[j];
+  flat[4 * j + 0] = make_float4(g_means[3 * j], g_means[3 * j + 1], g_means[3 * j + 2], g_colors[3 * j]);
+  flat[4 * j + 1] = make_float4(g_colors[3 * j + 1], g_colors[3 * j + 2], q.x, q.y);
+  flat[4 * j + 2] = make_float4(q.z, q.w, g_opac[j], g_scales[3 * j]);
+  flat[4 * j + 3] = make_float4(g_scales[3 * j + 1], g_scales[3 * j + 2], accum ? accum[j] : 0.f, count ? count[j] : 0.f);
+}
+
 }  // namespace gsb
 
 using namespace gsb;
@@ -151,6 +167,19 @@ int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii
   if (!radii || !grad_means2D || !grad_accum || !vis_count) return GSB_EINVAL;
   densify_accumulate_batch_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       P, n_cams, radii, grad_means2D, max_2d_radii, grad_accum, vis_count, visible);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_pack_flat(int32_t P, const float* g_means3D, const float* g_colors, const float* g_rotations,
+                  const float* g_opacities, const float* g_scales, const float* grad_accum, const float* vis_count,
+                  float* flat, void* stream) {
+  if (P < 0) return GSB_EINVAL;
+  if (P == 0) return GSB_OK;
+  if (!g_means3D || !g_colors || !g_rotations || !g_opacities || !g_scales || !flat) return GSB_EINVAL;
+  pack_flat_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      P, g_means3D, g_colors, g_rotations, g_opacities, g_scales, grad_accum, vis_count,
+      reinterpret_cast<float4*>(flat));
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -23,7 +23,19 @@ def shard_cameras(n_cams, rank, world):
 
 
 def pack(flat, grads, stats_delta=None):
-    """Write this rank's camera-summed gradients (and statistic increments) into flat [P, 16]."""
+    """Write this rank's camera-summed gradients (and statistic increments) into flat [P, 16].
+    CUDA tensors go through one gsb_pack_flat launch; CPU tensors (gloo tests) through slice copies."""
+    if flat.is_cuda:
+        from . import _lib as L
+        c = lambda t: t.contiguous()
+        acc = c(stats_delta["mean_2d_gradients_accumulated"]) if stats_delta is not None else None
+        cnt = c(stats_delta["visibility_count"]) if stats_delta is not None else None
+        keep = [c(grads[k]) for k in ("means3D", "colors", "rotations", "opacities", "scales")]
+        with torch.cuda.device(flat.device):
+            rc = L.lib().gsb_pack_flat(flat.shape[0], L.ptr(keep[0]), L.ptr(keep[1]), L.ptr(keep[2]), L.ptr(keep[3]),
+                                       L.ptr(keep[4]), L.ptr(acc), L.ptr(cnt), L.ptr(flat), L.stream_ptr())
+        L.check(rc, "gsb_pack_flat")
+        return flat
     for k in ("means3D", "colors", "rotations", "opacities", "scales"):
         a, b = COLS[k]
         flat[:, a:b] = grads[k].reshape(flat.shape[0], b - a)

@@ -535,6 +535,18 @@ def run_reference_cuda(args):
 
 
 if __name__ == "__main__":
+    # Libraries (NCCL's version banner, torchrun notices) write to stdout; the contract is ONE JSON line
+    # there.  Send everything else to stderr and print the result line on the real stdout.
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    _print = print
+
+    def print(*a, **k):  # noqa: A001
+        k.setdefault("file", _real_stdout)
+        _print(*a, **k)
+        _real_stdout.flush()
+
     a = parse()
     if a.impl == "reference":
         run_reference(a)

@@ -141,6 +141,13 @@ int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii
                                  float* max_2d_radii, float* grad_accum, float* vis_count, uint8_t* visible,
                                  void* stream);
 
+/* Multi-GPU exchange buffer (new; the reference has no distributed code): flat [P][16] =
+ * dL_dmeans3D(3) dL_dcolors(3) dL_drotations(4) dL_dopacity(1) dL_dscales(3) grad-norm accumulator(1)
+ * visibility count(1) in one pass, ready for ONE allreduce.  grad_accum / vis_count may be NULL (zeros). */
+int gsb_pack_flat(int32_t P, const float* g_means3D, const float* g_colors, const float* g_rotations,
+                  const float* g_opacities, const float* g_scales, const float* grad_accum, const float* vis_count,
+                  float* flat, void* stream);
+
 /* accumulate_mean_2d_gradients (external.py:113-124) taking the visibility mask (uint8 [P]) like the reference. */
 int gsb_densify_accumulate_masked(int32_t P, const uint8_t* visible, const float* grad_means2D, float* grad_accum,
                                   float* vis_count, void* stream);
