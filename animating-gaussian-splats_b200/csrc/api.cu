@@ -1,6 +1,8 @@
 // api.cu -- the extern "C" surface of libgsb200.so (see include/gsb200.h) and the host orchestration
 // that replaces CudaRasterizer::Rasterizer::forward/backward (cr/rasterizer_impl.cu:198-436).
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include "common.cuh"
@@ -61,13 +63,38 @@ struct Carver {
   }
 };
 
+// Digit widths of the two segmented sorts (overridable for experiments: GSB_DEPTH_DIGIT = 8 | 11,
+// GSB_TILE_DIGIT = 5 | 8 | 10).
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+static int depth_digit() {
+  static int d = env_int("GSB_DEPTH_DIGIT", 8);
+  return d == 11 ? 11 : 8;
+}
+struct TileSortPlan { int log_nb, passes; };
+static TileSortPlan tile_sort_plan(int tile_bits) {
+  static int forced = env_int("GSB_TILE_DIGIT", 0);
+  TileSortPlan p;
+  if (forced == 5 || forced == 8 || forced == 10) p.log_nb = forced;
+  else p.log_nb = tile_bits <= 5 ? 5 : tile_bits <= 8 ? 8 : tile_bits <= 10 ? 10 : 8;
+  p.passes = (std::max(tile_bits, 1) + p.log_nb - 1) / p.log_nb;
+  return p;
+}
+
 struct GeomExtras {
   CamParams* cams = nullptr;
   int* err = nullptr;
   void* scan_scratch = nullptr;
-  uint64_t* gkeys_in = nullptr;   // unsorted (camera << 32 | depth) keys, written by preprocess
-  uint32_t* gvals_in = nullptr;   // iota
+  uint32_t* gkeys_in = nullptr;    // unsorted depth keys [n_cams][P], written by preprocess
+  uint32_t* gkeys_b = nullptr;     // ping-pong key buffers of the depth sort
+  uint32_t* gkeys_c = nullptr;
+  uint32_t* gorder_alt = nullptr;  // ping-pong payload buffer of the depth sort
   void* gsort_temp = nullptr;
+  uint32_t* dseg_start = nullptr;  // [n_cams + 1] fixed-length segments of the depth sort
+  uint32_t* dseg_tile0 = nullptr;
+  uint32_t* seg_tile0 = nullptr;   // [n_cams + 1] sort-tile prefix of the instance sort
 };
 
 struct GeomLayout {
@@ -80,20 +107,29 @@ struct GeomLayout {
     float* cov3D = k.take<float>(6 * n);
     float* conic = k.take<float>(4 * n);
     uint32_t* tt = k.take<uint32_t>(n);
-    uint64_t* gk = k.take<uint64_t>(n);
     uint32_t* go = k.take<uint32_t>(n);
     uint32_t* po = k.take<uint32_t>(n);
+    uint32_t* ss = k.take<uint32_t>((size_t)n_cams + 1);
     CamParams* cp = k.take<CamParams>(n_cams);
     int* e = k.take<int>(4);
-    void* ss = k.take<char>(scan_scratch_bytes((int64_t)n));
-    uint64_t* gki = k.take<uint64_t>(n);
-    uint32_t* gvi = k.take<uint32_t>(n);
-    void* gt = k.take<char>(sort_temp_bytes((int64_t)n));
+    void* sc = k.take<char>(scan_scratch_bytes((int64_t)n));
+    uint32_t* gki = k.take<uint32_t>(n);
+    uint32_t* gkb = k.take<uint32_t>(n);
+    uint32_t* gkc = k.take<uint32_t>(n);
+    uint32_t* goa = k.take<uint32_t>(n);
+    uint32_t* ds = k.take<uint32_t>((size_t)n_cams + 1);
+    uint32_t* dt = k.take<uint32_t>((size_t)n_cams + 1);
+    uint32_t* st0 = k.take<uint32_t>((size_t)n_cams + 1);
+    const int dd = depth_digit();
+    void* gt = k.take<char>(seg_sort_temp_bytes((int64_t)n, n_cams, (32 + dd - 1) / dd, dd));
     if (c) {
       c->depths = depths; c->radii = radii; c->means2D = means2D; c->cov3D = cov3D; c->conic_opacity = conic;
-      c->tiles_touched = tt; c->gauss_keys = gk; c->gauss_order = go; c->point_offsets = po;
+      c->tiles_touched = tt; c->gauss_order = go; c->point_offsets = po; c->seg_start = ss;
     }
-    if (x) { x->cams = cp; x->err = e; x->scan_scratch = ss; x->gkeys_in = gki; x->gvals_in = gvi; x->gsort_temp = gt; }
+    if (x) {
+      x->cams = cp; x->err = e; x->scan_scratch = sc; x->gkeys_in = gki; x->gkeys_b = gkb; x->gkeys_c = gkc;
+      x->gorder_alt = goa; x->gsort_temp = gt; x->dseg_start = ds; x->dseg_tile0 = dt; x->seg_tile0 = st0;
+    }
     return align_up(k.off, 256);
   }
 };
@@ -108,18 +144,32 @@ static size_t carve_image(char* base, int W, int H, int n_cams, int tiles_total,
   return align_up(k.off, 256);
 }
 
-static size_t carve_binning(char* base, int64_t R, gsb_raster_ctx* c) {
+struct BinExtras {
+  uint32_t* vals_alt = nullptr;
+  uint16_t* keys_alt = nullptr;
+};
+
+static size_t carve_binning(char* base, int64_t R, int tile_bits, int n_cams, gsb_raster_ctx* c, BinExtras* x) {
   Carver k(base);
   const size_t n = (size_t)(R > 0 ? R : 1);
+  const TileSortPlan plan = tile_sort_plan(tile_bits);
   uint32_t* pl = k.take<uint32_t>(n);
   uint32_t* plu = k.take<uint32_t>(n);
-  uint32_t* tl = k.take<uint32_t>(n);
-  uint32_t* tlu = k.take<uint32_t>(n);
-  void* tmp = k.take<char>(sort_temp_bytes(R));
+  uint16_t* tku = k.take<uint16_t>(n);
+  uint32_t* va = nullptr;
+  uint16_t* tks = nullptr;
+  uint16_t* tka = nullptr;
+  if (plan.passes > 1) {
+    va = k.take<uint32_t>(n);
+    tks = k.take<uint16_t>(n);
+    tka = k.take<uint16_t>(n);
+  }
+  void* tmp = k.take<char>(seg_sort_temp_bytes(R, n_cams, plan.passes, plan.log_nb));
   if (c) {
-    c->point_list = pl; c->point_list_unsorted = plu; c->point_list_tiles = tl; c->point_list_tiles_unsorted = tlu;
+    c->point_list = pl; c->point_list_unsorted = plu; c->tile_keys_unsorted = tku; c->tile_keys_sorted = tks;
     c->sort_temp = tmp;
   }
+  if (x) { x->vals_alt = va; x->keys_alt = tka; }
   return align_up(k.off, 256);
 }
 
@@ -149,9 +199,9 @@ size_t gsb_image_bytes(int32_t width, int32_t height, int32_t n_cams) {
   const int tiles = ((width + GSB_TILE - 1) / GSB_TILE) * ((height + GSB_TILE - 1) / GSB_TILE) * n_cams;
   return carve_image(nullptr, width, height, n_cams, tiles, nullptr);
 }
-size_t gsb_binning_bytes(int64_t num_rendered, int32_t n_tiles_total) {
-  (void)n_tiles_total;
-  return carve_binning(nullptr, num_rendered, nullptr);
+size_t gsb_binning_bytes(int64_t num_rendered, int32_t tiles_per_cam, int32_t n_cams) {
+  return carve_binning(nullptr, num_rendered, (int)higher_msb((uint32_t)std::max(tiles_per_cam, 1)), n_cams, nullptr,
+                       nullptr);
 }
 uint32_t gsb_higher_msb(uint32_t n) { return higher_msb(n); }
 
@@ -166,9 +216,11 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   ctx->P = a->P; ctx->n_cams = a->n_cams; ctx->width = a->width; ctx->height = a->height;
   ctx->tiles_x = (a->width + GSB_TILE - 1) / GSB_TILE;
   ctx->tiles_y = (a->height + GSB_TILE - 1) / GSB_TILE;
-  const int tiles_total = ctx->tiles_x * ctx->tiles_y * a->n_cams;
-  ctx->tile_bits = (int)higher_msb((uint32_t)tiles_total);
-  ctx->sort_bits = 32 + ctx->tile_bits;
+  const int tiles_per_cam = ctx->tiles_x * ctx->tiles_y;
+  const int tiles_total = tiles_per_cam * a->n_cams;
+  if (tiles_per_cam > 65535 || a->n_cams > 1024) return GSB_EINVAL;   // 16-bit camera-local tile ids
+  ctx->tile_bits = (int)higher_msb((uint32_t)tiles_per_cam);
+  ctx->sort_bits = 32 + (int)higher_msb((uint32_t)tiles_total);
   if (a->P == 0) return GSB_OK;  // the glue returns zero images, like DGR/rasterize_points.cu:81
   if (!a->means3D || !a->colors || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->background ||
       !out_color || !out_depth)
@@ -199,18 +251,20 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
 
   prof_mark(PF_FWD_BEGIN, st);
-  if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, gx.gkeys_in, gx.gvals_in, err_dev, st))) return rc;
+  if ((rc = launch_preprocess(*a, cams_dev, *ctx, radii, gx.gkeys_in, err_dev, st))) return rc;
   prof_mark(PF_PREPROCESS, st);
   const int64_t n_slots = (int64_t)a->P * a->n_cams;
-  // the depth digits (and the camera id) are sorted here, on Gaussians, before duplication
-  const int depth_bits = 32 + (a->n_cams > 1 ? (int)higher_msb((uint32_t)a->n_cams) : 0);
-  if ((rc = launch_sort_pairs(n_slots, gx.gkeys_in, ctx->gauss_keys, gx.gvals_in, ctx->gauss_order, depth_bits,
-                              gx.gsort_temp, st)))
+  // the depth digits are sorted here, on Gaussians, one segment per camera, before duplication
+  if ((rc = launch_seg_setup(a->n_cams, 1, a->P, nullptr, gx.dseg_start, gx.dseg_tile0, st))) return rc;
+  if ((rc = launch_seg_sort_u32(n_slots, a->n_cams, gx.dseg_start, gx.dseg_tile0, gx.gkeys_in, gx.gkeys_b, gx.gkeys_c,
+                                nullptr, ctx->gauss_order, gx.gorder_alt, 32, depth_digit(), false, gx.gsort_temp, st,
+                                nullptr)))
     return rc;
   prof_mark(PF_DEPTH_SORT, st);
   if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st,
                                       ctx->gauss_order, a->P)))
     return rc;
+  if ((rc = launch_seg_setup(a->n_cams, 2, a->P, ctx->point_offsets, ctx->seg_start, gx.seg_tile0, st))) return rc;
   prof_mark(PF_SCAN, st);
 
   // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
@@ -220,19 +274,34 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   GSB_CUDA_CHECK(cudaStreamSynchronize(st));
   if ((int)down[1] != 0) return (int)down[1];
   ctx->num_rendered = (int64_t)down[0];
+  if (ctx->num_rendered >= (1ll << 30)) return GSB_EINVAL;
 
-  char* bin = binning_alloc(user, gsb_binning_bytes(ctx->num_rendered, tiles_total));
+  char* bin = binning_alloc(user, gsb_binning_bytes(ctx->num_rendered, tiles_per_cam, a->n_cams));
   if (!bin) return GSB_ENOMEM;
-  carve_binning(bin, ctx->num_rendered, ctx);
+  BinExtras bx;
+  carve_binning(bin, ctx->num_rendered, ctx->tile_bits, a->n_cams, ctx, &bx);
 
   prof_mark(PF_D2H, st);
   if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
   prof_mark(PF_DUPKEYS, st);
-  if ((rc = launch_sort_pairs_u32(ctx->num_rendered, ctx->point_list_tiles_unsorted, ctx->point_list_tiles,
-                                  ctx->point_list_unsorted, ctx->point_list, ctx->tile_bits, ctx->sort_temp, st)))
-    return rc;
+  const TileSortPlan plan = tile_sort_plan(ctx->tile_bits);
+  const uint32_t* tile_hist = nullptr;
+  if (ctx->num_rendered > 0) {
+    if ((rc = launch_seg_sort_u16(ctx->num_rendered, a->n_cams, ctx->seg_start, gx.seg_tile0, ctx->tile_keys_unsorted,
+                                  ctx->tile_keys_sorted, bx.keys_alt, ctx->point_list_unsorted, ctx->point_list,
+                                  bx.vals_alt, std::max(ctx->tile_bits, 1), plan.log_nb, plan.passes > 1, ctx->sort_temp,
+                                  st, &tile_hist)))
+      return rc;
+  }
   prof_mark(PF_SORT, st);
-  if ((rc = launch_tile_ranges(*ctx, st))) return rc;
+  if (plan.passes == 1 && ctx->num_rendered > 0) {
+    if ((rc = launch_ranges_from_hist(a->n_cams, tiles_per_cam, plan.log_nb, ctx->seg_start, tile_hist, ctx->ranges, st)))
+      return rc;
+  } else {
+    if ((rc = launch_tile_ranges_seg(ctx->num_rendered, a->n_cams, tiles_per_cam, ctx->seg_start, ctx->tile_keys_sorted,
+                                     ctx->ranges, st)))
+      return rc;
+  }
   prof_mark(PF_RANGES, st);
   if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
   prof_mark(PF_RENDER_FWD, st);
@@ -312,11 +381,45 @@ int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const
   return launch_sort_pairs(n, keys_in, keys_out, vals_in, vals_out, end_bit, temp,
                            reinterpret_cast<cudaStream_t>(stream));
 }
-int gsb_sort_pairs_u32(int64_t n, const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
-                       uint32_t* vals_out, int32_t end_bit, void* temp, void* stream) {
-  if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !temp))) return GSB_EINVAL;
-  return launch_sort_pairs_u32(n, keys_in, keys_out, vals_in, vals_out, end_bit, temp,
-                               reinterpret_cast<cudaStream_t>(stream));
+}  // extern "C"
+static int seg_passes(int end_bit, int digit_bits) { return (end_bit + digit_bits - 1) / digit_bits; }
+extern "C" size_t gsb_seg_sort_temp_bytes(int64_t n, int32_t n_seg, int32_t key_bytes, int32_t end_bit, int32_t digit_bits) {
+  if (n < 0 || n_seg <= 0 || digit_bits <= 0 || end_bit <= 0) return 0;
+  const size_t nn = (size_t)(n > 0 ? n : 1);
+  // sort temp + seg_tile0 + alternate key / payload buffers
+  return seg_sort_temp_bytes(n, n_seg, seg_passes(end_bit, digit_bits), digit_bits) + align_up(((size_t)n_seg + 1) * 4, 256) +
+         align_up(nn * (size_t)key_bytes, 256) + align_up(nn * 4, 256);
+}
+template <typename KeyT, typename Fn>
+static int seg_sort_debug(int64_t n, int32_t n_seg, const uint32_t* seg_start, const KeyT* kin, KeyT* kout,
+                          const uint32_t* vin, uint32_t* vout, int32_t end_bit, int32_t digit_bits, void* temp,
+                          cudaStream_t st, Fn launch) {
+  if (n < 0 || n_seg <= 0 || n_seg > 1024 || !seg_start || !temp || end_bit <= 0) return GSB_EINVAL;
+  if (n == 0) return GSB_OK;
+  if (!kin || !vout) return GSB_EINVAL;
+  const int passes = seg_passes(end_bit, digit_bits);
+  char* t = reinterpret_cast<char*>(temp);
+  const size_t s0 = seg_sort_temp_bytes(n, n_seg, passes, digit_bits);
+  uint32_t* tile0 = reinterpret_cast<uint32_t*>(t + s0);
+  KeyT* k_alt = reinterpret_cast<KeyT*>(t + s0 + align_up(((size_t)n_seg + 1) * 4, 256));
+  uint32_t* v_alt = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(k_alt) + align_up((size_t)n * sizeof(KeyT), 256));
+  int rc = launch_seg_setup(n_seg, 0, 0, nullptr, const_cast<uint32_t*>(seg_start), tile0, st);
+  if (rc) return rc;
+  return launch(n, n_seg, seg_start, tile0, kin, kout, k_alt, vin, vout, v_alt, end_bit, digit_bits, kout != nullptr, temp, st,
+                nullptr);
+}
+extern "C" {
+int gsb_seg_sort_u16(int64_t n, int32_t n_seg, const uint32_t* seg_start, const uint16_t* keys_in, uint16_t* keys_out,
+                     const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,
+                     void* stream) {
+  return seg_sort_debug<uint16_t>(n, n_seg, seg_start, keys_in, keys_out, vals_in, vals_out, end_bit, digit_bits, temp,
+                                  reinterpret_cast<cudaStream_t>(stream), launch_seg_sort_u16);
+}
+int gsb_seg_sort_u32(int64_t n, int32_t n_seg, const uint32_t* seg_start, const uint32_t* keys_in, uint32_t* keys_out,
+                     const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,
+                     void* stream) {
+  return seg_sort_debug<uint32_t>(n, n_seg, seg_start, keys_in, keys_out, vals_in, vals_out, end_bit, digit_bits, temp,
+                                  reinterpret_cast<cudaStream_t>(stream), launch_seg_sort_u32);
 }
 
 }  // extern "C"

@@ -138,7 +138,9 @@ int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void
 // duplicateWithKeys (cr/rasterizer_impl.cu:70-111), warp-cooperative: a warp owns 32 consecutive
 // (camera, Gaussian) slots, and its lanes walk the warp's contiguous instance range together, so the
 // key/value stores are coalesced (the reference runs a divergent serial loop per thread).
-// key = (camera*tiles + y*grid.x + x) << 32 | bits(depth);  value = Gaussian index in its camera.
+// The slots arrive camera-major and depth-sorted (gauss_order), so the depth digits of the reference's key
+// are already in order; what is emitted per instance is the camera-local tile id y*grid.x + x (16 bits)
+// and the Gaussian index in its camera.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tile_rect_dup(float px, float py, int rad, int gx, int gy, uint32_t& x0, uint32_t& y0,
                                               uint32_t& x1, uint32_t& y1) {
@@ -156,11 +158,11 @@ __device__ __forceinline__ void tile_rect_dup(float px, float py, int rad, int g
 __global__ void __launch_bounds__(256)
 duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_t* __restrict__ gauss_order,
                            const float2* __restrict__ means2D, const int32_t* __restrict__ radii,
-                           const uint32_t* __restrict__ offsets, uint32_t* __restrict__ tile_keys,
+                           const uint32_t* __restrict__ offsets, uint16_t* __restrict__ tile_keys,
                            uint32_t* __restrict__ vals) {
   const long long slot = (long long)blockIdx.x * 256 + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
-  uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, tile_base = 0, gidx = 0;
+  uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, gidx = 0;
   const long long warp_first = slot - lane;
   if (warp_first >= total) return;
   if (slot < total) {
@@ -169,7 +171,6 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
     gidx = gauss_order[slot];
     const size_t o = (size_t)cam * P + gidx;
     const int rad = radii[o];
-    tile_base = cam * (uint32_t)(gx * gy);
     start = end;
     if (rad > 0) {
       const float2 xy = means2D[o];
@@ -199,12 +200,11 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
     const uint32_t ox = __shfl_sync(0xffffffffu, x0, j);
     const uint32_t oy = __shfl_sync(0xffffffffu, y0, j);
     const uint32_t ow = __shfl_sync(0xffffffffu, w, j);
-    const uint32_t ot = __shfl_sync(0xffffffffu, tile_base, j);
     const uint32_t og = __shfl_sync(0xffffffffu, gidx, j);
     if (i < warp_end) {
       const uint32_t k = i - s;
       const uint32_t ry = k / ow, rx = k - ry * ow;
-      tile_keys[i] = ot + (oy + ry) * (uint32_t)gx + (ox + rx);
+      tile_keys[i] = (uint16_t)((oy + ry) * (uint32_t)gx + (ox + rx));
       vals[i] = og;
     }
   }
@@ -215,13 +215,14 @@ int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st) {
   if (total <= 0 || c.num_rendered <= 0) return GSB_OK;
   duplicate_with_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
       total, c.P, c.tiles_x, c.tiles_y, c.gauss_order, reinterpret_cast<const float2*>(c.means2D), c.radii,
-      c.point_offsets, c.point_list_tiles_unsorted, c.point_list_unsorted);
+      c.point_offsets, c.tile_keys_unsorted, c.point_list_unsorted);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------
-// Onesweep LSD radix sort, 8-bit digits, 64-bit keys + 32-bit payloads, stable.
+// General-purpose onesweep LSD radix sort, 8-bit digits, 64-bit keys + 32-bit payloads, stable
+// (gsb_sort_pairs; the product path uses the segmented wide-digit sort of segsort.cu).
 //   kernel 1: all per-pass digit histograms in one read of the keys;
 //   kernel 2 (per pass): each tile ranks its keys (warp match), publishes its digit counts and
 //     resolves its global offsets with a decoupled look-back over earlier tiles, then scatters
@@ -481,52 +482,4 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
   return sort_pairs_impl<unsigned long long>(n, reinterpret_cast<const unsigned long long*>(kin),
                                              reinterpret_cast<unsigned long long*>(kout), vin, vout, end_bit, temp, st);
 }
-int launch_sort_pairs_u32(int64_t n, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
-                          int end_bit, void* temp, cudaStream_t st) {
-  return sort_pairs_impl<uint32_t>(n, kin, kout, vin, vout, end_bit, temp, st);
-}
-
-// ------------------------------------------------------------------------------------------------
-// identifyTileRanges (cr/rasterizer_impl.cu:116-138); ranges pre-zeroed by the caller (:311).
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(long long R, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
-  // 4 consecutive sorted instances per thread (one 16-byte load + the predecessor)
-  const long long i0 = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
-  if (i0 >= R) return;
-  uint32_t k[4];
-  if (i0 + 4 <= R) {
-    const uint4 v = *reinterpret_cast<const uint4*>(keys + i0);
-    k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
-  } else {
-#pragma unroll
-    for (int j = 0; j < 4; j++) k[j] = (i0 + j < R) ? keys[i0 + j] : 0u;
-  }
-  uint32_t prev = (i0 > 0) ? keys[i0 - 1] : 0u;
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const long long i = i0 + j;
-    if (i >= R) break;
-    const uint32_t cur = k[j];
-    if (i == 0) {
-      ranges[cur].x = 0;
-    } else if (cur != prev) {
-      ranges[prev].y = (uint32_t)i;
-      ranges[cur].x = (uint32_t)i;
-    }
-    if (i == R - 1) ranges[cur].y = (uint32_t)R;
-    prev = cur;
-  }
-}
-
-int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st) {
-  const size_t tiles = (size_t)c.n_cams * c.tiles_x * c.tiles_y;
-  GSB_CUDA_CHECK(cudaMemsetAsync(c.ranges, 0, tiles * 8, st));
-  if (c.num_rendered <= 0) return GSB_OK;
-  tile_ranges_kernel<<<(unsigned)((c.num_rendered + 1023) / 1024), 256, 0, st>>>(
-      c.num_rendered, c.point_list_tiles, reinterpret_cast<uint2*>(c.ranges));
-  GSB_LAUNCH_CHECK();
-  return GSB_OK;
-}
-
 }  // namespace gsb

@@ -51,8 +51,7 @@ struct CamParams {  // per-camera scalars that live in a small device table
 };
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                      int32_t* radii_out, uint64_t* gauss_keys_in, uint32_t* gauss_vals_in, int* err_flag_dev,
-                      cudaStream_t st);
+                      int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
@@ -65,9 +64,23 @@ int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st);
 size_t sort_temp_bytes(int64_t n);
 int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
                       int end_bit, void* temp, cudaStream_t st);
-int launch_sort_pairs_u32(int64_t n, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
-                          int end_bit, void* temp, cudaStream_t st);
-int launch_tile_ranges(const gsb_raster_ctx& c, cudaStream_t st);
+
+// segsort.cu: segmented wide-digit onesweep (the product path's sorts) and tile ranges
+size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int passes, int log_nb);
+int launch_seg_setup(int n_seg, int mode, int len, const uint32_t* offsets, uint32_t* seg_start, uint32_t* seg_tile0,
+                     cudaStream_t st);
+int launch_seg_sort_u16(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
+                        const uint16_t* kin, uint16_t* k_out, uint16_t* k_alt, const uint32_t* vin, uint32_t* v_out,
+                        uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,
+                        const uint32_t** hist_out);
+int launch_seg_sort_u32(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
+                        const uint32_t* kin, uint32_t* k_out, uint32_t* k_alt, const uint32_t* vin, uint32_t* v_out,
+                        uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,
+                        const uint32_t** hist_out);
+int launch_ranges_from_hist(int n_cams, int tiles_per_cam, int log_nb, const uint32_t* seg_start, const uint32_t* hist,
+                            uint32_t* ranges, cudaStream_t st);
+int launch_tile_ranges_seg(int64_t R, int n_cams, int tiles_per_cam, const uint32_t* seg_start, const uint16_t* keys,
+                           uint32_t* ranges, cudaStream_t st);
 
 int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,
                       cudaStream_t st);

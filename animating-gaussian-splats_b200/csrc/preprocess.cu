@@ -106,8 +106,8 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
                       const float* __restrict__ projmatrix, const CamParams* __restrict__ cams,
                       float* __restrict__ depths, int32_t* __restrict__ radii_state, int32_t* __restrict__ radii_out,
                       float2* __restrict__ means2D, float* __restrict__ cov3D, float4* __restrict__ conic_opacity,
-                      uint32_t* __restrict__ tiles_touched, unsigned long long* __restrict__ gauss_keys,
-                      uint32_t* __restrict__ gauss_vals, int* __restrict__ err_flag) {
+                      uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ gauss_keys,
+                      int* __restrict__ err_flag) {
   __shared__ __align__(16) float s_mean[768];
   __shared__ __align__(16) float s_scale[768];
   __shared__ float s_V[16], s_Pm[16];
@@ -220,23 +220,21 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
     tt_w = area;
     depth_key = __float_as_uint(tz);
   } while (false);
-  gauss_keys[o] = ((unsigned long long)(uint32_t)cam << 32) | depth_key;
-  gauss_vals[o] = (uint32_t)idx;
+  gauss_keys[o] = depth_key;   // the camera's segment of the depth sort; the payload is the index itself
   radii_state[o] = rad_w;
   if (radii_out) radii_out[o] = rad_w;
   tiles_touched[o] = tt_w;
 }
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                      int32_t* radii_out, uint64_t* gauss_keys_in, uint32_t* gauss_vals_in, int* err_flag_dev,
-                      cudaStream_t st) {
+                      int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st) {
   if (a.P <= 0) return GSB_OK;
   dim3 grid((a.P + 255) / 256, a.n_cams);
   preprocess_fwd_kernel<<<grid, 256, 0, st>>>(
       a.P, a.width, a.height, c.tiles_x, c.tiles_y, a.scale_modifier, a.prefiltered, a.means3D, a.scales,
       a.rotations, a.opacities, a.cov3D_precomp, a.viewmatrix, a.projmatrix, cams_dev, c.depths, c.radii,
       radii_out, reinterpret_cast<float2*>(c.means2D), c.cov3D, reinterpret_cast<float4*>(c.conic_opacity),
-      c.tiles_touched, reinterpret_cast<unsigned long long*>(gauss_keys_in), gauss_vals_in, err_flag_dev);
+      c.tiles_touched, gauss_keys_in, err_flag_dev);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -10,7 +10,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libgsb200.so")
+LIB_PATH = os.environ.get("GSB200_LIB") or os.path.join(os.path.dirname(_HERE), "libgsb200.so")
 
 GSB_OK, GSB_EINVAL, GSB_ECUDA, GSB_ENOMEM, GSB_EPREFILTER = 0, -1, -2, -3, -4
 _ERR = {GSB_EINVAL: "invalid argument", GSB_ECUDA: "CUDA error", GSB_ENOMEM: "buffer allocation failed",
@@ -36,11 +36,11 @@ class RasterCtx(C.Structure):
         ("P", C.c_int32), ("n_cams", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
         ("tiles_x", C.c_int32), ("tiles_y", C.c_int32), ("sort_bits", C.c_int32), ("tile_bits", C.c_int32),
         ("depths", C.c_void_p), ("radii", C.c_void_p), ("means2D", C.c_void_p), ("cov3D", C.c_void_p),
-        ("conic_opacity", C.c_void_p), ("tiles_touched", C.c_void_p), ("gauss_keys", C.c_void_p),
-        ("gauss_order", C.c_void_p), ("point_offsets", C.c_void_p),
+        ("conic_opacity", C.c_void_p), ("tiles_touched", C.c_void_p),
+        ("gauss_order", C.c_void_p), ("point_offsets", C.c_void_p), ("seg_start", C.c_void_p),
         ("final_T", C.c_void_p), ("n_contrib", C.c_void_p), ("ranges", C.c_void_p),
-        ("point_list", C.c_void_p), ("point_list_tiles", C.c_void_p), ("point_list_unsorted", C.c_void_p),
-        ("point_list_tiles_unsorted", C.c_void_p), ("sort_temp", C.c_void_p),
+        ("point_list", C.c_void_p), ("point_list_unsorted", C.c_void_p), ("tile_keys_unsorted", C.c_void_p),
+        ("tile_keys_sorted", C.c_void_p), ("sort_temp", C.c_void_p),
     ]
 
 
@@ -50,7 +50,7 @@ SYMBOLS = {
     "gsb_last_error": (C.c_char_p, []),
     "gsb_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
-    "gsb_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32]),
+    "gsb_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
     "gsb_higher_msb": (C.c_uint32, [C.c_uint32]),
     "gsb_raster_forward": (C.c_int, [C.POINTER(RasterArgs), ALLOC_FN, ALLOC_FN, ALLOC_FN, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.POINTER(RasterCtx), C.c_void_p]),
@@ -71,8 +71,9 @@ SYMBOLS = {
     "gsb_sort_temp_bytes": (C.c_size_t, [C.c_int64]),
     "gsb_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                  C.c_void_p]),
-    "gsb_sort_pairs_u32": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
-                                     C.c_void_p]),
+    "gsb_seg_sort_temp_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "gsb_seg_sort_u16": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "gsb_seg_sort_u32": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),
     "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }

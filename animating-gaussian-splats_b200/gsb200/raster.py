@@ -46,22 +46,32 @@ class RasterState:
             "tiles_touched": self._view(c.tiles_touched, self.geom, torch.int32, (n, P)),
             "point_offsets": self._view(c.point_offsets, self.geom, torch.int32, (n, P)),
             "gauss_order": self._view(c.gauss_order, self.geom, torch.int32, (n, P)),
-            "gauss_keys": self._view(c.gauss_keys, self.geom, torch.int64, (n, P)),
+            "seg_start": self._view(c.seg_start, self.geom, torch.int32, (n + 1,)),
             "final_T": self._view(c.final_T, self.img, torch.float32, (n, c.height, c.width)),
             "n_contrib": self._view(c.n_contrib, self.img, torch.int32, (n, c.height, c.width)),
             "ranges": self._view(c.ranges, self.img, torch.int32, (tiles, 2)),
         }
         if R > 0:
-            out.update({
-                "point_list": self._view(c.point_list, self.binning, torch.int32, (R,)),
-                "point_list_tiles": self._view(c.point_list_tiles, self.binning, torch.int32, (R,)),
-            })
+            out["point_list"] = self._view(c.point_list, self.binning, torch.int32, (R,))
+            out["point_list_unsorted"] = self._view(c.point_list_unsorted, self.binning, torch.int32, (R,))
+            out["tile_keys_unsorted"] = self._view(c.tile_keys_unsorted, self.binning, torch.int16, (R,))
+            # Sorted tile ids.  With <= 1024 tiles per camera they are never materialised (the sort is one pass
+            # and the ranges come from its histogram), so they are reassembled from the ranges: instance i
+            # belongs to the tile whose [start, end) holds i.
+            rg = out["ranges"].long()
+            out["point_list_tiles"] = torch.repeat_interleave(torch.arange(tiles, device=rg.device), rg[:, 1] - rg[:, 0])
+            if c.tile_keys_sorted:
+                tiles_per_cam = c.tiles_x * c.tiles_y
+                local = self._view(c.tile_keys_sorted, self.binning, torch.int16, (R,)).long() & 0xFFFF
+                seg = out["seg_start"].long()
+                cam_of = torch.repeat_interleave(torch.arange(n, device=rg.device), seg[1:] - seg[:-1])
+                out["point_list_tiles_stored"] = cam_of * tiles_per_cam + local
             # the reference's sorted 64-bit keys, reassembled: (tile << 32) | bits(depth of the Gaussian)
             pl = out["point_list"].long()
             tiles_per_cam = c.tiles_x * c.tiles_y
-            cam = out["point_list_tiles"].long() // tiles_per_cam
+            cam = out["point_list_tiles"] // tiles_per_cam
             dbits = out["depths"].view(torch.int32).view(-1)[cam * P + pl].long() & 0xFFFFFFFF
-            out["point_list_keys"] = (out["point_list_tiles"].long() << 32) | dbits
+            out["point_list_keys"] = (out["point_list_tiles"] << 32) | dbits
         return out
 
 

@@ -280,21 +280,24 @@ def run_ours(args):
                 "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": tr("render_bwd_kernel"),
                 "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
                 "ms": bwd_ms, "pairs": walked}
-    # the HBM-bound kernel with the most bytes: the onesweep sort (152 B / instance at 6 passes)
-    passes = (st.ctx.tile_bits + 7) // 8
-    gpasses = (32 + (int(n_my).bit_length() if n_my > 1 else 0) + 7) // 8
-    sort_bytes = R * (4 + 16 * passes)     # 32-bit tile keys + 32-bit payloads
+    # the HBM-bound kernel with the most bytes: the instance sort (segmented onesweep on 16-bit camera-local
+    # tile ids).  Algorithmic bytes per pass: read key (2) + payload (4), write payload (4) (+ key (2) unless it is
+    # the last pass of a one-pass sort); the histogram reads the keys once more (2).  DESIGN.md section 5.
+    tile_digit = int(os.environ.get("GSB_TILE_DIGIT", "0")) or (5 if st.ctx.tile_bits <= 5 else 8 if st.ctx.tile_bits <= 8 else 10 if st.ctx.tile_bits <= 10 else 8)
+    passes = (max(st.ctx.tile_bits, 1) + tile_digit - 1) // tile_digit
+    depth_digit = 11 if os.environ.get("GSB_DEPTH_DIGIT") == "11" else 8
+    gpasses = (32 + depth_digit - 1) // depth_digit
+    sort_bytes = R * (2 + 10 * passes + (2 * passes if passes > 1 else 0))
     sort_ms = stages["sort"]
-    roofline_hbm = {"kernel": "rs_histogram_kernel<u32> + rs_onesweep_kernel<u32> x%d (instance sort on tile ids)" % passes, "bound": "hbm",
+    sort_name = f"seg_hist_kernel<u16> + seg_onesweep_kernel<u16,{tile_digit}> x{passes} (instance sort on camera-local tile ids)"
+    roofline_hbm = {"kernel": sort_name, "bound": "hbm",
                     "achieved": sort_bytes / (sort_ms * 1e-3) / 1e9 if sort_ms > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "ms": sort_ms, "instances": R,
-                    "traffic": (None if tr("rs_onesweep_kernel<unsigned int>") is None else
-                                passes * tr("rs_onesweep_kernel<unsigned int>") + tr("rs_histogram_kernel<unsigned int>")),
-                    "algorithmic_bytes": sort_bytes}
+                    "traffic": tr("seg_sort_instances"), "algorithmic_bytes": sort_bytes}
     roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
-    # preprocess, depth sort (hist + passes), scan, key emission, instance sort (hist + passes), ranges,
-    # blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
-    launches = 1 + (1 + gpasses) + 1 + 1 + (1 + passes) + 1 + 1 + 3 + 1 + 1 + 1
+    # preprocess, depth sort (setup + hist + passes), scan, setup, key emission, instance sort (hist + passes),
+    # ranges, blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
+    launches = 1 + (2 + gpasses) + 1 + 1 + 1 + (1 + passes) + 1 + 1 + 3 + 1 + 1 + 1
 
     out = {
         "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",

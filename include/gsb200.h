@@ -61,28 +61,32 @@ typedef struct gsb_raster_args {
  * fromChunk (cr/rasterizer_impl.cu:155-194, 373-375).  POD; pointers point into the three buffers.
  *
  * Binning layout.  The reference sorts R instances on 64-bit (tile << 32 | depth) keys, 6 radix passes
- * over 12 B records.  The low 32 key bits are the same for all instances of a Gaussian, so the LSD
- * passes over them are done BEFORE duplication, on the n_cams*P Gaussians (camera << 32 | depth keys),
- * instances are emitted in that order, and only the tile-id bits are sorted at instance granularity
- * (32-bit keys, 2 passes over 8 B records).  A stable LSD sort is digit-separable, so point_list and
- * ranges are bit-identical to the reference's. */
+ * over 12 B records.  A stable LSD sort is digit-separable and the low 32 key bits are the same for all
+ * instances of a Gaussian, so the depth digits are sorted BEFORE duplication, on the n_cams*P Gaussians
+ * (one segment per camera, 32-bit keys), instances are emitted in that order with their camera-local
+ * tile id as a 16-bit key, and one segmented pass with a 10-bit digit (two 8-bit passes above 1024
+ * tiles per camera) puts them in tile order.  point_list and ranges are bit-identical to the
+ * reference's; in the one-pass case the sorted tile ids are never materialised (the per-camera digit
+ * histogram is the per-tile count, so ranges are its exclusive scan). */
 typedef struct gsb_raster_ctx {
   int64_t num_rendered;      /* R: total (Gaussian, tile) instances over all cameras */
   int32_t P, n_cams, width, height, tiles_x, tiles_y;
   int32_t sort_bits;         /* 32 + getHigherMsb(tiles): what the reference passes to SortPairs */
-  int32_t tile_bits;         /* bits sorted at instance granularity */
+  int32_t tile_bits;         /* getHigherMsb(tiles per camera): bits sorted at instance granularity */
   /* geometry state, [n_cams][P] each (cr/rasterizer_impl.h:31-45) */
   float* depths; int32_t* radii; float* means2D; float* cov3D; float* conic_opacity;
   uint32_t* tiles_touched;
-  uint64_t* gauss_keys;      /* sorted (camera << 32 | bits(depth)); culled Gaussians carry depth bits 0xFFFFFFFF */
-  uint32_t* gauss_order;     /* Gaussian index per sorted slot: camera-major, depth-ascending, stable */
+  uint32_t* gauss_order;     /* Gaussian index per sorted slot: camera-major, depth-ascending, stable;
+                                culled Gaussians (depth key 0xFFFFFFFF) sort behind every visible one */
   uint32_t* point_offsets;   /* inclusive scan of tiles_touched taken in gauss_order */
+  uint32_t* seg_start;       /* [n_cams + 1]: camera c owns point_list[seg_start[c] .. seg_start[c+1]) */
   /* image state (cr/rasterizer_impl.h:47-54) */
   float* final_T; uint32_t* n_contrib; uint32_t* ranges; /* ranges: [n_cams*tiles][2] */
   /* binning state (cr/rasterizer_impl.h:56-66) */
   uint32_t* point_list;               /* sorted Gaussian indices == the reference's point_list */
-  uint32_t* point_list_tiles;         /* sorted tile ids == high words of the reference's point_list_keys */
-  uint32_t* point_list_unsorted; uint32_t* point_list_tiles_unsorted;
+  uint32_t* point_list_unsorted;      /* emission order (camera-major, depth order, row-major rect) */
+  uint16_t* tile_keys_unsorted;       /* camera-local tile id per emitted instance */
+  uint16_t* tile_keys_sorted;         /* sorted camera-local tile ids; NULL when one pass suffices */
   void* sort_temp;
 } gsb_raster_ctx;
 
@@ -94,7 +98,7 @@ const char* gsb_last_error(void);            /* text of the last CUDA error seen
  * (cr/rasterizer_impl.h:68-73). */
 size_t gsb_geom_bytes(int32_t P, int32_t n_cams);
 size_t gsb_image_bytes(int32_t width, int32_t height, int32_t n_cams);
-size_t gsb_binning_bytes(int64_t num_rendered, int32_t n_tiles_total);
+size_t gsb_binning_bytes(int64_t num_rendered, int32_t tiles_per_cam, int32_t n_cams);
 
 /* getHigherMsb (cr/rasterizer_impl.cu:35-50). */
 uint32_t gsb_higher_msb(uint32_t n);
@@ -174,8 +178,19 @@ int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* s
 size_t gsb_sort_temp_bytes(int64_t n);
 int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
                    uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
-int gsb_sort_pairs_u32(int64_t n, const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in,
-                       uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
+
+/* The segmented wide-digit onesweep of the product path (csrc/segsort.cu), exposed for the stability /
+ * edge-size tests: n elements in n_seg segments, seg_start DEVICE uint32 [n_seg + 1]; each segment is
+ * sorted stably and independently on key bits [0, end_bit) with digits of `digit_bits` bits (u16 keys:
+ * 5, 8 or 10; u32 keys: 8 or 11).  vals_in NULL: the payload is the element's index in its segment.
+ * keys_out may be NULL when only one pass is needed (end_bit <= digit_bits). */
+size_t gsb_seg_sort_temp_bytes(int64_t n, int32_t n_seg, int32_t key_bytes, int32_t end_bit, int32_t digit_bits);
+int gsb_seg_sort_u16(int64_t n, int32_t n_seg, const uint32_t* seg_start, const uint16_t* keys_in, uint16_t* keys_out,
+                     const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,
+                     void* stream);
+int gsb_seg_sort_u32(int64_t n, int32_t n_seg, const uint32_t* seg_start, const uint32_t* keys_in, uint32_t* keys_out,
+                     const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,
+                     void* stream);
 
 /* Per-stage CUDA-event timing of the last forward/backward on this thread's library instance (bench
  * instrumentation; off by default).  Stage order: fwd_begin, preprocess, depth_sort, scan, d2h_sync, duplicate_keys,

@@ -42,17 +42,62 @@ def test_sort_pairs_u64_stable(n, end_bit):
     assert torch.equal(keys, keys_copy)   # the input is never written
 
 
-@pytest.mark.parametrize("n,end_bit", [(5, 10), (8191, 15), (2_000_000, 13)])
-def test_sort_pairs_u32_stable(n, end_bit):
+def _seg_sort_case(key_bits, n, seg_lens, end_bit, digit_bits, iota):
+    """Segmented wide-digit onesweep (csrc/segsort.cu) against a stable torch sort per segment."""
     L, lib = _lib()
-    g = torch.Generator(device="cuda").manual_seed(n)
-    keys = torch.randint(0, 1 << end_bit, (n,), dtype=torch.int32, device="cuda", generator=g)
-    vals = torch.arange(n, dtype=torch.int32, device="cuda")
-    ko, vo = torch.empty_like(keys), torch.empty_like(vals)
-    temp = torch.empty(lib.gsb_sort_temp_bytes(n), dtype=torch.uint8, device="cuda")
-    L.check(lib.gsb_sort_pairs_u32(n, L.ptr(keys), L.ptr(ko), L.ptr(vals), L.ptr(vo), end_bit, L.ptr(temp), L.stream_ptr()), "sort32")
-    order = torch.sort(keys.long(), stable=True).indices
-    assert torch.equal(vo.long(), order) and torch.equal(ko, keys[order])
+    g = torch.Generator(device="cuda").manual_seed(n + end_bit + digit_bits)
+    kdt = torch.int16 if key_bits == 16 else torch.int32
+    keys = torch.randint(0, 1 << end_bit, (max(n, 1),), dtype=torch.int64, device="cuda", generator=g)[:n]
+    if end_bit > 12:   # few distinct low bits: ties exercise stability across passes
+        keys = (keys >> 6 << 6) | torch.randint(0, 3, (n,), dtype=torch.int64, device="cuda", generator=g)
+    kin = keys
+    kin_t = keys.to(kdt)   # wraps: the bit pattern is what the kernels see
+    vals = None if iota else torch.randint(0, 1 << 30, (n,), dtype=torch.int32, device="cuda", generator=g)
+    seg = torch.tensor([0] + list(torch.tensor(seg_lens).cumsum(0)), dtype=torch.int32, device="cuda")
+    assert int(seg[-1]) == n
+    n_seg = len(seg_lens)
+    passes = (end_bit + digit_bits - 1) // digit_bits
+    ko = torch.empty_like(kin_t) if passes > 1 or not iota else None
+    vo = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    temp = torch.empty(lib.gsb_seg_sort_temp_bytes(n, n_seg, key_bits // 8, end_bit, digit_bits), dtype=torch.uint8, device="cuda")
+    fn = lib.gsb_seg_sort_u16 if key_bits == 16 else lib.gsb_seg_sort_u32
+    L.check(fn(n, n_seg, L.ptr(seg), L.ptr(kin_t), L.ptr(ko), L.ptr(vals), L.ptr(vo), end_bit, digit_bits, L.ptr(temp),
+               L.stream_ptr()), "seg_sort")
+    torch.cuda.synchronize()
+    segc = seg.cpu().tolist()
+    for s in range(n_seg):
+        a, b = segc[s], segc[s + 1]
+        if a == b:
+            continue
+        order = torch.sort(kin[a:b], stable=True).indices
+        want_v = order.int() if iota else vals[a:b][order]
+        assert torch.equal(vo[a:b], want_v), (s, a, b)
+        if ko is not None:
+            assert torch.equal(ko[a:b], kin_t[a:b][order]), (s, a, b)
+
+
+@pytest.mark.parametrize("n_seg,digit_bits,end_bit", [(1, 10, 10), (3, 10, 10), (27, 10, 10), (5, 8, 8), (2, 8, 13),
+                                                       (4, 5, 10), (3, 5, 5), (1, 10, 7), (6, 8, 16)])
+def test_seg_sort_u16(n_seg, digit_bits, end_bit):
+    gen = torch.Generator().manual_seed(n_seg * 100 + end_bit)
+    lens = torch.randint(0, 20000, (n_seg,), generator=gen).tolist()
+    if n_seg >= 3:
+        lens[1] = 0            # an empty segment
+        lens[2] = 4096         # exactly one sort tile
+    lens[-1] = max(lens[-1], 1)
+    _seg_sort_case(16, sum(lens), lens, end_bit, digit_bits, iota=False)
+
+
+@pytest.mark.parametrize("n_seg,P,digit_bits,iota", [(1, 1, 11, True), (1, 100_003, 11, True), (4, 4097, 11, True),
+                                                      (27, 30_000, 11, True), (3, 12_345, 8, True), (2, 50_000, 8, False)])
+def test_seg_sort_u32_depth_keys(n_seg, P, digit_bits, iota):
+    _seg_sort_case(32, n_seg * P, [P] * n_seg, 32, digit_bits, iota)
+
+
+def test_seg_sort_large_one_pass():
+    """C2-like instance sort shape: a few long segments, 10-bit digits, one pass, payload only."""
+    lens = [1_500_000, 0, 2_300_001, 999_999]
+    _seg_sort_case(16, sum(lens), lens, 10, 10, iota=False)
 
 
 def test_tile_range_coverage_property():

@@ -25,7 +25,8 @@ def test_library_exports_every_declared_symbol():
     # pure host helpers are callable without a GPU
     assert [lib.gsb_higher_msb(n) for n in (256, 920, 8160)] == [9, 10, 13]
     assert lib.gsb_geom_bytes(1000, 2) > 2 * 1000 * 60
-    assert lib.gsb_binning_bytes(10_000, 920) >= 10_000 * 16
+    assert lib.gsb_binning_bytes(10_000, 920, 1) >= 10_000 * 10
+    assert lib.gsb_binning_bytes(10_000, 8160, 1) >= 10_000 * 18
 
 
 def test_struct_layout_matches_header(tmp_path):
