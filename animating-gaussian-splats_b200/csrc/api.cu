@@ -118,8 +118,8 @@ struct GeomLayout {
     uint32_t* gkc = k.take<uint32_t>(n);
     uint32_t* goa = k.take<uint32_t>(n);
     uint32_t* ds = k.take<uint32_t>((size_t)n_cams + 1);
-    uint32_t* dt = k.take<uint32_t>((size_t)n_cams + 1);
-    uint32_t* st0 = k.take<uint32_t>((size_t)n_cams + 1);
+    uint32_t* dt = k.take<uint32_t>(2 * ((size_t)n_cams + 1));   // tile prefix | chunk prefix
+    uint32_t* st0 = k.take<uint32_t>(2 * ((size_t)n_cams + 1));
     const int dd = depth_digit();
     void* gt = k.take<char>(seg_sort_temp_bytes((int64_t)n, n_cams, (32 + dd - 1) / dd, dd));
     if (c) {
@@ -387,7 +387,7 @@ extern "C" size_t gsb_seg_sort_temp_bytes(int64_t n, int32_t n_seg, int32_t key_
   if (n < 0 || n_seg <= 0 || digit_bits <= 0 || end_bit <= 0) return 0;
   const size_t nn = (size_t)(n > 0 ? n : 1);
   // sort temp + seg_tile0 + alternate key / payload buffers
-  return seg_sort_temp_bytes(n, n_seg, seg_passes(end_bit, digit_bits), digit_bits) + align_up(((size_t)n_seg + 1) * 4, 256) +
+  return seg_sort_temp_bytes(n, n_seg, seg_passes(end_bit, digit_bits), digit_bits) + align_up(((size_t)n_seg + 1) * 8, 256) +
          align_up(nn * (size_t)key_bytes, 256) + align_up(nn * 4, 256);
 }
 template <typename KeyT, typename Fn>
@@ -401,7 +401,7 @@ static int seg_sort_debug(int64_t n, int32_t n_seg, const uint32_t* seg_start, c
   char* t = reinterpret_cast<char*>(temp);
   const size_t s0 = seg_sort_temp_bytes(n, n_seg, passes, digit_bits);
   uint32_t* tile0 = reinterpret_cast<uint32_t*>(t + s0);
-  KeyT* k_alt = reinterpret_cast<KeyT*>(t + s0 + align_up(((size_t)n_seg + 1) * 4, 256));
+  KeyT* k_alt = reinterpret_cast<KeyT*>(t + s0 + align_up(((size_t)n_seg + 1) * 8, 256));
   uint32_t* v_alt = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(k_alt) + align_up((size_t)n * sizeof(KeyT), 256));
   int rc = launch_seg_setup(n_seg, 0, 0, nullptr, const_cast<uint32_t*>(seg_start), tile0, st);
   if (rc) return rc;

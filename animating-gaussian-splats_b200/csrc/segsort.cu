@@ -12,11 +12,16 @@
 //     (identifyTileRanges, cr/rasterizer_impl.cu:116-138) are its exclusive scan.
 // Results are integer and bit-identical to the reference's point_list / ranges by construction.
 //
-// Kernel structure (per pass): a tile of THREADS x ITEMS keys ranks its keys per warp (ballot-based digit
-// matching, rank order = memory order => stable), publishes its digit counts EARLY (before ranking),
-// resolves its global offsets by decoupled look-back over the earlier tiles of its segment (tile ids
-// come from an atomic ticket, so a tile only waits on tiles that already started), scatters into
-// tile-sorted order in shared memory and writes out in runs.
+// Pass structure.  A first version was a onesweep (chained scan with decoupled look-back).  With ~450
+// sort tiles resident on 148 SMs and a 1024-digit status row per tile, the serial look-back (one L2 round
+// trip per predecessor, ~17 predecessors on average) was a third of the kernel's instructions and most of
+// its stall samples.  A pass is therefore three kernels with no inter-block waiting:
+//   K1 seg_tile_hist   per sort tile (4096 keys) the digit counts (u16 row), per chunk of 16 tiles their sum;
+//   K2 seg_chunk_scan  per segment: exclusive scan of the chunk sums over the chunks and of the digit totals
+//                      over the digits (+ the segment's start) -> chunk_base, digit_base, totals;
+//   K3 seg_scatter     per sort tile: rank the keys per warp; global slot of digit d = digit_base[d] +
+//                      chunk_base[chunk][d] + the counts of the <= 15 earlier tiles of the chunk (independent
+//                      loads, one latency) + rank; scatter through shared memory, write out in runs.
 #include <algorithm>
 #include <cstdlib>
 #include <type_traits>
@@ -24,109 +29,186 @@
 
 namespace gsb {
 
-constexpr uint32_t SS_FLAG_AGG = 1u << 30, SS_FLAG_INC = 2u << 30, SS_VAL_MASK = (1u << 30) - 1;
 constexpr int SS_THREADS = 256;
 constexpr int SS_ITEMS = 16;
-constexpr int SS_TILE = SS_THREADS * SS_ITEMS;
+constexpr int SS_TILE = SS_THREADS * SS_ITEMS;   // keys per sort tile
+constexpr int SS_CHUNK = 16;                     // sort tiles per chunk
 constexpr int SS_MAX_PASSES = 4;
-constexpr size_t SS_HEADER = 256;  // tickets
-
-__device__ __forceinline__ uint32_t ss_ld_relaxed(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ uint4 ss_ld_relaxed_v4(const uint32_t* p) {
-  uint4 v;
-  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void ss_st_relaxed(uint32_t* p, uint32_t v) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 // ------------------------------------------------------------------------------------------------
 // Segment tables.  seg_start[n_seg + 1]: element range of each segment; seg_tile0[n_seg + 1]: exclusive
-// prefix of the segments' sort-tile counts.  mode 0: seg_start is given; 1: fixed-length segments;
-// 2: from the inclusive scan of tiles_touched taken camera-major (segment c ends at offsets[(c+1)*len-1]).
+// prefix of the segments' sort-tile counts, followed by seg_chunk0[n_seg + 1], the same for chunks.
+// mode 0: seg_start is given; 1: fixed-length segments; 2: from the inclusive scan of tiles_touched
+// taken camera-major (segment c ends at offsets[(c+1)*len-1]).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-seg_setup_kernel(int n_seg, int mode, int len, const uint32_t* __restrict__ offsets, int tile,
-                 uint32_t* __restrict__ seg_start, uint32_t* __restrict__ seg_tile0) {
+seg_setup_kernel(int n_seg, int mode, int len, const uint32_t* __restrict__ offsets, uint32_t* __restrict__ seg_start,
+                 uint32_t* __restrict__ seg_tile0) {
   __shared__ uint32_t s_tiles[1024];
+  uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
   for (int s = threadIdx.x; s <= n_seg; s += blockDim.x) {
     if (mode == 1) seg_start[s] = (uint32_t)s * (uint32_t)len;
     else if (mode == 2) seg_start[s] = (s == 0) ? 0u : offsets[(size_t)s * len - 1];
   }
   __syncthreads();
   for (int s = threadIdx.x; s < n_seg; s += blockDim.x)
-    s_tiles[s] = (seg_start[s + 1] - seg_start[s] + (uint32_t)tile - 1u) / (uint32_t)tile;
+    s_tiles[s] = (seg_start[s + 1] - seg_start[s] + (uint32_t)SS_TILE - 1u) / (uint32_t)SS_TILE;
   __syncthreads();
   if (threadIdx.x == 0) {
-    uint32_t run = 0;
-    for (int s = 0; s < n_seg; s++) { seg_tile0[s] = run; run += s_tiles[s]; }
-    seg_tile0[n_seg] = run;
+    uint32_t run = 0, crun = 0;
+    for (int s = 0; s < n_seg; s++) {
+      seg_tile0[s] = run; seg_chunk0[s] = crun;
+      run += s_tiles[s]; crun += (s_tiles[s] + SS_CHUNK - 1) / SS_CHUNK;
+    }
+    seg_tile0[n_seg] = run; seg_chunk0[n_seg] = crun;
+  }
+}
+
+// index of the segment that holds unit t (sort tile or chunk), given the exclusive prefix of the segments'
+// unit counts: #{ e in [1, n_seg] : prefix[e] <= t }; n_seg when t is past the last unit.  Whole warp.
+__device__ __forceinline__ int ss_find_segment(const uint32_t* __restrict__ prefix, int n_seg, uint32_t t, unsigned lane) {
+  int seg = 0;
+  for (int e0 = 1; e0 <= n_seg; e0 += 32) {
+    const int e = e0 + (int)lane;
+    const bool le = (e <= n_seg) && (prefix[e] <= t);
+    seg += __popc(__ballot_sync(0xffffffffu, le));
+  }
+  return seg;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: digit counts per sort tile (u16 rows) and per chunk (u32 rows).  One block per chunk.
+// ------------------------------------------------------------------------------------------------
+template <typename KeyT, int LOG_NB>
+__global__ void __launch_bounds__(SS_THREADS)
+seg_tile_hist_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
+                     const KeyT* __restrict__ keys, int shift, uint32_t dmask, uint16_t* __restrict__ tile_cnt,
+                     uint32_t* __restrict__ chunk_tot) {
+  constexpr int NB = 1 << LOG_NB;
+  constexpr int PER = (NB + SS_THREADS - 1) / SS_THREADS;
+  __shared__ uint32_t s_hist[NB];
+  __shared__ int s_seg;
+  const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
+  const unsigned tid = threadIdx.x, lane = tid & 31u;
+  const uint32_t chunk = blockIdx.x;
+  if (tid < 32) {
+    const int sg = ss_find_segment(seg_chunk0, n_seg, chunk, lane);
+    if (lane == 0) s_seg = sg;
+  }
+  __syncthreads();
+  const int seg = s_seg;
+  if (seg >= n_seg) return;  // the grid is an upper bound on the chunk count
+  const uint32_t sbeg = seg_start[seg], send = seg_start[seg + 1];
+  const uint32_t first_local = (chunk - seg_chunk0[seg]) * SS_CHUNK;
+  const uint32_t seg_tiles = seg_tile0[seg + 1] - seg_tile0[seg];
+  const int n_tiles = (int)min((uint32_t)SS_CHUNK, seg_tiles - first_local);
+  uint32_t tot[PER];
+#pragma unroll
+  for (int k = 0; k < PER; k++) tot[k] = 0;
+  for (int t = 0; t < n_tiles; t++) {
+#pragma unroll
+    for (int k = 0; k < PER; k++)
+      if (k * SS_THREADS + (int)tid < NB) s_hist[k * SS_THREADS + tid] = 0;
+    __syncthreads();
+    const uint32_t tbase = sbeg + (first_local + t) * SS_TILE;
+    const int n_valid = (int)min((uint32_t)SS_TILE, send - tbase);
+    const KeyT* kp = keys + tbase + tid;
+    if (n_valid == SS_TILE) {
+      uint32_t k[SS_ITEMS];
+#pragma unroll
+      for (int i = 0; i < SS_ITEMS; i++) k[i] = (uint32_t)kp[i * SS_THREADS];
+#pragma unroll
+      for (int i = 0; i < SS_ITEMS; i++) atomicAdd(&s_hist[(k[i] >> shift) & dmask], 1u);
+    } else {
+      for (int i = 0; i < SS_ITEMS; i++)
+        if (i * SS_THREADS + (int)tid < n_valid)
+          atomicAdd(&s_hist[((uint32_t)kp[i * SS_THREADS] >> shift) & dmask], 1u);
+    }
+    __syncthreads();
+    uint16_t* row = tile_cnt + (size_t)(seg_tile0[seg] + first_local + t) * NB;
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+      const int d = k * SS_THREADS + (int)tid;
+      if (d < NB) {
+        const uint32_t c = s_hist[d];
+        row[d] = (uint16_t)c;
+        tot[k] += c;
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < PER; k++) {
+    const int d = k * SS_THREADS + (int)tid;
+    if (d < NB) chunk_tot[(size_t)chunk * NB + d] = tot[k];
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// Per-segment digit histograms of every pass in one read of the keys.  hist[pass][seg][NB].
+// K2: one block per segment.  chunk_tot -> chunk_base (exclusive over the segment's chunks, in place);
+// digit_base[seg][d] = seg_start[seg] + exclusive scan over the digits of the segment's totals;
+// totals[seg][d] = the segment's count of digit d.
 // ------------------------------------------------------------------------------------------------
-template <typename KeyT, int LOG_NB>
+template <int LOG_NB>
 __global__ void __launch_bounds__(256)
-seg_hist_kernel(const uint32_t* __restrict__ seg_start, int n_seg, const KeyT* __restrict__ keys, int passes,
-                int end_bit, uint32_t* __restrict__ hist) {
+seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
+                      uint32_t* __restrict__ chunk_tot, uint32_t* __restrict__ digit_base, uint32_t* __restrict__ totals) {
   constexpr int NB = 1 << LOG_NB;
-  constexpr int G = 16 / (int)sizeof(KeyT);
-  extern __shared__ uint32_t s_hist[];  // [passes][NB]
-  const int seg = blockIdx.y;
-  const uint32_t b = seg_start[seg], e = seg_start[seg + 1];
-  for (int i = threadIdx.x; i < passes * NB; i += 256) s_hist[i] = 0;
-  __syncthreads();
-  const bool aligned = (reinterpret_cast<uintptr_t>(keys) & 15u) == 0;
-  const uint32_t g0 = b / G, g1 = (e + G - 1) / G;
-  for (uint32_t g = g0 + blockIdx.x * 256u + threadIdx.x; g < g1; g += gridDim.x * 256u) {
-    const uint32_t i0 = g * G;
-    KeyT k[G];
-    if (aligned && i0 >= b && i0 + G <= e) {
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(keys) + g);
-      memcpy(k, &v, 16);
-    } else {
+  constexpr int D = NB >= 256 ? NB / 256 : 1;
+  __shared__ uint32_t s_warp[8];
+  const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
+  const int seg = blockIdx.x;
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const bool act = (int)(tid * D) < NB;
+  const uint32_t c0 = seg_chunk0[seg], c1 = seg_chunk0[seg + 1];
+  uint32_t run[D];
 #pragma unroll
-      for (int j = 0; j < G; j++) k[j] = (i0 + j >= b && i0 + j < e) ? keys[i0 + j] : (KeyT)0;
-    }
+  for (int k = 0; k < D; k++) run[k] = 0;
+  if (act) {
+#pragma unroll 4
+    for (uint32_t c = c0; c < c1; c++) {
+      uint32_t* row = chunk_tot + (size_t)c * NB + tid * D;
 #pragma unroll
-    for (int j = 0; j < G; j++) {
-      if (i0 + j < b || i0 + j >= e) continue;
-      for (int p = 0; p < passes; p++) {
-        const int shift = p * LOG_NB;
-        const int nb = min(LOG_NB, end_bit - shift);
-        const uint32_t d = (uint32_t)(k[j] >> shift) & ((1u << nb) - 1u);
-        atomicAdd(&s_hist[p * NB + d], 1u);
+      for (int k = 0; k < D; k++) {
+        const uint32_t v = row[k];
+        row[k] = run[k];
+        run[k] += v;
       }
     }
   }
+  uint32_t tsum = 0, excl[D];
+#pragma unroll
+  for (int k = 0; k < D; k++) { excl[k] = tsum; tsum += run[k]; }
+  uint32_t inc = tsum;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const uint32_t a = __shfl_up_sync(0xffffffffu, inc, s);
+    if (lane >= (unsigned)s) inc += a;
+  }
+  if (lane == 31) s_warp[warp] = inc;
   __syncthreads();
-  for (int i = threadIdx.x; i < passes * NB; i += 256) {
-    const uint32_t c = s_hist[i];
-    const int p = i / NB, d = i - p * NB;
-    if (c) atomicAdd(&hist[((size_t)p * n_seg + seg) * NB + d], c);
+  uint32_t off = seg_start[seg] + inc - tsum;
+#pragma unroll
+  for (int w = 0; w < 8; w++)
+    if (w < (int)warp) off += s_warp[w];
+  if (act) {
+#pragma unroll
+    for (int k = 0; k < D; k++) {
+      digit_base[(size_t)seg * NB + tid * D + k] = off + excl[k];
+      totals[(size_t)seg * NB + tid * D + k] = run[k];
+    }
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// One onesweep pass.  Two ranking schemes:
-//   OPT = false  ballot ranking: peers (lanes with the same digit) from one ballot per digit bit; the
-//                tile's digit counts are taken EARLY with shared atomics and published as its aggregate
-//                before the (long) ranking phase.  Right for digits with many equal keys per warp (depth
-//                bits).
+// K3: rank + scatter of one sort tile.  Two ranking schemes:
+//   OPT = false  ballot ranking: peers (lanes with the same digit) from one ballot per digit bit.  Right for
+//                digits with many equal keys per warp (depth bits).
 //   OPT = true   optimistic ranking: every lane takes its slot with a returning shared atomic on the warp's
 //                digit counter; a warp in which two lanes met on one counter (detected by re-reading it)
 //                redoes that item with the ballot scheme, so the result is still in lane order (stable).
 //                Right for wide digits with few equal keys per warp (camera-local tile ids: 32
-//                consecutive instances rarely share a tile).  Ranking is short, so the aggregate is
-//                published after it.
+//                consecutive instances rarely share a tile).
 // ------------------------------------------------------------------------------------------------
 template <typename KeyT, int LOG_NB, bool OPT>
 struct SsLayout {
@@ -136,10 +218,10 @@ struct SsLayout {
   static constexpr size_t vals = 0;                                        // u32 [TILE]
   static constexpr size_t keys = vals + 4 * (size_t)SS_TILE;               // KeyT [TILE]
   static constexpr size_t wcnt = keys + sizeof(KeyT) * (size_t)SS_TILE;    // u16|u32 [WARPS][NB]
-  static constexpr size_t bcnt = wcnt + WCNT_BYTES * (size_t)WARPS * NB;   // u32 [NB]: tile counts, then digit starts
-  static constexpr size_t gbase = bcnt + 4 * (size_t)NB;                   // u32 [NB]
-  static constexpr size_t misc = gbase + 4 * (size_t)NB;                   // u32 [4 + 2 WARPS]
-  static constexpr size_t bytes = misc + 4 * (size_t)(4 + 2 * WARPS);
+  static constexpr size_t dstart = wcnt + WCNT_BYTES * (size_t)WARPS * NB; // u32 [NB]
+  static constexpr size_t gbase = dstart + 4 * (size_t)NB;                 // u32 [NB]
+  static constexpr size_t misc = gbase + 4 * (size_t)NB;                   // u32 [4 + WARPS]
+  static constexpr size_t bytes = misc + 4 * (size_t)(4 + WARPS);
 };
 
 template <int LOG_NB>
@@ -163,11 +245,13 @@ __device__ __forceinline__ unsigned ss_peers(uint32_t d) {
 #endif
 template <typename KeyT, int LOG_NB, bool OPT, bool FULL>
 __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t tile, const int seg,
-                                             const uint32_t local_tile, const uint32_t sbeg, const uint32_t tbase,
-                                             const int n_valid, const KeyT* __restrict__ kin, KeyT* __restrict__ kout,
-                                             const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout,
-                                             const int shift, const uint32_t dmask,
-                                             const uint32_t* __restrict__ seg_hist, uint32_t* __restrict__ status) {
+                                          const uint32_t local_tile, const uint32_t chunk, const uint32_t tbase,
+                                          const int n_valid, const KeyT* __restrict__ kin, KeyT* __restrict__ kout,
+                                          const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout,
+                                          const int shift, const uint32_t dmask,
+                                          const uint16_t* __restrict__ tile_cnt,
+                                          const uint32_t* __restrict__ chunk_base,
+                                          const uint32_t* __restrict__ digit_base) {
   using Lay = SsLayout<KeyT, LOG_NB, OPT>;
   using CntT = typename std::conditional<OPT, uint32_t, uint16_t>::type;
   constexpr int NB = Lay::NB, WARPS = Lay::WARPS;
@@ -176,12 +260,11 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(ss_smem + Lay::vals);
   KeyT* s_keys = reinterpret_cast<KeyT*>(ss_smem + Lay::keys);
   CntT* s_wcnt = reinterpret_cast<CntT*>(ss_smem + Lay::wcnt);
-  uint32_t* s_bcnt = reinterpret_cast<uint32_t*>(ss_smem + Lay::bcnt);
+  uint32_t* s_dstart = reinterpret_cast<uint32_t*>(ss_smem + Lay::dstart);
   uint32_t* s_gbase = reinterpret_cast<uint32_t*>(ss_smem + Lay::gbase);
   uint32_t* s_misc = reinterpret_cast<uint32_t*>(ss_smem + Lay::misc);
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
-  uint32_t* my_status = status + (size_t)tile * NB;
 
   // load (warp-striped: item i of lane l is element warp*512 + i*32 + l of the tile)
   uint32_t key[SS_ITEMS];   // zero-extended key (16-bit keys: rank in the high half later)
@@ -202,18 +285,38 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
       for (int i = 0; i < SS_ITEMS; i++) val[i] = local_tile * SS_TILE + (uint32_t)(e0 + i * 32);
     }
   }
+  // global slot of the tile's first key of each digit: independent loads, issued before the ranking
+  // phase so that their latency hides behind it.  Thread t owns digits [t*D, t*D + D).
+  const bool act = (int)(tid * D) < NB;
+  uint32_t gb[D];
+#pragma unroll
+  for (int k = 0; k < D; k++) gb[k] = 0;
+  if (act) {
+    const int d0 = tid * D;
+    const int before = (int)(local_tile % SS_CHUNK);   // earlier tiles of this chunk
+    if (D == 4) {
+      const uint4 a = *reinterpret_cast<const uint4*>(chunk_base + (size_t)chunk * NB + d0);
+      const uint4 b = *reinterpret_cast<const uint4*>(digit_base + (size_t)seg * NB + d0);
+      gb[0] = a.x + b.x; gb[1 % D] = a.y + b.y; gb[2 % D] = a.z + b.z; gb[3 % D] = a.w + b.w;
+#pragma unroll 5
+      for (int j = 1; j <= before; j++) {
+        const uint2 c = *reinterpret_cast<const uint2*>(tile_cnt + (size_t)(tile - j) * NB + d0);
+        gb[0] += c.x & 0xFFFFu; gb[1 % D] += c.x >> 16; gb[2 % D] += c.y & 0xFFFFu; gb[3 % D] += c.y >> 16;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < D; k++)
+        gb[k] = chunk_base[(size_t)chunk * NB + d0 + k] + digit_base[(size_t)seg * NB + d0 + k];
+#pragma unroll 5
+      for (int j = 1; j <= before; j++)
+#pragma unroll
+        for (int k = 0; k < D; k++) gb[k] += tile_cnt[(size_t)(tile - j) * NB + d0 + k];
+    }
+  }
+
   const unsigned lt = lanemask_lt();
   CntT* my_wcnt = s_wcnt + warp * NB;
-
   if (!OPT) {
-    // early counts, published as the tile's aggregate BEFORE the (long) ranking phase, so that by the time
-    // this tile looks back its predecessors have published too
-#pragma unroll
-    for (int i = 0; i < SS_ITEMS; i++)
-      if (FULL || e0 + i * 32 < n_valid) atomicAdd(&s_bcnt[(key[i] >> shift) & dmask], 1u);
-    __syncthreads();
-    for (int d = tid; d < NB; d += SS_THREADS)
-      ss_st_relaxed(my_status + d, (local_tile == 0 ? SS_FLAG_INC : SS_FLAG_AGG) | s_bcnt[d]);
     // rank within the warp, in (item, lane) order == memory order => stable.  Padding takes the last digit
     // and, being last in memory order, ranks behind every valid key of that digit.
 #pragma unroll
@@ -248,14 +351,13 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
   }
   __syncthreads();
 
-  // digit phase: thread t owns digits [t*D, t*D + D)
+  // digit phase: per-warp exclusive offsets of each digit, start of each digit in tile-sorted order
   {
-    const bool act = (int)(tid * D) < NB;
-    uint32_t gh[D], excl_c[D], excl_g[D], bc[D];
-    uint32_t tc = 0, tg = 0;
+    uint32_t excl_c[D];
+    uint32_t tc = 0;
 #pragma unroll
     for (int k = 0; k < D; k++) {
-      gh[k] = 0; excl_c[k] = 0; excl_g[k] = 0; bc[k] = 0;
+      excl_c[k] = 0;
       if (act) {
         const int d = tid * D + k;
         uint32_t run = 0;
@@ -265,77 +367,29 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
           s_wcnt[w * NB + d] = (CntT)run;
           run += c;
         }
-        gh[k] = seg_hist[(size_t)seg * NB + d];
-        bc[k] = OPT ? run : s_bcnt[d];   // OPT: the last tile of a segment counts its padding in the last digit;
-                                          // nothing looks back at it (the next segment starts a new chain)
-        excl_c[k] = tc; excl_g[k] = tg;
-        tc += run; tg += gh[k];
+        excl_c[k] = tc;
+        tc += run;
       }
     }
-    if (OPT && act) {
-#pragma unroll
-      for (int k = 0; k < D; k++)
-        ss_st_relaxed(my_status + tid * D + k, (local_tile == 0 ? SS_FLAG_INC : SS_FLAG_AGG) | bc[k]);
-    }
-    uint32_t inc_c = tc, inc_g = tg;
+    uint32_t inc_c = tc;
 #pragma unroll
     for (int s = 1; s < 32; s <<= 1) {
       const uint32_t a = __shfl_up_sync(full, inc_c, s);
-      const uint32_t b = __shfl_up_sync(full, inc_g, s);
-      if (lane >= (unsigned)s) { inc_c += a; inc_g += b; }
+      if (lane >= (unsigned)s) inc_c += a;
     }
-    if (lane == 31) { s_misc[4 + warp] = inc_c; s_misc[4 + WARPS + warp] = inc_g; }
+    if (lane == 31) s_misc[4 + warp] = inc_c;
     __syncthreads();
-    uint32_t off_c = inc_c - tc, off_g = inc_g - tg;
+    uint32_t off_c = inc_c - tc;
 #pragma unroll
     for (int w = 0; w < WARPS; w++)
-      if (w < (int)warp) { off_c += s_misc[4 + w]; off_g += s_misc[4 + WARPS + w]; }
-
-    uint32_t prefix[D];
-#pragma unroll
-    for (int k = 0; k < D; k++) prefix[k] = 0;
-    if (act && local_tile > 0) {
-      // decoupled look-back, the thread's D digit chains in lock step over the same predecessor tile
-      uint32_t p = tile - 1;
-      unsigned pend = (1u << D) - 1u;
-      while (pend) {
-        const uint32_t* ps = status + (size_t)p * NB + tid * D;
-        uint32_t s[D];
-        if (D % 4 == 0) {
-#pragma unroll
-          for (int q = 0; q < D / 4; q++) {
-            const uint4 v = ss_ld_relaxed_v4(ps + 4 * q);
-            s[4 * q] = v.x; s[4 * q + 1] = v.y; s[4 * q + 2] = v.z; s[4 * q + 3] = v.w;
-          }
-        } else {
-#pragma unroll
-          for (int k = 0; k < D; k++) s[k] = ss_ld_relaxed(ps + k);
-        }
-        bool ready = true;
-#pragma unroll
-        for (int k = 0; k < D; k++)
-          if (((pend >> k) & 1u) && (s[k] & ~SS_VAL_MASK) == 0) ready = false;
-        if (!ready) continue;
-#pragma unroll
-        for (int k = 0; k < D; k++) {
-          if ((pend >> k) & 1u) {
-            prefix[k] += s[k] & SS_VAL_MASK;
-            if (s[k] & SS_FLAG_INC) pend &= ~(1u << k);
-          }
-        }
-        p--;
-      }
-#pragma unroll
-      for (int k = 0; k < D; k++)
-        ss_st_relaxed(my_status + tid * D + k, SS_FLAG_INC | ((prefix[k] + bc[k]) & SS_VAL_MASK));
-    }
+      if (w < (int)warp) off_c += s_misc[4 + w];
     if (act) {
 #pragma unroll
       for (int k = 0; k < D; k++) {
         const int d = tid * D + k;
-        const uint32_t dstart = off_c + excl_c[k];
-        s_bcnt[d] = dstart;                                             // start of digit d in tile-sorted order
-        s_gbase[d] = sbeg + off_g + excl_g[k] + prefix[k] - dstart;     // + position in the tile = global slot
+        const uint32_t ds = off_c + excl_c[k];
+        s_dstart[d] = ds;            // start of digit d in tile-sorted order
+        s_gbase[d] = gb[k] - ds;     // + position in the tile = global slot
       }
     }
   }
@@ -347,7 +401,7 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
     const uint32_t k = PACK ? (key[i] & 0xFFFFu) : key[i];
     const uint32_t r = PACK ? (key[i] >> 16) : rank[PACK ? 0 : i];
     const uint32_t d = (FULL || e0 + i * 32 < n_valid) ? ((k >> shift) & dmask) : (uint32_t)(NB - 1);
-    const uint32_t pos = s_bcnt[d] + my_wcnt[d] + r;
+    const uint32_t pos = s_dstart[d] + my_wcnt[d] + r;
     s_keys[pos] = (KeyT)k;
     s_vals[pos] = val[i];
   }
@@ -374,68 +428,62 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
 #endif
 template <typename KeyT, int LOG_NB, bool OPT>
 __global__ void __launch_bounds__(SS_THREADS, sizeof(KeyT) > 2 ? SS_MINB32 : SS_MINB16)
-seg_onesweep_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
-                    const KeyT* __restrict__ kin, KeyT* __restrict__ kout, const uint32_t* __restrict__ vin,
-                    uint32_t* __restrict__ vout, int shift, uint32_t dmask, const uint32_t* __restrict__ seg_hist,
-                    uint32_t* __restrict__ ticket, uint32_t* __restrict__ status) {
+seg_scatter_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
+                   const KeyT* __restrict__ kin, KeyT* __restrict__ kout, const uint32_t* __restrict__ vin,
+                   uint32_t* __restrict__ vout, int shift, uint32_t dmask, const uint16_t* __restrict__ tile_cnt,
+                   const uint32_t* __restrict__ chunk_base, const uint32_t* __restrict__ digit_base) {
   using Lay = SsLayout<KeyT, LOG_NB, OPT>;
   constexpr int NB = Lay::NB, WARPS = Lay::WARPS;
   extern __shared__ __align__(16) unsigned char ss_smem[];
-  uint32_t* s_bcnt = reinterpret_cast<uint32_t*>(ss_smem + Lay::bcnt);
   uint32_t* s_misc = reinterpret_cast<uint32_t*>(ss_smem + Lay::misc);
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  const unsigned full = 0xffffffffu;
-
+  const uint32_t tile = blockIdx.x;
   if (warp == 0) {
-    uint32_t t = 0;
-    if (lane == 0) t = atomicAdd(ticket, 1u);
-    t = __shfl_sync(full, t, 0);
-    // segment of sort tile t = #{ e in [1, n_seg] : seg_tile0[e] <= t }  (n_seg: past the last tile)
-    int seg = 0;
-    for (int e0 = 1; e0 <= n_seg; e0 += 32) {
-      const int e = e0 + (int)lane;
-      const bool le = (e <= n_seg) && (seg_tile0[e] <= t);
-      seg += __popc(__ballot_sync(full, le));
-    }
-    if (lane == 0) { s_misc[0] = t; s_misc[1] = (uint32_t)seg; }
+    const int sg = ss_find_segment(seg_tile0, n_seg, tile, lane);
+    if (lane == 0) s_misc[1] = (uint32_t)sg;
   }
   {
     uint4* z = reinterpret_cast<uint4*>(ss_smem + Lay::wcnt);
     for (int i = tid; i < (Lay::WCNT_BYTES * WARPS * NB) / 16; i += SS_THREADS) z[i] = make_uint4(0, 0, 0, 0);
-    if (!OPT)
-      for (int i = tid; i < NB; i += SS_THREADS) s_bcnt[i] = 0;
   }
   __syncthreads();
-  const uint32_t tile = s_misc[0];
   const int seg = (int)s_misc[1];
   if (seg >= n_seg) return;  // the grid is an upper bound on the tile count
+  const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
   const uint32_t local_tile = tile - seg_tile0[seg];
+  const uint32_t chunk = seg_chunk0[seg] + local_tile / SS_CHUNK;
   const uint32_t sbeg = seg_start[seg], send = seg_start[seg + 1];
   const uint32_t tbase = sbeg + local_tile * SS_TILE;
   const int n_valid = (int)min((uint32_t)SS_TILE, send - tbase);
   if (n_valid == SS_TILE)
-    ss_tile_body<KeyT, LOG_NB, OPT, true>(ss_smem, tile, seg, local_tile, sbeg, tbase, n_valid, kin, kout, vin, vout,
-                                          shift, dmask, seg_hist, status);
+    ss_tile_body<KeyT, LOG_NB, OPT, true>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
+                                          shift, dmask, tile_cnt, chunk_base, digit_base);
   else
-    ss_tile_body<KeyT, LOG_NB, OPT, false>(ss_smem, tile, seg, local_tile, sbeg, tbase, n_valid, kin, kout, vin, vout,
-                                           shift, dmask, seg_hist, status);
+    ss_tile_body<KeyT, LOG_NB, OPT, false>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
+                                           shift, dmask, tile_cnt, chunk_base, digit_base);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Host side
 // ------------------------------------------------------------------------------------------------
 static inline int64_t ss_max_tiles(int64_t n_upper, int n_seg) { return (n_upper + SS_TILE - 1) / SS_TILE + n_seg; }
+static inline int64_t ss_max_chunks(int64_t n_upper, int n_seg) {
+  return (n_upper + (int64_t)SS_TILE * SS_CHUNK - 1) / ((int64_t)SS_TILE * SS_CHUNK) + n_seg;
+}
 
+// temp: tile_cnt u16 [max_tiles][NB] | chunk_base u32 [max_chunks][NB] | digit_base u32 [n_seg][NB] |
+//       totals u32 [n_seg][NB]; reused by every pass.  Nothing needs zeroing.
 size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int passes, int log_nb) {
+  (void)passes;
   const size_t nb = (size_t)1 << log_nb;
-  return SS_HEADER + align_up((size_t)passes * n_seg * nb * 4, 256) +
-         align_up((size_t)passes * (size_t)ss_max_tiles(n_upper, n_seg) * nb * 4, 256);
+  return align_up((size_t)ss_max_tiles(n_upper, n_seg) * nb * 2, 256) +
+         align_up((size_t)ss_max_chunks(n_upper, n_seg) * nb * 4, 256) + 2 * align_up((size_t)n_seg * nb * 4, 256);
 }
 
 int launch_seg_setup(int n_seg, int mode, int len, const uint32_t* offsets, uint32_t* seg_start, uint32_t* seg_tile0,
                      cudaStream_t st) {
   if (n_seg <= 0 || n_seg > 1024) return GSB_EINVAL;
-  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, offsets, SS_TILE, seg_start, seg_tile0);
+  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, offsets, seg_start, seg_tile0);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -453,38 +501,39 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
   if (want_keys && !k_out) return GSB_EINVAL;
   static bool attr_set = false;
   if (!attr_set) {
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_onesweep_kernel<KeyT, LOG_NB, OPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Lay::bytes));
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_onesweep_kernel<KeyT, LOG_NB, OPT>,
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT>,
                                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
-  const int64_t max_tiles = ss_max_tiles(n_upper, n_seg);
-  const size_t hist_bytes = align_up((size_t)passes * n_seg * NB * 4, 256);
-  GSB_CUDA_CHECK(cudaMemsetAsync(temp, 0, SS_HEADER + hist_bytes + (size_t)passes * max_tiles * NB * 4, st));
-  uint32_t* tickets = reinterpret_cast<uint32_t*>(temp);
-  uint32_t* hist = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(temp) + SS_HEADER);
-  uint32_t* status = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(temp) + SS_HEADER + hist_bytes);
-  if (hist_out) *hist_out = hist;
-  {
-    // enough blocks per segment to fill the GPU, few enough that the flush atomics stay cheap
-    const int per_seg = std::max(1, std::min<int>((int)((n_upper / std::max(n_seg, 1) + 16383) / 16384), (148 * 8 + n_seg - 1) / n_seg));
-    dim3 grid(per_seg, n_seg);
-    seg_hist_kernel<KeyT, LOG_NB><<<grid, 256, (size_t)passes * NB * 4, st>>>(seg_start, n_seg, kin, passes, end_bit, hist);
-    GSB_LAUNCH_CHECK();
-  }
+  const int64_t max_tiles = ss_max_tiles(n_upper, n_seg), max_chunks = ss_max_chunks(n_upper, n_seg);
+  char* t = reinterpret_cast<char*>(temp);
+  uint16_t* tile_cnt = reinterpret_cast<uint16_t*>(t);
+  t += align_up((size_t)max_tiles * NB * 2, 256);
+  uint32_t* chunk_base = reinterpret_cast<uint32_t*>(t);
+  t += align_up((size_t)max_chunks * NB * 4, 256);
+  uint32_t* digit_base = reinterpret_cast<uint32_t*>(t);
+  t += align_up((size_t)n_seg * NB * 4, 256);
+  uint32_t* totals = reinterpret_cast<uint32_t*>(t);
+  if (hist_out) *hist_out = totals;   // digit counts per segment of the LAST pass
   const KeyT* a = kin;
   const uint32_t* va = vin;
   for (int p = 0; p < passes; p++) {
     const int shift = p * LOG_NB;
     const int nb = std::min(LOG_NB, end_bit - shift);
+    const uint32_t dmask = (1u << nb) - 1u;
     const bool to_out = ((passes - 1 - p) % 2 == 0);
     const bool last = (p == passes - 1);
     KeyT* b = (last && !want_keys) ? nullptr : (to_out ? k_out : k_alt);
     uint32_t* vb = to_out ? v_out : v_alt;
-    seg_onesweep_kernel<KeyT, LOG_NB, OPT><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
-        seg_start, seg_tile0, n_seg, a, b, va, vb, shift, (1u << nb) - 1u, hist + (size_t)p * n_seg * NB, tickets + p,
-        status + (size_t)p * max_tiles * NB);
+    seg_tile_hist_kernel<KeyT, LOG_NB><<<(unsigned)max_chunks, SS_THREADS, 0, st>>>(seg_start, seg_tile0, n_seg, a, shift,
+                                                                                   dmask, tile_cnt, chunk_base);
+    GSB_LAUNCH_CHECK();
+    seg_chunk_scan_kernel<LOG_NB><<<n_seg, 256, 0, st>>>(seg_start, seg_tile0, n_seg, chunk_base, digit_base, totals);
+    GSB_LAUNCH_CHECK();
+    seg_scatter_kernel<KeyT, LOG_NB, OPT><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
+        seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
     GSB_LAUNCH_CHECK();
     a = b;
     va = vb;
