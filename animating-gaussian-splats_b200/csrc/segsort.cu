@@ -1,4 +1,4 @@
-// segsort.cu -- segmented onesweep LSD radix sort with wide digits, and tile ranges from its histogram.
+// segsort.cu -- segmented LSD radix sort with wide digits and two-level offsets; tile ranges from its histogram.
 //
 // Replaces cub::DeviceRadixSort::SortPairs (cr/rasterizer_impl.cu:304-309) on the product path.  The
 // reference sorts R instances on 64-bit (tile << 32 | depth) keys in 6 eight-bit passes.  A stable LSD
@@ -150,12 +150,13 @@ seg_tile_hist_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __r
 // totals[seg][d] = the segment's count of digit d.
 // ------------------------------------------------------------------------------------------------
 template <int LOG_NB>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(LOG_NB >= 10 ? 1024 : (1 << LOG_NB) < 32 ? 32 : (1 << LOG_NB))
 seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
                       uint32_t* __restrict__ chunk_tot, uint32_t* __restrict__ digit_base, uint32_t* __restrict__ totals) {
   constexpr int NB = 1 << LOG_NB;
-  constexpr int D = NB >= 256 ? NB / 256 : 1;
-  __shared__ uint32_t s_warp[8];
+  constexpr int THREADS = LOG_NB >= 10 ? 1024 : NB < 32 ? 32 : NB;
+  constexpr int D = NB / THREADS > 0 ? NB / THREADS : 1;
+  __shared__ uint32_t s_warp[32];
   const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
   const int seg = blockIdx.x;
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -165,7 +166,7 @@ seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __
 #pragma unroll
   for (int k = 0; k < D; k++) run[k] = 0;
   if (act) {
-#pragma unroll 4
+#pragma unroll 8
     for (uint32_t c = c0; c < c1; c++) {
       uint32_t* row = chunk_tot + (size_t)c * NB + tid * D;
 #pragma unroll
@@ -188,9 +189,7 @@ seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __
   if (lane == 31) s_warp[warp] = inc;
   __syncthreads();
   uint32_t off = seg_start[seg] + inc - tsum;
-#pragma unroll
-  for (int w = 0; w < 8; w++)
-    if (w < (int)warp) off += s_warp[w];
+  for (int w = 0; w < (int)warp; w++) off += s_warp[w];
   if (act) {
 #pragma unroll
     for (int k = 0; k < D; k++) {
@@ -205,7 +204,7 @@ seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __
 //   OPT = false  ballot ranking: peers (lanes with the same digit) from one ballot per digit bit.  Right for
 //                digits with many equal keys per warp (depth bits).
 //   OPT = true   optimistic ranking: every lane takes its slot with a returning shared atomic on the warp's
-//                digit counter; a warp in which two lanes met on one counter (detected by re-reading it)
+//                digit counter (16 bits, two per word); a warp in which two lanes met on one counter (detected by re-reading it)
 //                redoes that item with the ballot scheme, so the result is still in lane order (stable).
 //                Right for wide digits with few equal keys per warp (camera-local tile ids: 32
 //                consecutive instances rarely share a tile).
@@ -214,7 +213,7 @@ template <typename KeyT, int LOG_NB, bool OPT>
 struct SsLayout {
   static constexpr int NB = 1 << LOG_NB;
   static constexpr int WARPS = SS_THREADS / 32;
-  static constexpr int WCNT_BYTES = OPT ? 4 : 2;
+  static constexpr int WCNT_BYTES = 2;
   static constexpr size_t vals = 0;                                        // u32 [TILE]
   static constexpr size_t keys = vals + 4 * (size_t)SS_TILE;               // KeyT [TILE]
   static constexpr size_t wcnt = keys + sizeof(KeyT) * (size_t)SS_TILE;    // u16|u32 [WARPS][NB]
@@ -253,7 +252,7 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
                                           const uint32_t* __restrict__ chunk_base,
                                           const uint32_t* __restrict__ digit_base) {
   using Lay = SsLayout<KeyT, LOG_NB, OPT>;
-  using CntT = typename std::conditional<OPT, uint32_t, uint16_t>::type;
+  using CntT = uint16_t;
   constexpr int NB = Lay::NB, WARPS = Lay::WARPS;
   constexpr int D = NB >= SS_THREADS ? NB / SS_THREADS : 1;  // digits per thread in the digit phase
   constexpr bool PACK = sizeof(KeyT) == 2;
@@ -338,7 +337,9 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
 #pragma unroll
     for (int i = 0; i < SS_ITEMS; i++) {
       const uint32_t d = (FULL || e0 + i * 32 < n_valid) ? ((key[i] >> shift) & dmask) : (uint32_t)(NB - 1);
-      uint32_t r = atomicAdd(reinterpret_cast<uint32_t*>(&my_wcnt[d]), 1u);
+      // two 16-bit counters per word (a warp holds 512 keys): the atomic adds into the digit's half
+      const uint32_t sh = (d & 1u) * 16u;
+      uint32_t r = (atomicAdd(reinterpret_cast<uint32_t*>(my_wcnt) + (d >> 1), 1u << sh) >> sh) & 0xFFFFu;
       __syncwarp();
       const uint32_t now = my_wcnt[d];
       if (__any_sync(full, now != r + 1u)) {   // two lanes met on one counter: redo this item in lane order
@@ -421,7 +422,7 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
 }
 
 #ifndef SS_MINB16
-#define SS_MINB16 3
+#define SS_MINB16 4
 #endif
 #ifndef SS_MINB32
 #define SS_MINB32 3
@@ -530,7 +531,7 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
     seg_tile_hist_kernel<KeyT, LOG_NB><<<(unsigned)max_chunks, SS_THREADS, 0, st>>>(seg_start, seg_tile0, n_seg, a, shift,
                                                                                    dmask, tile_cnt, chunk_base);
     GSB_LAUNCH_CHECK();
-    seg_chunk_scan_kernel<LOG_NB><<<n_seg, 256, 0, st>>>(seg_start, seg_tile0, n_seg, chunk_base, digit_base, totals);
+    seg_chunk_scan_kernel<LOG_NB><<<n_seg, LOG_NB >= 10 ? 1024 : std::max(NB, 32), 0, st>>>(seg_start, seg_tile0, n_seg, chunk_base, digit_base, totals);
     GSB_LAUNCH_CHECK();
     seg_scatter_kernel<KeyT, LOG_NB, OPT><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
         seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
