@@ -61,3 +61,58 @@ def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2):
         g2 = grads["means2D"] if n > 1 else grads["means2D"][None]
         stats.accumulate_batch(radii.contiguous(), g2.contiguous())
     return loss_stats, grads, radii, st
+
+
+class HostFeed:
+    """End-to-end front of timestep_step for callers whose step inputs live in HOST memory (raw parameter
+    tables and target images in pinned buffers): every step copies its inputs host -> device, runs the
+    activations (create_render_arguments, shared.py:29-42) and the step, and reads the per-camera loss
+    numbers back.  The copies of step k+1 are issued on a side stream into the other half of a double
+    buffer while step k computes, so the PCIe transfer (91 MB at 300 k Gaussians x 27 cameras) hides
+    behind the rasterizer instead of preceding it."""
+
+    RAW_KEYS = ("means", "colors", "rotation_quaternions", "opacity_logits", "log_scales")
+
+    def __init__(self, host_raw, host_targets, device):
+        self.dev = device
+        self.host_raw = {k: host_raw[k] for k in self.RAW_KEYS}
+        self.host_targets = host_targets
+        for t in list(self.host_raw.values()) + [host_targets]:
+            if not t.is_pinned():
+                raise RuntimeError("HostFeed needs pinned host buffers")
+        self.bufs = [({k: torch.empty_like(v, device=device) for k, v in self.host_raw.items()},
+                      torch.empty_like(host_targets, device=device)) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.loss_host = torch.empty((host_targets.size(0), 3), dtype=torch.float32).pin_memory()
+        self.k = 0
+        self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_raw.values()) + \
+            host_targets.numel() * host_targets.element_size()
+        self.d2h_bytes = self.loss_host.numel() * 4
+        self._prefetch(0)
+
+    def _prefetch(self, k):
+        raw, tgt = self.bufs[k % 2]
+        # the buffer's previous consumer (step k-2) finished: step() synchronises every step
+        with torch.cuda.stream(self.copy_stream):
+            for key, h in self.host_raw.items():
+                raw[key].copy_(h, non_blocking=True)
+            tgt.copy_(self.host_targets, non_blocking=True)
+            self.ready[k % 2].record(self.copy_stream)
+
+    def step(self, cams, bg, stats=None, after=None):
+        """One end-to-end step.  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
+        loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix)."""
+        from . import scene
+        k = self.k
+        raw, tgt = self.bufs[k % 2]
+        torch.cuda.current_stream(self.dev).wait_event(self.ready[k % 2])
+        self._prefetch(k + 1)
+        act = {key: v.contiguous() for key, v in scene.activate(raw).items()}
+        loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats)
+        if after is not None:
+            after(loss_stats, grads, radii, st)
+        self.loss_host.copy_(loss_stats, non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        self.k += 1
+        return self.loss_host

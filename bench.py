@@ -211,14 +211,19 @@ def run_ours(args):
     ms_step = float(t.item()) / args.steps
 
     # ---- end to end: host buffers in, loss out, every step ------------------------------------
+    # gsb200.step.HostFeed: each step's inputs (raw parameter tables + target images, pinned host memory) are
+    # copied host -> device (double-buffered, the copy of step k+1 overlaps step k), activations + step run on
+    # the device, the per-camera loss numbers come back to pinned host memory; one stream sync per step.
+    feed = step_mod.HostFeed(host_raw, host_targets, dev)
+
+    def after(loss_stats, grads, radii, st_):
+        if world > 1:
+            gd.pack(flat, grads, {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
+                                  "visibility_count": stats.visibility_count})
+            gd.allreduce(flat, stats.max_2d_radii)
+
     def e2e_step():
-        for k in raw_keys:
-            dev_raw[k].copy_(host_raw[k], non_blocking=True)
-        dev_targets.copy_(host_targets, non_blocking=True)
-        a = activate()
-        ls, _, _ = one_step(a)
-        loss_host.copy_(ls, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        feed.step(sc, bg, stats, after)
 
     e2e_step()
     sync_all()
@@ -232,8 +237,8 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_e2e = float(t.item()) / args.steps
     clocks = sampler.stop() if rank == 0 else None
-    h2d = sum(v.numel() * 4 for v in host_raw.values()) + host_targets.numel() * 4
-    d2h = loss_host.numel() * 4
+    h2d = feed.h2d_bytes
+    d2h = feed.d2h_bytes
 
     # ---- per-stage timing of one step (CUDA events inside the library, on the launching stream) --
     lib.gsb_profile_enable(1)
@@ -281,23 +286,23 @@ def run_ours(args):
                 "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
                 "ms": bwd_ms, "pairs": walked}
     # the HBM-bound kernel with the most bytes: the instance sort (segmented onesweep on 16-bit camera-local
-    # tile ids).  Algorithmic bytes per pass: read key (2) + payload (4), write payload (4) (+ key (2) unless it is
-    # the last pass of a one-pass sort); the histogram reads the keys once more (2).  DESIGN.md section 5.
+    # tile ids).  Algorithmic bytes per pass: the histogram reads the key (2); the scatter reads key (2) + payload (4)
+    # and writes the payload (4) (+ the key (2) when another pass follows).  DESIGN.md section 5.
     tile_digit = int(os.environ.get("GSB_TILE_DIGIT", "0")) or (5 if st.ctx.tile_bits <= 5 else 8 if st.ctx.tile_bits <= 8 else 10 if st.ctx.tile_bits <= 10 else 8)
     passes = (max(st.ctx.tile_bits, 1) + tile_digit - 1) // tile_digit
     depth_digit = 11 if os.environ.get("GSB_DEPTH_DIGIT") == "11" else 8
     gpasses = (32 + depth_digit - 1) // depth_digit
-    sort_bytes = R * (2 + 10 * passes + (2 * passes if passes > 1 else 0))
+    sort_bytes = R * (12 * passes + (2 * passes if passes > 1 else 0))
     sort_ms = stages["sort"]
-    sort_name = f"seg_hist_kernel<u16> + seg_onesweep_kernel<u16,{tile_digit}> x{passes} (instance sort on camera-local tile ids)"
+    sort_name = (f"(seg_tile_hist + seg_chunk_scan + seg_scatter)<u16,{tile_digit}> x{passes}: instance sort on camera-local tile ids")
     roofline_hbm = {"kernel": sort_name, "bound": "hbm",
                     "achieved": sort_bytes / (sort_ms * 1e-3) / 1e9 if sort_ms > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "ms": sort_ms, "instances": R,
                     "traffic": tr("seg_sort_instances"), "algorithmic_bytes": sort_bytes}
     roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
-    # preprocess, depth sort (setup + hist + passes), scan, setup, key emission, instance sort (hist + passes),
+    # preprocess, depth sort (setup + 3 kernels per pass), scan, setup, key emission, instance sort (3 per pass),
     # ranges, blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
-    launches = 1 + (2 + gpasses) + 1 + 1 + 1 + (1 + passes) + 1 + 1 + 3 + 1 + 1 + 1
+    launches = 1 + (1 + 3 * gpasses) + 1 + 1 + 1 + 3 * passes + 1 + 1 + 3 + 1 + 1 + 1
 
     out = {
         "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",
