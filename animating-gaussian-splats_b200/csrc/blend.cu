@@ -112,7 +112,13 @@ __device__ __forceinline__ int compact_slot(bool keep, unsigned tid, int* s_wcnt
   return total;
 }
 
-__global__ void __launch_bounds__(GSB_BLOCK_SIZE, 6)
+#ifndef GSB_FWD_MINB
+#define GSB_FWD_MINB 6
+#endif
+#ifndef GSB_BWD_MINB
+#define GSB_BWD_MINB 4
+#endif
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_FWD_MINB)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
                   const float2* __restrict__ means2D, const float* __restrict__ colors, int color_cam_stride,
                   const float4* __restrict__ conic_opacity, const float* __restrict__ depths,
@@ -251,7 +257,7 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
   v[0] += __shfl_xor_sync(full, v[0], 1);
 }
 
-__global__ void __launch_bounds__(GSB_BLOCK_SIZE, 4)
+__global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_BWD_MINB)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
                   const float* __restrict__ bg, const float2* __restrict__ means2D,
                   const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,

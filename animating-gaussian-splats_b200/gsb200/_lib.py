@@ -44,6 +44,11 @@ class RasterCtx(C.Structure):
     ]
 
 
+class AdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("numel", C.c_int64), ("step", C.c_int64), ("lr", C.c_double)]
+
+
 # name -> (restype, argtypes): every symbol include/gsb200.h declares
 SYMBOLS = {
     "gsb_version": (C.c_char_p, []),
@@ -74,6 +79,9 @@ SYMBOLS = {
     "gsb_seg_sort_temp_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
     "gsb_seg_sort_u16": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "gsb_seg_sort_u32": (C.c_int, [C.c_int64, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "gsb_activate": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
+    "gsb_activate_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 10),
+    "gsb_adam_step": (C.c_int, [C.c_int32, C.POINTER(AdamGroup), C.c_double, C.c_double, C.c_double, C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),
     "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }

@@ -36,7 +36,7 @@ import torch  # noqa: E402
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference_cuda"])
     ap.add_argument("--gaussians", type=int, default=300_000)
@@ -59,47 +59,67 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: an NVML polling thread (nvidia_ml_py), started
+    before the warm-up so that its set-up cost stays out of the timed steps; only samples taken between
+    begin() and end() count.  (An nvidia-smi child process needs ~0.3 s to come up, longer than the timed region,
+    and its start-up was seen to stall kernel launches for tens of ms.)"""
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
-    def __init__(self, index=0):
-        self.proc = None
-        self.index = index
+    def __init__(self, index=0, period=0.002):
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.active, self.stop_flag = [], 0, False, False
+        self.h = self.nv = self.thread = None
+        self.max_mhz = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv = nv
+            self.h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
         except Exception:
-            self.proc = None
+            self.nv = None
+            return
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def _reasons(self):
+        nv = self.nv
+        for name in ("nvmlDeviceGetCurrentClocksEventReasons", "nvmlDeviceGetCurrentClocksThrottleReasons"):
+            fn = getattr(nv, name, None)
+            if fn is not None:
+                try:
+                    return int(fn(self.h))
+                except Exception:
+                    pass
+        return 0
+
+    def _run(self):
+        nv = self.nv
+        while not self.stop_flag:
+            if self.active:
+                try:
+                    self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                    self.reasons |= self._reasons()
+                except Exception:
+                    pass
+            time.sleep(self.period)
+
+    def begin(self):
+        self.active = True
+
+    def end(self):
+        self.active = False
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            out, _ = self.proc.communicate(timeout=5)
-        except Exception:
-            self.proc.kill()
-            out = ""
-        sm, mx, reasons = [], [], set()
-        for line in out.strip().splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["NVML unavailable"]}
+        self.stop_flag = True
+        self.thread.join(timeout=2)
+        names = sorted(k for k, b in self.BITS.items() if self.reasons & b)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": names, "samples": len(self.samples)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -192,18 +212,20 @@ def run_ours(args):
         return
 
     # ---- device-resident timing -------------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        loss_stats, grads, st = one_step(act)
-    sync_all()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        loss_stats, grads, st = one_step(act)
+    sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.begin()
     e0.record()
     for _ in range(args.steps):
         loss_stats, grads, st = one_step(act)
     e1.record()
     sync_all()
+    sampler.end()
     ms = e0.elapsed_time(e1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -227,11 +249,13 @@ def run_ours(args):
 
     e2e_step()
     sync_all()
+    sampler.begin()
     e0.record()
     for _ in range(args.steps):
         e2e_step()
     e1.record()
     sync_all()
+    sampler.end()
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -466,7 +490,12 @@ def densify_shaped(args, impl, iters=30, warm=5):
     targets = render_targets(tgt_raw, sc, args.cams, bg, dev)
     seg_targets = (targets > 0.5).float()
     params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in g_raw.items()}
-    opt = torch.optim.Adam([{"params": [v], "name": k, "lr": 1e-4} for k, v in params.items()], lr=0.0, eps=1e-15)
+    groups = [{"params": [v], "name": k, "lr": 1e-4} for k, v in params.items()]
+    if impl == "ours":   # the fused step of gsb200.optim (one launch over all tables); the reference arm keeps torch's
+        from gsb200 import optim as goptim
+        opt = goptim.FusedAdam(groups, lr=0.0, eps=1e-15)
+    else:
+        opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
     P = args.gaussians
     dv = gdens.DensificationVariables(visibility_count=torch.zeros(P, device=dev),
                                       mean_2d_gradients_accumulated=torch.zeros(P, device=dev),
@@ -481,6 +510,12 @@ def densify_shaped(args, impl, iters=30, warm=5):
             return None
 
     def render(i, colors):
+        if impl == "ours":   # fused activations (gsb200.optim.create_render_arguments, shared.py:29-42)
+            a = goptim.create_render_arguments(params)
+            a["colors_precomp"] = colors
+            a["means2D"].retain_grad()
+            im, radii, _ = Renderer(raster_settings=settings[i])(**a)
+            return im, radii, a["means2D"]
         a = {"means3D": params["means"], "colors_precomp": colors,
              "rotations": torch.nn.functional.normalize(params["rotation_quaternions"]),
              "opacities": torch.sigmoid(params["opacity_logits"]), "scales": torch.exp(params["log_scales"]),

@@ -172,6 +172,29 @@ int gsb_mask_scan(int32_t P, const uint8_t* keep, int32_t* dst_index, int32_t* c
 int gsb_gather_rows(int32_t P, const uint8_t* keep, const int32_t* dst_index, const float* src, float* dst,
                     int32_t row_floats, void* stream);
 
+/* create_render_arguments (shared.py:29-42), the three activations in one launch:
+ * rotations = normalize(quats) [P][4] (torch.nn.functional.normalize: q / max(||q||, 1e-12)),
+ * opacities = sigmoid(opacity_logits) [P], scales = exp(log_scales) [P][3].  New entry point:
+ * the reference runs three torch kernels + autograd nodes per render. */
+int gsb_activate(int32_t P, const float* quats, const float* opacity_logits, const float* log_scales,
+                 float* rotations, float* opacities, float* scales, void* stream);
+/* Its adjoint: gradients w.r.t. the activated tables -> gradients w.r.t. the raw parameter tables.  Any d_* input
+ * may be NULL (treated as zeros); any output may be NULL (skipped). */
+int gsb_activate_backward(int32_t P, const float* quats, const float* opacities, const float* scales,
+                          const float* d_rotations, const float* d_opacities, const float* d_scales,
+                          float* d_quats, float* d_opacity_logits, float* d_log_scales, void* stream);
+
+/* torch.optim.Adam as create_optimizer builds it (densify.py:68-86; no weight decay, no amsgrad) over up to 16
+ * parameter tables in ONE launch.  `groups_host` is a HOST array; step is the 1-based step count of the group
+ * AFTER this update (torch increments before use).  Groups with grad == NULL are skipped like torch skips
+ * parameters without a gradient. */
+typedef struct gsb_adam_group {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t numel; int64_t step; double lr;
+} gsb_adam_group;
+int gsb_adam_step(int32_t n_groups, const gsb_adam_group* groups_host, double beta1, double beta2, double eps,
+                  void* stream);
+
 /* Debug / test accessors: the individual stages, so that tests can compare every intermediate
  * bit-for-bit. */
 int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream);
