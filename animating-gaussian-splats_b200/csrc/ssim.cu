@@ -14,13 +14,14 @@
 
 namespace gsb {
 
-constexpr int SS_TW = 32, SS_TH = 16;            // output tile (one block of 256 threads)
+constexpr int SS_TW = 32, SS_TH = 32;            // output tile (one block of 256 threads, 4 outputs each)
 constexpr int SS_R = 5;                          // window radius
 constexpr int SS_HW = SS_TW + 2 * SS_R;          // 42 halo columns
-constexpr int SS_HH = SS_TH + 2 * SS_R;          // 26 halo rows
-constexpr int SS_PX = SS_HW + 1;                 // halo row pitch (conflict-free for the 4-wide strips)
-constexpr int SS_PH = SS_TW + 1;                 // row-filtered pitch
+constexpr int SS_HH = SS_TH + 2 * SS_R;          // 42 halo rows
+constexpr int SS_PX = SS_HW + 2;                 // halo row pitch: 44 floats, rows stay 16-byte aligned
+constexpr int SS_PH = SS_TW + 4;                 // row-filtered pitch: 36 floats
 constexpr int SS_THREADS = 256;
+constexpr int SS_ROW_ITEMS = SS_HH * (SS_TW / 4);  // (halo row, group of 4 output columns)
 
 struct SsimWindow { float g[11]; };
 
@@ -37,39 +38,80 @@ static SsimWindow make_window() {
   return w;
 }
 
-__device__ __forceinline__ void load_halo(const float* __restrict__ img, int H, int W, int x0, int y0,
-                                          float (*s)[SS_PX], unsigned tid) {
-  for (int e = tid; e < SS_HH * SS_HW; e += SS_THREADS) {
-    const int r = e / SS_HW, c = e - r * SS_HW;
-    const int y = y0 + r - SS_R, x = x0 + c - SS_R;
-    s[r][c] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(img + (size_t)y * W + x) : 0.f;
+// Zero-padded halos of N planes that share their geometry (the two images forward, the three derivative
+// maps backward).  A warp owns halo rows warp, warp + 8, ...; a lane the columns lane and lane + 32, so there
+// is no index arithmetic per element and all global loads of the block are in flight before the first store.
+// The two pad columns of each row are zeroed (they are loaded by the 16-byte row loads, never used).
+template <int N>
+__device__ __forceinline__ void load_halos(const float* const (&src)[N], int H, int W, int x0, int y0,
+                                           float (*const (&dst)[N])[SS_PX], unsigned tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  const int xa = x0 - SS_R + lane, xb = xa + 32;
+  const bool va = xa >= 0 && xa < W;
+  const bool vb = lane + 32 < SS_HW && xb >= 0 && xb < W;
+  constexpr int ROWS = (SS_HH + 7) / 8;
+  float a[N][ROWS], b[N][ROWS];
+#pragma unroll
+  for (int i = 0; i < ROWS; i++) {
+    const int r = warp + 8 * i;
+    const int y = y0 + r - SS_R;
+    const bool rok = r < SS_HH && y >= 0 && y < H;
+    const size_t ro = (size_t)(rok ? y : 0) * W;
+#pragma unroll
+    for (int n = 0; n < N; n++) {
+      a[n][i] = (rok && va) ? __ldg(src[n] + ro + xa) : 0.f;
+      b[n][i] = (rok && vb) ? __ldg(src[n] + ro + xb) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < ROWS; i++) {
+    const int r = warp + 8 * i;
+    if (r < SS_HH) {
+#pragma unroll
+      for (int n = 0; n < N; n++) {
+        dst[n][r][lane] = a[n][i];
+        if (lane + 32 < SS_PX) dst[n][r][lane + 32] = b[n][i];
+      }
+    }
   }
 }
 
-// Register-blocked separable filter.  Row pass: a thread filters 4 adjacent outputs of one halo row from
-// 14 inputs held in registers (208 of the 256 threads); column pass: a thread filters 2 vertically
-// adjacent outputs of one column from 12 row-filtered values.  Shared-memory loads per output drop from
-// 22 (one per tap and image) to ~7, which is what bounded the first version (issue-bound on LDS).
+// 16 consecutive halo values of one row starting at a column that is a multiple of 4 (four 16-byte loads)
+__device__ __forceinline__ void load16(const float* row, float (&v)[16]) {
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const float4 t = *reinterpret_cast<const float4*>(row + 4 * q);
+    v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+  }
+}
+
+// Register-blocked separable filter on a 32x32 output tile.  Row pass: a work item filters 4 adjacent
+// outputs of one halo row from 14 inputs fetched with four 16-byte shared loads per image (336 items over
+// 256 threads); column pass: a thread filters 4 vertically adjacent outputs of one column from 14 row-filtered
+// values.  Per output ~2.5 shared loads per filtered quantity instead of 22 (one per tap and image).
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ target, SsimWindow win,
                 double* __restrict__ accum /* [n][2] */, float* __restrict__ maps /* [3][planes][H][W] or null */,
                 size_t plane_count) {
-  __shared__ float s_x[SS_HH][SS_PX];
-  __shared__ float s_y[SS_HH][SS_PX];
-  __shared__ float s_h[5][SS_HH][SS_PH];
+  __shared__ __align__(16) float s_x[SS_HH][SS_PX];
+  __shared__ __align__(16) float s_y[SS_HH][SS_PX];
+  __shared__ __align__(16) float s_h[5][SS_HH][SS_PH];
   __shared__ float s_red[2][SS_THREADS / 32];
   const unsigned tid = threadIdx.x;
   const size_t plane = blockIdx.z;  // image * 3 + channel
   const size_t HW = (size_t)H * W;
   const int x0 = blockIdx.x * SS_TW, y0 = blockIdx.y * SS_TH;
-  load_halo(img + plane * HW, H, W, x0, y0, s_x, tid);
-  load_halo(target + plane * HW, H, W, x0, y0, s_y, tid);
+  {
+    const float* const src[2] = {img + plane * HW, target + plane * HW};
+    float (*const dst[2])[SS_PX] = {s_x, s_y};
+    load_halos<2>(src, H, W, x0, y0, dst, tid);
+  }
   __syncthreads();
-  if (tid < SS_HH * (SS_TW / 4)) {
-    const int r = tid / (SS_TW / 4), c0 = (tid % (SS_TW / 4)) * 4;
-    float xv[14], yv[14];
-#pragma unroll
-    for (int k = 0; k < 14; k++) { xv[k] = s_x[r][c0 + k]; yv[k] = s_y[r][c0 + k]; }
+  for (int item = tid; item < SS_ROW_ITEMS; item += SS_THREADS) {
+    const int r = item / (SS_TW / 4), c0 = (item % (SS_TW / 4)) * 4;
+    float xv[16], yv[16];
+    load16(&s_x[r][c0], xv);
+    load16(&s_y[r][c0], yv);
     float a[5][4];
 #pragma unroll
     for (int q = 0; q < 5; q++)
@@ -94,29 +136,28 @@ ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __rest
     }
 #pragma unroll
     for (int q = 0; q < 5; q++)
-#pragma unroll
-      for (int o = 0; o < 4; o++) s_h[q][r][c0 + o] = a[q][o];
+      *reinterpret_cast<float4*>(&s_h[q][r][c0]) = make_float4(a[q][0], a[q][1], a[q][2], a[q][3]);
   }
   __syncthreads();
-  const int tx = tid & 31, ty0 = (tid >> 5) * 2;
-  float f[5][2];
+  const int tx = tid & 31, ty0 = (tid >> 5) * 4;
+  float f[5][4];
 #pragma unroll
   for (int q = 0; q < 5; q++) {
-    float v[12];
+    float v[14];
 #pragma unroll
-    for (int k = 0; k < 12; k++) v[k] = s_h[q][ty0 + k][tx];
-    float b0 = 0.f, b1 = 0.f;
+    for (int k = 0; k < 14; k++) v[k] = s_h[q][ty0 + k][tx];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      b0 = fmaf(win.g[k], v[k], b0);
-      b1 = fmaf(win.g[k], v[k + 1], b1);
+    for (int o = 0; o < 4; o++) {
+      float b = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; k++) b = fmaf(win.g[k], v[k + o], b);
+      f[q][o] = b;
     }
-    f[q][0] = b0; f[q][1] = b1;
   }
   float ssim_sum = 0.f, l1_sum = 0.f;
   const int x = x0 + tx;
 #pragma unroll
-  for (int o = 0; o < 2; o++) {
+  for (int o = 0; o < 4; o++) {
     const int y = y0 + ty0 + o;
     if (x < W && y < H) {
       const float mu1 = f[0][o], mu2 = f[1][o], e11 = f[2][o], e22 = f[3][o], e12 = f[4][o];
@@ -170,50 +211,54 @@ __global__ void __launch_bounds__(SS_THREADS)
 ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ target, SsimWindow win,
                 const float* __restrict__ maps, size_t plane_count, float k_l1, float k_ssim,
                 float* __restrict__ dL_dimg) {
-  __shared__ float s_m[3][SS_HH][SS_PX];
-  __shared__ float s_h[3][SS_HH][SS_PH];
+  __shared__ __align__(16) float s_m[3][SS_HH][SS_PX];
+  __shared__ __align__(16) float s_h[3][SS_HH][SS_PH];
   const unsigned tid = threadIdx.x;
   const size_t plane = blockIdx.z;
   const size_t HW = (size_t)H * W;
   const int x0 = blockIdx.x * SS_TW, y0 = blockIdx.y * SS_TH;
-#pragma unroll
-  for (int m = 0; m < 3; m++) load_halo(maps + (m * plane_count + plane) * HW, H, W, x0, y0, s_m[m], tid);
+  {
+    const float* const src[3] = {maps + plane * HW, maps + (plane_count + plane) * HW, maps + (2 * plane_count + plane) * HW};
+    float (*const dst[3])[SS_PX] = {s_m[0], s_m[1], s_m[2]};
+    load_halos<3>(src, H, W, x0, y0, dst, tid);
+  }
   __syncthreads();
-  if (tid < SS_HH * (SS_TW / 4)) {
-    const int r = tid / (SS_TW / 4), c0 = (tid % (SS_TW / 4)) * 4;
+  for (int item = tid; item < SS_ROW_ITEMS; item += SS_THREADS) {
+    const int r = item / (SS_TW / 4), c0 = (item % (SS_TW / 4)) * 4;
 #pragma unroll
     for (int m = 0; m < 3; m++) {
-      float v[14];
-#pragma unroll
-      for (int k = 0; k < 14; k++) v[k] = s_m[m][r][c0 + k];
+      float v[16];
+      load16(&s_m[m][r][c0], v);
+      float acc[4];
 #pragma unroll
       for (int o = 0; o < 4; o++) {
-        float acc = 0.f;
+        float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 11; k++) acc = fmaf(win.g[k], v[o + k], acc);
-        s_h[m][r][c0 + o] = acc;
+        for (int k = 0; k < 11; k++) t = fmaf(win.g[k], v[o + k], t);
+        acc[o] = t;
       }
+      *reinterpret_cast<float4*>(&s_h[m][r][c0]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
     }
   }
   __syncthreads();
-  const int tx = tid & 31, ty0 = (tid >> 5) * 2;
-  float b[3][2];
+  const int tx = tid & 31, ty0 = (tid >> 5) * 4;
+  float b[3][4];
 #pragma unroll
   for (int m = 0; m < 3; m++) {
-    float v[12];
+    float v[14];
 #pragma unroll
-    for (int k = 0; k < 12; k++) v[k] = s_h[m][ty0 + k][tx];
-    float b0 = 0.f, b1 = 0.f;
+    for (int k = 0; k < 14; k++) v[k] = s_h[m][ty0 + k][tx];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      b0 = fmaf(win.g[k], v[k], b0);
-      b1 = fmaf(win.g[k], v[k + 1], b1);
+    for (int o = 0; o < 4; o++) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; k++) t = fmaf(win.g[k], v[k + o], t);
+      b[m][o] = t;
     }
-    b[m][0] = b0; b[m][1] = b1;
   }
   const int x = x0 + tx;
 #pragma unroll
-  for (int o = 0; o < 2; o++) {
+  for (int o = 0; o < 4; o++) {
     const int y = y0 + ty0 + o;
     if (x >= W || y >= H) continue;
     const size_t off = plane * HW + (size_t)y * W + x;

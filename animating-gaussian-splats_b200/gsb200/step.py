@@ -103,12 +103,13 @@ class HostFeed:
     def step(self, cams, bg, stats=None, after=None):
         """One end-to-end step.  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
         loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix)."""
-        from . import scene
+        from . import optim
         k = self.k
         raw, tgt = self.bufs[k % 2]
         torch.cuda.current_stream(self.dev).wait_event(self.ready[k % 2])
         self._prefetch(k + 1)
-        act = {key: v.contiguous() for key, v in scene.activate(raw).items()}
+        rot, opa, sca = optim.activate(raw)   # one launch (gsb_activate)
+        act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
         loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats)
         if after is not None:
             after(loss_stats, grads, radii, st)

@@ -220,12 +220,17 @@ def run_ours(args):
     sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.begin()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     e0.record()
-    for _ in range(args.steps):
+    marks[0].record()
+    for k in range(args.steps):
         loss_stats, grads, st = one_step(act)
+        marks[k + 1].record()
     e1.record()
     sync_all()
     sampler.end()
+    per_step = [marks[k].elapsed_time(marks[k + 1]) for k in range(args.steps)]
+    print("per-step ms:", " ".join(f"{x:.2f}" for x in per_step), file=sys.stderr)
     ms = e0.elapsed_time(e1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
