@@ -104,7 +104,7 @@ struct GeomLayout {
     float* depths = k.take<float>(n);
     int32_t* radii = k.take<int32_t>(n);
     float* means2D = k.take<float>(2 * n);
-    float* cov3D = k.take<float>(6 * n);
+    float* cov3D = k.take<float>(6 * (size_t)P);   // shared by the cameras of the batch
     float* conic = k.take<float>(4 * n);
     uint32_t* tt = k.take<uint32_t>(n);
     uint32_t* go = k.take<uint32_t>(n);

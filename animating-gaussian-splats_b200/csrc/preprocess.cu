@@ -150,7 +150,9 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
       const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
       cov3d_from_scale_rot(s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1], s_scale[3 * threadIdx.x + 2],
                            mod, q, c);
-      float2* dst = reinterpret_cast<float2*>(cov3D + 6 * o);
+      // one table for the whole batch: the covariance does not depend on the camera (every camera that sees the
+      // Gaussian writes the same six values)
+      float2* dst = reinterpret_cast<float2*>(cov3D + 6 * (size_t)idx);
       dst[0] = make_float2(c[0], c[1]);
       dst[1] = make_float2(c[2], c[3]);
       dst[2] = make_float2(c[4], c[5]);
@@ -304,6 +306,14 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
   float gm[3] = {0.f, 0.f, 0.f};
   float gc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   bool any = false;
+  // the 3D covariance does not depend on the camera: one row per Gaussian (cov_cam_stride is 0)
+  float cov3D[6];
+  {
+    const float* cp6 = cov3Ds + 6 * (size_t)idx;
+#pragma unroll
+    for (int k = 0; k < 6; k++) cov3D[k] = __ldg(cp6 + k);
+  }
+  (void)cov_cam_stride;
   for (int cam = 0; cam < n_cams; cam++) {
     const size_t o = (size_t)cam * P + idx;
     if (!(radii[o] > 0)) continue;
@@ -312,7 +322,6 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float* proj = view + 16;
     const CamParams cp = cams[cam];
     const float h_x = cp.focal_x, h_y = cp.focal_y;
-    const float* cov3D = cov3Ds + 6 * (cam * cov_cam_stride + (size_t)idx);
     const float4 dcon = __ldg(reinterpret_cast<const float4*>(dL_dconic) + o);
     const float dA = dcon.x, dB = dcon.y, dC = dcon.w;  // slot z is never written (cr/backward.cu:165)
 
@@ -438,8 +447,7 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
   if (smem > 40 * 1024) return GSB_EINVAL;  // <= 320 cameras per batch
   preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, smem, st>>>(
       a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
-      a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D,
-      a.cov3D_precomp ? (size_t)0 : (size_t)a.P, dL_dmean2D, dL_dconic, dL_dmean3D,
+      a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0, dL_dmean2D, dL_dconic, dL_dmean3D,
       dL_dcov3D, dL_dscale, dL_drot);
   GSB_LAUNCH_CHECK();
   return GSB_OK;

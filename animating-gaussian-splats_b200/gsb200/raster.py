@@ -41,7 +41,7 @@ class RasterState:
             "depths": self._view(c.depths, self.geom, torch.float32, (n, P)),
             "radii": self._view(c.radii, self.geom, torch.int32, (n, P)),
             "means2D": self._view(c.means2D, self.geom, torch.float32, (n, P, 2)),
-            "cov3D": self._view(c.cov3D, self.geom, torch.float32, (n, P, 6)),
+            "cov3D": self._view(c.cov3D, self.geom, torch.float32, (1, P, 6)).expand(n, P, 6),
             "conic_opacity": self._view(c.conic_opacity, self.geom, torch.float32, (n, P, 4)),
             "tiles_touched": self._view(c.tiles_touched, self.geom, torch.int32, (n, P)),
             "point_offsets": self._view(c.point_offsets, self.geom, torch.int32, (n, P)),

@@ -73,7 +73,7 @@ typedef struct gsb_raster_ctx {
   int32_t P, n_cams, width, height, tiles_x, tiles_y;
   int32_t sort_bits;         /* 32 + getHigherMsb(tiles): what the reference passes to SortPairs */
   int32_t tile_bits;         /* getHigherMsb(tiles per camera): bits sorted at instance granularity */
-  /* geometry state, [n_cams][P] each (cr/rasterizer_impl.h:31-45) */
+  /* geometry state, [n_cams][P] each (cr/rasterizer_impl.h:31-45); cov3D is [P][6], one table for all cameras */
   float* depths; int32_t* radii; float* means2D; float* cov3D; float* conic_opacity;
   uint32_t* tiles_touched;
   uint32_t* gauss_order;     /* Gaussian index per sorted slot: camera-major, depth-ascending, stable;
