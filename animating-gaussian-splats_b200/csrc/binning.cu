@@ -186,25 +186,44 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
   if (slot >= total) { end = last_end; start = last_end; }
   const uint32_t warp_start = __shfl_sync(0xffffffffu, start, 0);
   const uint32_t warp_end = last_end;
+  // owner of output position i = number of lanes whose `end` <= i (ends are non-decreasing).  When every lane
+  // of the warp owns at least one instance the ends are distinct, so that count is a population count over
+  // the bit set of ends that fall into the current 32-wide window (one warp OR-reduction); warps holding empty
+  // slots (culled Gaussians at the tail of a camera) take a 5-step shuffle search instead.
+  const bool has_empty = __any_sync(0xffffffffu, end == start);
+  const uint32_t xy0 = x0 | (y0 << 16);
+  const float inv_w = __frcp_rn((float)w);
   for (uint32_t b = warp_start; b < warp_end; b += 32) {
     const uint32_t i = b + lane;
-    // owner = number of lanes whose `end` <= i  (ends are non-decreasing)
-    unsigned j = 0;
+    unsigned j;
+    if (!has_empty) {
+      const uint32_t rel = end - b;                      // wraps for ends before the window
+      const unsigned before = __popc(__ballot_sync(0xffffffffu, end <= b));
+      const unsigned bits = __reduce_or_sync(0xffffffffu, (end > b && rel <= 32u) ? (1u << (rel - 1u)) : 0u);
+      // bit t set: some lane ends at b + t + 1, i.e. it owns position b + t but not b + t + 1
+      j = before + __popc(bits & ((1u << lane) - 1u));
+    } else {
+      j = 0;
 #pragma unroll
-    for (int step = 16; step >= 1; step >>= 1) {
-      const uint32_t e = __shfl_sync(0xffffffffu, end, (j + step - 1) & 31u);
-      if (e <= i) j += step;
+      for (int step = 16; step >= 1; step >>= 1) {
+        const uint32_t e = __shfl_sync(0xffffffffu, end, (j + step - 1) & 31u);
+        if (e <= i) j += step;
+      }
     }
     j &= 31u;
     const uint32_t s = __shfl_sync(0xffffffffu, start, j);
-    const uint32_t ox = __shfl_sync(0xffffffffu, x0, j);
-    const uint32_t oy = __shfl_sync(0xffffffffu, y0, j);
+    const uint32_t oxy = __shfl_sync(0xffffffffu, xy0, j);
     const uint32_t ow = __shfl_sync(0xffffffffu, w, j);
+    const float oinv = __shfl_sync(0xffffffffu, inv_w, j);
     const uint32_t og = __shfl_sync(0xffffffffu, gidx, j);
     if (i < warp_end) {
       const uint32_t k = i - s;
-      const uint32_t ry = k / ow, rx = k - ry * ow;
-      tile_keys[i] = (uint16_t)((oy + ry) * (uint32_t)gx + (ox + rx));
+      // k / ow by reciprocal multiplication with an exact fix-up (k < 65536 tiles)
+      uint32_t ry = __float2uint_rz(__uint2float_rn(k) * oinv);
+      int rx = (int)k - (int)(ry * ow);
+      if (rx < 0) { ry--; rx += (int)ow; }
+      else if (rx >= (int)ow) { ry++; rx -= (int)ow; }
+      tile_keys[i] = (uint16_t)(((oxy >> 16) + ry) * (uint32_t)gx + ((oxy & 0xFFFFu) + (uint32_t)rx));
       vals[i] = og;
     }
   }
