@@ -299,9 +299,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float bg_dot = 0.f;
   bg_dot += bg[0] * dpx0; bg_dot += bg[1] * dpx1; bg_dot += bg[2] * dpx2;
   float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // accum_rec
-  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;       // last_color
-  float last_alpha = 0.f;
-  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+  const float nTf_bg = -T_final * bg_dot;
 
   // this lane's gradient slot: lanes 0,4,..,28 own the 8 reduced components, lane 1 the opacity gradient
   float* lane_base;
@@ -379,29 +377,31 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         rcp = fmaf(rcp, fmaf(-om, rcp, 1.f), rcp);
         T = T * rcp;
         const float dchannel_dcolor = alpha * T;
-        float dL_dalpha = 0.0f;
-        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = ci.x;
-        dL_dalpha += (ci.x - ar0) * dpx0;
-        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = ci.y;
-        dL_dalpha += (ci.y - ar1) * dpx1;
-        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = ci.z;
-        dL_dalpha += (ci.z - ar2) * dpx2;
+        // accum_rec of cr/backward.cu:515 is kept up to date eagerly: after this entry it becomes
+        // alpha c + (1 - alpha) accum_rec = accum_rec + alpha (c - accum_rec), the value the reference forms at the
+        // next contributing entry from last_alpha / last_color.
+        const float d0 = ci.x - ar0, d1 = ci.y - ar1, d2 = ci.z - ar2;
+        float dL_dalpha = d0 * dpx0;
+        dL_dalpha = fmaf(d1, dpx1, dL_dalpha);
+        dL_dalpha = fmaf(d2, dpx2, dL_dalpha);
+        ar0 = fmaf(alpha, d0, ar0);
+        ar1 = fmaf(alpha, d1, ar1);
+        ar2 = fmaf(alpha, d2, ar2);
         v[0] = dchannel_dcolor * dpx0;
         v[1] = dchannel_dcolor * dpx1;
         v[2] = dchannel_dcolor * dpx2;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final * rcp) * bg_dot;
-        const float dL_dG = co2.w * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * co2.x - gdy * co2.y;
-        const float dG_ddely = -gdy * co2.z - gdx * co2.y;
-        v[3] = dL_dG * dG_ddelx * ddelx_dx;
-        v[4] = dL_dG * dG_ddely * ddely_dy;
-        v[5] = -0.5f * gdx * dx * dL_dG;
-        v[6] = -0.5f * gdx * dy * dL_dG;
-        v[7] = -0.5f * gdy * dy * dL_dG;
+        dL_dalpha = fmaf(dL_dalpha, T, nTf_bg * rcp);   // T (...) - T_final / (1 - alpha) * sum_c bg_c dL/dpix_c
+        // First and second moments of w = dL/dG * G over the pixels; the linear maps to dL/dmean2D
+        // (-ddelx_dx (A S1 + B S2), -ddely_dy (C S2 + B S1)) and dL/dconic (-0.5 q) are applied once per
+        // Gaussian in preprocess_bwd instead of once per pixel here (cr/backward.cu:536-548).
         g_op = G * dL_dalpha;
+        const float wg = co2.w * g_op;
+        const float s1 = wg * dx, s2 = wg * dy;
+        v[3] = s1;
+        v[4] = s2;
+        v[5] = s1 * dx;
+        v[6] = s1 * dy;
+        v[7] = s2 * dy;
       }
       warp_reduce8(v, lane);
 #pragma unroll

@@ -54,7 +54,7 @@ int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const
                       int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                          const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
+                          float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st);
 
 size_t scan_scratch_bytes(int64_t n);

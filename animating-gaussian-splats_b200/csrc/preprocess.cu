@@ -288,7 +288,8 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       const float* __restrict__ scales, const float* __restrict__ rotations,
                       const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
                       const CamParams* __restrict__ cams, const int32_t* __restrict__ radii,
-                      const float* __restrict__ cov3Ds, size_t cov_cam_stride, const float* __restrict__ dL_dmean2D,
+                      const float* __restrict__ cov3Ds, size_t cov_cam_stride,
+                      const float4* __restrict__ conic_opacity, float* __restrict__ dL_dmean2D,
                       const float* __restrict__ dL_dconic, float* __restrict__ dL_dmean3D,
                       float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
   extern __shared__ float s_mats[];  // [n_cams][32]: view then proj
@@ -322,8 +323,16 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float* proj = view + 16;
     const CamParams cp = cams[cam];
     const float h_x = cp.focal_x, h_y = cp.focal_y;
+    // the blend kernel leaves raw pixel moments of w = dL/dG * G: (S1, S2) in dL_dmean2D, (S1 dx, S1 dy, -, S2 dy)
+    // in dL_dconic; their linear maps to the gradients (cr/backward.cu:536-548) are applied here, once per Gaussian
     const float4 dcon = __ldg(reinterpret_cast<const float4*>(dL_dconic) + o);
-    const float dA = dcon.x, dB = dcon.y, dC = dcon.w;  // slot z is never written (cr/backward.cu:165)
+    const float4 con = __ldg(conic_opacity + o);
+    const float dA = -0.5f * dcon.x, dB = -0.5f * dcon.y, dC = -0.5f * dcon.w;  // slot z is never written (cr/backward.cu:165)
+    const float rs1 = dL_dmean2D[3 * o], rs2 = dL_dmean2D[3 * o + 1];
+    const float g2x = -(0.5f * W) * (con.x * rs1 + con.y * rs2);
+    const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
+    dL_dmean2D[3 * o] = g2x;
+    dL_dmean2D[3 * o + 1] = g2y;
 
     // computeCov2DCUDA (cr/backward.cu:144-274)
     float tx = view[0] * mx + view[4] * my + view[8] * mz + view[12];
@@ -385,7 +394,6 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float m_w = 1.0f / (m_hw + 0.0000001f);
     const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
     const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
-    const float g2x = __ldg(dL_dmean2D + 3 * o), g2y = __ldg(dL_dmean2D + 3 * o + 1);
     dmx += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
     dmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
     dmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
@@ -440,14 +448,15 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
 }
 
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
-                          const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
+                          float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st) {
   if (a.P <= 0) return GSB_OK;
   const size_t smem = (size_t)a.n_cams * 32 * sizeof(float);
   if (smem > 40 * 1024) return GSB_EINVAL;  // <= 320 cameras per batch
   preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, smem, st>>>(
       a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
-      a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0, dL_dmean2D, dL_dconic, dL_dmean3D,
+      a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
+      reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
       dL_dcov3D, dL_dscale, dL_drot);
   GSB_LAUNCH_CHECK();
   return GSB_OK;

@@ -113,7 +113,8 @@ int gsb_raster_forward(const gsb_raster_args* args, gsb_alloc_fn geom_alloc, gsb
 
 /* Rasterizer::backward (cr/rasterizer.h:56-83, cr/rasterizer_impl.cu:343-436).
  * dL_dpix [n_cams][3][H][W].  Outputs (all written in full, no pre-zeroing required):
- *   dL_dmean2D [n_cams][P][3] (z = 0), dL_dconic [n_cams][P][4] (slot 2 = 0),
+ *   dL_dmean2D [n_cams][P][3] (z = 0), dL_dconic [n_cams][P][4] (scratch: on return it holds the raw second
+ *   moments sum_pixels dL/dG G (dx dx, dx dy, -, dy dy); dL/dconic = -0.5 x these, consumed internally),
  *   dL_dopacity [P], dL_dcolor [P][3] (or [n_cams][P][3] if color_cam_stride != 0),
  *   dL_dmean3D [P][3], dL_dcov3D [P][6] (n_cams==1 only, else may be NULL), dL_dscale [P][3], dL_drot [P][4]
  * summed over the cameras of the batch. */
