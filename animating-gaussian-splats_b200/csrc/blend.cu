@@ -269,6 +269,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
   __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
   __shared__ int s_block_last;
+  __shared__ int s_warp_last[GSB_BLOCK_SIZE / 32];
 
   const int cam = blockIdx.z;
   const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
@@ -319,7 +320,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   for (int s = 16; s >= 1; s >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, s));
   if (tid == 0) s_block_last = 0;
   __syncthreads();
-  if (lane == 0 && warp_last > 0) atomicMax(&s_block_last, warp_last);
+  if (lane == 0) {
+    s_warp_last[tid >> 5] = warp_last;
+    if (warp_last > 0) atomicMax(&s_block_last, warp_last);
+  }
   __syncthreads();
   const int block_last = s_block_last;   // list positions [0, block_last) matter
   if (block_last == 0) return;
@@ -339,6 +343,15 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       xy = means2D[cam_off + id];
       co = conic_opacity[cam_off + id];
       keep = tile_cull_keep<true>(xy.x, xy.y, co, tx0, ty0, thr);
+      if (keep) {
+        // fold "behind warp w's deepest contributor" into the patch mask, so the walk tests one bit per entry
+        unsigned m = __float_as_uint(thr) & 0xFFu;
+#pragma unroll
+        for (int w = 0; w < GSB_BLOCK_SIZE / 32; w++)
+          if (pos_mine >= s_warp_last[w]) m &= ~(1u << w);
+        thr = pack_thr(thr, m);
+        keep = m != 0;
+      }
     }
     int slot;
     const int n = compact_slot(keep, tid, s_wcnt, slot);
@@ -352,8 +365,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int j = 0; j < n; j++) {
       const float4 a = s_a[j];
       const int pos = __float_as_int(a.w);
-      if (pos >= warp_last) continue;            // warp-uniform: behind this warp's deepest contributor
-      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;   // cannot reach this warp's 8x4 patch
+      // warp-uniform: the entry cannot reach this warp's 8x4 patch, or lies behind its deepest contributor
+      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
       const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
