@@ -145,14 +145,15 @@ seg_tile_hist_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------
-// K2: one block per segment.  chunk_tot -> chunk_base (exclusive over the segment's chunks, in place);
+// K2: one block per segment.  chunk_tot -> chunk_base (exclusive over the segment's chunks);
 // digit_base[seg][d] = seg_start[seg] + exclusive scan over the digits of the segment's totals;
 // totals[seg][d] = the segment's count of digit d.
 // ------------------------------------------------------------------------------------------------
 template <int LOG_NB>
 __global__ void __launch_bounds__(LOG_NB >= 10 ? 1024 : (1 << LOG_NB) < 32 ? 32 : (1 << LOG_NB))
 seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
-                      uint32_t* __restrict__ chunk_tot, uint32_t* __restrict__ digit_base, uint32_t* __restrict__ totals) {
+                      const uint32_t* __restrict__ chunk_tot, uint32_t* __restrict__ chunk_base,
+                      uint32_t* __restrict__ digit_base, uint32_t* __restrict__ totals) {
   constexpr int NB = 1 << LOG_NB;
   constexpr int THREADS = LOG_NB >= 10 ? 1024 : NB < 32 ? 32 : NB;
   constexpr int D = NB / THREADS > 0 ? NB / THREADS : 1;
@@ -166,13 +167,28 @@ seg_chunk_scan_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __
 #pragma unroll
   for (int k = 0; k < D; k++) run[k] = 0;
   if (act) {
-#pragma unroll 8
-    for (uint32_t c = c0; c < c1; c++) {
-      uint32_t* row = chunk_tot + (size_t)c * NB + tid * D;
+    // reads and writes go to different arrays so that the loads of the next chunks are in flight while the
+    // running sums of this one are stored (an in-place scan serialised one memory round trip per chunk)
+    uint32_t c = c0;
+    for (; c + 8 <= c1; c += 8) {
+      uint32_t v[8][D];
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+#pragma unroll
+        for (int k = 0; k < D; k++) v[u][k] = __ldg(chunk_tot + (size_t)(c + u) * NB + tid * D + k);
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+#pragma unroll
+        for (int k = 0; k < D; k++) {
+          chunk_base[(size_t)(c + u) * NB + tid * D + k] = run[k];
+          run[k] += v[u][k];
+        }
+    }
+    for (; c < c1; c++) {
 #pragma unroll
       for (int k = 0; k < D; k++) {
-        const uint32_t v = row[k];
-        row[k] = run[k];
+        const uint32_t v = __ldg(chunk_tot + (size_t)c * NB + tid * D + k);
+        chunk_base[(size_t)c * NB + tid * D + k] = run[k];
         run[k] += v;
       }
     }
@@ -472,13 +488,13 @@ static inline int64_t ss_max_chunks(int64_t n_upper, int n_seg) {
   return (n_upper + (int64_t)SS_TILE * SS_CHUNK - 1) / ((int64_t)SS_TILE * SS_CHUNK) + n_seg;
 }
 
-// temp: tile_cnt u16 [max_tiles][NB] | chunk_base u32 [max_chunks][NB] | digit_base u32 [n_seg][NB] |
-//       totals u32 [n_seg][NB]; reused by every pass.  Nothing needs zeroing.
+// temp: tile_cnt u16 [max_tiles][NB] | chunk_tot u32 [max_chunks][NB] | chunk_base u32 [max_chunks][NB] |
+//       digit_base u32 [n_seg][NB] | totals u32 [n_seg][NB]; reused by every pass.  Nothing needs zeroing.
 size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int passes, int log_nb) {
   (void)passes;
   const size_t nb = (size_t)1 << log_nb;
   return align_up((size_t)ss_max_tiles(n_upper, n_seg) * nb * 2, 256) +
-         align_up((size_t)ss_max_chunks(n_upper, n_seg) * nb * 4, 256) + 2 * align_up((size_t)n_seg * nb * 4, 256);
+         2 * align_up((size_t)ss_max_chunks(n_upper, n_seg) * nb * 4, 256) + 2 * align_up((size_t)n_seg * nb * 4, 256);
 }
 
 int launch_seg_setup(int n_seg, int mode, int len, const uint32_t* offsets, uint32_t* seg_start, uint32_t* seg_tile0,
@@ -512,6 +528,8 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
   char* t = reinterpret_cast<char*>(temp);
   uint16_t* tile_cnt = reinterpret_cast<uint16_t*>(t);
   t += align_up((size_t)max_tiles * NB * 2, 256);
+  uint32_t* chunk_tot = reinterpret_cast<uint32_t*>(t);
+  t += align_up((size_t)max_chunks * NB * 4, 256);
   uint32_t* chunk_base = reinterpret_cast<uint32_t*>(t);
   t += align_up((size_t)max_chunks * NB * 4, 256);
   uint32_t* digit_base = reinterpret_cast<uint32_t*>(t);
@@ -529,9 +547,10 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
     KeyT* b = (last && !want_keys) ? nullptr : (to_out ? k_out : k_alt);
     uint32_t* vb = to_out ? v_out : v_alt;
     seg_tile_hist_kernel<KeyT, LOG_NB><<<(unsigned)max_chunks, SS_THREADS, 0, st>>>(seg_start, seg_tile0, n_seg, a, shift,
-                                                                                   dmask, tile_cnt, chunk_base);
+                                                                                   dmask, tile_cnt, chunk_tot);
     GSB_LAUNCH_CHECK();
-    seg_chunk_scan_kernel<LOG_NB><<<n_seg, LOG_NB >= 10 ? 1024 : std::max(NB, 32), 0, st>>>(seg_start, seg_tile0, n_seg, chunk_base, digit_base, totals);
+    seg_chunk_scan_kernel<LOG_NB><<<n_seg, LOG_NB >= 10 ? 1024 : std::max(NB, 32), 0, st>>>(seg_start, seg_tile0, n_seg, chunk_tot, chunk_base, digit_base,
+                                                                                  totals);
     GSB_LAUNCH_CHECK();
     seg_scatter_kernel<KeyT, LOG_NB, OPT><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
         seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
