@@ -422,7 +422,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
       const uint32_t id2 = __float_as_uint(ci.w);
       const float val = (lane == 1) ? g_op : v[0];
-      if (lane_writes && val != 0.f) atomicAdd(lane_base + (size_t)id2 * lane_stride, val);
+      if (lane_writes && val != 0.f) atomicAdd(lane_base + id2 * lane_stride, val);   // 32-bit index: P * 4 < 2^32
     }
   }
 }
