@@ -11,7 +11,7 @@ scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 tscale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}
 k = {}
 for r in rows[2:]:
-    name = r[ki].split("(")[0].replace("void ", "").replace("gsb::", "")
+    name = r[ki].split("(")[0].split("<")[0].replace("void ", "").replace("gsb::", "")
     full = r[ki]
     if name.startswith("seg_") and "<" in full:
         name = name + "<" + full.split("<", 1)[1].split(">")[0].replace("unsigned short", "u16").replace("unsigned int", "u32").replace("(int)", "").replace("(bool)", "") + ">"
