@@ -82,6 +82,11 @@ SYMBOLS = {
     "gsb_activate": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
     "gsb_activate_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 10),
     "gsb_adam_step": (C.c_int, [C.c_int32, C.POINTER(AdamGroup), C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "gsb_rigidity_loss": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_void_p,
+                                    C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64] +
+                          [C.c_void_p] * 4),
+    "gsb_foreground_info": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 4 + [C.c_int64, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),
     "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }

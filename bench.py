@@ -361,9 +361,78 @@ def run_ours(args):
                 "reference_cuda": densify_shaped(args, "reference_cuda")}
         except Exception as ex:  # never lose the headline line to the extra measurement
             out["densify_loop_shape"] = {"error": repr(ex)[:300]}
+        try:
+            out["rigidity_loss"] = rigidity_shaped(args)
+        except Exception as ex:
+            out["rigidity_loss"] = {"error": repr(ex)[:300]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def rigidity_shaped(args, views=5, iters=20):
+    """the rigidity term of one train.py step (train.py:317-351) -- loss + gradient w.r.t.
+    means and rotation_quaternions for ~60% foreground Gaussians x 20 neighbours.  "ours": gsb200.rigidity, one
+    fused launch per step.  "stock_torch": the same formula in plain torch ops with autograd, evaluated once per
+    sampled view like the reference's loop (train.py:373-377 inside :402-412; 5 views, train.py:753)."""
+    from gsb200 import rigidity as R
+    dev = torch.device("cuda", torch.cuda.current_device())
+    gen = torch.Generator().manual_seed(11)
+    P, K = args.gaussians, 20
+    seg = torch.zeros(P, 3); seg[:, 0] = (torch.rand(P, generator=gen) > 0.4).float(); seg[:, 2] = 1 - seg[:, 0]
+    F = int(seg[:, 0].sum())
+    means = (torch.rand(P, 3, generator=gen) - 0.5) * 3
+    walk = torch.cumsum(0.02 * torch.randn(F, 3, generator=gen), 0)
+    means[seg[:, 0] > 0.5] = walk - walk.mean(0)
+    steps_ = torch.tensor([d for d in range(-10, 11) if d != 0])
+    nbr = torch.arange(F)[:, None] + steps_[None]
+    nbr = torch.where((nbr < 0) | (nbr >= F), torch.arange(F)[:, None] - steps_[None], nbr)
+    base = {"means": means.to(dev), "rotation_quaternions": torch.randn(P, 4, generator=gen).to(dev),
+            "segmentation_masks": seg.to(dev)}
+    ninfo = R.NeighborInfo(weights=torch.rand(F, K, generator=gen).to(dev), indices=nbr.to(dev))
+    prev = R.create_foreground_info(base, ninfo.indices)
+    cur = {"means": (base["means"] + 0.01 * torch.randn(P, 3, device=dev)).requires_grad_(True),
+           "rotation_quaternions": base["rotation_quaternions"].clone().requires_grad_(True),
+           "segmentation_masks": base["segmentation_masks"]}
+    prev_off = prev.offsets_to_neighbors.contiguous()
+    fg = base["segmentation_masks"][:, 0] > 0.5
+
+    def ours():
+        (views * R.calculate_rigidity_loss(cur, ninfo, prev)).backward()
+
+    def stock_one():
+        m = cur["means"][fg]
+        q = torch.nn.functional.normalize(cur["rotation_quaternions"])[fg]
+        a, b = q.unbind(-1), prev.inverted_rotations.unbind(-1)
+        rel = torch.stack([a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3],
+                           a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+                           a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1],
+                           a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]], -1)
+        r, x, y, z = (rel / rel.norm(dim=-1, keepdim=True)).unbind(-1)
+        rot = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                           2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                           2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).reshape(-1, 3, 3)
+        off = m[ninfo.indices] - m[:, None]
+        loc = (rot.transpose(2, 1)[:, None] @ off[..., None]).squeeze(-1)
+        return torch.sqrt(((loc - prev_off) ** 2).sum(-1) * ninfo.weights + 1e-20).mean()
+
+    def stock():
+        torch.stack([stock_one() for _ in range(views)]).sum().backward()
+
+    res = {"what": f"rigidity term of one train.py step: F={F} foreground Gaussians x K={K}, loss + gradients, "
+                   f"{views} views per step", "unit": "ms per step"}
+    for name, fn in (("ours", ours), ("stock_torch", stock)):
+        for _ in range(3):
+            fn()
+        cur["means"].grad = None; cur["rotation_quaternions"].grad = None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        res[name] = e0.elapsed_time(e1) / iters
+        res[name + "_loss"] = float((R.calculate_rigidity_loss(cur, ninfo, prev) if name == "ours" else stock_one()).detach())
+    return res
 
 
 # ------------------------------------------------------------------------------------------------

@@ -196,6 +196,28 @@ typedef struct gsb_adam_group {
 int gsb_adam_step(int32_t n_groups, const gsb_adam_group* groups_host, double beta1, double beta2, double eps,
                   void* stream);
 
+/* Rigidity loss of the per-timestep step (train.py:317-351 with quat_mult :301-308, weighted_l2_loss_v2 :311-315,
+ * build_rotation external.py:27-47): loss = mean_ij sqrt(w_ij |R_i^T (mean_nbr(i,j) - mean_i) - prev_offset_ij|^2
+ * + 1e-20), R_i from normalize(quats_i) (x) prev_inv_rot_i, over F foreground Gaussians x K neighbours.
+ * fg_index[F] maps a foreground Gaussian to its row of the [P,*] tables (NULL = identity); nbr holds neighbour
+ * ids in foreground space.  The per-pair tables are addressed as base[i * stride_i + j * stride_j (+ c *
+ * stride_c)] (strides in elements), so reference-layout [F,K] / [F,K,3] tensors and transposed copies both
+ * work.  *loss (a DEVICE double) receives the loss.  With d_means / d_quats non-NULL the gradients
+ * dloss/dmeans [P,3] and dloss/dquats [P,4] (raw, through the normalisation) are ADDED to them in the same
+ * launch (float atomics for the neighbour shares); pass both or neither. */
+int gsb_rigidity_loss(int32_t F, int32_t K, const int32_t* fg_index, const float* means, const float* quats,
+                      const float* prev_inv_rot, const int32_t* nbr, int64_t nbr_stride_i, int64_t nbr_stride_j,
+                      const float* weights, int64_t w_stride_i, int64_t w_stride_j, const float* prev_offsets,
+                      int64_t prev_stride_i, int64_t prev_stride_j, int64_t prev_stride_c, double* loss,
+                      float* d_means, float* d_quats, void* stream);
+
+/* create_foreground_info (train.py:226-247): inv_rot[F,4] = conjugate of normalize(quats[fg]); offsets
+ * (strided like prev_offsets above) = means[fg][nbr] - means[fg]. */
+int gsb_foreground_info(int32_t F, int32_t K, const int32_t* fg_index, const float* means, const float* quats,
+                        const int32_t* nbr, int64_t nbr_stride_i, int64_t nbr_stride_j, float* inv_rot,
+                        float* offsets, int64_t off_stride_i, int64_t off_stride_j, int64_t off_stride_c,
+                        void* stream);
+
 /* Debug / test accessors: the individual stages, so that tests can compare every intermediate
  * bit-for-bit. */
 int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream);

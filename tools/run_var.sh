@@ -1,2 +1,9 @@
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-for i in 1 2; do python bench.py --steps 10 --no-cpu-baseline --no-reference-cuda 2>gpurun_out/e.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); s=d['stage_ms']; print(round(d['ms_per_step'],3), round(d['e2e']['ms_per_step'],3), 'raster stages', round(sum(s.values()),3), {k: round(v,3) for k,v in s.items() if k in ('depth_sort','sort','render_fwd','render_bwd','preprocess_bwd','duplicate_keys')})"; done
+# scratch: tests + the extra bench legs
+timeout 800 python -m pytest tests/test_rigidity.py -x -q -m gpu 2>&1 | tail -5
+python - <<'P'
+import sys, json
+sys.path[:0]=['/root/repo','/root/repo/animating-gaussian-splats_b200','/root/repo/tests']
+import bench
+class A: gaussians=300000; cams=27; width=640; height=360
+print(json.dumps(bench.rigidity_shaped(A), indent=1))
+P
