@@ -1,0 +1,411 @@
+// gemm.cu -- the dense layers of the DeformationNetwork (train.py:57-110: Linear 192 -> H,
+// residual blocks of Linear H -> H, Linear H -> 7 over ALL Gaussians, N ~ 3e5 rows) on the 5th-generation tensor
+// cores:  Y[rows, N] = X[rows, K] . W[N, K]^T (+ bias), FP32 in HBM, TF32 multiply / FP32 accumulate.
+//
+// This is the only GEMM-shaped work in the product.  With K, N <= 256 the layer is HBM-bound (rows x (K + N) x 4 B
+// against 2 rows K N flop: 128 flop/B at K = N = 256, below the ~170 flop/B TF32 ridge), so the design goal is to
+// stream X once at full bandwidth and keep everything else out of the way:
+//   * persistent kernel, one CTA per SM, each looping over 128-row tiles of X;
+//   * warp 0 / one thread: TMA producer.  X and W tiles ([128 x 32] and [N x 32] floats, 128-byte rows, hardware
+//     128B swizzle) land in a multi-stage shared-memory ring; FP32 data is fed to the tensor core as it is
+//     (kind::tf32 reads the upper 19 bits), so there is no conversion pass over the activations;
+//   * warp 1 / one thread: tcgen05.mma issuer, 128 x N x 8 instructions, accumulator in TMEM, two accumulator
+//     stages (2 x N <= 512 columns) so the epilogue of tile i overlaps the loads and MMAs of tile i + 1;
+//   * warps 2-5: epilogue.  tcgen05.ld 16 columns at a time (lane = row), bias add, 64-byte row stores.
+// W (<= 256 KB) is re-read per tile from L2.  mbarrier pipelines: full/empty per smem stage (TMA <-> MMA),
+// full/empty per accumulator stage (MMA <-> epilogue).
+//
+// gsb_linear_tf32x3 (the same kernel with SPLIT = true) recovers FP32-level accuracy: four extra warps split every
+// landed tile in place into hi = x & ~0x1fff and lo = x - hi (lo in a second buffer with the same swizzled
+// offsets) and the issuer accumulates Xhi Whi + Xhi Wlo + Xlo Whi.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace gsb {
+
+constexpr int GM_BLOCK_M = 128;
+constexpr int GM_BLOCK_K = 32;                      // floats: one 128-byte swizzle row
+constexpr int GM_UMMA_K = 8;                        // tf32: 32 bytes per instruction
+constexpr int GM_A_BYTES = GM_BLOCK_M * GM_BLOCK_K * 4;   // 16 KB
+constexpr int GM_THREADS = 192;                     // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int GM_SPLIT_WARPS = 4;                   // SPLIT only: warps 6-9 split tiles into hi / lo
+constexpr int GM_MAX_STAGES = 8;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
+      "[%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile with 128-byte rows and the 128B swizzle (what TMA SWIZZLE_128B writes): 8-row groups are
+// 1024 bytes apart (SBO), LBO unused, descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                  // leading byte offset (ignored for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;        // stride byte offset
+  d |= (uint64_t)1 << 46;                  // version
+  d |= (uint64_t)2 << 61;                  // SWIZZLE_128B
+  return d;
+}
+
+struct GemmParams {
+  long long rows;
+  int K, N, umma_n, stages, b_bytes;
+  const float* bias;
+  float* Y;
+  long long ldy;
+};
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), 1)
+linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                   const __grid_constant__ CUtensorMap map_wlo, GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES], empty_bar[GM_MAX_STAGES], split_bar[GM_MAX_STAGES];
+  __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_base_s;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // 1024-byte aligned stage ring: [A | B] (+ [A_lo | B_lo] for SPLIT) per stage
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
+  const int k_blocks = (p.K + GM_BLOCK_K - 1) / GM_BLOCK_K;
+  const long long m_tiles = (p.rows + GM_BLOCK_M - 1) / GM_BLOCK_M;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&split_bar[s], GM_SPLIT_WARPS * 32);
+    }
+    for (int s = 0; s < 2; s++) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4 * 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {   // TMEM: 2 accumulator stages of umma_n columns (power of two >= 32)
+    uint32_t cols = 32;
+    while (cols < 2u * p.umma_n) cols <<= 1;
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long t = blockIdx.x; t < m_tiles; t += gridDim.x) {
+        for (int kb = 0; kb < k_blocks; kb++) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a = smem + (size_t)stage * stage_bytes;
+          uint8_t* b = a + GM_A_BYTES;
+          mbar_expect_tx(&full_bar[stage], GM_A_BYTES + p.b_bytes + (SPLIT ? p.b_bytes : 0));
+          tma_load_2d(&map_x, &full_bar[stage], a, kb * GM_BLOCK_K, (int)(t * GM_BLOCK_M));
+          tma_load_2d(&map_w, &full_bar[stage], b, kb * GM_BLOCK_K, 0);
+          if (SPLIT) tma_load_2d(&map_wlo, &full_bar[stage], b + GM_A_BYTES + p.b_bytes, kb * GM_BLOCK_K, 0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      // instruction descriptor: D = F32, A = B = TF32, both K-major, N >> 3, M >> 4
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.umma_n >> 3) << 17) |
+                             ((uint32_t)(GM_BLOCK_M >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = blockIdx.x; t < m_tiles; t += gridDim.x) {
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + (uint32_t)(acc * p.umma_n);
+        for (int kb = 0; kb < k_blocks; kb++) {
+          mbar_wait(SPLIT ? &split_bar[stage] : &full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t b = a + GM_A_BYTES;
+          const uint64_t ad = umma_desc_k_sw128(a), bd = umma_desc_k_sw128(b);
+#pragma unroll
+          for (int k = 0; k < GM_BLOCK_K / GM_UMMA_K; k++) {
+            const uint64_t step = (uint64_t)((k * GM_UMMA_K * 4) >> 4);
+            tc_mma_tf32(d, ad + step, bd + step, idesc, (kb | k) != 0);
+            if (SPLIT) {
+              const uint64_t alo = umma_desc_k_sw128(a + GM_A_BYTES + p.b_bytes) + step;
+              const uint64_t blo = umma_desc_k_sw128(b + GM_A_BYTES + p.b_bytes) + step;
+              tc_mma_tf32(d, ad + step, blo, idesc, 1);
+              tc_mma_tf32(d, alo, bd + step, idesc, 1);
+            }
+          }
+          tc_commit(&empty_bar[stage]);   // frees the smem stage when the MMAs above have read it
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&acc_full[acc]);        // accumulator complete
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp < 6) {
+    // ===== epilogue: TMEM -> registers -> (+ bias) -> global =====
+    const int q = warp & 3;               // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = blockIdx.x; t < m_tiles; t += gridDim.x) {
+      mbar_wait(&acc_full[acc], acc_phase);
+      tc_fence_after();
+      const long long row = t * GM_BLOCK_M + q * 32 + lane;
+      float* yrow = p.Y + row * p.ldy;
+      for (int c = 0; c < p.umma_n; c += 16) {
+        uint32_t v[16];
+        tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.umma_n + c), v);
+        tc_ld_wait();
+        if (row < p.rows) {
+          if (c + 16 <= p.N && (p.ldy & 3) == 0) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+              float4 o = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
+                                     __uint_as_float(v[i + 3]));
+              if (p.bias) {
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + c + i));
+                o.x += bb.x; o.y += bb.y; o.z += bb.z; o.w += bb.w;
+              }
+              *reinterpret_cast<float4*>(yrow + c + i) = o;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; i++)
+              if (c + i < p.N) yrow[c + i] = __uint_as_float(v[i]) + (p.bias ? __ldg(p.bias + c + i) : 0.f);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (SPLIT) {
+    // ===== splitter: X tile -> hi (in place) + lo; the W halves arrive pre-split through TMA =====
+    const int tid = threadIdx.x - GM_THREADS;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long t = blockIdx.x; t < m_tiles; t += gridDim.x) {
+      for (int kb = 0; kb < k_blocks; kb++) {
+        mbar_wait(&full_bar[stage], phase);
+        float4* a = reinterpret_cast<float4*>(smem + (size_t)stage * stage_bytes);
+        float4* alo = reinterpret_cast<float4*>(smem + (size_t)stage * stage_bytes + GM_A_BYTES + p.b_bytes);
+#pragma unroll
+        for (int i = 0; i < GM_A_BYTES / 16 / (GM_SPLIT_WARPS * 32); i++) {
+          const int o = tid + i * GM_SPLIT_WARPS * 32;
+          const float4 x = a[o];
+          float4 h;
+          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
+          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
+          a[o] = h;
+          alo[o] = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+        mbar_arrive(&split_bar[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    uint32_t cols = 32;
+    while (cols < 2u * p.umma_n) cols <<= 1;
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(cols) : "memory");
+  }
+}
+
+}  // namespace gsb
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------
+namespace gsb {
+
+__global__ void split_tf32_kernel(long long n, const float* __restrict__ w, float* __restrict__ hi,
+                                  float* __restrict__ lo) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = w[i];
+  const float h = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  hi[i] = h;
+  lo[i] = x - h;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D FP32 tensor [rows][cols] with row pitch ld (floats), box [box_rows][32 floats], 128B swizzle, zero fill.
+static bool make_map(CUtensorMap* m, const float* base, long long rows, int cols, long long ld, int box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {(cuuint32_t)GM_BLOCK_K, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <bool SPLIT>
+static int launch_linear(long long rows, int K, int N, const float* X, long long ldx, const float* W, long long ldw,
+                         const float* Wlo, const float* bias, float* Y, long long ldy, cudaStream_t st) {
+  GemmParams p;
+  p.rows = rows; p.K = K; p.N = N;
+  p.umma_n = (N + 15) / 16 * 16;
+  p.b_bytes = p.umma_n * GM_BLOCK_K * 4;
+  p.bias = bias; p.Y = Y; p.ldy = ldy;
+  const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
+  const int budget = 200 * 1024;
+  p.stages = budget / stage_bytes;
+  if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
+  if (p.stages < 2) return GSB_EINVAL;
+  CUtensorMap mx, mw, mwlo;
+  if (!make_map(&mx, X, rows, K, ldx, GM_BLOCK_M) || !make_map(&mw, W, N, K, ldw, p.umma_n) ||
+      !make_map(&mwlo, SPLIT ? Wlo : W, N, K, ldw, p.umma_n)) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return GSB_ECUDA;
+  }
+  const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+  auto kern = linear_tf32_kernel<SPLIT>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+    attr_set = true;
+  }
+  const long long m_tiles = (rows + GM_BLOCK_M - 1) / GM_BLOCK_M;
+  const int grid = (int)(m_tiles < sm_count() ? m_tiles : sm_count());
+  kern<<<grid, GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), smem, st>>>(mx, mw, mwlo, p);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+}  // namespace gsb
+
+using namespace gsb;
+
+extern "C" {
+
+static int linear_args_ok(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                          const float* Y, int64_t ldy) {
+  if (rows < 0 || K <= 0 || N <= 0 || N > 256 || rows > 0x7fffffffLL) return 0;
+  if (!X || !W || !Y || ldx < K || ldw < K || ldy < N) return 0;
+  // TMA: 16-byte aligned bases and row pitches
+  if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W)) & 15u) return 0;
+  if ((ldx & 3) || (ldw & 3)) return 0;
+  return 1;
+}
+
+int gsb_linear_tf32(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                    const float* bias, float* Y, int64_t ldy, void* stream) {
+  if (rows == 0) return GSB_OK;
+  if (!linear_args_ok(rows, K, N, X, ldx, W, ldw, Y, ldy)) return GSB_EINVAL;
+  return launch_linear<false>(rows, K, N, X, ldx, W, ldw, nullptr, bias, Y, ldy, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N) { return (size_t)2 * N * K * sizeof(float); }
+
+int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                      const float* bias, float* Y, int64_t ldy, void* scratch, void* stream) {
+  if (rows == 0) return GSB_OK;
+  if (!linear_args_ok(rows, K, N, X, ldx, W, ldw, Y, ldy) || !scratch || ldw != K) return GSB_EINVAL;
+  if (reinterpret_cast<uintptr_t>(scratch) & 15u) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  float* hi = reinterpret_cast<float*>(scratch);
+  float* lo = hi + (size_t)N * K;
+  const long long n = (long long)N * K;
+  split_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, W, hi, lo);
+  GSB_LAUNCH_CHECK();
+  return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, bias, Y, ldy, st);
+}
+
+}  // extern "C"

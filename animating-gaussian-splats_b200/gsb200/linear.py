@@ -1,0 +1,37 @@
+"""Dense layers on the tcgen05 GEMM of csrc/gemm.cu (the DeformationNetwork's nn.Linear
+layers, train.py:57-110).  linear(x, weight, bias) == torch.nn.functional.linear(x, weight, bias) with TF32
+multiplies (precise=False) or the 3xTF32 operand split (precise=True, FP32-level accuracy).  Forward only; CUDA only."""
+import torch
+
+from . import _lib as L
+
+_scratch = {}
+
+
+def linear(x, weight, bias=None, precise=False, out=None):
+    L.require_cuda(x, "x")
+    x = x if (x.dtype == torch.float32 and x.stride(-1) == 1 and x.dim() == 2) else x.reshape(-1, x.shape[-1]).float().contiguous()
+    w = weight.detach().float().contiguous()
+    b = None if bias is None else bias.detach().float().contiguous()
+    rows, K = x.shape
+    N = w.shape[0]
+    if w.shape[1] != K:
+        raise RuntimeError(f"linear: x has {K} columns, weight {tuple(w.shape)}")
+    if x.stride(0) % 4 or x.data_ptr() % 16:
+        x = x.contiguous()
+        if K % 4:
+            raise RuntimeError("linear: K must be a multiple of 4 (TMA row pitch)")
+    y = out if out is not None else torch.empty((rows, N), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        if precise:
+            nbytes = L.lib().gsb_linear_tf32x3_scratch_bytes(K, N)
+            key = (x.device, nbytes)
+            if key not in _scratch:
+                _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+            rc = L.lib().gsb_linear_tf32x3(rows, K, N, L.ptr(x), x.stride(0), L.ptr(w), K, L.ptr(b), L.ptr(y), y.stride(0),
+                                           L.ptr(_scratch[key]), L.stream_ptr())
+        else:
+            rc = L.lib().gsb_linear_tf32(rows, K, N, L.ptr(x), x.stride(0), L.ptr(w), K, L.ptr(b), L.ptr(y), y.stride(0),
+                                         L.stream_ptr())
+    L.check(rc, "gsb_linear_tf32")
+    return y

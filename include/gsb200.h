@@ -218,6 +218,19 @@ int gsb_foreground_info(int32_t F, int32_t K, const int32_t* fg_index, const flo
                         float* offsets, int64_t off_stride_i, int64_t off_stride_j, int64_t off_stride_c,
                         void* stream);
 
+/* Dense layer of the DeformationNetwork (train.py:57-110: nn.Linear over all Gaussians) on the tcgen05 tensor
+ * cores: Y[rows, N] = X[rows, K] . W[N, K]^T (+ bias[N] when non-NULL), all FP32 in memory, row pitches ldx / ldw /
+ * ldy in floats.  TF32 multiply, FP32 accumulate (what torch computes with allow_tf32).  Constraints: N <= 256;
+ * X and W 16-byte aligned with ldx, ldw multiples of 4 (TMA); rows < 2^31. */
+int gsb_linear_tf32(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                    const float* bias, float* Y, int64_t ldy, void* stream);
+/* Same layer with the 3xTF32 operand split (hi/lo halves of X in shared memory, of W in `scratch`): FP32-level
+ * accuracy (~2^-22 relative per product) at three tensor-core instructions per tile.  scratch: device buffer of
+ * gsb_linear_tf32x3_scratch_bytes(K, N) bytes, 16-byte aligned; W must be dense (ldw == K). */
+size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N);
+int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                      const float* bias, float* Y, int64_t ldy, void* scratch, void* stream);
+
 /* Debug / test accessors: the individual stages, so that tests can compare every intermediate
  * bit-for-bit. */
 int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream);
