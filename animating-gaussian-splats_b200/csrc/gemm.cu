@@ -11,7 +11,9 @@
 //     (kind::tf32 reads the upper 19 bits), so there is no conversion pass over the activations;
 //   * warp 1 / one thread: tcgen05.mma issuer, 128 x N x 8 instructions, accumulator in TMEM, two accumulator
 //     stages (2 x N <= 512 columns) so the epilogue of tile i overlaps the loads and MMAs of tile i + 1;
-//   * warps 2-5: epilogue.  tcgen05.ld 16 columns at a time (lane = row), bias add, 64-byte row stores.
+//   * warps 2-5: epilogue.  tcgen05.ld (lane = row) 32 columns at a time, bias add, swizzled staging in the warp's
+//     own shared-memory buffer, coalesced 16-byte global stores (8 lanes per 128-byte row segment).  A TMA store
+//     was measured slower here: it queues behind the producer's prefetched loads in the SM's TMA unit.
 // W (<= 256 KB) is re-read per tile from L2.  mbarrier pipelines: full/empty per smem stage (TMA <-> MMA),
 // full/empty per accumulator stage (MMA <-> epilogue).
 //
@@ -19,6 +21,7 @@
 // landed tile in place into hi = x & ~0x1fff and lo = x - hi (lo in a second buffer with the same swizzled
 // offsets) and the issuer accumulates Xhi Whi + Xhi Wlo + Xlo Whi.
 #include <cuda.h>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -105,24 +108,31 @@ struct GemmParams {
   const float* bias;
   float* Y;
   long long ldy;
+  int dbg_skip_b;  // timing experiment only: load W tiles for the first M tile only (results are wrong)
+  int tma_store;   // Y goes out through shared-memory staging as coalesced 16-byte stores (aligned Y, N % 4 == 0)
 };
+constexpr int GM_EPI_BYTES = 4 * 32 * 128;   // per epilogue warp: one [32 rows x 32 floats] swizzled staging buffer
 
 template <bool SPLIT>
 __global__ void __launch_bounds__(GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), 1)
 linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                   const __grid_constant__ CUtensorMap map_wlo, GemmParams p) {
+                   const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
+                   GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES], empty_bar[GM_MAX_STAGES], split_bar[GM_MAX_STAGES];
   __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2];
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[256];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // 1024-byte aligned stage ring: [A | B] (+ [A_lo | B_lo] for SPLIT) per stage
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* epi = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = epi + GM_EPI_BYTES;
   const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
   const int k_blocks = (p.K + GM_BLOCK_K - 1) / GM_BLOCK_K;
   const long long m_tiles = (p.rows + GM_BLOCK_M - 1) / GM_BLOCK_M;
 
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) bias_s[i] = (p.bias && i < p.N) ? __ldg(p.bias + i) : 0.f;
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; s++) {
       mbar_init(&full_bar[s], 1);
@@ -158,9 +168,11 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a = smem + (size_t)stage * stage_bytes;
           uint8_t* b = a + GM_A_BYTES;
-          mbar_expect_tx(&full_bar[stage], GM_A_BYTES + p.b_bytes + (SPLIT ? p.b_bytes : 0));
+          const bool load_b = !(p.dbg_skip_b && t != blockIdx.x);
+          mbar_expect_tx(&full_bar[stage], GM_A_BYTES + (load_b ? p.b_bytes + (SPLIT ? p.b_bytes : 0) : 0));
           tma_load_2d(&map_x, &full_bar[stage], a, kb * GM_BLOCK_K, (int)(t * GM_BLOCK_M));
-          tma_load_2d(&map_w, &full_bar[stage], b, kb * GM_BLOCK_K, 0);
+          if (load_b) tma_load_2d(&map_w, &full_bar[stage], b, kb * GM_BLOCK_K, 0);
+          if (!load_b) { if (++stage == p.stages) { stage = 0; phase ^= 1; } continue; }
           if (SPLIT) tma_load_2d(&map_wlo, &full_bar[stage], b + GM_A_BYTES + p.b_bytes, kb * GM_BLOCK_K, 0);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -213,29 +225,48 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       mbar_wait(&acc_full[acc], acc_phase);
       tc_fence_after();
       const long long row = t * GM_BLOCK_M + q * 32 + lane;
+      if (p.tma_store) {
+        // 32 columns at a time: registers -> this warp's swizzled [32 x 128 B] buffer -> one TMA store per chunk
+        for (int c = 0; c < p.umma_n; c += 32) {
+          uint32_t v[32];
+          tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.umma_n + c), *reinterpret_cast<uint32_t(*)[16]>(v));
+          if (c + 16 < p.umma_n)
+            tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.umma_n + c + 16),
+                    *reinterpret_cast<uint32_t(*)[16]>(v + 16));
+          tc_ld_wait();
+          uint8_t* buf = epi + q * 4096;
+          __syncwarp();   // the previous chunk's reads of this buffer are done
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            float4 o = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                   __uint_as_float(v[4 * j + 3]));
+            const float4 bb = *reinterpret_cast<const float4*>(bias_s + c + 4 * j);   // zeros without a bias
+            o.x += bb.x; o.y += bb.y; o.z += bb.z; o.w += bb.w;
+            *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
+          }
+          __syncwarp();
+          // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
+          const int j = lane & 7;
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int r = i * 4 + (lane >> 3);
+            const long long grow = t * GM_BLOCK_M + q * 32 + r;
+            const float4 o = *reinterpret_cast<const float4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
+            if (grow < p.rows && c + 4 * j < p.N) *reinterpret_cast<float4*>(p.Y + grow * p.ldy + c + 4 * j) = o;
+          }
+        }
+      } else {
       float* yrow = p.Y + row * p.ldy;
       for (int c = 0; c < p.umma_n; c += 16) {
         uint32_t v[16];
         tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.umma_n + c), v);
         tc_ld_wait();
         if (row < p.rows) {
-          if (c + 16 <= p.N && (p.ldy & 3) == 0) {
 #pragma unroll
-            for (int i = 0; i < 16; i += 4) {
-              float4 o = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
-                                     __uint_as_float(v[i + 3]));
-              if (p.bias) {
-                const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + c + i));
-                o.x += bb.x; o.y += bb.y; o.z += bb.z; o.w += bb.w;
-              }
-              *reinterpret_cast<float4*>(yrow + c + i) = o;
-            }
-          } else {
-#pragma unroll
-            for (int i = 0; i < 16; i++)
-              if (c + i < p.N) yrow[c + i] = __uint_as_float(v[i]) + (p.bias ? __ldg(p.bias + c + i) : 0.f);
-          }
+          for (int i = 0; i < 16; i++)
+            if (c + i < p.N) yrow[c + i] = __uint_as_float(v[i]) + bias_s[c + i];
         }
+      }
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[acc]);
@@ -345,26 +376,29 @@ static int launch_linear(long long rows, int K, int N, const float* X, long long
   p.b_bytes = p.umma_n * GM_BLOCK_K * 4;
   p.bias = bias; p.Y = Y; p.ldy = ldy;
   const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
-  const int budget = 200 * 1024;
+  p.dbg_skip_b = getenv("GSB_GEMM_SKIPB") ? 1 : 0;
+  p.tma_store = ((reinterpret_cast<uintptr_t>(Y) & 15u) == 0 && (ldy & 3) == 0 && (N & 3) == 0) ? 1 : 0;
+  const int budget = 223 * 1024 - GM_EPI_BYTES;   // 227 KB per block minus static shared memory and alignment slack
   p.stages = budget / stage_bytes;
   if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
   if (p.stages < 2) return GSB_EINVAL;
-  CUtensorMap mx, mw, mwlo;
+  CUtensorMap mx, mw, mwlo, my;
   if (!make_map(&mx, X, rows, K, ldx, GM_BLOCK_M) || !make_map(&mw, W, N, K, ldw, p.umma_n) ||
-      !make_map(&mwlo, SPLIT ? Wlo : W, N, K, ldw, p.umma_n)) {
+      !make_map(&mwlo, SPLIT ? Wlo : W, N, K, ldw, p.umma_n) ||
+      !make_map(&my, p.tma_store ? Y : X, rows, p.tma_store ? N : K, p.tma_store ? ldy : ldx, 32)) {
     set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
     return GSB_ECUDA;
   }
-  const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+  const size_t smem = (size_t)p.stages * stage_bytes + GM_EPI_BYTES + 1024;
   auto kern = linear_tf32_kernel<SPLIT>;
   static bool attr_set = false;
   if (!attr_set) {
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
   const long long m_tiles = (rows + GM_BLOCK_M - 1) / GM_BLOCK_M;
   const int grid = (int)(m_tiles < sm_count() ? m_tiles : sm_count());
-  kern<<<grid, GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), smem, st>>>(mx, mw, mwlo, p);
+  kern<<<grid, GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), smem, st>>>(mx, mw, mwlo, my, p);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
