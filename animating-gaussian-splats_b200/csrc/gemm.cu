@@ -21,7 +21,6 @@
 // landed tile in place into hi = x & ~0x1fff and lo = x - hi (lo in a second buffer with the same swizzled
 // offsets) and the issuer accumulates Xhi Whi + Xhi Wlo + Xlo Whi.
 #include <cuda.h>
-#include <cstdlib>
 
 #include "common.cuh"
 
@@ -108,7 +107,7 @@ struct GemmParams {
   const float* bias;
   float* Y;
   long long ldy;
-  int dbg_skip_b;  // timing experiment only: load W tiles for the first M tile only (results are wrong)
+  double* col_stats;   // [2][N] column sums and sums of squares of Y over the rows (BatchNorm statistics), or NULL
   int tma_store;   // Y goes out through shared-memory staging as coalesced 16-byte stores (aligned Y, N % 4 == 0)
 };
 constexpr int GM_EPI_BYTES = 4 * 32 * 128;   // per epilogue warp: one [32 rows x 32 floats] swizzled staging buffer
@@ -168,11 +167,9 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a = smem + (size_t)stage * stage_bytes;
           uint8_t* b = a + GM_A_BYTES;
-          const bool load_b = !(p.dbg_skip_b && t != blockIdx.x);
-          mbar_expect_tx(&full_bar[stage], GM_A_BYTES + (load_b ? p.b_bytes + (SPLIT ? p.b_bytes : 0) : 0));
+          mbar_expect_tx(&full_bar[stage], GM_A_BYTES + p.b_bytes + (SPLIT ? p.b_bytes : 0));
           tma_load_2d(&map_x, &full_bar[stage], a, kb * GM_BLOCK_K, (int)(t * GM_BLOCK_M));
-          if (load_b) tma_load_2d(&map_w, &full_bar[stage], b, kb * GM_BLOCK_K, 0);
-          if (!load_b) { if (++stage == p.stages) { stage = 0; phase ^= 1; } continue; }
+          tma_load_2d(&map_w, &full_bar[stage], b, kb * GM_BLOCK_K, 0);
           if (SPLIT) tma_load_2d(&map_wlo, &full_bar[stage], b + GM_A_BYTES + p.b_bytes, kb * GM_BLOCK_K, 0);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
@@ -219,6 +216,9 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   } else if (warp < 6) {
     // ===== epilogue: TMEM -> registers -> (+ bias) -> global =====
     const int q = warp & 3;               // TMEM lane quarter this warp may read
+    double st_sum[8], st_sq[8];           // column statistics: lane = column within the 32-column chunk
+#pragma unroll
+    for (int i = 0; i < 8; i++) st_sum[i] = st_sq[i] = 0.0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (long long t = blockIdx.x; t < m_tiles; t += gridDim.x) {
@@ -227,7 +227,10 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       const long long row = t * GM_BLOCK_M + q * 32 + lane;
       if (p.tma_store) {
         // 32 columns at a time: registers -> this warp's swizzled [32 x 128 B] buffer -> one TMA store per chunk
-        for (int c = 0; c < p.umma_n; c += 32) {
+#pragma unroll
+        for (int ci = 0; ci < 8; ci++) {
+          const int c = ci * 32;
+          if (c >= p.umma_n) break;
           uint32_t v[32];
           tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.umma_n + c), *reinterpret_cast<uint32_t(*)[16]>(v));
           if (c + 16 < p.umma_n)
@@ -254,6 +257,18 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const float4 o = *reinterpret_cast<const float4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
             if (grow < p.rows && c + 4 * j < p.N) *reinterpret_cast<float4*>(p.Y + grow * p.ldy + c + 4 * j) = o;
           }
+          if (p.col_stats) {   // column `lane` of the chunk over this warp's valid rows (conflict-free: 32 consecutive floats)
+            const long long left = p.rows - (t * GM_BLOCK_M + q * 32);
+            const int nr = left < 32 ? (int)left : 32;
+            float s1 = 0.f, s2 = 0.f;
+            for (int r = 0; r < nr; r++) {
+              const float x = *reinterpret_cast<const float*>(buf + r * 128 + (((lane >> 2) ^ (r & 7)) << 4) + ((lane & 3) << 2));
+              s1 += x;
+              s2 = fmaf(x, x, s2);
+            }
+            st_sum[ci] += (double)s1;
+            st_sq[ci] += (double)s2;
+          }
         }
       } else {
       float* yrow = p.Y + row * p.ldy;
@@ -271,6 +286,14 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
       tc_fence_before();
       mbar_arrive(&acc_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (p.col_stats && p.tma_store) {
+#pragma unroll
+      for (int ci = 0; ci < 8; ci++)
+        if (ci * 32 + lane < p.N) {
+          atomicAdd(p.col_stats + ci * 32 + lane, st_sum[ci]);
+          atomicAdd(p.col_stats + p.N + ci * 32 + lane, st_sq[ci]);
+        }
     }
   } else if (SPLIT) {
     // ===== splitter: X tile -> hi (in place) + lo; the W halves arrive pre-split through TMA =====
@@ -369,15 +392,17 @@ static int sm_count() {
 
 template <bool SPLIT>
 static int launch_linear(long long rows, int K, int N, const float* X, long long ldx, const float* W, long long ldw,
-                         const float* Wlo, const float* bias, float* Y, long long ldy, cudaStream_t st) {
+                         const float* Wlo, const float* bias, float* Y, long long ldy, double* col_stats,
+                         cudaStream_t st) {
   GemmParams p;
+  p.col_stats = col_stats;
   p.rows = rows; p.K = K; p.N = N;
   p.umma_n = (N + 15) / 16 * 16;
   p.b_bytes = p.umma_n * GM_BLOCK_K * 4;
   p.bias = bias; p.Y = Y; p.ldy = ldy;
   const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
-  p.dbg_skip_b = getenv("GSB_GEMM_SKIPB") ? 1 : 0;
   p.tma_store = ((reinterpret_cast<uintptr_t>(Y) & 15u) == 0 && (ldy & 3) == 0 && (N & 3) == 0) ? 1 : 0;
+  if (col_stats && !p.tma_store) return GSB_EINVAL;   // statistics come from the staged (vector) epilogue
   const int budget = 223 * 1024 - GM_EPI_BYTES;   // 227 KB per block minus static shared memory and alignment slack
   p.stages = budget / stage_bytes;
   if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
@@ -420,16 +445,17 @@ static int linear_args_ok(int64_t rows, int32_t K, int32_t N, const float* X, in
 }
 
 int gsb_linear_tf32(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
-                    const float* bias, float* Y, int64_t ldy, void* stream) {
+                    const float* bias, float* Y, int64_t ldy, double* col_stats, void* stream) {
   if (rows == 0) return GSB_OK;
   if (!linear_args_ok(rows, K, N, X, ldx, W, ldw, Y, ldy)) return GSB_EINVAL;
-  return launch_linear<false>(rows, K, N, X, ldx, W, ldw, nullptr, bias, Y, ldy, reinterpret_cast<cudaStream_t>(stream));
+  return launch_linear<false>(rows, K, N, X, ldx, W, ldw, nullptr, bias, Y, ldy, col_stats,
+                              reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N) { return (size_t)2 * N * K * sizeof(float); }
 
 int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
-                      const float* bias, float* Y, int64_t ldy, void* scratch, void* stream) {
+                      const float* bias, float* Y, int64_t ldy, double* col_stats, void* scratch, void* stream) {
   if (rows == 0) return GSB_OK;
   if (!linear_args_ok(rows, K, N, X, ldx, W, ldw, Y, ldy) || !scratch || ldw != K) return GSB_EINVAL;
   if (reinterpret_cast<uintptr_t>(scratch) & 15u) return GSB_EINVAL;
@@ -439,7 +465,7 @@ int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_
   const long long n = (long long)N * K;
   split_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, W, hi, lo);
   GSB_LAUNCH_CHECK();
-  return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, bias, Y, ldy, st);
+  return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, bias, Y, ldy, col_stats, st);
 }
 
 }  // extern "C"

@@ -88,10 +88,15 @@ SYMBOLS = {
     "gsb_foreground_info": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 4 + [C.c_int64, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "gsb_linear_tf32": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
-                                  C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+                                  C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "gsb_linear_tf32x3_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_linear_tf32x3": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
-                                    C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+                                    C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsb_bn_gelu": (C.c_int, [C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
+                              C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_float,
+                              C.c_int32, C.c_void_p]),
+    "gsb_positional_encoding": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),
     "gsb_profile_read": (C.c_int, [C.POINTER(C.c_float), C.c_int32]),
 }

@@ -8,7 +8,8 @@ from . import _lib as L
 _scratch = {}
 
 
-def linear(x, weight, bias=None, precise=False, out=None):
+def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
+    """col_stats: optional zeroed float64 [2, N] tensor receiving the column sums / sums of squares of the output."""
     L.require_cuda(x, "x")
     x = x if (x.dtype == torch.float32 and x.stride(-1) == 1 and x.dim() == 2) else x.reshape(-1, x.shape[-1]).float().contiguous()
     w = weight.detach().float().contiguous()
@@ -29,9 +30,9 @@ def linear(x, weight, bias=None, precise=False, out=None):
             if key not in _scratch:
                 _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
             rc = L.lib().gsb_linear_tf32x3(rows, K, N, L.ptr(x), x.stride(0), L.ptr(w), K, L.ptr(b), L.ptr(y), y.stride(0),
-                                           L.ptr(_scratch[key]), L.stream_ptr())
+                                           L.ptr(col_stats), L.ptr(_scratch[key]), L.stream_ptr())
         else:
             rc = L.lib().gsb_linear_tf32(rows, K, N, L.ptr(x), x.stride(0), L.ptr(w), K, L.ptr(b), L.ptr(y), y.stride(0),
-                                         L.stream_ptr())
+                                         L.ptr(col_stats), L.stream_ptr())
     L.check(rc, "gsb_linear_tf32")
     return y

@@ -221,15 +221,33 @@ int gsb_foreground_info(int32_t F, int32_t K, const int32_t* fg_index, const flo
 /* Dense layer of the DeformationNetwork (train.py:57-110: nn.Linear over all Gaussians) on the tcgen05 tensor
  * cores: Y[rows, N] = X[rows, K] . W[N, K]^T (+ bias[N] when non-NULL), all FP32 in memory, row pitches ldx / ldw /
  * ldy in floats.  TF32 multiply, FP32 accumulate (what torch computes with allow_tf32).  Constraints: N <= 256;
- * X and W 16-byte aligned with ldx, ldw multiples of 4 (TMA); rows < 2^31. */
+ * X and W 16-byte aligned with ldx, ldw multiples of 4 (TMA); rows < 2^31.
+ * col_stats (optional, DEVICE double[2][N], zeroed by the caller): the epilogue adds the column sums and sums of
+ * squares of Y over the rows -- the BatchNorm1d batch statistics of the layer that follows (train.py:57-78) --
+ * so no extra pass over Y is needed; requires a 16-byte aligned Y with ldy and N multiples of 4. */
 int gsb_linear_tf32(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
-                    const float* bias, float* Y, int64_t ldy, void* stream);
+                    const float* bias, float* Y, int64_t ldy, double* col_stats, void* stream);
 /* Same layer with the 3xTF32 operand split (hi/lo halves of X in shared memory, of W in `scratch`): FP32-level
  * accuracy (~2^-22 relative per product) at three tensor-core instructions per tile.  scratch: device buffer of
  * gsb_linear_tf32x3_scratch_bytes(K, N) bytes, 16-byte aligned; W must be dense (ldw == K). */
 size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N);
 int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
-                      const float* bias, float* Y, int64_t ldy, void* scratch, void* stream);
+                      const float* bias, float* Y, int64_t ldy, double* col_stats, void* scratch, void* stream);
+
+/* BatchNorm1d in training mode (batch statistics; the reference never switches the network to eval) + optional
+ * residual + exact (erf) GELU in one pass over Z [rows, N]: Y = act(gamma (Z - mean) / sqrt(var + eps) + beta
+ * [+ residual]), mean / biased var from col_stats = the [2][N] sums gsb_linear_tf32 accumulated (train.py:57-78).
+ * running_mean / running_var (both or neither) receive torch's momentum update with the unbiased variance.
+ * N <= 256, N and all pitches multiples of 4. */
+int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const double* col_stats, const float* gamma,
+                const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
+                float* running_mean, float* running_var, float momentum, int32_t apply_gelu, void* stream);
+
+/* PositionalEncoding (train.py:113-127) of x [rows, D] with F frequencies 2^k pi into out[:, col0 + j D + d],
+ * j in [0, 2F): even j -> sin(f x), odd j -> cos(sin(f x)) (the reference's in-place quirk).  With lo / span [D]
+ * the input is first mapped to 2 (x - lo) / span - 1 (normalize_and_encode_means_and_rotations, train.py:186-205). */
+int gsb_positional_encoding(int64_t rows, int32_t D, int32_t F, const float* x, int64_t ldx, const float* lo,
+                            const float* span, float* out, int64_t ldo, int32_t col0, void* stream);
 
 /* Debug / test accessors: the individual stages, so that tests can compare every intermediate
  * bit-for-bit. */

@@ -1,0 +1,104 @@
+"""DeformationNetwork forward on the tcgen05 path against the same architecture in stock
+torch ops (train.py:57-127 restated below with nn.Linear / nn.BatchNorm1d / gelu, FP32 matmuls, training-mode
+BatchNorm like the reference).  Tolerances: 3xTF32 path 1e-4, TF32 path 2e-2, both relative to the output's RMS --
+BatchNorm divides by the batch standard deviation in every block, which carries the matmul rounding forward."""
+import pytest
+import torch
+from torch import nn
+
+pytestmark = pytest.mark.gpu
+
+
+class _Block(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.fc1 = nn.Linear(d, d, bias=False); self.bn1 = nn.BatchNorm1d(d)
+        self.fc2 = nn.Linear(d, d, bias=False); self.bn2 = nn.BatchNorm1d(d)
+
+    def forward(self, x):
+        y = nn.functional.gelu(self.bn1(self.fc1(x)))
+        return nn.functional.gelu(self.bn2(self.fc2(y)) + x)
+
+
+class _StockNetwork(nn.Module):
+    def __init__(self, h, blocks):
+        super().__init__()
+        self.fc_in = nn.Linear(192, h)
+        self.residual_blocks = nn.Sequential(*(_Block(h) for _ in range(blocks)))
+        self.fc_out = nn.Linear(h, 7)
+
+    def forward(self, init, x):
+        return self.fc_out(self.residual_blocks(self.fc_in(x))) + init
+
+
+def _stock_posenc(x, f):
+    freq = ((torch.ones(f) * 2).pow(torch.arange(f)) * torch.pi).to(x.device)
+    e = (freq * x[:, :, None]).repeat_interleave(2, 2)
+    e[:, :, ::2] = torch.sin(e[:, :, ::2])
+    e[:, :, 1::2] = torch.cos(e[:, :, ::2])
+    return e.permute(0, 2, 1).flatten(start_dim=1)
+
+
+def test_positional_encoding_and_normalisation():
+    from gsb200 import deform
+    g = torch.Generator().manual_seed(0)
+    means = (torch.randn(5000, 3, generator=g) * 1.3).cuda()
+    rots = torch.randn(5000, 4, generator=g).cuda()
+    got = deform.normalize_and_encode_means_and_rotations({"means": means, "rotation_quaternions": rots})
+
+    def norm(t):
+        t = t - t.min(dim=0).values
+        return 2.0 * t / t.max(dim=0).values - 1.0
+    want = torch.cat((_stock_posenc(norm(means), 10), _stock_posenc(norm(rots), 4)), dim=1)
+    assert got.shape == (5000, 92)
+    # |f u| reaches 2^9 pi: a 1-ulp difference in the float32 argument moves sin by up to 2^9 pi 2^-24 ~ 1e-4
+    assert (got - want).abs().max().item() < 3e-4
+    assert (got[:, :6] - want[:, :6]).abs().max().item() < 2e-6   # lowest frequency: tight
+    prog = torch.full((5000, 1), 7 / 150, device="cuda")
+    assert (deform.positional_encoding(prog, 4) - _stock_posenc(prog, 4)).abs().max().item() < 2e-6
+
+
+@pytest.mark.parametrize("rows,h,blocks", [(20_000, 128, 3), (4097, 64, 1), (300_000, 256, 2)])
+@pytest.mark.parametrize("precise", [True, False])
+def test_forward_matches_stock_torch(rows, h, blocks, precise):
+    from gsb200 import deform
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(rows % 13)
+    ref = _StockNetwork(h, blocks).cuda().train()
+    with torch.no_grad():   # non-trivial affine parameters and running buffers
+        for m in ref.modules():
+            if isinstance(m, nn.BatchNorm1d):
+                m.weight.uniform_(0.5, 1.5); m.bias.normal_(0, 0.3)
+                m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.5, 2.0)
+    ours = deform.DeformationNetwork(h, blocks, precise=precise).cuda()
+    ours.load_state_dict(ref.state_dict())   # same parameter names as the reference module
+    x = torch.randn(rows, 192, device="cuda")
+    init = torch.randn(rows, 7, device="cuda")
+    with torch.no_grad():
+        want = ref(init, x)
+    got = ours(init, network_input=x)
+    rms = (want - init).pow(2).mean().sqrt().item()
+    err = (got - want).abs().max().item() / rms
+    assert err < (1e-4 if precise else 2e-2), err
+    for a, b in zip(ours.modules(), ref.modules()):
+        if isinstance(a, nn.BatchNorm1d):
+            tol = 1e-5 if precise else 2e-3
+            assert torch.allclose(a.running_mean, b.running_mean, rtol=tol, atol=tol)
+            assert torch.allclose(a.running_var, b.running_var, rtol=tol, atol=tol)
+            assert int(a.num_batches_tracked) == int(b.num_batches_tracked) == 1
+    # state_dicts stay interchangeable after a forward
+    ref.load_state_dict(ours.state_dict())
+
+
+def test_update_gaussian_cloud_parameters_shapes():
+    from gsb200 import deform
+    torch.manual_seed(1)
+    n = 10_000
+    p = {"means": torch.randn(n, 3, device="cuda"), "rotation_quaternions": torch.randn(n, 4, device="cuda"),
+         "colors": torch.rand(n, 3, device="cuda")}
+    enc = deform.normalize_and_encode_means_and_rotations(p)
+    net = deform.DeformationNetwork(64, 2).cuda()
+    out = deform.update_gaussian_cloud_parameters(net, p, enc, enc, timestep=3, timestep_count=10)
+    assert out["means"].shape == (n, 3) and out["rotation_quaternions"].shape == (n, 4)
+    assert out["colors"] is p["colors"]
+    assert torch.isfinite(out["means"]).all() and not torch.equal(out["means"], p["means"])
