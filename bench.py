@@ -365,9 +365,86 @@ def run_ours(args):
             out["rigidity_loss"] = rigidity_shaped(args)
         except Exception as ex:
             out["rigidity_loss"] = {"error": repr(ex)[:300]}
+        try:
+            out["deformation_forward"] = deformation_shaped(args)
+        except Exception as ex:
+            out["deformation_forward"] = {"error": repr(ex)[:300]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def deformation_shaped(args, hidden=256, blocks=4, iters=10):
+    """DeformationNetwork forward (train.py:80-110; 192 -> H, `blocks` residual blocks, H -> 7,
+    training-mode BatchNorm) over all Gaussians.  "ours_tf32" / "ours_3xtf32": gsb200.deform on the hand-written
+    tcgen05 GEMM; "torch_fp32" (the reference's setting: torch's default keeps FP32 matmuls) and "torch_tf32"
+    (allow_tf32): the same architecture in stock torch ops.  Also the 192 -> H layer alone with its HBM roofline."""
+    from gsb200 import deform
+    from gsb200.linear import linear
+    from torch import nn
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = args.gaussians
+
+    class Block(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.fc1 = nn.Linear(d, d, bias=False); self.bn1 = nn.BatchNorm1d(d)
+            self.fc2 = nn.Linear(d, d, bias=False); self.bn2 = nn.BatchNorm1d(d)
+
+        def forward(self, x):
+            y = nn.functional.gelu(self.bn1(self.fc1(x)))
+            return nn.functional.gelu(self.bn2(self.fc2(y)) + x)
+
+    class Stock(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc_in = nn.Linear(192, hidden)
+            self.residual_blocks = nn.Sequential(*(Block(hidden) for _ in range(blocks)))
+            self.fc_out = nn.Linear(hidden, 7)
+
+        def forward(self, init, x):
+            return self.fc_out(self.residual_blocks(self.fc_in(x))) + init
+
+    torch.manual_seed(0)
+    stock = Stock().to(dev).train()
+    x = torch.randn(n, 192, device=dev); init = torch.randn(n, 7, device=dev)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    res = {"what": f"DeformationNetwork forward, {n} Gaussians, hidden {hidden}, {blocks} residual blocks", "unit": "ms"}
+    for precise in (False, True):
+        net = deform.DeformationNetwork(hidden, blocks, precise=precise).to(dev)
+        net.load_state_dict(stock.state_dict())
+        res["ours_3xtf32" if precise else "ours_tf32"] = timed(lambda: net(init, network_input=x))
+    with torch.no_grad():
+        for name, flag in (("torch_fp32", False), ("torch_tf32", True)):
+            torch.backends.cuda.matmul.allow_tf32 = flag
+            res[name] = timed(lambda: stock(init, x))
+        torch.backends.cuda.matmul.allow_tf32 = False
+    w, b = stock.fc_in.weight.detach(), stock.fc_in.bias.detach()
+    y = torch.empty(n, hidden, device=dev)
+    ms = timed(lambda: linear(x, w, b, out=y))
+    peak = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mp = json.load(f)
+        peak = float(mp["hbm_gbs"])
+    except Exception:
+        pass
+    byts = n * (192 + hidden) * 4
+    res["fc_in_layer"] = {"kernel": "linear_tf32_kernel (TMA + tcgen05.mma kind::tf32, TMEM accumulators)", "ms": ms,
+                          "bound": "hbm", "algorithmic_bytes": byts, "achieved": byts / (ms * 1e-3) / 1e9,
+                          "peak": peak, "unit": "GB/s", "frac": (byts / (ms * 1e-3) / 1e9 / peak) if peak else None,
+                          "tflops": 2.0 * n * 192 * hidden / (ms * 1e-3) / 1e12}
+    return res
 
 
 def rigidity_shaped(args, views=5, iters=20):
