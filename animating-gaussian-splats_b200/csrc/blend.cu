@@ -13,6 +13,8 @@
 // multi-value shuffle reduction (14 SHFL for 9 values) and only the per-warp sums go to global
 // atomics in one RED instruction (the reference issues 9 global atomics per pixel-Gaussian pair).
 // Warps skip list entries behind their deepest contributor, and whole batches behind the tile's.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace gsb {
@@ -427,9 +429,244 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Backward, two pixels per thread: 128 threads per tile, a warp owns an 8x8 block = two of the 8x4 patches
+// above (rows y and y + 4 of the same column), so one staged entry that touches both patches costs ONE
+// loop iteration, ONE 9-value warp reduction and ONE atomic instruction instead of two.  Per-pixel
+// arithmetic is the same as render_bwd_kernel's; only the order in which partial sums meet changes.
+// ------------------------------------------------------------------------------------------------
+struct BwdPixel {
+  float T, ar0, ar1, ar2, dpx0, dpx1, dpx2, nTf_bg, pfy;
+  int last;
+};
+
+__device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, float G, float dx, float dy, float4 ci,
+                                          float opac, float (&v)[8], float& g_op) {
+  if (!valid) return;
+  const float om = 1.f - alpha;
+  float rcp;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(om));
+  rcp = fmaf(rcp, fmaf(-om, rcp, 1.f), rcp);
+  s.T = s.T * rcp;
+  const float dchannel_dcolor = alpha * s.T;
+  const float d0 = ci.x - s.ar0, d1 = ci.y - s.ar1, d2 = ci.z - s.ar2;
+  float dL_dalpha = d0 * s.dpx0;
+  dL_dalpha = fmaf(d1, s.dpx1, dL_dalpha);
+  dL_dalpha = fmaf(d2, s.dpx2, dL_dalpha);
+  s.ar0 = fmaf(alpha, d0, s.ar0);
+  s.ar1 = fmaf(alpha, d1, s.ar1);
+  s.ar2 = fmaf(alpha, d2, s.ar2);
+  v[0] = fmaf(dchannel_dcolor, s.dpx0, v[0]);
+  v[1] = fmaf(dchannel_dcolor, s.dpx1, v[1]);
+  v[2] = fmaf(dchannel_dcolor, s.dpx2, v[2]);
+  dL_dalpha = fmaf(dL_dalpha, s.T, s.nTf_bg * rcp);
+  const float g = G * dL_dalpha;
+  g_op += g;
+  const float wg = opac * g;
+  const float s1 = wg * dx, s2 = wg * dy;
+  v[3] += s1;
+  v[4] += s2;
+  v[5] = fmaf(s1, dx, v[5]);
+  v[6] = fmaf(s1, dy, v[6]);
+  v[7] = fmaf(s2, dy, v[7]);
+}
+
+#ifndef GSB_BWD2_MINB
+#define GSB_BWD2_MINB 6
+#endif
+
+__global__ void __launch_bounds__(128, GSB_BWD2_MINB)
+render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int P,
+                   const float* __restrict__ bg, const float2* __restrict__ means2D,
+                   const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,
+                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                   const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
+                   float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
+  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold | patch mask, bits(list position)
+  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
+  __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
+  __shared__ int s_wcnt[8];
+  __shared__ int s_block_last;
+  __shared__ int s_patch_last[8];
+
+  const int cam = blockIdx.z;
+  const uint32_t tiles_per_cam = gridDim.x * gridDim.y;
+  const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const unsigned tid = threadIdx.x;
+  const unsigned lane = tid & 31u, warp = tid >> 5;
+  const unsigned pt = (warp & 1u) + 4u * (warp >> 1), pb = pt + 2u;   // the two 8x4 patches of this warp
+  const uint32_t px = blockIdx.x * GSB_BLOCK_X + (warp & 1u) * 8u + (lane & 7u);
+  const uint32_t pyA = blockIdx.y * GSB_BLOCK_Y + (warp >> 1) * 8u + (lane >> 3);
+  const uint32_t pyB = pyA + 4u;
+  const float pfx = (float)px;
+  const float tx0 = (float)(blockIdx.x * GSB_BLOCK_X), ty0 = (float)(blockIdx.y * GSB_BLOCK_Y);
+  const size_t HW = (size_t)H * W;
+
+  const uint2 range = ranges[(size_t)cam * tiles_per_cam + tile];
+  const size_t cam_off = (size_t)cam * P;
+  const float* col_tab = colors + (size_t)cam * color_cam_stride;
+  float* dcol_tab = dL_dcolor + (size_t)cam * color_cam_stride;
+  const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
+
+  BwdPixel A, B;
+  auto init = [&](BwdPixel& s, uint32_t py) {
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const size_t pid = (size_t)py * W + px;
+    const float T_final = inside ? final_Ts[cam * HW + pid] : 0.f;
+    s.T = T_final;
+    s.last = inside ? (int)n_contrib[cam * HW + pid] : 0;
+    s.dpx0 = s.dpx1 = s.dpx2 = 0.f;
+    if (inside) {
+      const float* dp = dL_dpixels + (size_t)cam * 3 * HW;
+      s.dpx0 = dp[pid]; s.dpx1 = dp[HW + pid]; s.dpx2 = dp[2 * HW + pid];
+    }
+    float bg_dot = 0.f;
+    bg_dot += b0 * s.dpx0; bg_dot += b1 * s.dpx1; bg_dot += b2 * s.dpx2;
+    s.ar0 = s.ar1 = s.ar2 = 0.f;
+    s.nTf_bg = -T_final * bg_dot;
+    s.pfy = (float)py;
+  };
+  init(A, pyA);
+  init(B, pyB);
+
+  float* lane_base;
+  unsigned lane_stride;
+  {
+    const unsigned comp = lane >> 2;
+    if (lane == 1) { lane_base = dL_dopacity; lane_stride = 1; }
+    else if (comp < 3) { lane_base = dcol_tab + comp; lane_stride = 3; }
+    else if (comp < 5) { lane_base = dL_dmean2D + 3 * cam_off + (comp - 3); lane_stride = 3; }
+    else { lane_base = dL_dconic + 4 * cam_off + (comp == 7 ? 3 : comp - 5); lane_stride = 4; }
+  }
+  const bool lane_writes = ((lane & 3u) == 0) || lane == 1;
+
+  int lastA = A.last, lastB = B.last;
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    lastA = max(lastA, __shfl_xor_sync(0xffffffffu, lastA, s));
+    lastB = max(lastB, __shfl_xor_sync(0xffffffffu, lastB, s));
+  }
+  if (tid == 0) s_block_last = 0;
+  __syncthreads();
+  if (lane == 0) {
+    s_patch_last[pt] = lastA;
+    s_patch_last[pb] = lastB;
+    const int m = max(lastA, lastB);
+    if (m > 0) atomicMax(&s_block_last, m);
+  }
+  __syncthreads();
+  const int block_last = s_block_last;
+  if (block_last == 0) return;
+
+  const int rounds = (block_last + GSB_BLOCK_SIZE - 1) / GSB_BLOCK_SIZE;
+  for (int i = 0; i < rounds; i++) {
+    if (i > 0) __syncthreads();
+    // each thread stages two list positions of the 256-entry batch: k = tid and k = tid + 128
+    bool keep[2];
+    uint32_t id[2];
+    float2 xy[2];
+    float4 co[2];
+    float thr[2];
+    int pos[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      pos[h] = block_last - 1 - i * GSB_BLOCK_SIZE - (int)(tid + 128u * h);
+      keep[h] = false; id[h] = 0; xy[h] = make_float2(0.f, 0.f); co[h] = make_float4(0.f, 0.f, 0.f, 0.f); thr[h] = 0.f;
+      if (pos[h] >= 0) {
+        id[h] = point_list[range.x + (uint32_t)pos[h]];
+        xy[h] = means2D[cam_off + id[h]];
+        co[h] = conic_opacity[cam_off + id[h]];
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      if (pos[h] >= 0) {
+        keep[h] = tile_cull_keep<true>(xy[h].x, xy[h].y, co[h], tx0, ty0, thr[h]);
+        if (keep[h]) {
+          unsigned m = __float_as_uint(thr[h]) & 0xFFu;
+#pragma unroll
+          for (int w = 0; w < 8; w++)
+            if (pos[h] >= s_patch_last[w]) m &= ~(1u << w);
+          thr[h] = pack_thr(thr[h], m);
+          keep[h] = m != 0;
+        }
+      }
+    }
+    const unsigned bal0 = __ballot_sync(0xffffffffu, keep[0]), bal1 = __ballot_sync(0xffffffffu, keep[1]);
+    if (lane == 0) { s_wcnt[warp] = __popc(bal0); s_wcnt[4 + warp] = __popc(bal1); }
+    __syncthreads();
+    int before0 = 0, before1 = 0, n = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+      const int c = s_wcnt[w];
+      if (w < (int)warp) before0 += c;
+      if (w < (int)warp + 4) before1 += c;
+      n += c;
+    }
+    const int slot[2] = {before0 + __popc(bal0 & lanemask_lt()), before1 + __popc(bal1 & lanemask_lt())};
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+      if (keep[h]) {
+        s_a[slot[h]] = make_float4(xy[h].x, xy[h].y, thr[h], __int_as_float(pos[h]));
+        s_co[slot[h]] = co[h];
+        s_ci[slot[h]] = make_float4(col_tab[3 * (size_t)id[h]], col_tab[3 * (size_t)id[h] + 1],
+                                    col_tab[3 * (size_t)id[h] + 2], __uint_as_float(id[h]));
+      }
+    __syncthreads();
+    for (int j = 0; j < n; j++) {
+      const float4 a = s_a[j];
+      const unsigned m = __float_as_uint(a.z);
+      const bool mt = (m >> pt) & 1u, mb = (m >> pb) & 1u;   // warp-uniform
+      if (!(mt || mb)) continue;
+      const int pos_j = __float_as_int(a.w);
+      const float4 co2 = s_co[j];
+      const float dx = SUB(a.x, pfx);
+      const float dyA = SUB(a.y, A.pfy), dyB = SUB(a.y, B.pfy);
+      bool preA = false, preB = false;
+      float powA = 0.f, powB = 0.f;
+      if (mt) {
+        powA = blend_power(dx, dyA, co2.x, co2.y, co2.z);
+        preA = (pos_j < A.last) && !(powA > 0.0f) && !(powA < a.z);
+      }
+      if (mb) {
+        powB = blend_power(dx, dyB, co2.x, co2.y, co2.z);
+        preB = (pos_j < B.last) && !(powB > 0.0f) && !(powB < a.z);
+      }
+      if (!__any_sync(0xffffffffu, preA || preB)) continue;
+      const float GA = expf(powA), GB = expf(powB);
+      const float alphaA = fminf(0.99f, MUL(co2.w, GA)), alphaB = fminf(0.99f, MUL(co2.w, GB));
+      const bool validA = preA && !(alphaA < 1.0f / 255.0f), validB = preB && !(alphaB < 1.0f / 255.0f);
+      if (!__any_sync(0xffffffffu, validA || validB)) continue;
+
+      float v[8];
+      float g_op = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; k++) v[k] = 0.f;
+      const float4 ci = s_ci[j];
+      bwd_pixel(A, validA, alphaA, GA, dx, dyA, ci, co2.w, v, g_op);
+      bwd_pixel(B, validB, alphaB, GB, dx, dyB, ci, co2.w, v, g_op);
+      warp_reduce8(v, lane);
+#pragma unroll
+      for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
+      const uint32_t id2 = __float_as_uint(ci.w);
+      const float val = (lane == 1) ? g_op : v[0];
+      if (lane_writes && val != 0.f) atomicAdd(lane_base + id2 * lane_stride, val);
+    }
+  }
+}
+
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
                       float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st) {
   dim3 grid(c.tiles_x, c.tiles_y, a.n_cams), block(GSB_BLOCK_X, GSB_BLOCK_Y);
+  static const int two_px = [] { const char* e = getenv("GSB_BWD_2PX"); return e ? atoi(e) : 1; }();
+  if (two_px) {
+    render_bwd2_kernel<<<grid, 128, 0, st>>>(
+        reinterpret_cast<const uint2*>(c.ranges), c.point_list, a.width, a.height, a.P, a.background,
+        reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
+        a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+    GSB_LAUNCH_CHECK();
+    return GSB_OK;
+  }
   render_bwd_kernel<<<grid, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), c.point_list, a.width, a.height, a.P, a.background,
       reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
