@@ -310,8 +310,8 @@ def run_ours(args):
     # dominant kernel: backward blend.  Algorithmic work: 70 FP32 flop per walked pair.
     bwd_ms = stages["render_bwd"]
     achieved = (walked * 70.0) / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else 0.0
-    roofline = {"kernel": "render_bwd_kernel", "bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops,
-                "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": tr("render_bwd_kernel"),
+    roofline = {"kernel": "render_bwd2_kernel", "bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops,
+                "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": tr("render_bwd2_kernel"),
                 "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
                 "ms": bwd_ms, "pairs": walked}
     # the HBM-bound kernel with the most bytes: the instance sort (segmented onesweep on 16-bit camera-local
