@@ -308,6 +308,20 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   return GSB_OK;
 }
 
+int gsb_raster_forward_colors(const gsb_raster_args* a, const gsb_raster_ctx* ctx, float* out_color, float* out_depth,
+                              void* stream) {
+  if (!a || !ctx) return GSB_EINVAL;
+  if (a->P == 0) return GSB_OK;
+  if (!a->colors || !a->background || !out_color || !out_depth) return GSB_EINVAL;
+  if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height || !ctx->ranges)
+    return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  prof_mark(PF_FWD_BEGIN, st);
+  int rc;
+  if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
+  return GSB_OK;
+}
+
 int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix,
                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                         float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot, void* stream) {

@@ -43,7 +43,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         rs = raster_settings
         color, depth, radii, state = _raster.forward(
             means3D, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs.bg, rs.scale_modifier,
-            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, rs.prefiltered)
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, rs.prefiltered,
+            reuse_geometry=True)
         ctx.state = state
         ctx.num_rendered = state.num_rendered
         ctx.has_cov = cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0

@@ -60,6 +60,8 @@ SYMBOLS = {
     "gsb_raster_forward": (C.c_int, [C.POINTER(RasterArgs), ALLOC_FN, ALLOC_FN, ALLOC_FN, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.POINTER(RasterCtx), C.c_void_p]),
     "gsb_raster_backward": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx)] + [C.c_void_p] * 10),
+    "gsb_raster_forward_colors": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p,
+                                            C.c_void_p]),
     "gsb_mark_visible": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
     "gsb_ssim_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "gsb_ssim_l1": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
@@ -137,7 +139,28 @@ def ptr(t):
 
 
 def stream_ptr():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    """The current device's current CUDA stream as a void*.  Raw C accessors: torch.cuda.current_stream() builds
+    a Stream object (~15 us) and this is called once per kernel launch."""
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
+
+
+class _NoGuard:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def device_guard(dev):
+    """`with torch.cuda.device(dev)` only when dev is not already the current device (the common case)."""
+    idx = dev.index if dev.index is not None else torch._C._cuda_getDevice()
+    if idx == torch._C._cuda_getDevice():
+        return _NO_GUARD
+    return torch.cuda.device(idx)
 
 
 def require_cuda(t, name):

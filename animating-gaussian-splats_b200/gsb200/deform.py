@@ -31,7 +31,7 @@ def positional_encoding(x, frequency_count, lo=None, span=None, out=None, col0=0
     if out is None:
         out = torch.empty((n, 2 * frequency_count * d), dtype=torch.float32, device=x.device)
         col0 = 0
-    with torch.cuda.device(x.device):
+    with L.device_guard(x.device):
         rc = L.lib().gsb_positional_encoding(n, d, frequency_count, L.ptr(x), x.stride(0), L.ptr(lo), L.ptr(span), L.ptr(out),
                                              out.stride(0), col0, L.stream_ptr())
     L.check(rc, "gsb_positional_encoding")
@@ -78,7 +78,7 @@ class DeformationNetwork(nn.Module):
     def _bn_act(self, z, stats, bn, residual, gelu=True):
         rows, n = z.shape
         y = torch.empty_like(z)
-        with torch.cuda.device(z.device):
+        with L.device_guard(z.device):
             rc = L.lib().gsb_bn_gelu(rows, n, L.ptr(z), z.stride(0), L.ptr(stats), L.ptr(bn.weight.detach()),
                                      L.ptr(bn.bias.detach()), float(bn.eps), L.ptr(residual),
                                      0 if residual is None else residual.stride(0), L.ptr(y), y.stride(0),

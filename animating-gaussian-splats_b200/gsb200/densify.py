@@ -48,7 +48,7 @@ def accumulate_mean_2d_gradients(densification_variables):
     grad = dv.means_2d.grad.contiguous()
     vis = dv.gaussian_is_visible_mask.contiguous()
     P = vis.numel()
-    with torch.cuda.device(vis.device):
+    with L.device_guard(vis.device):
         rc = L.lib().gsb_densify_accumulate_masked(P, L.ptr(vis), L.ptr(grad), L.ptr(dv.mean_2d_gradients_accumulated),
                                                    L.ptr(dv.visibility_count), _stream())
     L.check(rc, "gsb_densify_accumulate_masked")
@@ -65,7 +65,7 @@ class _Mask:
         cnt = torch.zeros(1, dtype=torch.int32, device=dev)
         lib = L.lib()
         scratch = torch.empty(lib.gsb_scan_scratch_bytes(max(P, 1)), dtype=torch.uint8, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             rc = lib.gsb_mask_scan(P, L.ptr(self.mask), L.ptr(self.rank), L.ptr(cnt), L.ptr(scratch), _stream())
         L.check(rc, "gsb_mask_scan")
         self.count = int(cnt.item())   # sizes the new tensors: the one host sync per mask
@@ -76,7 +76,7 @@ class _Mask:
             return
         src = src.contiguous()
         row = src[0].numel()
-        with torch.cuda.device(src.device):
+        with L.device_guard(src.device):
             rc = L.lib().gsb_gather_rows(src.shape[0], L.ptr(self.mask), L.ptr(self.rank), L.ptr(src), L.ptr(dst),
                                          row, _stream())
         L.check(rc, "gsb_gather_rows")
@@ -141,7 +141,7 @@ def densify_step(tables, stats, visible, means2d_grad, scene_radius, i, samples=
         for k in KEYS:
             new[k] = _append_selected(tables[k][0], split, repeat=2)
         if S > 0:
-            with torch.cuda.device(dev):
+            with L.device_guard(dev):
                 rc = L.lib().gsb_split_rows(N1, S, L.ptr(split.mask), L.ptr(split.rank), L.ptr(tables["means"][0]),
                                             L.ptr(tables["rotation_quaternions"][0].contiguous()),
                                             L.ptr(tables["log_scales"][0]), L.ptr(samples),

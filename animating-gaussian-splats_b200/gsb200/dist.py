@@ -31,7 +31,7 @@ def pack(flat, grads, stats_delta=None):
         acc = c(stats_delta["mean_2d_gradients_accumulated"]) if stats_delta is not None else None
         cnt = c(stats_delta["visibility_count"]) if stats_delta is not None else None
         keep = [c(grads[k]) for k in ("means3D", "colors", "rotations", "opacities", "scales")]
-        with torch.cuda.device(flat.device):
+        with L.device_guard(flat.device):
             rc = L.lib().gsb_pack_flat(flat.shape[0], L.ptr(keep[0]), L.ptr(keep[1]), L.ptr(keep[2]), L.ptr(keep[3]),
                                        L.ptr(keep[4]), L.ptr(acc), L.ptr(cnt), L.ptr(flat), L.stream_ptr())
         L.check(rc, "gsb_pack_flat")

@@ -23,7 +23,7 @@ def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
         if K % 4:
             raise RuntimeError("linear: K must be a multiple of 4 (TMA row pitch)")
     y = out if out is not None else torch.empty((rows, N), dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device):
+    with L.device_guard(x.device):
         if precise:
             nbytes = L.lib().gsb_linear_tf32x3_scratch_bytes(K, N)
             key = (x.device, nbytes)

@@ -23,7 +23,7 @@ def _run(img, target, w_l1, w_ssim, want_grad):
     scratch = torch.empty(lib.gsb_ssim_scratch_bytes(n, H, W), dtype=torch.uint8, device=x.device)
     out = torch.empty((n, 3), dtype=torch.float32, device=x.device)
     grad = torch.empty_like(x) if want_grad else None
-    with torch.cuda.device(x.device):
+    with L.device_guard(x.device):
         rc = lib.gsb_ssim_l1(n, H, W, L.ptr(x), L.ptr(y), float(w_l1), float(w_ssim), 1.0, L.ptr(out), L.ptr(grad),
                              L.ptr(scratch), L.stream_ptr())
     L.check(rc, "gsb_ssim_l1")

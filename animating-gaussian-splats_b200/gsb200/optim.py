@@ -26,7 +26,7 @@ class _Activate(torch.autograd.Function):
         if q.shape != (P, 4) or lg.numel() != P or ls.shape != (P, 3):
             raise RuntimeError("expected rotation_quaternions [P,4], opacity_logits [P,1], log_scales [P,3]")
         rot, opa, sca = torch.empty_like(q), torch.empty_like(lg), torch.empty_like(ls)
-        with torch.cuda.device(q.device):
+        with L.device_guard(q.device):
             rc = L.lib().gsb_activate(P, L.ptr(q), L.ptr(lg), L.ptr(ls), L.ptr(rot), L.ptr(opa), L.ptr(sca), L.stream_ptr())
         L.check(rc, "gsb_activate")
         ctx.save_for_backward(q, opa, sca)
@@ -42,7 +42,7 @@ class _Activate(torch.autograd.Function):
         gq = torch.empty_like(q) if need[0] else None
         gl = torch.empty_like(opa) if need[1] else None
         gs = torch.empty_like(sca) if need[2] else None
-        with torch.cuda.device(q.device):
+        with L.device_guard(q.device):
             rc = L.lib().gsb_activate_backward(P, L.ptr(q), L.ptr(opa), L.ptr(sca), L.ptr(d_rot), L.ptr(d_opa), L.ptr(d_sca),
                                                L.ptr(gq), L.ptr(gl), L.ptr(gs), L.stream_ptr())
         L.check(rc, "gsb_activate_backward")
@@ -50,8 +50,16 @@ class _Activate(torch.autograd.Function):
 
 
 def activate(params):
-    """(rotations, opacities, scales) of a raw parameter dict, differentiable."""
-    return _Activate.apply(params["rotation_quaternions"], params["opacity_logits"], params["log_scales"])
+    """(rotations, opacities, scales) of a raw parameter dict, differentiable.  The outputs remember which raw
+    tensors (object + version counter) they were computed from, so gsb200.raster can recognise two activations of
+    the same parameters as the same geometry (see "Geometry reuse" there)."""
+    q, lg, ls = params["rotation_quaternions"], params["opacity_logits"], params["log_scales"]
+    out = _Activate.apply(q, lg, ls)
+    rot, opa, sca = out
+    rot._gsb_src = (("rot", 0), (q, q._version))
+    opa._gsb_src = (("opa", 0), (lg, lg._version))
+    sca._gsb_src = (("sca", 0), (ls, ls._version))
+    return out
 
 
 def create_render_arguments(gaussian_cloud_parameters):
@@ -112,9 +120,13 @@ class FusedAdam(torch.optim.Optimizer):
                     a.param, a.grad = p.data_ptr(), g.data_ptr()
                     a.exp_avg, a.exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
                     a.numel, a.step, a.lr = p.numel(), int(st["step"]), lr
-                with torch.cuda.device(dev):
+                with L.device_guard(dev):
                     rc = lib.gsb_adam_step(len(chunk), arr, betas[0], betas[1], eps, L.stream_ptr())
                 L.check(rc, "gsb_adam_step")
+                for p, _, st, _ in chunk:   # the kernel wrote through raw pointers: tell torch the contents changed
+                    torch.autograd.graph.increment_version(p)
+                    torch.autograd.graph.increment_version(st["exp_avg"])
+                    torch.autograd.graph.increment_version(st["exp_avg_sq"])
         return loss
 
 

@@ -75,6 +75,43 @@ class RasterState:
         return out
 
 
+# ------------------------------------------------------------------------------------------------
+# Geometry reuse.  Everything a forward call computes before the blend depends only on (means3D, opacities,
+# scales, rotations / cov3D, cameras, image size); densify.py:116-150 renders the SAME Gaussians through the SAME
+# camera twice per iteration (colours, then segmentation colours), so the second call can take the first call's
+# state and run the blend kernel alone: no preprocess, no sorts, no host synchronisation.  A hit requires every
+# geometry input to be provably unchanged: the same tensor object at the same torch version counter, or an output
+# of gsb200.optim.activate whose raw inputs are the same objects at the same versions (`_gsb_src`).  The cache
+# keeps the previous call's tensors alive, so a recycled address can never alias.  GSB_GEOM_CACHE=0 disables it.
+# ------------------------------------------------------------------------------------------------
+import os as _os
+
+_GEOM_CACHE_ON = _os.environ.get("GSB_GEOM_CACHE", "1") != "0"
+_geom_cache = None   # (ident list, scalar key, RasterState, radii)
+geom_cache_hits = 0
+
+
+def _ident(t):
+    """(object, version) pairs that pin down the contents of a geometry input."""
+    if t is None or t.numel() == 0:   # the reference's "not provided" convention: None or an empty tensor
+        return None
+    src = getattr(t, "_gsb_src", None)
+    if src is not None:
+        return src
+    return ((t, t._version),)
+
+
+def _same_ident(a, b):
+    if a is None or b is None:
+        return a is None and b is None
+    return len(a) == len(b) and all(x[0] is y[0] and x[1] == y[1] for x, y in zip(a, b))
+
+
+def invalidate_geometry_cache():
+    global _geom_cache
+    _geom_cache = None
+
+
 def _f32c(t, name):
     if t is None or t.numel() == 0:
         return None
@@ -93,14 +130,25 @@ def _as_list(x, n):
 
 def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, scale_modifier, viewmatrix,
             projmatrix, tanfovx, tanfovy, image_height, image_width, prefiltered=False, n_cams=1,
-            colors_per_camera=False):
-    """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim."""
+            colors_per_camera=False, reuse_geometry=False):
+    """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim.
+    reuse_geometry: allow this call to take (and to leave behind) pre-blend state, see "Geometry reuse" above; the
+    drop-in autograd node passes True, the batched step does not (every step there has new parameters)."""
+    global _geom_cache, geom_cache_hits
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # DGR/rasterize_points.cu:56-58
     L.require_cuda(means3D, "means3D")
     dev = means3D.device
     P = means3D.size(0)
     H, W = int(image_height), int(image_width)
+    idents = [_ident(t) for t in (means3D, opacities, scales, rotations, cov3D_precomp, viewmatrix, projmatrix)]
+    scalars = (P, n_cams, H, W, float(scale_modifier), bool(prefiltered), tuple(_as_list(tanfovx, n_cams)),
+               tuple(_as_list(tanfovy, n_cams)), dev,
+               torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None else torch._C._cuda_getDevice()))
+    cached = _geom_cache
+    use_cache = _GEOM_CACHE_ON and reuse_geometry
+    hit = (use_cache and cached is not None and P > 0 and cached[1] == scalars and
+           all(_same_ident(a, b) for a, b in zip(cached[0], idents)))
     st = RasterState()
     st.keep = [_f32c(means3D, "means3D"), _f32c(colors, "colors_precomp"), _f32c(opacities, "opacities"),
                _f32c(scales, "scales"), _f32c(rotations, "rotations"), _f32c(cov3D_precomp, "cov3D_precomp"),
@@ -126,7 +174,16 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
     depth = torch.empty((n_cams, 1, H, W), dtype=torch.float32, device=dev)
     radii = torch.empty((n_cams, P), dtype=torch.int32, device=dev)
     st.geom = st.binning = st.img = None
-    if P == 0:
+    if hit:
+        prev = cached[2]
+        C.memmove(C.byref(st.ctx), C.byref(prev.ctx), C.sizeof(L.RasterCtx))
+        st.geom, st.binning, st.img = prev.geom, prev.binning, prev.img
+        radii = cached[3]
+        with L.device_guard(dev):
+            rc = L.lib().gsb_raster_forward_colors(C.byref(a), C.byref(st.ctx), L.ptr(color), L.ptr(depth), L.stream_ptr())
+        L.check(rc, "gsb_raster_forward_colors")
+        geom_cache_hits += 1
+    elif P == 0:
         color.zero_(); depth.zero_()
         st.ctx.P, st.ctx.n_cams, st.ctx.width, st.ctx.height = 0, n_cams, W, H
     else:
@@ -140,11 +197,13 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
             return L.ALLOC_FN(cb)
 
         cbs = [make_cb("geom"), make_cb("binning"), make_cb("img")]
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             rc = L.lib().gsb_raster_forward(C.byref(a), cbs[0], cbs[1], cbs[2], None, L.ptr(color), L.ptr(depth),
                                             L.ptr(radii), C.byref(st.ctx), L.stream_ptr())
         L.check(rc, "gsb_raster_forward")
         st.geom, st.binning, st.img = bufs.get("geom"), bufs.get("binning"), bufs.get("img")
+        if use_cache:
+            _geom_cache = (idents, scalars, st, radii)
     if n_cams == 1:
         return color[0], depth[0], radii[0], st
     return color, depth, radii, st
@@ -168,7 +227,7 @@ def backward(st, dL_dpix, need_cov3D_grad=True):
         dpix = dL_dpix.contiguous()
         if dpix.dtype != torch.float32:
             dpix = dpix.float()
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             rc = L.lib().gsb_raster_backward(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(g["means2D"]), L.ptr(g["conic"]),
                                              L.ptr(g["opacities"]), L.ptr(g["colors"]), L.ptr(g["means3D"]),
                                              L.ptr(g["cov3D"]), L.ptr(g["scales"]), L.ptr(g["rotations"]),
@@ -189,7 +248,7 @@ def mark_visible(means3D, viewmatrix, projmatrix):
         m = means3D.contiguous().float()
         v = viewmatrix.contiguous().float()
         p = projmatrix.contiguous().float()
-        with torch.cuda.device(means3D.device):
+        with L.device_guard(means3D.device):
             rc = L.lib().gsb_mark_visible(P, L.ptr(m), L.ptr(v), L.ptr(p), L.ptr(present), L.stream_ptr())
         L.check(rc, "gsb_mark_visible")
     return present

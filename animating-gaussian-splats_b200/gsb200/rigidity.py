@@ -92,7 +92,7 @@ def create_foreground_info(gaussian_cloud_parameters, initial_neighbor_indices):
     F, K = prep.F, prep.K
     inv = torch.empty((F, 4), dtype=torch.float32, device=means.device)
     off = _offsets_storage(F, K, means.device)
-    with torch.cuda.device(means.device):
+    with L.device_guard(means.device):
         rc = L.lib().gsb_foreground_info(F, K, L.ptr(prep.fg_index), L.ptr(means), L.ptr(quats), L.ptr(prep.nbr_t), 1, F,
                                          L.ptr(inv), C_ptr(off), off.stride(0), off.stride(1), off.stride(2),
                                          L.stream_ptr())
@@ -109,7 +109,7 @@ class _Rigidity(torch.autograd.Function):
         dm = torch.zeros_like(m) if need else None
         dq = torch.zeros_like(q) if need else None
         F, K = prep.F, prep.K
-        with torch.cuda.device(m.device):
+        with L.device_guard(m.device):
             rc = L.lib().gsb_rigidity_loss(F, K, L.ptr(prep.fg_index), L.ptr(m), L.ptr(q), L.ptr(prev_inv),
                                            L.ptr(prep.nbr_t), 1, F, L.ptr(prep.w_t), 1, F, C_ptr(prev_off),
                                            prev_off.stride(0), prev_off.stride(1), prev_off.stride(2),

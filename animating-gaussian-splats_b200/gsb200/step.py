@@ -26,7 +26,7 @@ class DensifyStats:
 
     def accumulate(self, radii, grad_means2D):
         P = radii.numel()
-        with torch.cuda.device(radii.device):
+        with L.device_guard(radii.device):
             rc = L.lib().gsb_densify_accumulate(P, L.ptr(radii), L.ptr(grad_means2D), L.ptr(self.max_2d_radii),
                                                 L.ptr(self.mean_2d_gradients_accumulated),
                                                 L.ptr(self.visibility_count), L.ptr(self.gaussian_is_visible_mask),
@@ -36,7 +36,7 @@ class DensifyStats:
     def accumulate_batch(self, radii, grad_means2D):
         """radii [n,P], grad_means2D [n,P,3]: all cameras of the batch in one launch."""
         n, P = radii.shape
-        with torch.cuda.device(radii.device):
+        with L.device_guard(radii.device):
             rc = L.lib().gsb_densify_accumulate_batch(P, n, L.ptr(radii), L.ptr(grad_means2D), L.ptr(self.max_2d_radii),
                                                       L.ptr(self.mean_2d_gradients_accumulated),
                                                       L.ptr(self.visibility_count),

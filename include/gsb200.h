@@ -111,6 +111,16 @@ int gsb_raster_forward(const gsb_raster_args* args, gsb_alloc_fn geom_alloc, gsb
                        gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth,
                        int32_t* radii, gsb_raster_ctx* ctx, void* stream);
 
+/* Re-blend an existing forward state with different colours: everything a forward call computes before the
+ * blend (preprocess, sorts, instance lists, tile ranges) depends only on the geometry, opacities and cameras, so
+ * a second render of the SAME Gaussians through the SAME cameras -- the segmentation render that follows every
+ * colour render in densify.py:116-150 -- only needs the blend kernel: no sorts and no host synchronisation.
+ * `a` = the forward call's arguments with `colors` replaced; `ctx` = the state that call left behind (its
+ * final_T / n_contrib are rewritten with identical values).  gsb_raster_backward then takes the same `ctx`
+ * together with these arguments. */
+int gsb_raster_forward_colors(const gsb_raster_args* a, const gsb_raster_ctx* ctx, float* out_color, float* out_depth,
+                              void* stream);
+
 /* Rasterizer::backward (cr/rasterizer.h:56-83, cr/rasterizer_impl.cu:343-436).
  * dL_dpix [n_cams][3][H][W].  Outputs (all written in full, no pre-zeroing required):
  *   dL_dmean2D [n_cams][P][3] (z = 0), dL_dconic [n_cams][P][4] (scratch: on return it holds the raw second
