@@ -139,7 +139,7 @@ static size_t carve_image(char* base, int W, int H, int n_cams, int tiles_total,
   const size_t n = (size_t)W * H * n_cams;
   float* ft = k.take<float>(n);
   uint32_t* nc = k.take<uint32_t>(n);
-  uint32_t* rg = k.take<uint32_t>(2 * (size_t)tiles_total);
+  uint32_t* rg = k.take<uint32_t>(3 * (size_t)tiles_total);   // ranges (uint2 per tile) + heaviest-first tile order
   if (c) { c->final_T = ft; c->n_contrib = nc; c->ranges = rg; }
   return align_up(k.off, 256);
 }
@@ -219,6 +219,7 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   const int tiles_per_cam = ctx->tiles_x * ctx->tiles_y;
   const int tiles_total = tiles_per_cam * a->n_cams;
   if (tiles_per_cam > 65535 || a->n_cams > 1024) return GSB_EINVAL;   // 16-bit camera-local tile ids
+  if (tiles_total >= (1 << 24)) return GSB_EINVAL;                    // blend kernels: float-assisted tile coordinates
   ctx->tile_bits = (int)higher_msb((uint32_t)tiles_per_cam);
   ctx->sort_bits = 32 + (int)higher_msb((uint32_t)tiles_total);
   if (a->P == 0) return GSB_OK;  // the glue returns zero images, like DGR/rasterize_points.cu:81
@@ -302,6 +303,7 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
                                      ctx->ranges, st)))
       return rc;
   }
+  if ((rc = launch_tile_order(tiles_total, ctx->ranges, ctx->ranges + 2 * (size_t)tiles_total, st))) return rc;
   prof_mark(PF_RANGES, st);
   if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
   prof_mark(PF_RENDER_FWD, st);

@@ -82,6 +82,7 @@ int launch_ranges_from_hist(int n_cams, int tiles_per_cam, int log_nb, const uin
 int launch_tile_ranges_seg(int64_t R, int n_cams, int tiles_per_cam, const uint32_t* seg_start, const uint16_t* keys,
                            uint32_t* ranges, cudaStream_t st);
 
+int launch_tile_order(int tiles_total, const uint32_t* ranges, uint32_t* order, cudaStream_t st);
 int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,
                       cudaStream_t st);
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
