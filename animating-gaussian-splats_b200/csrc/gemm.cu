@@ -333,6 +333,145 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Weight gradient: dW[N, K] = G[rows, N]^T . X[rows, K], the reduction runs over the ROWS (3e5), so both operands are
+// "MN-major" for the tensor core: A = G^T is contiguous along M (= n), B = X along N (= k).  For 32-bit MN-major operands
+// the only shared-memory layout is the 128-byte swizzle with 32-byte atoms (UMMA layout type SWIZZLE_128B_BASE32B:
+// 128-byte rows, the four 32-byte chunks of a row XOR-permuted by row % 4), which is what a TMA box of
+// [32 rows x 32 floats] with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B writes: blocks of 32 floats along M / N are LBO = 4096 B
+// apart, groups of 4 reduction rows SBO = 512 B apart, and one kind::tf32 instruction (K = 8) consumes two groups.  Each CTA owns a contiguous range of 32-row blocks, accumulates its
+// whole range in TMEM (up to 2 x [128 x 256] FP32 = all 512 columns) and writes ONE partial [N, K]; a second kernel sums
+// the partials.  N, K multiples of 32, <= 256.
+// ------------------------------------------------------------------------------------------------
+constexpr int WG_BK = 32;   // reduction rows per stage
+
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((WG_BK * 128) >> 4) << 16;   // leading byte offset: next block of 32 floats along M / N
+  d |= (uint64_t)(512 >> 4) << 32;             // stride byte offset: next group of 4 reduction rows
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;                      // SWIZZLE_128B_BASE32B: the only MN-major layout for 32-bit operands
+  return d;
+}
+
+struct WgradParams {
+  long long rows;
+  int N, K, npad, stages;
+  float* partial;   // [gridDim.x][N][K]
+};
+
+__global__ void __launch_bounds__(GM_THREADS, 1)
+wgrad_tf32_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_x, WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES], empty_bar[GM_MAX_STAGES], acc_full;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int a_bytes = p.npad * 128, b_bytes = p.K * 128;
+  const int stage_bytes = a_bytes + b_bytes;
+  const long long blocks = (p.rows + WG_BK - 1) / WG_BK;
+  const long long b0 = blocks * blockIdx.x / gridDim.x, b1 = blocks * (blockIdx.x + 1) / gridDim.x;
+  const int halves = p.npad / 128;
+  const uint32_t cols = halves * p.K <= 32 ? 32 : halves * p.K <= 64 ? 64 : halves * p.K <= 128 ? 128
+                        : halves * p.K <= 256 ? 256 : 512;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long b = b0; b < b1; b++) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* a = smem + (size_t)stage * stage_bytes;
+        uint8_t* bt = a + a_bytes;
+        mbar_expect_tx(&full_bar[stage], (uint32_t)((p.N + p.K) * 128));
+        for (int nb = 0; nb < p.N / 32; nb++) tma_load_2d(&map_g, &full_bar[stage], a + nb * (WG_BK * 128), nb * 32, (int)(b * WG_BK));
+        for (int kb = 0; kb < p.K / 32; kb++) tma_load_2d(&map_x, &full_bar[stage], bt + kb * (WG_BK * 128), kb * 32, (int)(b * WG_BK));
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // D = F32, A = B = TF32, both MN-major (bits 15, 16), N = K_dim, M = 128
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
+                             ((uint32_t)(p.K >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long b = b0; b < b1; b++) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint32_t bt = a + a_bytes;
+#pragma unroll
+        for (int s = 0; s < WG_BK / GM_UMMA_K; s++) {
+          const uint64_t bd = umma_desc_mn_sw128(bt + s * 1024);
+          for (int h = 0; h < halves; h++) {
+            const uint64_t ad = umma_desc_mn_sw128(a + h * (4 * WG_BK * 128) + s * 1024);
+            tc_mma_tf32(tmem_base + (uint32_t)(h * p.K), ad, bd, idesc, (b != b0 || s != 0) ? 1u : 0u);
+          }
+        }
+        tc_commit(&empty_bar[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(&acc_full);
+    }
+  } else {
+    const int q = warp & 3;
+    float* out = p.partial + (size_t)blockIdx.x * p.N * p.K;
+    if (b1 > b0) {
+      mbar_wait(&acc_full, 0);
+      tc_fence_after();
+    }
+    for (int h = 0; h < halves; h++) {
+      const int n = h * 128 + q * 32 + lane;
+      for (int c = 0; c < p.K; c += 16) {
+        uint32_t v[16];
+        if (b1 > b0) {
+          tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * p.K + c), v);
+          tc_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; i++) v[i] = 0u;
+        }
+        if (n < p.N) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 4)
+            *reinterpret_cast<float4*>(out + (size_t)n * p.K + c + i) =
+                make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(cols) : "memory");
+}
+
+__global__ void wgrad_reduce_kernel(int parts, long long n, const float* __restrict__ partial, float* __restrict__ dW,
+                                    int accumulate) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int c = 0; c < parts; c++) s += partial[(size_t)c * n + i];
+  dW[i] = accumulate ? dW[i] + s : s;
+}
+
 }  // namespace gsb
 
 // ------------------------------------------------------------------------------------------------
@@ -368,7 +507,8 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // 2-D FP32 tensor [rows][cols] with row pitch ld (floats), box [box_rows][32 floats], 128B swizzle, zero fill.
-static bool make_map(CUtensorMap* m, const float* base, long long rows, int cols, long long ld, int box_rows) {
+static bool make_map(CUtensorMap* m, const float* base, long long rows, int cols, long long ld, int box_rows,
+                     CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return false;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -376,7 +516,7 @@ static bool make_map(CUtensorMap* m, const float* base, long long rows, int cols
   cuuint32_t box[2] = {(cuuint32_t)GM_BLOCK_K, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -466,6 +606,50 @@ int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_
   split_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, W, hi, lo);
   GSB_LAUNCH_CHECK();
   return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, bias, Y, ldy, col_stats, st);
+}
+
+size_t gsb_linear_wgrad_scratch_bytes(int32_t N, int32_t K) { return (size_t)148 * 2 * N * K * sizeof(float); }
+
+int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                          float* dW, int32_t accumulate, void* scratch, void* stream) {
+  if (rows < 0 || N <= 0 || K <= 0 || N > 256 || K > 256 || (N & 31) || (K & 31) || rows > 0x7fffffffLL) return GSB_EINVAL;
+  if (!dW || !scratch) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (rows == 0) {
+    if (!accumulate) GSB_CUDA_CHECK(cudaMemsetAsync(dW, 0, (size_t)N * K * sizeof(float), st));
+    return GSB_OK;
+  }
+  if (!G || !X || ldg < N || ldx < K || (ldg & 3) || (ldx & 3)) return GSB_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(G) | reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(scratch)) & 15u)
+    return GSB_EINVAL;
+  WgradParams p;
+  p.rows = rows; p.N = N; p.K = K; p.npad = (N + 127) / 128 * 128;
+  p.partial = reinterpret_cast<float*>(scratch);
+  const int stage_bytes = (p.npad + K) * 128;
+  p.stages = (220 * 1024) / stage_bytes;
+  if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
+  if (p.stages < 2) return GSB_EINVAL;
+  CUtensorMap mg, mx;
+  if (!make_map(&mg, G, rows, N, ldg, WG_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
+      !make_map(&mx, X, rows, K, ldx, WG_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return GSB_ECUDA;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    attr_set = true;
+  }
+  const long long blocks = (rows + WG_BK - 1) / WG_BK;
+  int grid = sm_count() < 296 ? sm_count() : 296;
+  if (grid > blocks) grid = (int)blocks;
+  const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+  wgrad_tf32_kernel<<<grid, GM_THREADS, smem, st>>>(mg, mx, p);
+  GSB_LAUNCH_CHECK();
+  const long long n = (long long)N * K;
+  wgrad_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(grid, n, p.partial, dW, accumulate);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
 }
 
 }  // extern "C"

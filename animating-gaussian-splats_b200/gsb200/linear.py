@@ -36,3 +36,24 @@ def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
                                          L.ptr(col_stats), L.stream_ptr())
     L.check(rc, "gsb_linear_tf32")
     return y
+
+
+def linear_wgrad(grad_out, x, out=None, accumulate=False):
+    """dW [N, K] = grad_out[rows, N]^T @ x[rows, K] on the tcgen05 weight-gradient kernel (TF32)."""
+    L.require_cuda(x, "x")
+    g = grad_out if (grad_out.dtype == torch.float32 and grad_out.stride(-1) == 1) else grad_out.float().contiguous()
+    x = x if (x.dtype == torch.float32 and x.stride(-1) == 1) else x.float().contiguous()
+    rows, n = g.shape
+    k = x.shape[1]
+    if x.shape[0] != rows:
+        raise RuntimeError("linear_wgrad: row counts differ")
+    dw = out if out is not None else torch.empty((n, k), dtype=torch.float32, device=x.device)
+    nbytes = L.lib().gsb_linear_wgrad_scratch_bytes(n, k)
+    key = (x.device, "wgrad", nbytes)
+    if key not in _scratch:
+        _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    with L.device_guard(x.device):
+        rc = L.lib().gsb_linear_wgrad_tf32(rows, n, k, L.ptr(g), g.stride(0), L.ptr(x), x.stride(0), L.ptr(dw),
+                                           1 if accumulate else 0, L.ptr(_scratch[key]), L.stream_ptr())
+    L.check(rc, "gsb_linear_wgrad_tf32")
+    return dw

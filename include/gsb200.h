@@ -244,6 +244,15 @@ size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N);
 int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
                       const float* bias, float* Y, int64_t ldy, double* col_stats, void* scratch, void* stream);
 
+/* Weight gradient of the dense layer: dW[N, K] (dense, row pitch K) = G[rows, N]^T . X[rows, K] (+= when accumulate),
+ * TF32 multiply / FP32 accumulate on tcgen05 with both operands MN-major (the reduction runs over the rows).
+ * N, K multiples of 32 and <= 256; G, X 16-byte aligned with pitches multiples of 4; scratch: device buffer of
+ * gsb_linear_wgrad_scratch_bytes(N, K) bytes (per-CTA partial sums).  The input gradient dX = G . W is
+ * gsb_linear_tf32 with the transposed weight. */
+size_t gsb_linear_wgrad_scratch_bytes(int32_t N, int32_t K);
+int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                          float* dW, int32_t accumulate, void* scratch, void* stream);
+
 /* BatchNorm1d in training mode (batch statistics; the reference never switches the network to eval) + optional
  * residual + exact (erf) GELU in one pass over Z [rows, N]: Y = act(gamma (Z - mean) / sqrt(var + eps) + beta
  * [+ residual]), mean / biased var from col_stats = the [2][N] sums gsb_linear_tf32 accumulated (train.py:57-78).

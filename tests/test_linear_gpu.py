@@ -36,3 +36,20 @@ def test_linear_no_bias_and_strided_input():
     wide[:, :64] = x
     y = linear(wide[:, :64], w, None)     # row pitch 96 floats: no copy needed
     assert ((y.double() - want).abs() / scale).max().item() < 2e-3
+
+
+@pytest.mark.parametrize("rows,N,K", [(32, 128, 32), (1000, 128, 192), (4096, 256, 256), (300_000, 256, 192), (5, 64, 64),
+                                      (300_001, 128, 128), (70_000, 192, 96)])
+def test_wgrad_matches_float64(rows, N, K):
+    from gsb200.linear import linear_wgrad
+    g = torch.Generator().manual_seed(rows % 89)
+    go = torch.randn(rows, N, generator=g).cuda()
+    x = torch.randn(rows, K, generator=g).cuda()
+    dw = linear_wgrad(go, x)
+    torch.cuda.synchronize()
+    want = go.double().t() @ x.double()
+    scale = go.double().norm(dim=0)[:, None] * x.double().norm(dim=0)[None]
+    err = ((dw.double() - want).abs() / scale).max().item()
+    assert err < 2e-3, err
+    acc = linear_wgrad(go, x, out=dw.clone(), accumulate=True)
+    assert ((acc.double() - 2 * want).abs() / scale).max().item() < 4e-3
