@@ -76,6 +76,112 @@ posenc_kernel(long long rows, int D, int F, const float* __restrict__ x, long lo
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Backward of the BatchNorm (training mode) + residual + GELU stage, two passes over [rows, N]:
+//   pass 1 (bn_act_bwd_reduce):  g = dy * act'(s z + t [+ r]);  writes g, accumulates per column sum(g) and
+//                                sum(g xhat), xhat = (z - mean) inv_std  -> dbeta, dgamma
+//   pass 2 (bn_bwd_apply):       dz = gamma inv_std (g - dbeta / rows - xhat dgamma / rows)     (in place over g)
+// g is also the gradient of the residual input.  Threads keep a fixed column group (4 columns) and stride over
+// rows, so the column sums are per-thread registers, one shared-memory reduction and 2 N double atomics per block.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  return cdf + x * 0.39894228040143267794f * expf(-0.5f * x * x);
+}
+
+struct BnCols { float mean, inv_std, scale, shift; };
+
+__device__ __forceinline__ BnCols bn_col(const double* stats, int N, int c, long long rows, const float* gamma,
+                                         const float* beta, float eps) {
+  const double mean = stats[c] / (double)rows;
+  double var = stats[N + c] / (double)rows - mean * mean;
+  var = var < 0.0 ? 0.0 : var;
+  BnCols b;
+  b.mean = (float)mean;
+  b.inv_std = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[c] : 1.f;
+  b.scale = g * b.inv_std;
+  b.shift = (beta ? beta[c] : 0.f) - b.mean * b.scale;
+  return b;
+}
+
+__global__ void __launch_bounds__(256)
+bn_act_bwd_reduce_kernel(long long rows, int N, const float* __restrict__ dY, long long ldd, const float* __restrict__ Z,
+                         long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, float eps, const float* __restrict__ residual, long long ldr,
+                         int apply_gelu, float* __restrict__ G, long long ldg, double* __restrict__ sums) {
+  __shared__ float s_red[2][256][4];
+  const int n4 = N >> 2;
+  const int row_lanes = blockDim.x / n4;              // blockDim.x = n4 * row_lanes
+  const int cg = threadIdx.x % n4, rl = threadIdx.x / n4;
+  const int c = cg << 2;
+  BnCols b[4];
+#pragma unroll
+  for (int e = 0; e < 4; e++) b[e] = bn_col(stats, N, c + e, rows, gamma, beta, eps);
+  float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long r = (long long)blockIdx.x * row_lanes + rl; r < rows; r += (long long)gridDim.x * row_lanes) {
+    const float4 z = *reinterpret_cast<const float4*>(Z + r * ldz + c);
+    const float4 dy = *reinterpret_cast<const float4*>(dY + r * ldd + c);
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (residual) q = *reinterpret_cast<const float4*>(residual + r * ldr + c);
+    float g[4];
+    const float zz[4] = {z.x, z.y, z.z, z.w}, dd[4] = {dy.x, dy.y, dy.z, dy.w}, qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      const float pre = fmaf(zz[e], b[e].scale, b[e].shift) + qq[e];
+      g[e] = apply_gelu ? dd[e] * gelu_erf_grad(pre) : dd[e];
+      s1[e] += g[e];
+      s2[e] = fmaf(g[e], (zz[e] - b[e].mean) * b[e].inv_std, s2[e]);
+    }
+    *reinterpret_cast<float4*>(G + r * ldg + c) = make_float4(g[0], g[1], g[2], g[3]);
+  }
+#pragma unroll
+  for (int e = 0; e < 4; e++) { s_red[0][threadIdx.x][e] = s1[e]; s_red[1][threadIdx.x][e] = s2[e]; }
+  __syncthreads();
+  if (rl == 0) {
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      double a1 = 0.0, a2 = 0.0;
+      for (int k = 0; k < row_lanes; k++) { a1 += (double)s_red[0][k * n4 + cg][e]; a2 += (double)s_red[1][k * n4 + cg][e]; }
+      atomicAdd(sums + c + e, a1);
+      atomicAdd(sums + N + c + e, a2);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(long long rows, int N, float* __restrict__ G, long long ldg, const float* __restrict__ Z,
+                    long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma, float eps,
+                    const double* __restrict__ sums, float* __restrict__ d_gamma, float* __restrict__ d_beta) {
+  __shared__ float s_k0[256], s_k1[256], s_k2[256];   // dz = k0 g + k1 + k2 z
+  for (int c = threadIdx.x; c < N; c += 256) {
+    const BnCols b = bn_col(stats, N, c, rows, gamma, nullptr, eps);
+    const float db = (float)(sums[c] / (double)rows), dg = (float)(sums[N + c] / (double)rows);
+    // dz = scale (g - db - xhat dg), xhat = (z - mean) inv_std
+    s_k0[c] = b.scale;
+    s_k2[c] = -b.scale * dg * b.inv_std;
+    s_k1[c] = -b.scale * db - s_k2[c] * b.mean;
+    if (blockIdx.x == 0) {
+      if (d_gamma) d_gamma[c] = (float)sums[N + c];
+      if (d_beta) d_beta[c] = (float)sums[c];
+    }
+  }
+  __syncthreads();
+  const int n4 = N >> 2;
+  const long long total = rows * n4;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const long long r = i / n4;
+    const int c = (int)(i - r * n4) << 2;
+    float4 g = *reinterpret_cast<float4*>(G + r * ldg + c);
+    const float4 z = *reinterpret_cast<const float4*>(Z + r * ldz + c);
+    g.x = fmaf(s_k0[c], g.x, fmaf(s_k2[c], z.x, s_k1[c]));
+    g.y = fmaf(s_k0[c + 1], g.y, fmaf(s_k2[c + 1], z.y, s_k1[c + 1]));
+    g.z = fmaf(s_k0[c + 2], g.z, fmaf(s_k2[c + 2], z.z, s_k1[c + 2]));
+    g.w = fmaf(s_k0[c + 3], g.w, fmaf(s_k2[c + 3], z.w, s_k1[c + 3]));
+    *reinterpret_cast<float4*>(G + r * ldg + c) = g;
+  }
+}
+
 }  // namespace gsb
 
 using namespace gsb;
@@ -107,6 +213,35 @@ int gsb_positional_encoding(int64_t rows, int32_t D, int32_t F, const float* x, 
   const long long total = rows * D;
   posenc_kernel<<<(unsigned)((total + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       rows, D, F, x, ldx, lo, span, out, ldo, col0);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, const float* Z, int64_t ldz,
+                         const double* col_stats, const float* gamma, const float* beta, float eps,
+                         const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg, float* dZ,
+                         int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream) {
+  if (rows < 0 || N <= 0 || N > 256 || (N & 3)) return GSB_EINVAL;
+  if (rows == 0) return GSB_OK;
+  if (!dY || !Z || !col_stats || !G || !dZ || !sums) return GSB_EINVAL;
+  if ((ldd & 3) || (ldz & 3) || (ldg & 3) || (lddz & 3) || (residual && (ldr & 3))) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  GSB_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * (size_t)N * sizeof(double), st));
+  const int n4 = N >> 2;
+  const int row_lanes = 256 / n4;
+  bn_act_bwd_reduce_kernel<<<148 * 4, n4 * row_lanes, 0, st>>>(rows, N, dY, ldd, Z, ldz, col_stats, gamma, beta, eps,
+                                                                residual, ldr, apply_gelu, G, ldg, sums);
+  GSB_LAUNCH_CHECK();
+  // dZ = pass 2 over G (copied first when the caller wants G kept, e.g. as the residual branch's gradient)
+  if (dZ != G) {
+    if (ldg != lddz || ldg != N) return GSB_EINVAL;
+    GSB_CUDA_CHECK(cudaMemcpyAsync(dZ, G, (size_t)rows * N * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  }
+  const long long total = rows * n4;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, dZ, lddz, Z, ldz, col_stats, gamma, eps, sums, d_gamma,
+                                                        d_beta);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

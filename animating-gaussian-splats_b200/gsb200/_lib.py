@@ -100,6 +100,9 @@ SYMBOLS = {
     "gsb_bn_gelu": (C.c_int, [C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
                               C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_float,
                               C.c_int32, C.c_void_p]),
+    "gsb_bn_gelu_backward": (C.c_int, [C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                                       C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsb_positional_encoding": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "gsb_profile_enable": (C.c_int, [C.c_int]),

@@ -10,14 +10,18 @@ normalises, adds the residual and applies GELU.  BatchNorm always uses batch sta
 buffers, because the reference never leaves training mode.  `precise=True` selects the 3xTF32 split (FP32-level
 accuracy); the default is plain TF32 (what torch does with allow_tf32).
 
-FORWARD ONLY in this round: outputs carry no autograd graph.  Training the network needs the backward GEMMs
-(dX = dY W, dW = dY^T X) and the BatchNorm / GELU adjoints, which are the next step of this row.
+Training: when gradients are enabled the forward runs inside ONE autograd node (_DeformFn) that keeps the per-block
+activations (x, z1, a, z2 and the BatchNorm sums) and whose backward is built from the same pieces: dX = dY W on the
+forward GEMM with the transposed weight, dW = dY^T X on the MN-major tcgen05 weight-gradient kernel, and the two-pass
+BatchNorm / GELU adjoint (gsb_bn_gelu_backward).  The backward GEMMs run in TF32 (like torch with allow_tf32), also
+when the forward uses the 3xTF32 split.  The 7-wide output layer's two backward products stay on torch.mm: 7 is not a
+tensor-core tile, and they are 2% of the backward's bytes.
 """
 import torch
 from torch import nn
 
 from . import _lib as L
-from .linear import linear
+from .linear import linear, linear_wgrad
 
 
 def positional_encoding(x, frequency_count, lo=None, span=None, out=None, col0=0):
@@ -88,7 +92,46 @@ class DeformationNetwork(nn.Module):
         bn.num_batches_tracked += 1
         return y
 
-    @torch.no_grad()
+    def _bn_bwd(self, dy, z, stats, bn, residual, gelu=True):
+        """-> (dz, g, d_gamma, d_beta): g = dy * act'(.) is also the residual branch's gradient."""
+        rows, n = z.shape
+        g = torch.empty_like(z)
+        dz = torch.empty_like(z) if residual is not None else g
+        sums = torch.empty((2, n), dtype=torch.float64, device=z.device)
+        dgam, dbet = torch.empty(n, device=z.device), torch.empty(n, device=z.device)
+        dy = dy.contiguous()
+        with L.device_guard(z.device):
+            rc = L.lib().gsb_bn_gelu_backward(rows, n, L.ptr(dy), dy.stride(0), L.ptr(z), z.stride(0), L.ptr(stats),
+                                              L.ptr(bn.weight.detach()), L.ptr(bn.bias.detach()), float(bn.eps),
+                                              L.ptr(residual), 0 if residual is None else residual.stride(0),
+                                              1 if gelu else 0, L.ptr(g), g.stride(0), L.ptr(dz), dz.stride(0), L.ptr(sums),
+                                              L.ptr(dgam), L.ptr(dbet), L.stream_ptr())
+        L.check(rc, "gsb_bn_gelu_backward")
+        return dz, g, dgam, dbet
+
+    def _forward_impl(self, x, keep):
+        """Shared by inference and training; keep = list that receives the per-block activations (or None)."""
+        h = self.fc_in.out_features
+        out = linear(x, self.fc_in.weight, self.fc_in.bias, precise=self.precise)
+        for block in self.residual_blocks:
+            identity = out
+            st1 = torch.zeros((2, h), dtype=torch.float64, device=x.device)
+            z1 = linear(identity, block.fc1.weight, None, precise=self.precise, col_stats=st1)
+            a = self._bn_act(z1, st1, block.bn1, None)
+            st2 = torch.zeros((2, h), dtype=torch.float64, device=x.device)
+            z2 = linear(a, block.fc2.weight, None, precise=self.precise, col_stats=st2)
+            out = self._bn_act(z2, st2, block.bn2, identity)
+            if keep is not None:
+                keep.append((identity, z1, st1, a, z2, st2))
+        delta = linear(out, self.fc_out.weight, self.fc_out.bias, precise=self.precise)
+        return delta, out
+
+    def _parameter_list(self):
+        ps = [self.fc_in.weight, self.fc_in.bias]
+        for b in self.residual_blocks:
+            ps += [b.fc1.weight, b.bn1.weight, b.bn1.bias, b.fc2.weight, b.bn2.weight, b.bn2.bias]
+        return ps + [self.fc_out.weight, self.fc_out.bias]
+
     def forward(self, initial_means_and_rotations, encoded_normalized_initial_means_and_rotations=None,
                 encoded_normalized_previous_means_and_rotations=None, encoded_progress=None, network_input=None):
         """train.py:88-110.  Pass either the three encoded blocks (concatenated here, like the reference) or the
@@ -96,26 +139,59 @@ class DeformationNetwork(nn.Module):
         if network_input is None:
             network_input = torch.cat((encoded_normalized_initial_means_and_rotations,
                                        encoded_normalized_previous_means_and_rotations, encoded_progress), dim=1)
-        x = network_input.float().contiguous()
-        h = self.fc_in.out_features
-        out = linear(x, self.fc_in.weight, self.fc_in.bias, precise=self.precise)
-        for block in self.residual_blocks:
-            identity = out
-            stats = torch.zeros((2, h), dtype=torch.float64, device=x.device)
-            z = linear(identity, block.fc1.weight, None, precise=self.precise, col_stats=stats)
-            a = self._bn_act(z, stats, block.bn1, None)
-            stats = torch.zeros((2, h), dtype=torch.float64, device=x.device)
-            z = linear(a, block.fc2.weight, None, precise=self.precise, col_stats=stats)
-            out = self._bn_act(z, stats, block.bn2, identity)
-        delta = linear(out, self.fc_out.weight, self.fc_out.bias, precise=self.precise)
-        return delta + initial_means_and_rotations
+        x = network_input.detach().float().contiguous()
+        params = self._parameter_list()
+        if torch.is_grad_enabled() and any(p.requires_grad for p in params):
+            return _DeformFn.apply(self, x, initial_means_and_rotations, *params)
+        with torch.no_grad():
+            delta, _ = self._forward_impl(x, None)
+            return delta + initial_means_and_rotations
+
+
+class _DeformFn(torch.autograd.Function):
+    """The whole network as one autograd node (inputs: the [N,192] encoding (no gradient), the [N,7] initial means and
+    rotations, the parameters in DeformationNetwork._parameter_list order)."""
+
+    @staticmethod
+    def forward(ctx, net, x, init, *params):
+        keep = []
+        delta, last = net._forward_impl(x, keep)
+        ctx.net, ctx.x, ctx.keep, ctx.last = net, x, keep, last
+        return delta + init
+
+    @staticmethod
+    def backward(ctx, d_out):
+        net, x, keep, last = ctx.net, ctx.x, ctx.keep, ctx.last
+        d_out = d_out.contiguous().float()
+        grads = {}
+        # output layer (7 columns): plain torch products
+        w_out = net.fc_out.weight.detach()
+        grads[net.fc_out.weight] = d_out.t() @ last
+        grads[net.fc_out.bias] = d_out.sum(0)
+        dh = d_out @ w_out
+        for block, (identity, z1, st1, a, z2, st2) in zip(reversed(list(net.residual_blocks)), reversed(keep)):
+            dz2, g2, dgam2, dbet2 = net._bn_bwd(dh, z2, st2, block.bn2, identity)
+            grads[block.bn2.weight], grads[block.bn2.bias] = dgam2, dbet2
+            grads[block.fc2.weight] = linear_wgrad(dz2, a)
+            da = linear(dz2, block.fc2.weight.detach().t().contiguous(), None)
+            dz1, _, dgam1, dbet1 = net._bn_bwd(da, z1, st1, block.bn1, None)
+            grads[block.bn1.weight], grads[block.bn1.bias] = dgam1, dbet1
+            grads[block.fc1.weight] = linear_wgrad(dz1, identity)
+            dh = linear(dz1, block.fc1.weight.detach().t().contiguous(), None)
+            dh += g2                                     # the residual branch
+        grads[net.fc_in.weight] = linear_wgrad(dh, x)
+        grads[net.fc_in.bias] = dh.sum(0)
+        ctx.keep = ctx.last = ctx.x = None
+        plist = net._parameter_list()
+        return (None, None, d_out) + tuple(grads[p] if p.requires_grad else None for p in plist)
 
 
 def update_gaussian_cloud_parameters(deformation_network, initial_gaussian_cloud_parameters,
                                      encoded_normalized_initial_means_and_rotations,
                                      encoded_normalized_previous_means_and_rotations, timestep, timestep_count):
-    """train.py:268-306 (forward only): means += 0.01 delta[:, :3], rotation_quaternions += 0.01 delta[:, 3:].
-    The [N, 192] input is assembled without the torch.cat: the progress encoding is written in place."""
+    """train.py:268-306: means += 0.01 delta[:, :3], rotation_quaternions += 0.01 delta[:, 3:] (differentiable w.r.t. the
+    network's parameters).  The [N, 192] input is assembled without the torch.cat: the progress encoding is written
+    in place."""
     p = initial_gaussian_cloud_parameters
     n, dev = p["means"].shape[0], p["means"].device
     x = torch.empty((n, 192), dtype=torch.float32, device=dev)

@@ -47,6 +47,12 @@ def linear_wgrad(grad_out, x, out=None, accumulate=False):
     k = x.shape[1]
     if x.shape[0] != rows:
         raise RuntimeError("linear_wgrad: row counts differ")
+    if n % 32 or k % 32 or n > 256 or k > 256:   # outside the tensor-core tiling: plain product
+        dw = g.t() @ x
+        if out is not None:
+            out.copy_(out + dw if accumulate else dw)
+            return out
+        return dw
     dw = out if out is not None else torch.empty((n, k), dtype=torch.float32, device=x.device)
     nbytes = L.lib().gsb_linear_wgrad_scratch_bytes(n, k)
     key = (x.device, "wgrad", nbytes)

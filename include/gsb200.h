@@ -262,6 +262,15 @@ int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const doub
                 const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
                 float* running_mean, float* running_var, float momentum, int32_t apply_gelu, void* stream);
 
+/* Adjoint of gsb_bn_gelu (same arguments for the forward quantities): given dY it forms G = dY * act'(pre-activation)
+ * (also the gradient of the residual input), the per-column sums (`sums`, DEVICE double[2][N], zeroed here) that are
+ * d_beta = sum G and d_gamma = sum G xhat, and dZ = gamma inv_std (G - d_beta / rows - xhat d_gamma / rows).
+ * dZ may alias G (in place); when it does not, both must be dense [rows, N].  d_gamma / d_beta [N] optional. */
+int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, const float* Z, int64_t ldz,
+                         const double* col_stats, const float* gamma, const float* beta, float eps,
+                         const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg, float* dZ,
+                         int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream);
+
 /* PositionalEncoding (train.py:113-127) of x [rows, D] with F frequencies 2^k pi into out[:, col0 + j D + d],
  * j in [0, 2F): even j -> sin(f x), odd j -> cos(sin(f x)) (the reference's in-place quirk).  With lo / span [D]
  * the input is first mapped to 2 (x - lo) / span - 1 (normalize_and_encode_means_and_rotations, train.py:186-205). */

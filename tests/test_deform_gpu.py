@@ -102,3 +102,57 @@ def test_update_gaussian_cloud_parameters_shapes():
     assert out["means"].shape == (n, 3) and out["rotation_quaternions"].shape == (n, 4)
     assert out["colors"] is p["colors"]
     assert torch.isfinite(out["means"]).all() and not torch.equal(out["means"], p["means"])
+
+
+@pytest.mark.parametrize("rows,h,blocks", [(20_000, 128, 2), (5000, 64, 1), (100_000, 256, 3)])
+def test_backward_matches_stock_torch(rows, h, blocks):
+    """Gradients of every parameter and of the [N,7] input through the tcgen05 backward (TF32 products) against torch
+    autograd on the same architecture in FP32: 3e-2 of each gradient's RMS (BatchNorm's 1/std carries the TF32 rounding
+    of the forward into every later layer, as in the forward test)."""
+    from gsb200 import deform
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(rows % 11)
+    ref = _StockNetwork(h, blocks).cuda().train()
+    with torch.no_grad():
+        for m in ref.modules():
+            if isinstance(m, nn.BatchNorm1d):
+                m.weight.uniform_(0.5, 1.5); m.bias.normal_(0, 0.3)
+    ours = deform.DeformationNetwork(h, blocks, precise=True).cuda()
+    ours.load_state_dict(ref.state_dict())
+    x = torch.randn(rows, 192, device="cuda")
+    init_a = torch.randn(rows, 7, device="cuda", requires_grad=True)
+    init_b = init_a.detach().clone().requires_grad_(True)
+    w = torch.randn(rows, 7, device="cuda")
+    (ref(init_a, x) * w).sum().backward()
+    out = ours(init_b, network_input=x)
+    assert out.requires_grad
+    (out * w).sum().backward()
+    assert torch.allclose(init_b.grad, init_a.grad)
+    for (name, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert p.grad is not None, name
+        rms = q.grad.pow(2).mean().sqrt().item() + 1e-12
+        err = (p.grad - q.grad).abs().max().item() / rms
+        assert err < 3e-2, (name, err)
+
+
+def test_training_steps_follow_stock_torch():
+    """Ten Adam steps on a regression target: the loss trajectory follows the stock network's."""
+    from gsb200 import deform
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(5)
+    ref = _StockNetwork(64, 2).cuda().train()
+    ours = deform.DeformationNetwork(64, 2, precise=True).cuda()
+    ours.load_state_dict(ref.state_dict())
+    x = torch.randn(8192, 192, device="cuda"); init = torch.zeros(8192, 7, device="cuda")
+    target = torch.randn(8192, 7, device="cuda") * 0.1
+    oa, ob = torch.optim.Adam(ref.parameters(), lr=1e-3), torch.optim.Adam(ours.parameters(), lr=1e-3)
+    la, lb = [], []
+    for _ in range(10):
+        for net, opt, log, call in ((ref, oa, la, lambda: ref(init, x)), (ours, ob, lb, lambda: ours(init, network_input=x))):
+            opt.zero_grad()
+            loss = (call() - target).pow(2).mean()
+            loss.backward()
+            opt.step()
+            log.append(float(loss.detach()))
+    assert lb[-1] < lb[0]
+    assert max(abs(a - b) / a for a, b in zip(la, lb)) < 2e-2, (la, lb)
