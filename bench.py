@@ -375,7 +375,7 @@ def run_ours(args):
 
 
 def deformation_shaped(args, hidden=256, blocks=4, iters=10):
-    """DeformationNetwork forward (train.py:80-110; 192 -> H, `blocks` residual blocks, H -> 7,
+    """DeformationNetwork forward and forward + backward (train.py:80-110; 192 -> H, `blocks` residual blocks, H -> 7,
     training-mode BatchNorm) over all Gaussians.  "ours_tf32" / "ours_3xtf32": gsb200.deform on the hand-written
     tcgen05 GEMM; "torch_fp32" (the reference's setting: torch's default keeps FP32 matmuls) and "torch_tf32"
     (allow_tf32): the same architecture in stock torch ops.  Also the 192 -> H layer alone with its HBM roofline."""
@@ -429,6 +429,22 @@ def deformation_shaped(args, hidden=256, blocks=4, iters=10):
             torch.backends.cuda.matmul.allow_tf32 = flag
             res[name] = timed(lambda: stock(init, x))
         torch.backends.cuda.matmul.allow_tf32 = False
+    # forward + backward (one training step of the network without the optimiser), gradient of sum(out * w)
+    wgt = torch.randn(n, 7, device=dev)
+
+    def train(net_call, net):
+        net.zero_grad(set_to_none=True)
+        (net_call() * wgt).sum().backward()
+
+    for precise in (False, True):
+        net = deform.DeformationNetwork(hidden, blocks, precise=precise).to(dev)
+        net.load_state_dict(stock.state_dict())
+        res["fwd_bwd_ours_3xtf32_fwd" if precise else "fwd_bwd_ours_tf32"] = timed(
+            lambda: train(lambda: net(init, network_input=x), net))
+    for name, flag in (("fwd_bwd_torch_fp32", False), ("fwd_bwd_torch_tf32", True)):
+        torch.backends.cuda.matmul.allow_tf32 = flag
+        res[name] = timed(lambda: train(lambda: stock(init, x), stock))
+    torch.backends.cuda.matmul.allow_tf32 = False
     w, b = stock.fc_in.weight.detach(), stock.fc_in.bias.detach()
     y = torch.empty(n, hidden, device=dev)
     ms = timed(lambda: linear(x, w, b, out=y))
