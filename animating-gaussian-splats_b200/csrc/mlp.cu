@@ -150,8 +150,8 @@ bn_act_bwd_reduce_kernel(long long rows, int N, const float* __restrict__ dY, lo
 }
 
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(long long rows, int N, float* __restrict__ G, long long ldg, const float* __restrict__ Z,
-                    long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma, float eps,
+bn_bwd_apply_kernel(long long rows, int N, const float* G, long long ldg, float* dZ, long long lddz,
+                    const float* __restrict__ Z, long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma, float eps,
                     const double* __restrict__ sums, float* __restrict__ d_gamma, float* __restrict__ d_beta) {
   __shared__ float s_k0[256], s_k1[256], s_k2[256];   // dz = k0 g + k1 + k2 z
   for (int c = threadIdx.x; c < N; c += 256) {
@@ -172,13 +172,13 @@ bn_bwd_apply_kernel(long long rows, int N, float* __restrict__ G, long long ldg,
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
     const long long r = i / n4;
     const int c = (int)(i - r * n4) << 2;
-    float4 g = *reinterpret_cast<float4*>(G + r * ldg + c);
+    float4 g = *reinterpret_cast<const float4*>(G + r * ldg + c);
     const float4 z = *reinterpret_cast<const float4*>(Z + r * ldz + c);
     g.x = fmaf(s_k0[c], g.x, fmaf(s_k2[c], z.x, s_k1[c]));
     g.y = fmaf(s_k0[c + 1], g.y, fmaf(s_k2[c + 1], z.y, s_k1[c + 1]));
     g.z = fmaf(s_k0[c + 2], g.z, fmaf(s_k2[c + 2], z.z, s_k1[c + 2]));
     g.w = fmaf(s_k0[c + 3], g.w, fmaf(s_k2[c + 3], z.w, s_k1[c + 3]));
-    *reinterpret_cast<float4*>(G + r * ldg + c) = g;
+    *reinterpret_cast<float4*>(dZ + r * lddz + c) = g;   // dZ may alias G (same element, read before written)
   }
 }
 
@@ -232,16 +232,11 @@ int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, 
   bn_act_bwd_reduce_kernel<<<148 * 4, n4 * row_lanes, 0, st>>>(rows, N, dY, ldd, Z, ldz, col_stats, gamma, beta, eps,
                                                                 residual, ldr, apply_gelu, G, ldg, sums);
   GSB_LAUNCH_CHECK();
-  // dZ = pass 2 over G (copied first when the caller wants G kept, e.g. as the residual branch's gradient)
-  if (dZ != G) {
-    if (ldg != lddz || ldg != N) return GSB_EINVAL;
-    GSB_CUDA_CHECK(cudaMemcpyAsync(dZ, G, (size_t)rows * N * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  }
   const long long total = rows * n4;
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, dZ, lddz, Z, ldz, col_stats, gamma, eps, sums, d_gamma,
-                                                        d_beta);
+  bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, G, ldg, dZ, lddz, Z, ldz, col_stats, gamma, eps, sums,
+                                                        d_gamma, d_beta);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -265,7 +265,7 @@ int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const doub
 /* Adjoint of gsb_bn_gelu (same arguments for the forward quantities): given dY it forms G = dY * act'(pre-activation)
  * (also the gradient of the residual input), the per-column sums (`sums`, DEVICE double[2][N], zeroed here) that are
  * d_beta = sum G and d_gamma = sum G xhat, and dZ = gamma inv_std (G - d_beta / rows - xhat d_gamma / rows).
- * dZ may alias G (in place); when it does not, both must be dense [rows, N].  d_gamma / d_beta [N] optional. */
+ * dZ may alias G (in place) or be a separate buffer (G is then kept).  d_gamma / d_beta [N] optional. */
 int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, const float* Z, int64_t ldz,
                          const double* col_stats, const float* gamma, const float* beta, float eps,
                          const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg, float* dZ,
