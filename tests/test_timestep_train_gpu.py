@@ -1,0 +1,68 @@
+"""Per-timestep training step (gsb200.timestep_train, the train.py:700-790 caller): the batched image loss node
+against the per-view drop-in autograd path, the total loss composition of train.py:385-433, and a short training run
+through DeformationNetwork -> rasterizer -> losses -> Adam."""
+import pytest
+import torch
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+def _scene(P=5000, n_cams=3, W=96, H=64, seed=0):
+    from gsb200 import scene
+    dev = torch.device("cuda")
+    raw = {k: v.to(dev) for k, v in scene.make_gaussians(P, seed=seed, extent=1.0).items()}
+    cams = scene.make_cameras(n_cams, W, H, seed=seed)
+    return raw, cams, scene.stack_cameras(cams, dev), [scene.settings_for(c, dev) for c in cams]
+
+
+def test_batched_image_loss_matches_per_view_autograd():
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from gsb200 import loss as gloss, optim, timestep_train as tt
+    raw, cams, stacked, settings = _scene()
+    targets = torch.rand(3, 3, 64, 96, device="cuda", generator=torch.Generator(device="cuda").manual_seed(2))
+    keys = ("means", "rotation_quaternions", "colors", "opacity_logits", "log_scales")
+    a = {k: (raw[k].clone().requires_grad_(True) if k in keys else raw[k]) for k in raw}
+    b = {k: (raw[k].clone().requires_grad_(True) if k in keys else raw[k]) for k in raw}
+    total = tt.batched_image_loss(a, stacked, targets)
+    (2.0 * total).backward()
+    want = 0
+    for i, s in enumerate(settings):
+        args = optim.create_render_arguments(b)
+        im, _, _ = GaussianRasterizer(s)(**args)
+        want = want + gloss.l1_ssim_loss(im, targets[i])
+    (2.0 * want).backward()
+    assert abs(float(total.detach()) - float(want.detach())) < 1e-5 * abs(float(want.detach()))
+    for k in keys:
+        bad, worst = helpers.grad_close(helpers.to_np(a[k].grad), helpers.to_np(b[k].grad), rel=1e-4, floor=2e-6)
+        assert bad == 0, (k, bad, worst)
+
+
+def test_train_steps_reduce_the_loss():
+    from gsb200 import deform, rigidity, timestep_train as tt, io as gio
+    torch.manual_seed(0)
+    raw, cams, stacked, settings = _scene(P=4000, n_cams=4, seed=1)
+    dev = raw["means"].device
+    # targets: the same cloud translated by 3 cm -- a motion the network can learn
+    moved = dict(raw); moved["means"] = raw["means"] + torch.tensor([0.03, 0.0, 0.0], device=dev)
+    from gsb200 import step as gstep, optim
+    rot, opa, sca = optim.activate(moved)
+    with torch.no_grad():
+        from gsb200 import raster
+        targets, _, _, _ = raster.forward(moved["means"], moved["colors"], opa, sca, rot, None, torch.zeros(3, device=dev), 1.0,
+                                          stacked["viewmatrix"], stacked["projmatrix"], stacked["tanfovx"], stacked["tanfovy"],
+                                          64, 96, n_cams=4)
+    init = {k: v.clone() for k, v in raw.items()}
+    ninfo = rigidity.create_neighbor_info(init, k=8)
+    enc0 = deform.normalize_and_encode_means_and_rotations(init)
+    fg0 = rigidity.create_foreground_info(init, ninfo.indices)
+    net = deform.DeformationNetwork(64, 1, precise=True).to(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=2e-3)
+    losses, enc, fg = [], enc0, fg0
+    for it in range(25):
+        loss, enc_next, fg_next = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, (stacked, targets), 1, 1)
+        losses.append(float(loss))
+    assert all(torch.isfinite(torch.tensor(losses)))
+    assert enc_next.shape == (4000, 92) and fg_next.offsets_to_neighbors.shape[1:] == (8, 3)
+    assert sum(losses[-5:]) / 5 < 0.9 * sum(losses[:5]) / 5, losses
