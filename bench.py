@@ -369,6 +369,10 @@ def run_ours(args):
             out["deformation_forward"] = deformation_shaped(args)
         except Exception as ex:
             out["deformation_forward"] = {"error": repr(ex)[:300]}
+        try:
+            out["train_step_shape"] = train_step_shaped(args)
+        except Exception as ex:
+            out["train_step_shape"] = {"error": repr(ex)[:300]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -460,6 +464,133 @@ def deformation_shaped(args, hidden=256, blocks=4, iters=10):
                           "bound": "hbm", "algorithmic_bytes": byts, "achieved": byts / (ms * 1e-3) / 1e9,
                           "peak": peak, "unit": "GB/s", "frac": (byts / (ms * 1e-3) / 1e9 / peak) if peak else None,
                           "tflops": 2.0 * n * 192 * hidden / (ms * 1e-3) / 1e12}
+    return res
+
+
+def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=8):
+    """SURVEY.md 8(d) metric (ii), train.py's shape (train.py:745-790): one optimiser step of the DeformationNetwork =
+    network forward over all Gaussians -> 5 sampled cameras rendered, 0.8 L1 + 0.2 (1 - SSIM) each -> rigidity term ->
+    backward -> Adam.  "ours": gsb200.timestep_train.train_step (tcgen05 network, camera-batched rasterizer, fused loss,
+    fused rigidity once per step).  "stock": the same step composed the reference's way -- unmodified reference
+    extension camera by camera, conv2d SSIM, the rigidity formula in torch ops once per view, nn.Linear/BatchNorm1d
+    network with FP32 matmuls, torch Adam."""
+    import random
+    import helpers
+    import oracle_lib
+    from torch import nn
+    from gsb200 import scene, deform, rigidity as R, timestep_train as tt
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g_raw, tgt_raw, cams = build_workload(args)
+    sc = scene.stack_cameras(cams, dev)
+    bg = torch.zeros(3, device=dev)
+    targets = render_targets(tgt_raw, sc, args.cams, bg, dev)
+    init = {k: v.to(dev).contiguous() for k, v in g_raw.items()}
+    ninfo = R.create_neighbor_info(init, k=neighbours)
+    enc0 = deform.normalize_and_encode_means_and_rotations(init)
+    fg0 = R.create_foreground_info(init, ninfo.indices)
+    rng = random.Random(0)
+    picks = [sorted(rng.sample(range(args.cams), views)) for _ in range(iters + 3)]
+
+    def sub(ix):
+        return ({"viewmatrix": sc["viewmatrix"][ix].contiguous(), "projmatrix": sc["projmatrix"][ix].contiguous(),
+                 "tanfovx": [sc["tanfovx"][i] for i in ix], "tanfovy": [sc["tanfovy"][i] for i in ix],
+                 "image_width": sc["image_width"], "image_height": sc["image_height"]}, targets[ix].contiguous())
+
+    def timed(fn):
+        for k in range(3):
+            fn(k)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for k in range(iters):
+            fn(3 + k)
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    torch.manual_seed(0)
+    net = deform.DeformationNetwork(hidden, blocks, precise=True).to(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    last = {}
+
+    def ours(k):
+        loss, _, _ = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, sub(picks[k]), 7, 150)
+        last["ours"] = loss
+
+    res = {"what": f"one train.py step: DeformationNetwork ({hidden} x {blocks} blocks) over {args.gaussians} Gaussians, "
+                   f"{views} of {args.cams} cameras {args.width}x{args.height}, rigidity K={neighbours}, Adam",
+           "unit": "ms per step", "ours": timed(ours)}
+    res["ours_steps_per_s"] = 1e3 / res["ours"]
+    res["network_matmuls"] = "3xTF32 forward (FP32-level), TF32 backward"
+    torch.manual_seed(0)
+    net = deform.DeformationNetwork(hidden, blocks, precise=False).to(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    res["ours_tf32_forward"] = timed(ours)
+    ref = oracle_lib.load_reference_ext()
+    if ref is None:
+        return res
+
+    class Block(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.fc1 = nn.Linear(d, d, bias=False); self.bn1 = nn.BatchNorm1d(d)
+            self.fc2 = nn.Linear(d, d, bias=False); self.bn2 = nn.BatchNorm1d(d)
+
+        def forward(self, x):
+            y = nn.functional.gelu(self.bn1(self.fc1(x)))
+            return nn.functional.gelu(self.bn2(self.fc2(y)) + x)
+
+    class Stock(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc_in = nn.Linear(192, hidden)
+            self.residual_blocks = nn.Sequential(*(Block(hidden) for _ in range(blocks)))
+            self.fc_out = nn.Linear(hidden, 7)
+
+        def forward(self, i7, x):
+            return self.fc_out(self.residual_blocks(self.fc_in(x))) + i7
+
+    torch.backends.cuda.matmul.allow_tf32 = False
+    snet = Stock().to(dev).train()
+    sopt = torch.optim.Adam(snet.parameters(), lr=1e-4)
+    fgm = init["segmentation_masks"][:, 0] > 0.5
+    prev_off = fg0.offsets_to_neighbors.contiguous()
+    i7 = torch.cat((init["means"], init["rotation_quaternions"]), dim=1)
+    xin = torch.cat((enc0, enc0, deform.positional_encoding(torch.full((args.gaussians, 1), 7 / 150, device=dev), 4)), dim=1)
+
+    def stock_rigidity(means, quats):
+        m = means[fgm]
+        q = torch.nn.functional.normalize(quats)[fgm]
+        a, b = q.unbind(-1), fg0.inverted_rotations.unbind(-1)
+        rel = torch.stack([a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3],
+                           a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+                           a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1],
+                           a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]], -1)
+        r, x, y, z = (rel / rel.norm(dim=-1, keepdim=True)).unbind(-1)
+        rot = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                           2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                           2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).reshape(-1, 3, 3)
+        off = m[ninfo.indices] - m[:, None]
+        loc = (rot.transpose(2, 1)[:, None] @ off[..., None]).squeeze(-1)
+        return torch.sqrt(((loc - prev_off) ** 2).sum(-1) * ninfo.weights + 1e-20).mean()
+
+    def stock(k):
+        delta = snet(i7, xin)
+        means = init["means"] + delta[:, :3] * 0.01
+        quats = init["rotation_quaternions"] + delta[:, 3:] * 0.01
+        total = 0
+        for c in picks[k]:
+            a = {"means3D": means, "colors_precomp": init["colors"], "rotations": torch.nn.functional.normalize(quats),
+                 "opacities": torch.sigmoid(init["opacity_logits"]), "scales": torch.exp(init["log_scales"]),
+                 "means2D": torch.zeros_like(means, requires_grad=True) + 0}
+            im, _, _ = helpers.RefRasterize.apply(ref, a["means3D"], a["means2D"], a["colors_precomp"], a["opacities"],
+                                                  a["scales"], a["rotations"], cams[c], bg)
+            total = total + torch_ssim_l1(im, targets[c]) + 3 * stock_rigidity(means, quats)
+        total.backward()
+        sopt.step()
+        sopt.zero_grad()
+        last["stock"] = total.detach()
+
+    res["stock"] = timed(stock)
+    res["stock_steps_per_s"] = 1e3 / res["stock"]
     return res
 
 
