@@ -121,7 +121,7 @@ struct GeomLayout {
     uint32_t* dt = k.take<uint32_t>(2 * ((size_t)n_cams + 1));   // tile prefix | chunk prefix
     uint32_t* st0 = k.take<uint32_t>(2 * ((size_t)n_cams + 1));
     const int dd = depth_digit();
-    void* gt = k.take<char>(seg_sort_temp_bytes((int64_t)n, n_cams, (32 + dd - 1) / dd, dd));
+    void* gt = k.take<char>(seg_sort_temp_bytes((int64_t)n, n_cams, 4, dd));
     if (c) {
       c->depths = depths; c->radii = radii; c->means2D = means2D; c->cov3D = cov3D; c->conic_opacity = conic;
       c->tiles_touched = tt; c->gauss_order = go; c->point_offsets = po; c->seg_start = ss;
@@ -164,7 +164,7 @@ static size_t carve_binning(char* base, int64_t R, int tile_bits, int n_cams, gs
     tks = k.take<uint16_t>(n);
     tka = k.take<uint16_t>(n);
   }
-  void* tmp = k.take<char>(seg_sort_temp_bytes(R, n_cams, plan.passes, plan.log_nb));
+  void* tmp = k.take<char>(seg_sort_temp_bytes(R, n_cams, 2, plan.log_nb));
   if (c) {
     c->point_list = pl; c->point_list_unsorted = plu; c->tile_keys_unsorted = tku; c->tile_keys_sorted = tks;
     c->sort_temp = tmp;
@@ -256,7 +256,7 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   prof_mark(PF_PREPROCESS, st);
   const int64_t n_slots = (int64_t)a->P * a->n_cams;
   // the depth digits are sorted here, on Gaussians, one segment per camera, before duplication
-  if ((rc = launch_seg_setup(a->n_cams, 1, a->P, nullptr, gx.dseg_start, gx.dseg_tile0, st))) return rc;
+  if ((rc = launch_seg_setup(a->n_cams, 1, a->P, 4, nullptr, gx.dseg_start, gx.dseg_tile0, st))) return rc;
   if ((rc = launch_seg_sort_u32(n_slots, a->n_cams, gx.dseg_start, gx.dseg_tile0, gx.gkeys_in, gx.gkeys_b, gx.gkeys_c,
                                 nullptr, ctx->gauss_order, gx.gorder_alt, 32, depth_digit(), false, gx.gsort_temp, st,
                                 nullptr)))
@@ -265,7 +265,7 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st,
                                       ctx->gauss_order, a->P)))
     return rc;
-  if ((rc = launch_seg_setup(a->n_cams, 2, a->P, ctx->point_offsets, ctx->seg_start, gx.seg_tile0, st))) return rc;
+  if ((rc = launch_seg_setup(a->n_cams, 2, a->P, 2, ctx->point_offsets, ctx->seg_start, gx.seg_tile0, st))) return rc;
   prof_mark(PF_SCAN, st);
 
   // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
@@ -403,7 +403,7 @@ extern "C" size_t gsb_seg_sort_temp_bytes(int64_t n, int32_t n_seg, int32_t key_
   if (n < 0 || n_seg <= 0 || digit_bits <= 0 || end_bit <= 0) return 0;
   const size_t nn = (size_t)(n > 0 ? n : 1);
   // sort temp + seg_tile0 + alternate key / payload buffers
-  return seg_sort_temp_bytes(n, n_seg, seg_passes(end_bit, digit_bits), digit_bits) + align_up(((size_t)n_seg + 1) * 8, 256) +
+  return seg_sort_temp_bytes(n, n_seg, key_bytes, digit_bits) + align_up(((size_t)n_seg + 1) * 8, 256) +
          align_up(nn * (size_t)key_bytes, 256) + align_up(nn * 4, 256);
 }
 template <typename KeyT, typename Fn>
@@ -415,11 +415,11 @@ static int seg_sort_debug(int64_t n, int32_t n_seg, const uint32_t* seg_start, c
   if (!kin || !vout) return GSB_EINVAL;
   const int passes = seg_passes(end_bit, digit_bits);
   char* t = reinterpret_cast<char*>(temp);
-  const size_t s0 = seg_sort_temp_bytes(n, n_seg, passes, digit_bits);
+  const size_t s0 = seg_sort_temp_bytes(n, n_seg, (int)sizeof(KeyT), digit_bits);
   uint32_t* tile0 = reinterpret_cast<uint32_t*>(t + s0);
   KeyT* k_alt = reinterpret_cast<KeyT*>(t + s0 + align_up(((size_t)n_seg + 1) * 8, 256));
   uint32_t* v_alt = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(k_alt) + align_up((size_t)n * sizeof(KeyT), 256));
-  int rc = launch_seg_setup(n_seg, 0, 0, nullptr, const_cast<uint32_t*>(seg_start), tile0, st);
+  int rc = launch_seg_setup(n_seg, 0, 0, (int)sizeof(KeyT), nullptr, const_cast<uint32_t*>(seg_start), tile0, st);
   if (rc) return rc;
   return launch(n, n_seg, seg_start, tile0, kin, kout, k_alt, vin, vout, v_alt, end_bit, digit_bits, kout != nullptr, temp, st,
                 nullptr);

@@ -66,9 +66,9 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
                       int end_bit, void* temp, cudaStream_t st);
 
 // segsort.cu: segmented wide-digit onesweep (the product path's sorts) and tile ranges
-size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int passes, int log_nb);
-int launch_seg_setup(int n_seg, int mode, int len, const uint32_t* offsets, uint32_t* seg_start, uint32_t* seg_tile0,
-                     cudaStream_t st);
+size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int key_bytes, int log_nb);
+int launch_seg_setup(int n_seg, int mode, int len, int key_bytes, const uint32_t* offsets, uint32_t* seg_start,
+                     uint32_t* seg_tile0, cudaStream_t st);
 int launch_seg_sort_u16(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                         const uint16_t* kin, uint16_t* k_out, uint16_t* k_alt, const uint32_t* vin, uint32_t* v_out,
                         uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,

@@ -16,12 +16,14 @@
 // sort tiles resident on 148 SMs and a 1024-digit status row per tile, the serial look-back (one L2 round
 // trip per predecessor, ~17 predecessors on average) was a third of the kernel's instructions and most of
 // its stall samples.  A pass is therefore three kernels with no inter-block waiting:
-//   K1 seg_tile_hist   per sort tile (4096 keys) the digit counts (u16 row), per chunk of 16 tiles their sum;
+//   K1 seg_tile_hist   per sort tile (4096 keys) a u16 row: the digit counts of the EARLIER tiles of its chunk
+//                      (the block walks its chunk's tiles in order, so the row is its running total); per chunk
+//                      (16 tiles; 4 in the depth sort) the digit totals;
 //   K2 seg_chunk_scan  per segment: exclusive scan of the chunk sums over the chunks and of the digit totals
 //                      over the digits (+ the segment's start) -> chunk_base, digit_base, totals;
 //   K3 seg_scatter     per sort tile: rank the keys per warp; global slot of digit d = digit_base[d] +
-//                      chunk_base[chunk][d] + the counts of the <= 15 earlier tiles of the chunk (independent
-//                      loads, one latency) + rank; scatter through shared memory, write out in runs.
+//                      chunk_base[chunk][d] + tile row [d] (three independent loads, one latency) + rank;
+//                      scatter through shared memory, write out in runs.
 #include <algorithm>
 #include <cstdlib>
 #include <type_traits>
@@ -32,7 +34,10 @@ namespace gsb {
 constexpr int SS_THREADS = 256;
 constexpr int SS_ITEMS = 16;
 constexpr int SS_TILE = SS_THREADS * SS_ITEMS;   // keys per sort tile
-constexpr int SS_CHUNK = 16;                     // sort tiles per chunk
+// Sort tiles per chunk (= per block of the histogram kernel).  16 for the instance sort (20 k tiles: plenty of
+// blocks, few chunk rows to scan); 4 for the depth sort, whose ~2 k tiles would otherwise be histogrammed by
+// ~150 blocks of 8 warps, one per SM, each walking 16 tiles serially (12% of the warp slots, 1.4 TB/s).
+template <typename KeyT> struct SsChunk { static constexpr int value = sizeof(KeyT) > 2 ? 4 : 16; };
 constexpr int SS_MAX_PASSES = 4;
 
 // ------------------------------------------------------------------------------------------------
@@ -42,8 +47,8 @@ constexpr int SS_MAX_PASSES = 4;
 // taken camera-major (segment c ends at offsets[(c+1)*len-1]).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-seg_setup_kernel(int n_seg, int mode, int len, const uint32_t* __restrict__ offsets, uint32_t* __restrict__ seg_start,
-                 uint32_t* __restrict__ seg_tile0) {
+seg_setup_kernel(int n_seg, int mode, int len, int chunk_tiles, const uint32_t* __restrict__ offsets,
+                 uint32_t* __restrict__ seg_start, uint32_t* __restrict__ seg_tile0) {
   __shared__ uint32_t s_tiles[1024];
   uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
   for (int s = threadIdx.x; s <= n_seg; s += blockDim.x) {
@@ -58,7 +63,7 @@ seg_setup_kernel(int n_seg, int mode, int len, const uint32_t* __restrict__ offs
     uint32_t run = 0, crun = 0;
     for (int s = 0; s < n_seg; s++) {
       seg_tile0[s] = run; seg_chunk0[s] = crun;
-      run += s_tiles[s]; crun += (s_tiles[s] + SS_CHUNK - 1) / SS_CHUNK;
+      run += s_tiles[s]; crun += (s_tiles[s] + chunk_tiles - 1) / chunk_tiles;
     }
     seg_tile0[n_seg] = run; seg_chunk0[n_seg] = crun;
   }
@@ -86,6 +91,7 @@ seg_tile_hist_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __r
                      uint32_t* __restrict__ chunk_tot) {
   constexpr int NB = 1 << LOG_NB;
   constexpr int PER = (NB + SS_THREADS - 1) / SS_THREADS;
+  constexpr int SS_CHUNK = SsChunk<KeyT>::value;
   __shared__ uint32_t s_hist[NB];
   __shared__ int s_seg;
   const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
@@ -131,7 +137,7 @@ seg_tile_hist_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __r
       const int d = k * SS_THREADS + (int)tid;
       if (d < NB) {
         const uint32_t c = s_hist[d];
-        row[d] = (uint16_t)c;
+        row[d] = (uint16_t)tot[k];   // keys of digit d in the EARLIER tiles of this chunk (<= 15 * 4096)
         tot[k] += c;
       }
     }
@@ -308,24 +314,17 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
   for (int k = 0; k < D; k++) gb[k] = 0;
   if (act) {
     const int d0 = tid * D;
-    const int before = (int)(local_tile % SS_CHUNK);   // earlier tiles of this chunk
     if (D == 4) {
       const uint4 a = *reinterpret_cast<const uint4*>(chunk_base + (size_t)chunk * NB + d0);
       const uint4 b = *reinterpret_cast<const uint4*>(digit_base + (size_t)seg * NB + d0);
-      gb[0] = a.x + b.x; gb[1 % D] = a.y + b.y; gb[2 % D] = a.z + b.z; gb[3 % D] = a.w + b.w;
-#pragma unroll 5
-      for (int j = 1; j <= before; j++) {
-        const uint2 c = *reinterpret_cast<const uint2*>(tile_cnt + (size_t)(tile - j) * NB + d0);
-        gb[0] += c.x & 0xFFFFu; gb[1 % D] += c.x >> 16; gb[2 % D] += c.y & 0xFFFFu; gb[3 % D] += c.y >> 16;
-      }
+      const uint2 c = *reinterpret_cast<const uint2*>(tile_cnt + (size_t)tile * NB + d0);
+      gb[0] = a.x + b.x + (c.x & 0xFFFFu); gb[1 % D] = a.y + b.y + (c.x >> 16);
+      gb[2 % D] = a.z + b.z + (c.y & 0xFFFFu); gb[3 % D] = a.w + b.w + (c.y >> 16);
     } else {
 #pragma unroll
       for (int k = 0; k < D; k++)
-        gb[k] = chunk_base[(size_t)chunk * NB + d0 + k] + digit_base[(size_t)seg * NB + d0 + k];
-#pragma unroll 5
-      for (int j = 1; j <= before; j++)
-#pragma unroll
-        for (int k = 0; k < D; k++) gb[k] += tile_cnt[(size_t)(tile - j) * NB + d0 + k];
+        gb[k] = chunk_base[(size_t)chunk * NB + d0 + k] + digit_base[(size_t)seg * NB + d0 + k] +
+                tile_cnt[(size_t)tile * NB + d0 + k];
     }
   }
 
@@ -372,20 +371,36 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
   {
     uint32_t excl_c[D];
     uint32_t tc = 0;
-#pragma unroll
-    for (int k = 0; k < D; k++) {
-      excl_c[k] = 0;
+    if (D == 4) {
+      // a thread's four 16-bit counters of one warp row are one 8-byte word
+      uint32_t run[4] = {0, 0, 0, 0};
       if (act) {
-        const int d = tid * D + k;
-        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < WARPS; w++) {
-          const uint32_t c = s_wcnt[w * NB + d];
-          s_wcnt[w * NB + d] = (CntT)run;
-          run += c;
+          uint2* p = reinterpret_cast<uint2*>(s_wcnt + w * NB + tid * 4);
+          const uint2 v = *p;
+          *p = make_uint2(run[0] | (run[1] << 16), run[2] | (run[3] << 16));
+          run[0] += v.x & 0xFFFFu; run[1] += v.x >> 16; run[2] += v.y & 0xFFFFu; run[3] += v.y >> 16;
         }
-        excl_c[k] = tc;
-        tc += run;
+      }
+#pragma unroll
+      for (int k = 0; k < D; k++) { excl_c[k] = tc; tc += run[k % 4]; }
+    } else {
+#pragma unroll
+      for (int k = 0; k < D; k++) {
+        excl_c[k] = 0;
+        if (act) {
+          const int d = tid * D + k;
+          uint32_t run = 0;
+#pragma unroll
+          for (int w = 0; w < WARPS; w++) {
+            const uint32_t c = s_wcnt[w * NB + d];
+            s_wcnt[w * NB + d] = (CntT)run;
+            run += c;
+          }
+          excl_c[k] = tc;
+          tc += run;
+        }
       }
     }
     uint32_t inc_c = tc;
@@ -468,7 +483,7 @@ seg_scatter_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __res
   if (seg >= n_seg) return;  // the grid is an upper bound on the tile count
   const uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
   const uint32_t local_tile = tile - seg_tile0[seg];
-  const uint32_t chunk = seg_chunk0[seg] + local_tile / SS_CHUNK;
+  const uint32_t chunk = seg_chunk0[seg] + local_tile / SsChunk<KeyT>::value;
   const uint32_t sbeg = seg_start[seg], send = seg_start[seg + 1];
   const uint32_t tbase = sbeg + local_tile * SS_TILE;
   const int n_valid = (int)min((uint32_t)SS_TILE, send - tbase);
@@ -484,23 +499,24 @@ seg_scatter_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __res
 // Host side
 // ------------------------------------------------------------------------------------------------
 static inline int64_t ss_max_tiles(int64_t n_upper, int n_seg) { return (n_upper + SS_TILE - 1) / SS_TILE + n_seg; }
-static inline int64_t ss_max_chunks(int64_t n_upper, int n_seg) {
-  return (n_upper + (int64_t)SS_TILE * SS_CHUNK - 1) / ((int64_t)SS_TILE * SS_CHUNK) + n_seg;
+static inline int64_t ss_max_chunks(int64_t n_upper, int n_seg, int chunk_tiles) {
+  return (n_upper + (int64_t)SS_TILE * chunk_tiles - 1) / ((int64_t)SS_TILE * chunk_tiles) + n_seg;
 }
 
 // temp: tile_cnt u16 [max_tiles][NB] | chunk_tot u32 [max_chunks][NB] | chunk_base u32 [max_chunks][NB] |
 //       digit_base u32 [n_seg][NB] | totals u32 [n_seg][NB]; reused by every pass.  Nothing needs zeroing.
-size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int passes, int log_nb) {
-  (void)passes;
+size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int key_bytes, int log_nb) {
+  const int chunk_tiles = key_bytes > 2 ? SsChunk<uint32_t>::value : SsChunk<uint16_t>::value;
   const size_t nb = (size_t)1 << log_nb;
   return align_up((size_t)ss_max_tiles(n_upper, n_seg) * nb * 2, 256) +
-         2 * align_up((size_t)ss_max_chunks(n_upper, n_seg) * nb * 4, 256) + 2 * align_up((size_t)n_seg * nb * 4, 256);
+         2 * align_up((size_t)ss_max_chunks(n_upper, n_seg, chunk_tiles) * nb * 4, 256) + 2 * align_up((size_t)n_seg * nb * 4, 256);
 }
 
-int launch_seg_setup(int n_seg, int mode, int len, const uint32_t* offsets, uint32_t* seg_start, uint32_t* seg_tile0,
-                     cudaStream_t st) {
+int launch_seg_setup(int n_seg, int mode, int len, int key_bytes, const uint32_t* offsets, uint32_t* seg_start,
+                     uint32_t* seg_tile0, cudaStream_t st) {
   if (n_seg <= 0 || n_seg > 1024) return GSB_EINVAL;
-  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, offsets, seg_start, seg_tile0);
+  const int chunk_tiles = key_bytes > 2 ? SsChunk<uint32_t>::value : SsChunk<uint16_t>::value;
+  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, chunk_tiles, offsets, seg_start, seg_tile0);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -524,7 +540,8 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
                                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
-  const int64_t max_tiles = ss_max_tiles(n_upper, n_seg), max_chunks = ss_max_chunks(n_upper, n_seg);
+  const int64_t max_tiles = ss_max_tiles(n_upper, n_seg);
+  const int64_t max_chunks = ss_max_chunks(n_upper, n_seg, SsChunk<KeyT>::value);
   char* t = reinterpret_cast<char*>(temp);
   uint16_t* tile_cnt = reinterpret_cast<uint16_t*>(t);
   t += align_up((size_t)max_tiles * NB * 2, 256);
