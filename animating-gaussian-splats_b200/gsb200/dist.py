@@ -17,9 +17,42 @@ COLS = {"means3D": (0, 3), "colors": (3, 6), "rotations": (6, 10), "opacities": 
 WIDTH = 16
 
 
-def shard_cameras(n_cams, rank, world):
-    """Indices of the cameras rank `rank` renders."""
-    return list(range(rank, n_cams, world))
+def shard_cameras(n_cams, rank, world, costs=None):
+    """Indices of the cameras rank `rank` renders.  Without costs: round-robin (camera c -> rank c % world).
+    With per-camera costs (camera_costs of the previous step or timestep; every rank must pass the same numbers):
+    longest-processing-time-first -- cameras in decreasing cost, each to the least loaded rank.  A step ends with
+    an allreduce, so it lasts as long as its slowest rank, and cameras of one rig differ in cost by tens of percent
+    (distance to the subject); ranks may end up with different camera counts."""
+    if costs is None:
+        return list(range(rank, n_cams, world))
+    costs = [float(c) for c in costs]
+    assert len(costs) == n_cams
+    load = [0.0] * world
+    mine = [[] for _ in range(world)]
+    for c in sorted(range(n_cams), key=lambda i: (-costs[i], i)):
+        r = min(range(world), key=lambda j: (load[j], j))
+        load[r] += costs[c]
+        mine[r].append(c)
+    return sorted(mine[rank])
+
+
+# cost model of one camera of a step, in ms, fitted to the per-stage times of the C2 workload on a B200
+# (bench.py stage_ms): blend forward + backward per walked (pixel, Gaussian) pair, key emission + instance sort per
+# instance, and the per-Gaussian / per-pixel stages that every camera pays alike.
+COST_PER_PAIR_MS = 3.3e-9
+COST_PER_INSTANCE_MS = 8.7e-9
+COST_PER_CAMERA_MS = 0.044
+
+
+def camera_costs(state):
+    """Estimated cost of each camera of a rendered batch (RasterState of raster.forward): list of floats."""
+    c = state.ctx
+    n = c.n_cams
+    walked = state._view(c.n_contrib, state.img, torch.int32, (n, c.height * c.width)).long().sum(dim=1).double()
+    seg = state._view(c.seg_start, state.geom, torch.int32, (n + 1,)).long()
+    inst = (seg[1:] - seg[:-1]).double()
+    cost = COST_PER_PAIR_MS * walked + COST_PER_INSTANCE_MS * inst + COST_PER_CAMERA_MS
+    return [float(x) for x in cost.cpu()]
 
 
 def pack(flat, grads, stats_delta=None):

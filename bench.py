@@ -149,7 +149,7 @@ def render_targets(tgt_raw, cams_stacked, n, bg, dev):
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
     import torch.distributed as dist
-    from gsb200 import _lib, scene, step as step_mod, dist as gd
+    from gsb200 import _lib, raster, scene, step as step_mod, dist as gd
     import ctypes as C
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -164,7 +164,22 @@ def run_ours(args):
     lib = _lib.lib()
 
     g_raw, tgt_raw, cams = build_workload(args)
-    my_cam_ids = list(range(rank, args.cams, world))
+    # camera -> rank.  N > 1: cost-balanced (gsb200.dist.shard_cameras with per-camera costs): every rank renders
+    # all cameras once, untimed, and estimates each camera's cost from its walked pairs and instance count (what a
+    # trainer takes from the previous timestep's renders); rank 0's numbers are broadcast so all ranks agree.
+    cam_costs = None
+    if world > 1 and os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
+        all_sc = scene.stack_cameras(cams, dev)
+        a0 = {k: v.to(dev).contiguous() for k, v in scene.activate(g_raw).items()}
+        _, _, _, st0 = raster.forward(a0["means3D"], a0["colors_precomp"], a0["opacities"], a0["scales"], a0["rotations"],
+                                      None, torch.zeros(3, device=dev), 1.0, all_sc["viewmatrix"], all_sc["projmatrix"],
+                                      all_sc["tanfovx"], all_sc["tanfovy"], all_sc["image_height"], all_sc["image_width"],
+                                      n_cams=args.cams)
+        ct = torch.tensor(gd.camera_costs(st0), dtype=torch.float64, device=dev)
+        dist.broadcast(ct, 0)
+        cam_costs = [float(x) for x in ct.cpu()]
+        del st0, a0, all_sc
+    my_cam_ids = gd.shard_cameras(args.cams, rank, world, cam_costs)
     my_cams = [cams[i] for i in my_cam_ids]
     n_my = len(my_cams)
     sc = scene.stack_cameras(my_cams, dev)
@@ -236,6 +251,37 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
+
+    # ---- N > 1: what the exchange costs (each piece timed alone, max over ranks) -----------------
+    exchange = None
+    if world > 1:
+        def timed_loop(fn, iters=10):
+            fn()
+            sync_all()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(iters):
+                fn()
+            b.record()
+            sync_all()
+            tt_ = torch.tensor([a.elapsed_time(b) / iters], dtype=torch.float64, device=dev)
+            own = float(tt_.item())
+            dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+            timed_loop.own = own
+            return float(tt_.item())
+        sd = {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
+              "visibility_count": stats.visibility_count}
+        exchange = {
+            "pack": timed_loop(lambda: gd.pack(flat, grads, sd)),
+            "allreduce_sum": timed_loop(lambda: dist.all_reduce(flat)),
+            "allreduce_max": timed_loop(lambda: dist.all_reduce(stats.max_2d_radii, op=dist.ReduceOp.MAX)),
+            "step_without_exchange": timed_loop(lambda: step_mod.timestep_step(act, sc, dev_targets, bg, stats)),
+            "bytes_sum": flat.numel() * 4, "bytes_max": stats.max_2d_radii.numel() * 4,
+        }
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, {"rank": rank, "cameras": my_cam_ids, "step_without_exchange": timed_loop.own,
+                                          "est_cost": None if cam_costs is None else sum(cam_costs[c] for c in my_cam_ids)})
+        exchange["per_rank"] = per_rank
 
     # ---- end to end: host buffers in, loss out, every step ------------------------------------
     # gsb200.step.HostFeed: each step's inputs (raw parameter tables + target images, pinned host memory) are
@@ -341,6 +387,8 @@ def run_ours(args):
         "config": {"workload": f"Panoptic-shaped timestep: {P} gaussians, {args.cams} cameras {args.width}x{args.height}, "
                                "fwd + L1/SSIM + bwd + densify stats (BASELINE.json configs[1])",
                    "cameras_per_rank": n_my, "parallelism": f"camera-sharded dp{world}",
+                   "camera_assignment": ("round-robin" if cam_costs is None else
+                                         "cost-balanced (LPT on per-camera walked pairs + instances of an untimed calibration render)"),
                    "l2": "per-step working set (state + instance lists) is several hundred MB > 126 MB L2; no explicit flush"},
         "blends_per_sec": 2.0 * walked_all / (ms_step * 1e-3), "walked_pairs_per_step": walked_all,
         "num_rendered_per_step": R_all,
@@ -349,6 +397,8 @@ def run_ours(args):
         "gpu_launches": launches * args.steps,
         "stage_ms": stages, "roofline": roofline, "roofline_hbm": roofline_hbm, "clocks": clocks,
     }
+    if exchange is not None:
+        out["exchange_ms"] = exchange
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, g_raw, cams, host_targets)
     if world == 1 and not args.no_reference_cuda:

@@ -67,3 +67,18 @@ def test_two_rank_camera_sharding_allreduce(tmp_path):
     # replicas end bit-identical
     for k in want:
         assert np.array_equal(r0[k], r1[k])
+
+
+def test_shard_cameras_cost_balanced():
+    """LPT assignment: a partition of the cameras, identical on every rank, never worse than round-robin here."""
+    from gsb200 import dist as gd
+    costs = [1.0 + 0.6 * ((7 * c) % 5) / 4 + (1.5 if c % 8 == 0 else 0.0) for c in range(27)]
+    for world in (1, 2, 4, 8):
+        parts = [gd.shard_cameras(27, r, world, costs) for r in range(world)]
+        assert sorted(c for p in parts for c in p) == list(range(27))
+        assert parts == [gd.shard_cameras(27, r, world, list(costs)) for r in range(world)]
+        lpt = max(sum(costs[c] for c in p) for p in parts)
+        rr = max(sum(costs[c] for c in gd.shard_cameras(27, r, world)) for r in range(world))
+        assert lpt <= rr + 1e-12
+        assert lpt <= sum(costs) / world + max(costs)
+    assert gd.shard_cameras(27, 3, 8) == list(range(3, 27, 8))
