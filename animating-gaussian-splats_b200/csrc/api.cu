@@ -291,7 +291,7 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
     if ((rc = launch_seg_sort_u16(ctx->num_rendered, a->n_cams, ctx->seg_start, gx.seg_tile0, ctx->tile_keys_unsorted,
                                   ctx->tile_keys_sorted, bx.keys_alt, ctx->point_list_unsorted, ctx->point_list,
                                   bx.vals_alt, std::max(ctx->tile_bits, 1), plan.log_nb, plan.passes > 1, ctx->sort_temp,
-                                  st, &tile_hist)))
+                                  st, &tile_hist, (int)higher_msb((uint32_t)a->P))))   // payloads are Gaussian ids < P
       return rc;
   }
   prof_mark(PF_SORT, st);
@@ -429,7 +429,12 @@ int gsb_seg_sort_u16(int64_t n, int32_t n_seg, const uint32_t* seg_start, const 
                      const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,
                      void* stream) {
   return seg_sort_debug<uint16_t>(n, n_seg, seg_start, keys_in, keys_out, vals_in, vals_out, end_bit, digit_bits, temp,
-                                  reinterpret_cast<cudaStream_t>(stream), launch_seg_sort_u16);
+                                  reinterpret_cast<cudaStream_t>(stream),
+                                  [](int64_t n_, int ns, const uint32_t* ss, const uint32_t* t0, const uint16_t* ki, uint16_t* ko,
+                                     uint16_t* ka, const uint32_t* vi, uint32_t* vo, uint32_t* va, int eb, int db, bool wk,
+                                     void* tp, cudaStream_t s, const uint32_t** h) {
+                                    return launch_seg_sort_u16(n_, ns, ss, t0, ki, ko, ka, vi, vo, va, eb, db, wk, tp, s, h, 32);
+                                  });
 }
 int gsb_seg_sort_u32(int64_t n, int32_t n_seg, const uint32_t* seg_start, const uint32_t* keys_in, uint32_t* keys_out,
                      const uint32_t* vals_in, uint32_t* vals_out, int32_t end_bit, int32_t digit_bits, void* temp,

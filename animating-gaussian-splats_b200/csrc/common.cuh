@@ -72,7 +72,7 @@ int launch_seg_setup(int n_seg, int mode, int len, int key_bytes, const uint32_t
 int launch_seg_sort_u16(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                         const uint16_t* kin, uint16_t* k_out, uint16_t* k_alt, const uint32_t* vin, uint32_t* v_out,
                         uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,
-                        const uint32_t** hist_out);
+                        const uint32_t** hist_out, int val_bits = 32);
 int launch_seg_sort_u32(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                         const uint32_t* kin, uint32_t* k_out, uint32_t* k_alt, const uint32_t* vin, uint32_t* v_out,
                         uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,

@@ -264,7 +264,10 @@ __device__ __forceinline__ unsigned ss_peers(uint32_t d) {
 #else
 #define SS_BODY_ATTR __forceinline__
 #endif
-template <typename KeyT, int LOG_NB, bool OPT, bool FULL>
+// PACKV (one-pass sorts whose payload fits beside the digit in 32 bits, e.g. Gaussian ids < 2^22 with a 10-bit
+// digit): digit and payload are staged as ONE shared-memory word, so the scatter into tile order is one random
+// store instead of two and the write-out one load instead of two (the kernel is bound by shared-memory wavefronts).
+template <typename KeyT, int LOG_NB, bool OPT, bool FULL, bool PACKV>
 __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t tile, const int seg,
                                           const uint32_t local_tile, const uint32_t chunk, const uint32_t tbase,
                                           const int n_valid, const KeyT* __restrict__ kin, KeyT* __restrict__ kout,
@@ -434,8 +437,8 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
     const uint32_t r = PACK ? (key[i] >> 16) : rank[PACK ? 0 : i];
     const uint32_t d = (FULL || e0 + i * 32 < n_valid) ? ((k >> shift) & dmask) : (uint32_t)(NB - 1);
     const uint32_t pos = s_dstart[d] + my_wcnt[d] + r;
-    s_keys[pos] = (KeyT)k;
-    s_vals[pos] = val[i];
+    if (PACKV) s_vals[pos] = (d << (32 - LOG_NB)) | val[i];
+    else { s_keys[pos] = (KeyT)k; s_vals[pos] = val[i]; }
   }
   __syncthreads();
   // write out in runs; padding sits at the very end of the tile-sorted order
@@ -443,11 +446,16 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
   for (int i = 0; i < SS_ITEMS; i++) {
     const int p = i * SS_THREADS + (int)tid;
     if (FULL || p < n_valid) {
-      const KeyT k = s_keys[p];
-      const uint32_t d = ((uint32_t)k >> shift) & dmask;
-      const uint32_t dst = s_gbase[d] + (uint32_t)p;
-      if (kout) kout[dst] = k;
-      vout[dst] = s_vals[p];
+      if (PACKV) {
+        const uint32_t w = s_vals[p];
+        vout[s_gbase[w >> (32 - LOG_NB)] + (uint32_t)p] = w & ((1u << (32 - LOG_NB)) - 1u);
+      } else {
+        const KeyT k = s_keys[p];
+        const uint32_t d = ((uint32_t)k >> shift) & dmask;
+        const uint32_t dst = s_gbase[d] + (uint32_t)p;
+        if (kout) kout[dst] = k;
+        vout[dst] = s_vals[p];
+      }
     }
   }
 }
@@ -458,7 +466,7 @@ __device__ SS_BODY_ATTR void ss_tile_body(unsigned char* ss_smem, const uint32_t
 #ifndef SS_MINB32
 #define SS_MINB32 3
 #endif
-template <typename KeyT, int LOG_NB, bool OPT>
+template <typename KeyT, int LOG_NB, bool OPT, bool PACKV>
 __global__ void __launch_bounds__(SS_THREADS, sizeof(KeyT) > 2 ? SS_MINB32 : SS_MINB16)
 seg_scatter_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ seg_tile0, int n_seg,
                    const KeyT* __restrict__ kin, KeyT* __restrict__ kout, const uint32_t* __restrict__ vin,
@@ -488,10 +496,10 @@ seg_scatter_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __res
   const uint32_t tbase = sbeg + local_tile * SS_TILE;
   const int n_valid = (int)min((uint32_t)SS_TILE, send - tbase);
   if (n_valid == SS_TILE)
-    ss_tile_body<KeyT, LOG_NB, OPT, true>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
+    ss_tile_body<KeyT, LOG_NB, OPT, true, PACKV>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
                                           shift, dmask, tile_cnt, chunk_base, digit_base);
   else
-    ss_tile_body<KeyT, LOG_NB, OPT, false>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
+    ss_tile_body<KeyT, LOG_NB, OPT, false, PACKV>(ss_smem, tile, seg, local_tile, chunk, tbase, n_valid, kin, kout, vin, vout,
                                            shift, dmask, tile_cnt, chunk_base, digit_base);
 }
 
@@ -525,19 +533,27 @@ template <typename KeyT, int LOG_NB, bool OPT>
 static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                          const KeyT* kin, KeyT* k_out, KeyT* k_alt, const uint32_t* vin, uint32_t* v_out,
                          uint32_t* v_alt, int end_bit, bool want_keys, void* temp, cudaStream_t st,
-                         const uint32_t** hist_out) {
+                         const uint32_t** hist_out, int val_bits = 32) {
   using Lay = SsLayout<KeyT, LOG_NB, OPT>;
   constexpr int NB = Lay::NB;
   const int passes = (end_bit + LOG_NB - 1) / LOG_NB;
   if (passes < 1 || passes > SS_MAX_PASSES || n_upper >= (1ll << 30)) return GSB_EINVAL;
   if (passes > 1 && (!v_alt || !k_alt || !k_out)) return GSB_EINVAL;
   if (want_keys && !k_out) return GSB_EINVAL;
+  constexpr bool CAN_PACK = sizeof(KeyT) == 2 && OPT;
+  const bool packv = CAN_PACK && passes == 1 && !want_keys && vin && val_bits + LOG_NB <= 32;
   static bool attr_set = false;
   if (!attr_set) {
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Lay::bytes));
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT>,
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT, false>,
                                         cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    if (CAN_PACK) {
+      GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT, CAN_PACK>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lay::bytes));
+      GSB_CUDA_CHECK(cudaFuncSetAttribute(seg_scatter_kernel<KeyT, LOG_NB, OPT, CAN_PACK>,
+                                          cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
     attr_set = true;
   }
   const int64_t max_tiles = ss_max_tiles(n_upper, n_seg);
@@ -569,8 +585,12 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
     seg_chunk_scan_kernel<LOG_NB><<<n_seg, LOG_NB >= 10 ? 1024 : std::max(NB, 32), 0, st>>>(seg_start, seg_tile0, n_seg, chunk_tot, chunk_base, digit_base,
                                                                                   totals);
     GSB_LAUNCH_CHECK();
-    seg_scatter_kernel<KeyT, LOG_NB, OPT><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
-        seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
+    if (packv)
+      seg_scatter_kernel<KeyT, LOG_NB, OPT, CAN_PACK><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
+          seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
+    else
+      seg_scatter_kernel<KeyT, LOG_NB, OPT, false><<<(unsigned)max_tiles, SS_THREADS, Lay::bytes, st>>>(
+          seg_start, seg_tile0, n_seg, a, b, va, vb, shift, dmask, tile_cnt, chunk_base, digit_base);
     GSB_LAUNCH_CHECK();
     a = b;
     va = vb;
@@ -581,11 +601,11 @@ static int seg_sort_impl(int64_t n_upper, int n_seg, const uint32_t* seg_start, 
 int launch_seg_sort_u16(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                         const uint16_t* kin, uint16_t* k_out, uint16_t* k_alt, const uint32_t* vin, uint32_t* v_out,
                         uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,
-                        const uint32_t** hist_out) {
+                        const uint32_t** hist_out, int val_bits) {
 #define GSB_SS_CASE(B)                                                                                              \
   case B:                                                                                                           \
     return opt ? seg_sort_impl<uint16_t, B, true>(n_upper, n_seg, seg_start, seg_tile0, kin, k_out, k_alt, vin, v_out,  \
-                                                  v_alt, end_bit, want_keys, temp, st, hist_out)                    \
+                                                  v_alt, end_bit, want_keys, temp, st, hist_out, val_bits)          \
                : seg_sort_impl<uint16_t, B, false>(n_upper, n_seg, seg_start, seg_tile0, kin, k_out, k_alt, vin, v_out, \
                                                    v_alt, end_bit, want_keys, temp, st, hist_out)
   static const bool opt = getenv("GSB_SS_OPT") ? atoi(getenv("GSB_SS_OPT")) != 0 : true;
