@@ -241,3 +241,26 @@ def test_c4_full_size_forward_only(refdgr):
     rg = mine["ranges"].long()
     assert int((rg[:, 1] - rg[:, 0]).sum()) == R
     assert bool((mine["point_list_keys"][1:] >= mine["point_list_keys"][:-1]).all())
+
+
+def test_many_gaussians_unpacked_sort_path(refdgr):
+    """More than 2^22 Gaussians at 257..1024 tiles (10-bit digit): the one-pass instance sort cannot stage digit and
+    Gaussian id as one 32-bit word and takes the separate key / payload path.  Binning bit-exact against the reference."""
+    dev = "cuda"
+    P, W, H = (1 << 22) + 1234, 512, 384
+    g = helpers.scene.make_gaussians(P, seed=41, scale_override=0.004)
+    a = {k: v.to(dev).contiguous() for k, v in helpers.scene.activate(g).items()}
+    cam = helpers.scene.make_cameras(4, W, H, seed=41)[1]
+    bg = torch.zeros(3, device=dev)
+    fw = helpers.ref_forward(refdgr, a, cam, bg, dev)
+    color, depth, radii, st = run_mine(a, cam, bg)
+    R = fw["num_rendered"]
+    assert st.num_rendered == R and R > 100_000
+    assert int(fw["radii"].argmax()) >= 0 and int((fw["radii"] > 0).nonzero().max()) >= (1 << 22)  # ids beyond 22 bits occur
+    ref = oracle_lib.decode_reference_buffers(P, H, W, R, fw["geom"], fw["binning"], fw["img"])
+    mine = st.tensors()
+    assert torch.equal(radii, fw["radii"])
+    assert torch.equal(mine["point_list"], ref["point_list"])
+    assert torch.equal(mine["ranges"], ref["ranges"])
+    assert torch.equal(mine["n_contrib"][0], ref["n_contrib"])
+    assert (color - fw["color"]).abs().max().item() <= 1e-5
