@@ -54,11 +54,24 @@ scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
 
   uint32_t v[SCAN_ITEMS];
   if (perm) {
-    // element i is in[(i / perm_block) * perm_block + perm[i]]: the scan runs in a permuted order
+    // element i is in[(i / perm_block) * perm_block + perm[i]]: the scan runs in a permuted order.  One division
+    // per thread; the block index advances by at most one per element.
+    uint32_t pidx[SCAN_ITEMS];
+    if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(perm) & 15u) == 0)) {
+      const uint4 a = *reinterpret_cast<const uint4*>(perm + base);
+      const uint4 b = *reinterpret_cast<const uint4*>(perm + base + 4);
+      pidx[0] = a.x; pidx[1] = a.y; pidx[2] = a.z; pidx[3] = a.w; pidx[4] = b.x; pidx[5] = b.y; pidx[6] = b.z; pidx[7] = b.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < SCAN_ITEMS; k++) pidx[k] = (base + k < n) ? perm[base + k] : 0u;
+    }
+    long long blk0 = (base / perm_block) * (long long)perm_block;
+    int rem = (int)(base - blk0);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-      const long long i = base + k;
-      v[k] = (i < n) ? in[(i / perm_block) * perm_block + perm[i]] : 0u;
+      if (rem == perm_block) { rem = 0; blk0 += perm_block; }
+      v[k] = (base + k < n) ? in[blk0 + pidx[k]] : 0u;
+      rem++;
     }
   } else if (base + SCAN_ITEMS <= n && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0)) {
     const uint4 a = *reinterpret_cast<const uint4*>(in + base);
