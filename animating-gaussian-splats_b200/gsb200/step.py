@@ -84,7 +84,9 @@ class HostFeed:
                       torch.empty_like(host_targets, device=device)) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=device)
         self.ready = [torch.cuda.Event(), torch.cuda.Event()]
-        self.loss_host = torch.empty((host_targets.size(0), 3), dtype=torch.float32).pin_memory()
+        self.loss_hosts = [torch.empty((host_targets.size(0), 3), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.loss_host = self.loss_hosts[0]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]   # step k's kernels and loss read-back finished
         self.k = 0
         self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_raw.values()) + \
             host_targets.numel() * host_targets.element_size()
@@ -93,27 +95,43 @@ class HostFeed:
 
     def _prefetch(self, k):
         raw, tgt = self.bufs[k % 2]
-        # the buffer's previous consumer (step k-2) finished: step() synchronises every step
+        # the buffer's previous consumer is step k-2: the copy stream waits for its `done` event
+        if k >= 2:
+            self.copy_stream.wait_event(self.done[k % 2])
         with torch.cuda.stream(self.copy_stream):
             for key, h in self.host_raw.items():
                 raw[key].copy_(h, non_blocking=True)
             tgt.copy_(self.host_targets, non_blocking=True)
             self.ready[k % 2].record(self.copy_stream)
 
-    def step(self, cams, bg, stats=None, after=None):
+    def step(self, cams, bg, stats=None, after=None, wait=True):
         """One end-to-end step.  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
-        loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix)."""
+        loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix) of this
+        step.  wait=True blocks until it is filled.  wait=False returns at once -- the way a training loop that only
+        logs the loss calls it: the host goes on to issue the next step while this one's backward still runs; the
+        buffer is valid after wait() and until the step after next is issued (two buffers alternate)."""
         from . import optim
         k = self.k
         raw, tgt = self.bufs[k % 2]
-        torch.cuda.current_stream(self.dev).wait_event(self.ready[k % 2])
+        cur = torch.cuda.current_stream(self.dev)
+        cur.wait_event(self.ready[k % 2])
         self._prefetch(k + 1)
         rot, opa, sca = optim.activate(raw)   # one launch (gsb_activate)
         act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
         loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats)
         if after is not None:
             after(loss_stats, grads, radii, st)
-        self.loss_host.copy_(loss_stats, non_blocking=True)
-        torch.cuda.current_stream(self.dev).synchronize()
+        out = self.loss_hosts[k % 2]
+        out.copy_(loss_stats, non_blocking=True)
+        self.done[k % 2].record(cur)
+        self.loss_host = out
         self.k += 1
+        if wait:
+            self.done[k % 2].synchronize()
+        return out
+
+    def wait(self):
+        """Block until the last issued step (kernels and loss read-back) has finished; returns its loss buffer."""
+        if self.k > 0:
+            self.done[(self.k - 1) % 2].synchronize()
         return self.loss_host

@@ -288,6 +288,7 @@ def run_ours(args):
     # copied host -> device (double-buffered, the copy of step k+1 overlaps step k), activations + step run on
     # the device, the per-camera loss numbers come back to pinned host memory; one stream sync per step.
     feed = step_mod.HostFeed(host_raw, host_targets, dev)
+    E2E_BLOCKING = os.environ.get("GSB_BENCH_E2E_BLOCKING", "0") == "1"
 
     def after(loss_stats, grads, radii, st_):
         if world > 1:
@@ -296,7 +297,9 @@ def run_ours(args):
             gd.allreduce(flat, stats.max_2d_radii)
 
     def e2e_step():
-        feed.step(sc, bg, stats, after)
+        # non-blocking: the loss numbers are copied to pinned host memory every step, the host does not wait for
+        # them before issuing the next step (a training loop only logs them); GSB_BENCH_E2E_BLOCKING=1 waits
+        feed.step(sc, bg, stats, after, wait=E2E_BLOCKING)
 
     e2e_step()
     sync_all()

@@ -26,6 +26,13 @@ def test_host_feed_matches_device_step():
         seen.append(feed.step(sc, bg, None).clone())
     for got in seen:
         assert torch.allclose(got, want.cpu(), rtol=0, atol=1e-6), (got, want)
+    # non-blocking steps: the host runs ahead, results are read after wait()
+    for i in range(5):
+        out = feed.step(sc, bg, None, wait=False)
+        if i % 2 == 1:
+            assert feed.wait() is out
+            assert torch.allclose(out, want.cpu(), rtol=0, atol=1e-6), (i, out, want)
+    assert torch.allclose(feed.wait(), want.cpu(), rtol=0, atol=1e-6)
     assert feed.h2d_bytes == sum(v.numel() * 4 for v in host_raw.values()) + targets.numel() * 4
     assert feed.d2h_bytes == n * 3 * 4
 
