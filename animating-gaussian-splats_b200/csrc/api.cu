@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <nvtx3/nvToolsExt.h>
 #include "common.cuh"
 
 namespace gsb {
@@ -39,10 +40,24 @@ static int stage_reserve(size_t bytes) {
 // each kernel live on the launching stream.
 enum { PF_FWD_BEGIN = 0, PF_PREPROCESS, PF_DEPTH_SORT, PF_SCAN, PF_D2H, PF_DUPKEYS, PF_SORT, PF_RANGES, PF_RENDER_FWD,
        PF_BWD_BEGIN, PF_BWD_ZERO, PF_RENDER_BWD, PF_PREPROCESS_BWD, PF_COUNT };
-static bool g_prof_on = false;
-static cudaEvent_t g_prof_ev[PF_COUNT];
-static bool g_prof_seen[PF_COUNT];
+static thread_local bool g_prof_on = false;   // per thread, like g_stage: two threads profiling two streams do not race
+static thread_local cudaEvent_t g_prof_ev[PF_COUNT];
+static thread_local bool g_prof_seen[PF_COUNT];
+static const char* const kStageName[PF_COUNT] = {"gsb.fwd", "gsb.preprocess", "gsb.depth_sort", "gsb.scan", "gsb.d2h_sync",
+                                                 "gsb.duplicate_keys", "gsb.sort", "gsb.tile_ranges", "gsb.render_fwd",
+                                                 "gsb.bwd", "gsb.bwd_zero", "gsb.render_bwd", "gsb.preprocess_bwd"};
+// NVTX ranges per stage: GSB_NVTX=1 brackets the host-side issue of each stage, so a
+// timeline tool shows which launches belong to which stage.  Off by default (one getenv at first use).
+static bool nvtx_on() {
+  static const bool on = [] { const char* e = getenv("GSB_NVTX"); return e && atoi(e) != 0; }();
+  return on;
+}
+static thread_local int g_nvtx_depth = 0;
 static inline void prof_mark(int i, cudaStream_t st) {
+  if (nvtx_on()) {
+    if (i != PF_FWD_BEGIN && i != PF_BWD_BEGIN && g_nvtx_depth > 0) { nvtxRangePop(); g_nvtx_depth--; }
+    if (i != PF_RENDER_FWD && i != PF_PREPROCESS_BWD && i + 1 < PF_COUNT) { nvtxRangePushA(kStageName[i + 1]); g_nvtx_depth++; }
+  }
   if (!g_prof_on) return;
   cudaEventRecord(g_prof_ev[i], st);
   g_prof_seen[i] = true;
@@ -205,20 +220,32 @@ size_t gsb_binning_bytes(int64_t num_rendered, int32_t tiles_per_cam, int32_t n_
 }
 uint32_t gsb_higher_msb(uint32_t n) { return higher_msb(n); }
 
-int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_alloc_fn binning_alloc,
-                       gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth, int32_t* radii,
-                       gsb_raster_ctx* ctx, void* stream) {
-  if (!a || !ctx || !geom_alloc || !binning_alloc || !image_alloc) return GSB_EINVAL;
+}  // extern "C"
+
+namespace gsb {
+// Rasterizer::forward host orchestration (cr/rasterizer_impl.cu:198-339), shared by the blocking entry point
+// (callbacks, one D2H of num_rendered that sizes the binning buffer) and the asynchronous one (caller-owned arenas,
+// capacity-guarded instance count that never leaves the device).
+struct FwdBuffers {
+  bool async = false;
+  char* geom = nullptr; char* img = nullptr; char* bin = nullptr;
+  int64_t capacity = 0;
+  const float* tanfov_dev = nullptr;
+  gsb_alloc_fn geom_alloc = nullptr, binning_alloc = nullptr, image_alloc = nullptr;
+  void* user = nullptr;
+};
+
+static int forward_impl(const gsb_raster_args* a, FwdBuffers& fb, float* out_color, float* out_depth, int32_t* radii,
+                        gsb_raster_ctx* ctx, cudaStream_t st) {
   if (a->P < 0 || a->n_cams <= 0 || a->width <= 0 || a->height <= 0) return GSB_EINVAL;
-  if (!a->tanfovx_host || !a->tanfovy_host) return GSB_EINVAL;
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   memset(ctx, 0, sizeof(*ctx));
   ctx->P = a->P; ctx->n_cams = a->n_cams; ctx->width = a->width; ctx->height = a->height;
   ctx->tiles_x = (a->width + GSB_TILE - 1) / GSB_TILE;
   ctx->tiles_y = (a->height + GSB_TILE - 1) / GSB_TILE;
   const int tiles_per_cam = ctx->tiles_x * ctx->tiles_y;
   const int tiles_total = tiles_per_cam * a->n_cams;
-  if (tiles_per_cam > 65535 || a->n_cams > 1024) return GSB_EINVAL;   // 16-bit camera-local tile ids
+  // 16-bit camera-local tile ids; the backward keeps one 128-byte matrix pair per camera in shared memory
+  if (tiles_per_cam > 65535 || a->n_cams > GSB_MAX_CAMS) return GSB_EINVAL;
   if (tiles_total >= (1 << 24)) return GSB_EINVAL;                    // blend kernels: float-assisted tile coordinates
   ctx->tile_bits = (int)higher_msb((uint32_t)tiles_per_cam);
   ctx->sort_bits = 32 + (int)higher_msb((uint32_t)tiles_total);
@@ -229,26 +256,32 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSB_EINVAL;
 
   // geometry + image state
-  char* geom = geom_alloc(user, gsb_geom_bytes(a->P, a->n_cams));
-  char* img = image_alloc(user, gsb_image_bytes(a->width, a->height, a->n_cams));
+  char* geom = fb.async ? fb.geom : fb.geom_alloc(fb.user, gsb_geom_bytes(a->P, a->n_cams));
+  char* img = fb.async ? fb.img : fb.image_alloc(fb.user, gsb_image_bytes(a->width, a->height, a->n_cams));
   if (!geom || !img) return GSB_ENOMEM;
   GeomExtras gx;
   GeomLayout::carve(geom, a->P, a->n_cams, ctx, &gx);
   CamParams* cams_dev = gx.cams; int* err_dev = gx.err; void* scan_scratch = gx.scan_scratch;
+  ctx->status = err_dev;
   carve_image(img, a->width, a->height, a->n_cams, tiles_total, ctx);
 
-  // per-camera scalars: focal = dim / (2 tanfov) (cr/rasterizer_impl.cu:222-223)
-  int rc = stage_reserve(64 + sizeof(CamParams) * (size_t)a->n_cams);
-  if (rc) return rc;
-  if (g_stage.ev_pending) { GSB_CUDA_CHECK(cudaEventSynchronize(g_stage.ev)); g_stage.ev_pending = false; }
-  CamParams* cams_host = reinterpret_cast<CamParams*>(reinterpret_cast<char*>(g_stage.pinned) + 64);
-  for (int i = 0; i < a->n_cams; i++) {
-    cams_host[i].tanfovx = a->tanfovx_host[i];
-    cams_host[i].tanfovy = a->tanfovy_host[i];
-    cams_host[i].focal_y = (float)a->height / (2.0f * a->tanfovy_host[i]);
-    cams_host[i].focal_x = (float)a->width / (2.0f * a->tanfovx_host[i]);
+  int rc;
+  if (fb.async) {
+    // per-camera scalars computed on the device from the caller's table: nothing host-resident enters the stream
+    if ((rc = launch_cam_params(a->n_cams, a->width, a->height, fb.tanfov_dev, cams_dev, st))) return rc;
+  } else {
+    // per-camera scalars: focal = dim / (2 tanfov) (cr/rasterizer_impl.cu:222-223)
+    if ((rc = stage_reserve(64 + sizeof(CamParams) * (size_t)a->n_cams))) return rc;
+    if (g_stage.ev_pending) { GSB_CUDA_CHECK(cudaEventSynchronize(g_stage.ev)); g_stage.ev_pending = false; }
+    CamParams* cams_host = reinterpret_cast<CamParams*>(reinterpret_cast<char*>(g_stage.pinned) + 64);
+    for (int i = 0; i < a->n_cams; i++) {
+      cams_host[i].tanfovx = a->tanfovx_host[i];
+      cams_host[i].tanfovy = a->tanfovy_host[i];
+      cams_host[i].focal_y = (float)a->height / (2.0f * a->tanfovy_host[i]);
+      cams_host[i].focal_x = (float)a->width / (2.0f * a->tanfovx_host[i]);
+    }
+    GSB_CUDA_CHECK(cudaMemcpyAsync(cams_dev, cams_host, sizeof(CamParams) * (size_t)a->n_cams, cudaMemcpyHostToDevice, st));
   }
-  GSB_CUDA_CHECK(cudaMemcpyAsync(cams_dev, cams_host, sizeof(CamParams) * (size_t)a->n_cams, cudaMemcpyHostToDevice, st));
   GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
 
   prof_mark(PF_FWD_BEGIN, st);
@@ -265,41 +298,51 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   if ((rc = launch_inclusive_scan_u32(n_slots, ctx->tiles_touched, ctx->point_offsets, scan_scratch, st,
                                       ctx->gauss_order, a->P)))
     return rc;
-  if ((rc = launch_seg_setup(a->n_cams, 2, a->P, 2, ctx->point_offsets, ctx->seg_start, gx.seg_tile0, st))) return rc;
+  // instance segments per camera; writes num_rendered to status[1] and applies the capacity guard
+  if ((rc = launch_seg_setup(a->n_cams, 2, a->P, 2, ctx->point_offsets, ctx->seg_start, gx.seg_tile0, st,
+                             fb.async ? fb.capacity : (int64_t)-1, err_dev)))
+    return rc;
   prof_mark(PF_SCAN, st);
 
-  // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
-  uint32_t* down = reinterpret_cast<uint32_t*>(g_stage.pinned);
-  GSB_CUDA_CHECK(cudaMemcpyAsync(down, ctx->point_offsets + n_slots - 1, 4, cudaMemcpyDeviceToHost, st));
-  GSB_CUDA_CHECK(cudaMemcpyAsync(down + 1, err_dev, 4, cudaMemcpyDeviceToHost, st));
-  GSB_CUDA_CHECK(cudaStreamSynchronize(st));
-  if ((int)down[1] != 0) return (int)down[1];
-  ctx->num_rendered = (int64_t)down[0];
-  if (ctx->num_rendered >= (1ll << 30)) return GSB_EINVAL;
-
-  char* bin = binning_alloc(user, gsb_binning_bytes(ctx->num_rendered, tiles_per_cam, a->n_cams));
+  char* bin;
+  if (fb.async) {
+    ctx->num_rendered = -1;   // known on the device only (status[1])
+    ctx->capacity = fb.capacity;
+    bin = fb.bin;
+  } else {
+    // num_rendered: one blocking 8-byte D2H (cr/rasterizer_impl.cu:281-282)
+    uint32_t* down = reinterpret_cast<uint32_t*>(g_stage.pinned);
+    GSB_CUDA_CHECK(cudaMemcpyAsync(down, ctx->point_offsets + n_slots - 1, 4, cudaMemcpyDeviceToHost, st));
+    GSB_CUDA_CHECK(cudaMemcpyAsync(down + 1, err_dev, 4, cudaMemcpyDeviceToHost, st));
+    GSB_CUDA_CHECK(cudaStreamSynchronize(st));
+    if ((int)down[1] != 0) return (int)down[1];
+    ctx->num_rendered = (int64_t)down[0];
+    if (ctx->num_rendered >= (1ll << 30)) return GSB_EINVAL;
+    ctx->capacity = ctx->num_rendered;
+    bin = fb.binning_alloc(fb.user, gsb_binning_bytes(ctx->num_rendered, tiles_per_cam, a->n_cams));
+  }
   if (!bin) return GSB_ENOMEM;
   BinExtras bx;
-  carve_binning(bin, ctx->num_rendered, ctx->tile_bits, a->n_cams, ctx, &bx);
+  carve_binning(bin, ctx->capacity, ctx->tile_bits, a->n_cams, ctx, &bx);
 
   prof_mark(PF_D2H, st);
   if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
   prof_mark(PF_DUPKEYS, st);
   const TileSortPlan plan = tile_sort_plan(ctx->tile_bits);
   const uint32_t* tile_hist = nullptr;
-  if (ctx->num_rendered > 0) {
-    if ((rc = launch_seg_sort_u16(ctx->num_rendered, a->n_cams, ctx->seg_start, gx.seg_tile0, ctx->tile_keys_unsorted,
+  if (ctx->capacity > 0) {
+    if ((rc = launch_seg_sort_u16(ctx->capacity, a->n_cams, ctx->seg_start, gx.seg_tile0, ctx->tile_keys_unsorted,
                                   ctx->tile_keys_sorted, bx.keys_alt, ctx->point_list_unsorted, ctx->point_list,
                                   bx.vals_alt, std::max(ctx->tile_bits, 1), plan.log_nb, plan.passes > 1, ctx->sort_temp,
                                   st, &tile_hist, (int)higher_msb((uint32_t)a->P))))   // payloads are Gaussian ids < P
       return rc;
   }
   prof_mark(PF_SORT, st);
-  if (plan.passes == 1 && ctx->num_rendered > 0) {
+  if (plan.passes == 1 && ctx->capacity > 0) {
     if ((rc = launch_ranges_from_hist(a->n_cams, tiles_per_cam, plan.log_nb, ctx->seg_start, tile_hist, ctx->ranges, st)))
       return rc;
   } else {
-    if ((rc = launch_tile_ranges_seg(ctx->num_rendered, a->n_cams, tiles_per_cam, ctx->seg_start, ctx->tile_keys_sorted,
+    if ((rc = launch_tile_ranges_seg(ctx->capacity, a->n_cams, tiles_per_cam, ctx->seg_start, ctx->tile_keys_sorted,
                                      ctx->ranges, st)))
       return rc;
   }
@@ -308,6 +351,43 @@ int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_al
   if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
   prof_mark(PF_RENDER_FWD, st);
   return GSB_OK;
+}
+}  // namespace gsb
+
+extern "C" {
+
+int gsb_raster_forward(const gsb_raster_args* a, gsb_alloc_fn geom_alloc, gsb_alloc_fn binning_alloc,
+                       gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth, int32_t* radii,
+                       gsb_raster_ctx* ctx, void* stream) {
+  if (!a || !ctx || !geom_alloc || !binning_alloc || !image_alloc) return GSB_EINVAL;
+  if (!a->tanfovx_host || !a->tanfovy_host) return GSB_EINVAL;
+  FwdBuffers fb;
+  fb.geom_alloc = geom_alloc; fb.binning_alloc = binning_alloc; fb.image_alloc = image_alloc; fb.user = user;
+  return forward_impl(a, fb, out_color, out_depth, radii, ctx, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int gsb_raster_forward_async(const gsb_raster_args* a, const float* tanfov_dev, char* geom, size_t geom_bytes,
+                             char* image, size_t image_bytes, char* binning, size_t binning_bytes, int64_t capacity,
+                             float* out_color, float* out_depth, int32_t* radii, gsb_raster_ctx* ctx, void* stream) {
+  if (!a || !ctx || !tanfov_dev || !geom || !image || !binning) return GSB_EINVAL;
+  if (capacity < 0 || capacity >= (1ll << 30) || a->n_cams <= 0 || a->width <= 0 || a->height <= 0 || a->P < 0)
+    return GSB_EINVAL;
+  const int tiles_per_cam = ((a->width + GSB_TILE - 1) / GSB_TILE) * ((a->height + GSB_TILE - 1) / GSB_TILE);
+  if (geom_bytes < gsb_geom_bytes(a->P, a->n_cams) || image_bytes < gsb_image_bytes(a->width, a->height, a->n_cams) ||
+      binning_bytes < gsb_binning_bytes(capacity, tiles_per_cam, a->n_cams))
+    return GSB_ENOMEM;
+  if (((uintptr_t)geom | (uintptr_t)image | (uintptr_t)binning) & 255u) return GSB_EINVAL;
+  FwdBuffers fb;
+  fb.async = true; fb.geom = geom; fb.img = image; fb.bin = binning; fb.capacity = capacity; fb.tanfov_dev = tanfov_dev;
+  return forward_impl(a, fb, out_color, out_depth, radii, ctx, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int gsb_raster_count_pairs(const gsb_raster_args* a, const gsb_raster_ctx* ctx, uint64_t* counts, void* stream) {
+  if (!a || !ctx || !counts) return GSB_EINVAL;
+  if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height || !ctx->ranges)
+    return GSB_EINVAL;
+  if (!a->colors || !a->background) return GSB_EINVAL;
+  return launch_count_pairs(*a, *ctx, reinterpret_cast<unsigned long long*>(counts), reinterpret_cast<cudaStream_t>(stream));
 }
 
 int gsb_raster_forward_colors(const gsb_raster_args* a, const gsb_raster_ctx* ctx, float* out_color, float* out_depth,
@@ -321,6 +401,7 @@ int gsb_raster_forward_colors(const gsb_raster_args* a, const gsb_raster_ctx* ct
   prof_mark(PF_FWD_BEGIN, st);
   int rc;
   if ((rc = launch_render_fwd(*a, *ctx, out_color, out_depth, st))) return rc;
+  if (nvtx_on() && g_nvtx_depth > 0) { nvtxRangePop(); g_nvtx_depth--; }
   return GSB_OK;
 }
 
@@ -343,7 +424,7 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
   GSB_CUDA_CHECK(cudaMemsetAsync(dL_dcolor, 0, ncol * sizeof(float), st));
   int rc;
   prof_mark(PF_BWD_ZERO, st);
-  if (ctx->num_rendered > 0)
+  if (ctx->num_rendered != 0)   // -1: known on the device only (asynchronous forward)
     if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, st))) return rc;
   prof_mark(PF_RENDER_BWD, st);
   // the per-camera scalar table still sits in the geometry buffer next to the state arrays
@@ -355,6 +436,90 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
     return rc;
   prof_mark(PF_PREPROCESS_BWD, st);
   return GSB_OK;
+}
+
+size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams) {
+  // raw first moments [n_cams][P][3] | raw second moments [n_cams][P][4] | dL/dopacity [P] | dL/dcolor [P][3]
+  return align_up(((size_t)P * n_cams * 7 + (size_t)P * 4) * sizeof(float), 256);
+}
+
+int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix, void* scratch,
+                             float* flat, int32_t mode, float* dL_dmean2D_out, void* stream) {
+  if (!a || !ctx) return GSB_EINVAL;
+  if (a->P == 0) return GSB_OK;
+  if (!dL_dpix || !scratch || !flat || (mode != 0 && mode != 1) || a->color_cam_stride != 0) return GSB_EINVAL;
+  if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height)
+    return GSB_EINVAL;
+  if (((uintptr_t)flat & 15u) || ((uintptr_t)scratch & 15u)) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t n = (size_t)a->P * a->n_cams;
+  float* m1 = reinterpret_cast<float*>(scratch);
+  float* m2 = m1 + 3 * n;
+  float* dop = m2 + 4 * n;
+  float* dcol = dop + a->P;
+  prof_mark(PF_BWD_BEGIN, st);
+  GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * 4) * sizeof(float), st));   // one fill for all four
+  prof_mark(PF_BWD_ZERO, st);
+  int rc;
+  if (ctx->num_rendered != 0)
+    if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st))) return rc;
+  prof_mark(PF_RENDER_BWD, st);
+  GeomExtras gx;
+  GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
+  if ((rc = launch_preprocess_bwd(*a, gx.cams, *ctx, m1, m2, nullptr, nullptr, nullptr, nullptr, st, flat, mode, dop, dcol,
+                                  dL_dmean2D_out)))
+    return rc;
+  prof_mark(PF_PREPROCESS_BWD, st);
+  return GSB_OK;
+}
+
+int gsb_flat_apply_stats(int32_t P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
+                         void* stream) {
+  if (P < 0 || (P > 0 && (!flat || !grad_accum || !vis_count))) return GSB_EINVAL;
+  return launch_flat_apply_stats(P, flat, grad_accum, vis_count, max_2d_radii, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t gsb_comm_bytes(size_t payload_bytes) { return comm_bytes(payload_bytes); }
+
+int gsb_comm_alloc(size_t bytes, void** block, unsigned char* handle64) {
+  if (!block || !handle64 || bytes == 0) return GSB_EINVAL;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  GSB_CUDA_CHECK(cudaMalloc(&p, bytes));
+  GSB_CUDA_CHECK(cudaMemset(p, 0, bytes));
+  cudaIpcMemHandle_t h;
+  GSB_CUDA_CHECK(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle64, &h, 64);
+  *block = p;
+  return GSB_OK;
+}
+
+int gsb_comm_open(const unsigned char* handle64, void** peer_block) {
+  if (!handle64 || !peer_block) return GSB_EINVAL;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  GSB_CUDA_CHECK(cudaIpcOpenMemHandle(peer_block, h, cudaIpcMemLazyEnablePeerAccess));
+  return GSB_OK;
+}
+
+int gsb_comm_close(void* peer_block) {
+  if (peer_block) GSB_CUDA_CHECK(cudaIpcCloseMemHandle(peer_block));
+  return GSB_OK;
+}
+
+int gsb_comm_free(void* block) {
+  if (block) GSB_CUDA_CHECK(cudaFree(block));
+  return GSB_OK;
+}
+
+int gsb_allreduce_flat(int32_t rank, int32_t world, void* const* peers_host, size_t payload_bytes, int64_t n_float4,
+                       int32_t row_float4, int32_t max_word, int32_t max_comp, void* stream) {
+  if (world < 1 || world > GSB_COMM_MAX_RANKS || rank < 0 || rank >= world || !peers_host || n_float4 < 0) return GSB_EINVAL;
+  if ((size_t)n_float4 * 16 > payload_bytes || row_float4 <= 0 || max_comp < -1 || max_comp > 3) return GSB_EINVAL;
+  for (int i = 0; i < world; i++)
+    if (!peers_host[i] || ((uintptr_t)peers_host[i] & 15u)) return GSB_EINVAL;
+  return launch_allreduce_flat(rank, world, peers_host, payload_bytes, n_float4, row_float4, max_word, max_comp,
+                               reinterpret_cast<cudaStream_t>(stream));
 }
 
 int gsb_profile_enable(int on) {

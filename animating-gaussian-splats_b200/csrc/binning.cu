@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(256)
 duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_t* __restrict__ gauss_order,
                            const float2* __restrict__ means2D, const int32_t* __restrict__ radii,
                            const uint32_t* __restrict__ offsets, uint16_t* __restrict__ tile_keys,
-                           uint32_t* __restrict__ vals) {
+                           uint32_t* __restrict__ vals, const uint32_t* __restrict__ n_emit) {
   const long long slot = (long long)blockIdx.x * 256 + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
   uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, gidx = 0;
@@ -198,7 +198,8 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
   uint32_t last_end = __shfl_sync(0xffffffffu, end, (unsigned)min(31ll, total - 1 - warp_first));
   if (slot >= total) { end = last_end; start = last_end; }
   const uint32_t warp_start = __shfl_sync(0xffffffffu, start, 0);
-  const uint32_t warp_end = last_end;
+  // *n_emit = seg_start[n_cams]: the instance total, or 0 when it did not fit the arena (capacity guard)
+  const uint32_t warp_end = min(last_end, __ldg(n_emit));
   // owner of output position i = number of lanes whose `end` <= i (ends are non-decreasing).  When every lane
   // of the warp owns at least one instance the ends are distinct, so that count is a population count over
   // the bit set of ends that fall into the current 32-wide window (one warp OR-reduction); warps holding empty
@@ -244,10 +245,10 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
 
 int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st) {
   const long long total = (long long)c.n_cams * c.P;
-  if (total <= 0 || c.num_rendered <= 0) return GSB_OK;
+  if (total <= 0 || c.capacity <= 0) return GSB_OK;
   duplicate_with_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
       total, c.P, c.tiles_x, c.tiles_y, c.gauss_order, reinterpret_cast<const float2*>(c.means2D), c.radii,
-      c.point_offsets, c.tile_keys_unsorted, c.point_list_unsorted);
+      c.point_offsets, c.tile_keys_unsorted, c.point_list_unsorted, c.seg_start + c.n_cams);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

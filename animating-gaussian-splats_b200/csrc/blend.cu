@@ -182,13 +182,18 @@ __device__ __forceinline__ TileCoord tile_coord(const uint32_t* __restrict__ ord
 #ifndef GSB_BWD_MINB
 #define GSB_BWD_MINB 4
 #endif
+// COUNT: the measurement variant behind gsb_raster_count_pairs -- the same walk, no image outputs; per camera it
+// adds up the walked pairs (sum of n_contrib) and the pairs actually composited (alpha >= 1/255 and not the
+// terminating entry): the B and B_alpha of SURVEY.md section 8(d).
+template <bool COUNT>
 __global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_FWD_MINB)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                   const uint32_t* __restrict__ point_list, int W, int H, int P,
                   const float2* __restrict__ means2D, const float* __restrict__ colors, int color_cam_stride,
                   const float4* __restrict__ conic_opacity, const float* __restrict__ depths,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                  float* __restrict__ out_color, float* __restrict__ out_depth) {
+                  float* __restrict__ out_color, float* __restrict__ out_depth,
+                  unsigned long long* __restrict__ pair_counts) {
   __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position + 1)
   __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_cd[GSB_BLOCK_SIZE];  // r, g, b, depth
@@ -218,6 +223,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f;
   float D = 15.0f;  // median depth default (cr/forward.cu:308)
+  uint32_t blended = 0;
 
   for (int i = 0; i < rounds; i++) {
     if (__syncthreads_count(done) == GSB_BLOCK_SIZE) break;
@@ -259,7 +265,22 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       if (T > 0.5f && test_T < 0.5f) D = cd.w;
       T = test_T;
       last_contributor = __float_as_uint(a.w);
+      if (COUNT) blended++;
     }
+  }
+
+  if (COUNT) {
+    unsigned long long w = last_contributor, b = blended;
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+      w += __shfl_xor_sync(0xffffffffu, w, s);
+      b += __shfl_xor_sync(0xffffffffu, b, s);
+    }
+    if ((tid & 31u) == 0) {
+      atomicAdd(pair_counts + 2 * cam, w);
+      atomicAdd(pair_counts + 2 * cam + 1, b);
+    }
+    return;
   }
 
   // the tile coordinates are recomputed here rather than kept in registers across the loop (40-register budget)
@@ -288,11 +309,24 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  render_fwd_kernel<<<tiles_total, block, 0, st>>>(
+  render_fwd_kernel<false><<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
       reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, c.final_T, c.n_contrib, out_color,
-      out_depth);
+      out_depth, nullptr);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsigned long long* counts, cudaStream_t st) {
+  const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
+  GSB_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * 2 * (size_t)a.n_cams, st));
+  dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
+  render_fwd_kernel<true><<<tiles_total, block, 0, st>>>(
+      reinterpret_cast<const uint2*>(c.ranges), nullptr, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
+      reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
+      reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, nullptr, nullptr, nullptr, nullptr,
+      counts);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -14,6 +14,7 @@
 #define GSB_BLOCK_Y 16
 #define GSB_BLOCK_SIZE (GSB_BLOCK_X * GSB_BLOCK_Y)
 #define GSB_NCH 3
+#define GSB_MAX_CAMS 320   // cameras per batch: the backward keeps [n_cams][32] matrix floats in 40 KB of shared memory
 
 namespace gsb {
 
@@ -52,10 +53,20 @@ struct CamParams {  // per-camera scalars that live in a small device table
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                       int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st);
+int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, CamParams* cams_dev, cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+// flat != nullptr: the exchange form (gsb_raster_backward_flat): rows of GSB_FLAT_WIDTH floats instead of the
+// separate tables; dL_dopacity / dL_dcolor are then the blend's camera-summed tables (inputs), flat_mode 0 | 1
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
-                          float* dL_dscale, float* dL_drot, cudaStream_t st);
+                          float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat = nullptr, int flat_mode = 0,
+                          const float* dL_dopacity = nullptr, const float* dL_dcolor = nullptr,
+                          float* dL_dmean2D_out = nullptr);
+int launch_flat_apply_stats(int P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
+                            cudaStream_t st);
+int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payload_bytes, int64_t n_float4, int row_float4,
+                          int max_word, int max_comp, cudaStream_t st);
+size_t comm_bytes(size_t payload_bytes);
 
 size_t scan_scratch_bytes(int64_t n);
 int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st,
@@ -68,7 +79,7 @@ int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint
 // segsort.cu: segmented wide-digit onesweep (the product path's sorts) and tile ranges
 size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int key_bytes, int log_nb);
 int launch_seg_setup(int n_seg, int mode, int len, int key_bytes, const uint32_t* offsets, uint32_t* seg_start,
-                     uint32_t* seg_tile0, cudaStream_t st);
+                     uint32_t* seg_tile0, cudaStream_t st, int64_t capacity = -1, int* status = nullptr);
 int launch_seg_sort_u16(int64_t n_upper, int n_seg, const uint32_t* seg_start, const uint32_t* seg_tile0,
                         const uint16_t* kin, uint16_t* k_out, uint16_t* k_alt, const uint32_t* vin, uint32_t* v_out,
                         uint32_t* v_alt, int end_bit, int log_nb, bool want_keys, void* temp, cudaStream_t st,
@@ -85,6 +96,7 @@ int launch_tile_ranges_seg(int64_t R, int n_cams, int tiles_per_cam, const uint3
 int launch_tile_order(int tiles_total, const uint32_t* ranges, uint32_t* order, cudaStream_t st);
 int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* out_color, float* out_depth,
                       cudaStream_t st);
+int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsigned long long* counts, cudaStream_t st);
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
                       float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st);
 

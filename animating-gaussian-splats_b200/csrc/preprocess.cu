@@ -283,6 +283,12 @@ __device__ __forceinline__ M3 m3_t(const M3& A) {
   return R;
 }
 
+// FLAT: the exchange form of the step's backward (gsb_raster_backward_flat): the thread's results go into one
+// GSB_FLAT_WIDTH-float row (five 16-byte stores, rows contiguous across the warp) together with the blend's
+// camera-summed opacity / colour gradients and the densification-statistic increments of this batch
+// (per-camera ||dL/dmean2D.xy|| summed over the visible cameras, their count, the largest radius), so that no
+// pack pass, no statistics launch and no separate gradient tables exist on the multi-GPU path.
+template <bool FLAT>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* __restrict__ means3D,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -291,7 +297,9 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       const float* __restrict__ cov3Ds, size_t cov_cam_stride,
                       const float4* __restrict__ conic_opacity, float* __restrict__ dL_dmean2D,
                       const float* __restrict__ dL_dconic, float* __restrict__ dL_dmean3D,
-                      float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+                      float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot,
+                      float* __restrict__ flat, int flat_mode, const float* __restrict__ dL_dopacity,
+                      const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out) {
   extern __shared__ float s_mats[];  // [n_cams][32]: view then proj
   for (int i = threadIdx.x; i < n_cams * 32; i += blockDim.x) {
     const int cam = i >> 5, k = i & 31;
@@ -307,6 +315,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
   float gm[3] = {0.f, 0.f, 0.f};
   float gc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   bool any = false;
+  float st_norm = 0.f, st_cnt = 0.f, st_rad = 0.f;   // FLAT: statistic increments of this batch
   // the 3D covariance does not depend on the camera: one row per Gaussian (cov_cam_stride is 0)
   float cov3D[6];
   {
@@ -317,7 +326,11 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
   (void)cov_cam_stride;
   for (int cam = 0; cam < n_cams; cam++) {
     const size_t o = (size_t)cam * P + idx;
-    if (!(radii[o] > 0)) continue;
+    const int rad = radii[o];
+    if (!(rad > 0)) {
+      if (FLAT && dL_dmean2D_out) { dL_dmean2D_out[3 * o] = 0.f; dL_dmean2D_out[3 * o + 1] = 0.f; dL_dmean2D_out[3 * o + 2] = 0.f; }
+      continue;
+    }
     any = true;
     const float* view = s_mats + 32 * cam;
     const float* proj = view + 16;
@@ -331,8 +344,15 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float rs1 = dL_dmean2D[3 * o], rs2 = dL_dmean2D[3 * o + 1];
     const float g2x = -(0.5f * W) * (con.x * rs1 + con.y * rs2);
     const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
-    dL_dmean2D[3 * o] = g2x;
-    dL_dmean2D[3 * o + 1] = g2y;
+    if (FLAT) {
+      st_norm += sqrtf(g2x * g2x + g2y * g2y);   // torch.norm of the first two components, one term per camera
+      st_cnt += 1.0f;
+      st_rad = fmaxf(st_rad, (float)rad);
+      if (dL_dmean2D_out) { dL_dmean2D_out[3 * o] = g2x; dL_dmean2D_out[3 * o + 1] = g2y; dL_dmean2D_out[3 * o + 2] = 0.f; }
+    } else {
+      dL_dmean2D[3 * o] = g2x;
+      dL_dmean2D[3 * o + 1] = g2y;
+    }
 
     // computeCov2DCUDA (cr/backward.cu:144-274)
     float tx = view[0] * mx + view[4] * my + view[8] * mz + view[12];
@@ -400,14 +420,16 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     gm[0] += dmx; gm[1] += dmy; gm[2] += dmz;
   }
 
-  dL_dmean3D[3 * (size_t)idx] = gm[0];
-  dL_dmean3D[3 * (size_t)idx + 1] = gm[1];
-  dL_dmean3D[3 * (size_t)idx + 2] = gm[2];
-  if (dL_dcov3D) {
+  if (!FLAT) {
+    dL_dmean3D[3 * (size_t)idx] = gm[0];
+    dL_dmean3D[3 * (size_t)idx + 1] = gm[1];
+    dL_dmean3D[3 * (size_t)idx + 2] = gm[2];
+    if (dL_dcov3D) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = gc[k];
+      for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = gc[k];
+    }
+    if (!dL_dscale || !dL_drot) return;
   }
-  if (!dL_dscale || !dL_drot) return;
   float gs[3] = {0.f, 0.f, 0.f};
   float4 gq = make_float4(0.f, 0.f, 0.f, 0.f);
   if (any && scales && rotations) {
@@ -441,23 +463,98 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     gq.w = 2 * r * (D(0, 1) - D(1, 0)) + 2 * x * (D(2, 0) + D(0, 2)) + 2 * y * (D(1, 2) + D(2, 1)) - 4 * z * (D(1, 1) + D(0, 0));
 #undef D
   }
+  if (FLAT) {
+    float4* row = reinterpret_cast<float4*>(flat) + (size_t)idx * (GSB_FLAT_WIDTH / 4);
+    const float dop = dL_dopacity[idx];
+    const float c0 = dL_dcolor[3 * (size_t)idx], c1 = dL_dcolor[3 * (size_t)idx + 1], c2 = dL_dcolor[3 * (size_t)idx + 2];
+    if (flat_mode == 0) {
+      row[0] = make_float4(gm[0], gm[1], gm[2], c0);
+      row[1] = make_float4(c1, c2, gq.x, gq.y);
+      row[2] = make_float4(gq.z, gq.w, dop, gs[0]);
+      row[3] = make_float4(gs[1], gs[2], st_norm, st_cnt);
+      row[4] = make_float4(st_rad, 0.f, 0.f, 0.f);
+    } else {
+      // second render of the iteration (another colour table): geometry gradients add up, colours go to 17-19
+      float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
+      r0.x += gm[0]; r0.y += gm[1]; r0.z += gm[2];
+      r1.z += gq.x; r1.w += gq.y;
+      r2.x += gq.z; r2.y += gq.w; r2.z += dop; r2.w += gs[0];
+      r3.x += gs[1]; r3.y += gs[2];
+      row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3;
+      row[4] = make_float4(row[4].x, c0, c1, c2);
+    }
+    return;
+  }
   dL_dscale[3 * (size_t)idx] = gs[0];
   dL_dscale[3 * (size_t)idx + 1] = gs[1];
   dL_dscale[3 * (size_t)idx + 2] = gs[2];
   reinterpret_cast<float4*>(dL_drot)[idx] = gq;
 }
 
+// DensificationVariables += the statistic columns of a (reduced) flat buffer
+__global__ void __launch_bounds__(256)
+flat_apply_stats_kernel(int P, const float* __restrict__ flat, float* __restrict__ grad_accum,
+                        float* __restrict__ vis_count, float* __restrict__ max_2d_radii) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  const float* row = flat + (size_t)i * GSB_FLAT_WIDTH;
+  const float2 nc = *reinterpret_cast<const float2*>(row + GSB_FLAT_COL_GRADNORM);
+  const float mr = row[GSB_FLAT_COL_MAXRADIUS];
+  if (nc.y > 0.f) {
+    grad_accum[i] += nc.x;
+    vis_count[i] += nc.y;
+  }
+  if (max_2d_radii) max_2d_radii[i] = fmaxf(max_2d_radii[i], mr);
+}
+
+int launch_flat_apply_stats(int P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
+                            cudaStream_t st) {
+  if (P <= 0) return GSB_OK;
+  flat_apply_stats_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, flat, grad_accum, vis_count, max_2d_radii);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+// per-camera scalars on the device (asynchronous forward): focal = dim / (2 tanfov), the same two FP32 operations
+// the host performs on the blocking path (cr/rasterizer_impl.cu:222-223), so the bits agree
+__global__ void cam_params_kernel(int n_cams, int W, int H, const float* __restrict__ tanfov, CamParams* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_cams) return;
+  CamParams c;
+  c.tanfovx = tanfov[2 * i];
+  c.tanfovy = tanfov[2 * i + 1];
+  c.focal_y = __fdiv_rn((float)H, __fmul_rn(2.0f, c.tanfovy));
+  c.focal_x = __fdiv_rn((float)W, __fmul_rn(2.0f, c.tanfovx));
+  out[i] = c;
+}
+
+int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, CamParams* cams_dev, cudaStream_t st) {
+  cam_params_kernel<<<(n_cams + 127) / 128, 128, 0, st>>>(n_cams, W, H, tanfov_dev, cams_dev);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
-                          float* dL_dscale, float* dL_drot, cudaStream_t st) {
+                          float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat, int flat_mode,
+                          const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out) {
   if (a.P <= 0) return GSB_OK;
   const size_t smem = (size_t)a.n_cams * 32 * sizeof(float);
-  if (smem > 40 * 1024) return GSB_EINVAL;  // <= 320 cameras per batch
-  preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, smem, st>>>(
-      a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
-      a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
-      reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
-      dL_dcov3D, dL_dscale, dL_drot);
+  if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
+  if (flat) {
+    if (!dL_dopacity || !dL_dcolor || !a.scales || !a.rotations) return GSB_EINVAL;
+    preprocess_bwd_kernel<true><<<(a.P + 255) / 256, 256, smem, st>>>(
+        a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
+        a.projmatrix, cams_dev, c.radii, c.cov3D, (size_t)0, reinterpret_cast<const float4*>(c.conic_opacity),
+        dL_dmean2D, dL_dconic, nullptr, nullptr, nullptr, nullptr, flat, flat_mode, dL_dopacity, dL_dcolor,
+        dL_dmean2D_out);
+  } else {
+    preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, smem, st>>>(
+        a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
+        a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
+        reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
+        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr);
+  }
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -45,15 +45,28 @@ constexpr int SS_MAX_PASSES = 4;
 // prefix of the segments' sort-tile counts, followed by seg_chunk0[n_seg + 1], the same for chunks.
 // mode 0: seg_start is given; 1: fixed-length segments; 2: from the inclusive scan of tiles_touched
 // taken camera-major (segment c ends at offsets[(c+1)*len-1]).
+// Mode 2 also publishes the element total in status[1] and applies the capacity guard of the asynchronous
+// forward: a total above `capacity` (>= 0) sets status[0] = GSB_ENOMEM (unless an earlier error is recorded),
+// status[2] = the total, and empties every segment, so that nothing downstream touches memory past the arena.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 seg_setup_kernel(int n_seg, int mode, int len, int chunk_tiles, const uint32_t* __restrict__ offsets,
-                 uint32_t* __restrict__ seg_start, uint32_t* __restrict__ seg_tile0) {
+                 uint32_t* __restrict__ seg_start, uint32_t* __restrict__ seg_tile0, long long capacity,
+                 int* __restrict__ status) {
   __shared__ uint32_t s_tiles[1024];
   uint32_t* seg_chunk0 = seg_tile0 + n_seg + 1;
+  bool overflow = false;
+  if (mode == 2) {
+    const uint32_t total = offsets[(size_t)n_seg * len - 1];
+    overflow = capacity >= 0 && (long long)total > capacity;
+    if (threadIdx.x == 0 && status) {
+      status[1] = (int)total;
+      if (overflow) { if (status[0] == 0) status[0] = GSB_ENOMEM; status[2] = (int)total; }
+    }
+  }
   for (int s = threadIdx.x; s <= n_seg; s += blockDim.x) {
     if (mode == 1) seg_start[s] = (uint32_t)s * (uint32_t)len;
-    else if (mode == 2) seg_start[s] = (s == 0) ? 0u : offsets[(size_t)s * len - 1];
+    else if (mode == 2) seg_start[s] = (s == 0 || overflow) ? 0u : offsets[(size_t)s * len - 1];
   }
   __syncthreads();
   for (int s = threadIdx.x; s < n_seg; s += blockDim.x)
@@ -521,10 +534,11 @@ size_t seg_sort_temp_bytes(int64_t n_upper, int n_seg, int key_bytes, int log_nb
 }
 
 int launch_seg_setup(int n_seg, int mode, int len, int key_bytes, const uint32_t* offsets, uint32_t* seg_start,
-                     uint32_t* seg_tile0, cudaStream_t st) {
+                     uint32_t* seg_tile0, cudaStream_t st, int64_t capacity, int* status) {
   if (n_seg <= 0 || n_seg > 1024) return GSB_EINVAL;
   const int chunk_tiles = key_bytes > 2 ? SsChunk<uint32_t>::value : SsChunk<uint16_t>::value;
-  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, chunk_tiles, offsets, seg_start, seg_tile0);
+  seg_setup_kernel<<<1, 256, 0, st>>>(n_seg, mode, len, chunk_tiles, offsets, seg_start, seg_tile0, (long long)capacity,
+                                      status);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GSB200_LIB") or os.path.join(os.path.dirname(_HERE), "libgsb200.so")
 
 GSB_OK, GSB_EINVAL, GSB_ECUDA, GSB_ENOMEM, GSB_EPREFILTER = 0, -1, -2, -3, -4
+FLAT_WIDTH, FLAT_COL_GRADNORM, FLAT_COL_VISCOUNT, FLAT_COL_MAXRADIUS = 20, 14, 15, 16
 _ERR = {GSB_EINVAL: "invalid argument", GSB_ECUDA: "CUDA error", GSB_ENOMEM: "buffer allocation failed",
         GSB_EPREFILTER: "Point is filtered although prefiltered is set. This shouldn't happen!"}
 
@@ -41,6 +42,7 @@ class RasterCtx(C.Structure):
         ("final_T", C.c_void_p), ("n_contrib", C.c_void_p), ("ranges", C.c_void_p),
         ("point_list", C.c_void_p), ("point_list_unsorted", C.c_void_p), ("tile_keys_unsorted", C.c_void_p),
         ("tile_keys_sorted", C.c_void_p), ("sort_temp", C.c_void_p),
+        ("capacity", C.c_int64), ("status", C.c_void_p),
     ]
 
 
@@ -62,6 +64,21 @@ SYMBOLS = {
     "gsb_raster_backward": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx)] + [C.c_void_p] * 10),
     "gsb_raster_forward_colors": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p,
                                             C.c_void_p]),
+    "gsb_raster_forward_async": (C.c_int, [C.POINTER(RasterArgs), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
+                                           C.c_void_p, C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.POINTER(RasterCtx), C.c_void_p]),
+    "gsb_raster_count_pairs": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p]),
+    "gsb_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "gsb_raster_backward_flat": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_int32, C.c_void_p, C.c_void_p]),
+    "gsb_flat_apply_stats": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
+    "gsb_comm_bytes": (C.c_size_t, [C.c_size_t]),
+    "gsb_comm_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
+    "gsb_comm_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "gsb_comm_close": (C.c_int, [C.c_void_p]),
+    "gsb_comm_free": (C.c_int, [C.c_void_p]),
+    "gsb_allreduce_flat": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.c_size_t, C.c_int64, C.c_int32,
+                                     C.c_int32, C.c_int32, C.c_void_p]),
     "gsb_mark_visible": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
     "gsb_ssim_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "gsb_ssim_l1": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_float,

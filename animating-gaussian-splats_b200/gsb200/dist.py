@@ -1,20 +1,34 @@
 """Camera-sharded data parallelism (the reference has no multi-GPU code).
 
-One process per GPU.  The cameras of a timestep are dealt round-robin (camera c -> rank c % world); every
-rank rasterizes its cameras against the replicated Gaussian set; parameter gradients and the summed
-densification statistics are packed into ONE flat [P, 16] buffer and summed with ONE allreduce (NCCL over
-NVLink on GPUs, gloo in the CPU tests); max_2d_radii takes a MAX allreduce.  The densification
+One process per GPU.  The cameras of a timestep are dealt over the ranks (round-robin, or cost-balanced with
+shard_cameras(costs=)); every rank rasterizes its cameras against the replicated Gaussian set; its backward writes
+the step's whole per-Gaussian record -- parameter gradients, the densification-statistic increments of THIS step
+and the step's largest radius -- into ONE flat [P, 20] buffer (gsb_raster_backward_flat), and ONE exchange reduces
+it in place over the ranks: SUM for every column except col 16 (max_2d_radii), which takes MAX.  The densification
 statistic is the per-camera norm of the means2D gradient, so norms are taken BEFORE the reduction
-(external.py:113-124).  After the reduction every rank holds identical gradients and statistics, so
-the replicated parameters stay bit-identical without a broadcast.
+(external.py:113-124).  After the exchange every rank holds identical gradients and statistics, so the replicated
+parameters stay bit-identical without a broadcast.
+
+Exchange.allreduce() runs the hand-written NVLink kernel (csrc/comm.cu: every rank's flat buffer is mapped by all
+peers through CUDA IPC; slice r is pulled from all peers, reduced and pushed back by rank r in one launch); on CPU
+tensors (gloo tests) or with GSB_EXCHANGE=nccl it is torch.distributed: one SUM all_reduce + one MAX on the radius
+column.
 """
+import ctypes as C
+import os
+
 import torch
 import torch.distributed as dist
 
-# column layout of the flat buffer
+from . import _lib as L
+
+# column layout of the flat buffer (include/gsb200.h: gsb_raster_backward_flat)
 COLS = {"means3D": (0, 3), "colors": (3, 6), "rotations": (6, 10), "opacities": (10, 11), "scales": (11, 14),
-        "mean_2d_gradients_accumulated": (14, 15), "visibility_count": (15, 16)}
-WIDTH = 16
+        "mean_2d_gradients_accumulated": (14, 15), "visibility_count": (15, 16), "max_2d_radii": (16, 17),
+        "segmentation_colors": (17, 20)}
+WIDTH = L.FLAT_WIDTH
+MAX_COL = L.FLAT_COL_MAXRADIUS
+_SCALARS = ("mean_2d_gradients_accumulated", "visibility_count", "max_2d_radii")
 
 
 def shard_cameras(n_cams, rank, world, costs=None):
@@ -55,43 +69,115 @@ def camera_costs(state):
     return [float(x) for x in cost.cpu()]
 
 
-def pack(flat, grads, stats_delta=None):
-    """Write this rank's camera-summed gradients (and statistic increments) into flat [P, 16].
-    CUDA tensors go through one gsb_pack_flat launch; CPU tensors (gloo tests) through slice copies."""
-    if flat.is_cuda:
-        from . import _lib as L
-        c = lambda t: t.contiguous()
-        acc = c(stats_delta["mean_2d_gradients_accumulated"]) if stats_delta is not None else None
-        cnt = c(stats_delta["visibility_count"]) if stats_delta is not None else None
-        keep = [c(grads[k]) for k in ("means3D", "colors", "rotations", "opacities", "scales")]
-        with L.device_guard(flat.device):
-            rc = L.lib().gsb_pack_flat(flat.shape[0], L.ptr(keep[0]), L.ptr(keep[1]), L.ptr(keep[2]), L.ptr(keep[3]),
-                                       L.ptr(keep[4]), L.ptr(acc), L.ptr(cnt), L.ptr(flat), L.stream_ptr())
-        L.check(rc, "gsb_pack_flat")
-        return flat
+def pack(flat, grads, stats_delta=None, max_radii=None):
+    """Slice-copy form of the flat record for tensors that were NOT produced by gsb_raster_backward_flat (the gloo
+    tests, callers holding separate gradient tables): gradients, THIS step's statistic increments (not running
+    totals) and this step's largest radius per Gaussian into flat [P, 20]."""
+    P = flat.shape[0]
+    flat.zero_()
     for k in ("means3D", "colors", "rotations", "opacities", "scales"):
         a, b = COLS[k]
-        flat[:, a:b] = grads[k].reshape(flat.shape[0], b - a)
+        flat[:, a:b] = grads[k].reshape(P, b - a)
+    if "segmentation_colors" in grads:
+        flat[:, 17:20] = grads["segmentation_colors"].reshape(P, 3)
     if stats_delta is not None:
         flat[:, 14] = stats_delta["mean_2d_gradients_accumulated"]
         flat[:, 15] = stats_delta["visibility_count"]
-    else:
-        flat[:, 14:16] = 0
+    if max_radii is not None:
+        flat[:, 16] = max_radii
     return flat
 
 
 def unpack(flat):
+    """Views into the flat record: name -> [P, k] (the three statistics: [P])."""
     out = {}
     for k, (a, b) in COLS.items():
         v = flat[:, a:b]
-        out[k] = v[:, 0] if k in ("mean_2d_gradients_accumulated", "visibility_count") else v
+        out[k] = v[:, 0] if k in _SCALARS else v
     return out
 
 
-def allreduce(flat, max_2d_radii=None, group=None):
-    """The step's exchange: one SUM allreduce of the flat buffer (+ one MAX for max_2d_radii)."""
+def allreduce(flat, group=None):
+    """The exchange through torch.distributed (gloo on CPU, NCCL on GPUs): SUM of the record, MAX of the radius
+    column.  In place; returns flat."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        rad = flat[:, MAX_COL].contiguous()
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-        if max_2d_radii is not None:
-            dist.all_reduce(max_2d_radii, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(rad, op=dist.ReduceOp.MAX, group=group)
+        flat[:, MAX_COL] = rad
     return flat
+
+
+class _DevMem:
+    """A raw device allocation exposed through the CUDA array interface (so torch can alias it without owning it)."""
+
+    def __init__(self, ptr, nfloats):
+        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class Exchange:
+    """The flat step record of this rank in peer-mapped memory + the one-kernel all-reduce over it.
+
+        ex = Exchange(P, device)                # collective: every rank of the (default) group calls it
+        ... gsb_raster_backward_flat writes ex.flat ...
+        ex.allreduce()                          # in place; afterwards ex.flat is identical on every rank
+
+    world == 1 (or no process group): a plain device buffer, allreduce() does nothing."""
+
+    def __init__(self, P, device, group=None):
+        self.P, self.device, self.group = int(P), torch.device(device), group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.mode = os.environ.get("GSB_EXCHANGE", "nvlink") if (self.world > 1 and self.device.type == "cuda") else "local"
+        self.block = None
+        self.peer_blocks = []
+        self.payload = self.P * WIDTH * 4
+        if self.mode == "nvlink":
+            lib = L.lib()
+            self.nbytes = lib.gsb_comm_bytes(self.payload)
+            blk = C.c_void_p()
+            handle = C.create_string_buffer(64)
+            with L.device_guard(self.device):
+                L.check(lib.gsb_comm_alloc(self.nbytes, C.byref(blk), handle), "gsb_comm_alloc")
+            self.block = blk.value
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle.raw), group=group)
+            self.ptrs = (C.c_void_p * self.world)()
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    self.ptrs[r] = self.block
+                    continue
+                p = C.c_void_p()
+                with L.device_guard(self.device):
+                    L.check(lib.gsb_comm_open(h, C.byref(p)), "gsb_comm_open")
+                self.peer_blocks.append(p.value)
+                self.ptrs[r] = p.value
+            self._mem = _DevMem(self.block, self.P * WIDTH)
+            self.flat = torch.as_tensor(self._mem, device=self.device).view(self.P, WIDTH)
+            dist.barrier(group=group)   # every rank has mapped every block before anyone launches
+        else:
+            self.flat = torch.zeros((self.P, WIDTH), dtype=torch.float32, device=self.device)
+
+    def allreduce(self):
+        if self.world == 1:
+            return self.flat
+        if self.mode != "nvlink":
+            return allreduce(self.flat, self.group)
+        with L.device_guard(self.device):
+            rc = L.lib().gsb_allreduce_flat(self.rank, self.world, self.ptrs, self.payload, self.P * (WIDTH // 4), WIDTH // 4,
+                                            MAX_COL // 4, MAX_COL % 4, L.stream_ptr())
+        L.check(rc, "gsb_allreduce_flat")
+        return self.flat
+
+    def close(self):
+        if self.block is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier(group=self.group)   # no peer is still inside a kernel that touches this block
+        lib = L.lib()
+        self.flat = None
+        for p in self.peer_blocks:
+            lib.gsb_comm_close(p)
+        lib.gsb_comm_free(self.block)
+        self.block, self.peer_blocks = None, []

@@ -11,7 +11,7 @@ import torch
 from . import _lib as L
 
 
-def _run(img, target, w_l1, w_ssim, want_grad):
+def _run(img, target, w_l1, w_ssim, want_grad, arena=None):
     L.require_cuda(img, "img")
     squeeze = img.ndim == 3
     x = (img[None] if squeeze else img).contiguous().float()
@@ -20,9 +20,14 @@ def _run(img, target, w_l1, w_ssim, want_grad):
         raise RuntimeError("expected matching [n,3,H,W] (or [3,H,W]) images")
     n, _, H, W = x.shape
     lib = L.lib()
-    scratch = torch.empty(lib.gsb_ssim_scratch_bytes(n, H, W), dtype=torch.uint8, device=x.device)
-    out = torch.empty((n, 3), dtype=torch.float32, device=x.device)
-    grad = torch.empty_like(x) if want_grad else None
+    if arena is not None:   # buffers that live with the arena: stable addresses, no allocation per step
+        scratch = arena.output("ssim_scratch", (lib.gsb_ssim_scratch_bytes(n, H, W),), torch.uint8)
+        out = arena.output("loss_stats", (n, 3), torch.float32)
+        grad = arena.output("dL_dimage", tuple(x.shape), torch.float32) if want_grad else None
+    else:
+        scratch = torch.empty(lib.gsb_ssim_scratch_bytes(n, H, W), dtype=torch.uint8, device=x.device)
+        out = torch.empty((n, 3), dtype=torch.float32, device=x.device)
+        grad = torch.empty_like(x) if want_grad else None
     with L.device_guard(x.device):
         rc = lib.gsb_ssim_l1(n, H, W, L.ptr(x), L.ptr(y), float(w_l1), float(w_ssim), 1.0, L.ptr(out), L.ptr(grad),
                              L.ptr(scratch), L.stream_ptr())
@@ -72,7 +77,8 @@ def calc_ssim(img1, img2, window_size=11, size_average=True):
     return r[0] if img1.ndim == 3 else r.mean()
 
 
-def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True):
-    """Non-autograd fast path used by the training step: one call, returns (stats [n,3], dL/dimg or None)."""
-    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad)
+def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None):
+    """Non-autograd fast path used by the training step: one call, returns (stats [n,3], dL/dimg or None).
+    arena (gsb200.raster.RasterArena): outputs and scratch live in the arena instead of fresh allocations."""
+    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena)
     return out, (g[0] if (squeeze and g is not None) else g)

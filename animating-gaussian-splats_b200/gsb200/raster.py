@@ -16,11 +16,38 @@ from . import _lib as L
 class RasterState:
     """What the reference returns to Python as (num_rendered, geomBuffer, binningBuffer, imgBuffer)."""
 
-    __slots__ = ("ctx", "args", "geom", "binning", "img", "keep", "tan_x", "tan_y")
+    __slots__ = ("ctx", "args", "geom", "binning", "img", "keep", "tan_x", "tan_y", "_status")
 
     @property
     def num_rendered(self):
+        """R.  After an asynchronous forward it is known on the device only: reading it here synchronises."""
+        if int(self.ctx.num_rendered) < 0:
+            err, r, _ = self.status()
+            if err == 0:
+                self.ctx.num_rendered = r
+            return r
         return int(self.ctx.num_rendered)
+
+    def status_tensor(self):
+        """The call's device status words (int32 [4]: error code, num_rendered, instances needed, -) or None (P == 0)."""
+        if not self.ctx.status:
+            return None
+        return self._view(self.ctx.status, self.geom, torch.int32, (4,))
+
+    def status(self):
+        """(error code, num_rendered, instances needed on overflow) -- blocks until the forward has run."""
+        t = self.status_tensor()
+        if t is None:
+            return 0, 0, 0
+        e, r, need, _ = (int(x) for x in t.cpu())
+        return e, r, need
+
+    def check(self):
+        """Raise if the (asynchronous) forward recorded an error: ArenaOverflow when the instances did not fit."""
+        e, r, need = self.status()
+        if e == L.GSB_ENOMEM:
+            raise ArenaOverflow(need, int(self.ctx.capacity))
+        L.check(e, "gsb_raster_forward_async")
 
     # ---- debug accessors for the bit-exact tests: views into the state buffers ------------------
     def _view(self, addr, base_t, dtype, shape):
@@ -34,7 +61,7 @@ class RasterState:
     def tensors(self):
         c = self.ctx
         n, P = c.n_cams, c.P
-        R = int(c.num_rendered)
+        R = self.num_rendered
         tiles = c.tiles_x * c.tiles_y * n
         hw = c.width * c.height
         out = {
@@ -73,6 +100,59 @@ class RasterState:
             dbits = out["depths"].view(torch.int32).view(-1)[cam * P + pl].long() & 0xFFFFFFFF
             out["point_list_keys"] = (out["point_list_tiles"] << 32) | dbits
         return out
+
+
+class ArenaOverflow(RuntimeError):
+    """An asynchronous forward produced more (Gaussian, tile) instances than its arena holds."""
+
+    def __init__(self, needed, capacity):
+        super().__init__(f"rasterizer arena overflow: {needed} instances, capacity {capacity}")
+        self.needed, self.capacity = needed, capacity
+
+
+class RasterArena:
+    """Caller-owned state buffers of the asynchronous forward (the reference allocates and grows three torch byte
+    tensors per call, DGR/rasterize_points.cu:27-33,73-78): allocated once, grown on demand, reused by every step.
+    `capacity` bounds the (Gaussian, tile) instances of a call; size it from an earlier render of the same scene
+    (reserve(..., capacity=int(1.25 * R))).  One arena serves one forward state at a time: the state of the previous
+    call is overwritten by the next."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.geom = self.img = self.binning = self.bwd_scratch = None
+        self.capacity = 0
+        self.outputs = {}
+
+    def _grow(self, name, nbytes):
+        t = getattr(self, name)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            setattr(self, name, t)
+        return t
+
+    def reserve(self, P, n_cams, W, H, capacity):
+        lib = L.lib()
+        tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        self._grow("geom", lib.gsb_geom_bytes(P, n_cams))
+        self._grow("img", lib.gsb_image_bytes(W, H, n_cams))
+        self.capacity = max(int(capacity), self.capacity if self.binning is not None else 0)
+        self._grow("binning", lib.gsb_binning_bytes(self.capacity, tiles, n_cams))
+        self._grow("bwd_scratch", lib.gsb_backward_scratch_bytes(P, n_cams))
+        return self
+
+    def output(self, name, shape, dtype):
+        """Output tensors that live as long as the arena (stable addresses for CUDA-graph replays)."""
+        t = self.outputs.get(name)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            self.outputs[name] = t
+        return t
+
+
+def tanfov_table(tanfovx, tanfovy, n_cams, device):
+    """DEVICE float [n_cams][2] for the asynchronous forward (build once per camera set, not per step)."""
+    return torch.tensor(list(zip(_as_list(tanfovx, n_cams), _as_list(tanfovy, n_cams))), dtype=torch.float32,
+                        device=device).contiguous()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -130,10 +210,13 @@ def _as_list(x, n):
 
 def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, scale_modifier, viewmatrix,
             projmatrix, tanfovx, tanfovy, image_height, image_width, prefiltered=False, n_cams=1,
-            colors_per_camera=False, reuse_geometry=False):
+            colors_per_camera=False, reuse_geometry=False, arena=None, tanfov_dev=None):
     """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim.
     reuse_geometry: allow this call to take (and to leave behind) pre-blend state, see "Geometry reuse" above; the
-    drop-in autograd node passes True, the batched step does not (every step there has new parameters)."""
+    drop-in autograd node passes True, the batched step does not (every step there has new parameters).
+    arena (RasterArena, reserved by the caller): the asynchronous form -- no host synchronisation, no allocation,
+    CUDA-graph capturable; outputs live in the arena; tanfov_dev = tanfov_table(...) (built here if None, which
+    costs a host -> device copy and is therefore not capturable)."""
     global _geom_cache, geom_cache_hits
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # DGR/rasterize_points.cu:56-58
@@ -169,11 +252,28 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
     st.args = a
     st.ctx = L.RasterCtx()
 
+    st.geom = st.binning = st.img = None
+    if arena is not None and P > 0:
+        if tanfov_dev is None:
+            tanfov_dev = tanfov_table(tanfovx, tanfovy, n_cams, dev)
+        st.keep.append(tanfov_dev)
+        color = arena.output("color", (n_cams, 3, H, W), torch.float32)
+        depth = arena.output("depth", (n_cams, 1, H, W), torch.float32)
+        radii = arena.output("radii", (n_cams, P), torch.int32)
+        st.geom, st.binning, st.img = arena.geom, arena.binning, arena.img
+        with L.device_guard(dev):
+            rc = L.lib().gsb_raster_forward_async(
+                C.byref(a), L.ptr(tanfov_dev), L.ptr(arena.geom), arena.geom.numel(), L.ptr(arena.img),
+                arena.img.numel(), L.ptr(arena.binning), arena.binning.numel(), int(arena.capacity), L.ptr(color),
+                L.ptr(depth), L.ptr(radii), C.byref(st.ctx), L.stream_ptr())
+        L.check(rc, "gsb_raster_forward_async")
+        if n_cams == 1:
+            return color[0], depth[0], radii[0], st
+        return color, depth, radii, st
     # outputs (DGR/rasterize_points.cu:67-69); every pixel / slot is written by the kernels
     color = torch.empty((n_cams, 3, H, W), dtype=torch.float32, device=dev)
     depth = torch.empty((n_cams, 1, H, W), dtype=torch.float32, device=dev)
     radii = torch.empty((n_cams, P), dtype=torch.int32, device=dev)
-    st.geom = st.binning = st.img = None
     if hit:
         prev = cached[2]
         C.memmove(C.byref(st.ctx), C.byref(prev.ctx), C.sizeof(L.RasterCtx))
@@ -237,6 +337,44 @@ def backward(st, dL_dpix, need_cov3D_grad=True):
         g["means2D"] = g["means2D"][0]
         g["conic"] = g["conic"][0]
     return g
+
+
+def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None):
+    """The step's backward in its exchange form (gsb_raster_backward_flat): the per-Gaussian record -- gradients,
+    statistic increments, largest radius -- goes into `flat` [P, 20] (layout: gsb200.dist.COLS).  mode 0 writes every
+    column; mode 1 (a second render of the same Gaussians with another colour table) adds the geometry gradients and
+    writes the colour gradient into cols 17-19.  scratch: uint8 tensor of gsb_backward_scratch_bytes (allocated here if
+    None).  means2D_out: optional [n, P, 3] for the per-camera screen-space gradients."""
+    a, c = st.args, st.ctx
+    P, n = a.P, a.n_cams
+    if P == 0:
+        return flat
+    if flat.dtype != torch.float32 or tuple(flat.shape) != (P, L.FLAT_WIDTH) or not flat.is_contiguous():
+        raise RuntimeError(f"flat must be a contiguous float32 [P, {L.FLAT_WIDTH}] tensor")
+    L.require_cuda(flat, "flat")
+    lib = L.lib()
+    if scratch is None:
+        scratch = torch.empty(lib.gsb_backward_scratch_bytes(P, n), dtype=torch.uint8, device=flat.device)
+    dpix = dL_dpix.contiguous()
+    if dpix.dtype != torch.float32:
+        dpix = dpix.float()
+    with L.device_guard(flat.device):
+        rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat), int(mode),
+                                          L.ptr(means2D_out), L.stream_ptr())
+    L.check(rc, "gsb_raster_backward_flat")
+    return flat
+
+
+def count_pairs(st):
+    """(walked, composited) (pixel, Gaussian) pairs per camera of a forward state: int64 tensor [n_cams, 2].
+    walked = sum of n_contrib (B of SURVEY.md 8(d)); composited = pairs with alpha >= 1/255 that were blended (B_alpha)."""
+    n = st.args.n_cams
+    dev = st.geom.device
+    counts = torch.zeros((n, 2), dtype=torch.int64, device=dev)
+    with L.device_guard(dev):
+        rc = L.lib().gsb_raster_count_pairs(C.byref(st.args), C.byref(st.ctx), L.ptr(counts), L.stream_ptr())
+    L.check(rc, "gsb_raster_count_pairs")
+    return counts
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

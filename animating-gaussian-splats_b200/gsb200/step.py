@@ -43,24 +43,72 @@ class DensifyStats:
                                                       L.ptr(self.gaussian_is_visible_mask), L.stream_ptr())
         L.check(rc, "gsb_densify_accumulate_batch")
 
+    def apply_flat(self, flat):
+        """Add the statistic columns of a flat step record (after the multi-GPU exchange: the sums / maximum over all
+        ranks' cameras): accum += col 14, count += col 15, max_2d_radii = max(., col 16).  One launch."""
+        P = flat.shape[0]
+        with L.device_guard(flat.device):
+            rc = L.lib().gsb_flat_apply_stats(P, L.ptr(flat), L.ptr(self.mean_2d_gradients_accumulated),
+                                              L.ptr(self.visibility_count), L.ptr(self.max_2d_radii), L.stream_ptr())
+        L.check(rc, "gsb_flat_apply_stats")
 
-def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2):
+
+def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2, flat=None, flat_mode=0, arena=None):
     """act: activated parameters (means3D, colors_precomp, opacities, scales, rotations) on the GPU;
     cams: gsb200.scene.stack_cameras(...); targets [n,3,H,W].
-    Returns (loss_stats [n,3], grads dict summed over cameras, radii [n,P], RasterState)."""
+    Returns (loss_stats [n,3], grads dict summed over cameras, radii [n,P], RasterState).
+
+    flat ([P, 20], e.g. gsb200.dist.Exchange.flat): the exchange form -- the backward writes the step's whole
+    per-Gaussian record (gradients + statistic increments of THIS step, gsb200.dist.COLS) into it and `flat` is
+    returned in place of the gradient dict; `stats` is left alone (apply the record with stats.apply_flat after the
+    exchange).  arena (gsb200.raster.RasterArena): asynchronous forward -- no host synchronisation or allocation in the
+    step, so the whole call can be captured into a CUDA graph (StepGraph)."""
     n = targets.size(0)
     color, depth, radii, st = raster.forward(
         act["means3D"], act["colors_precomp"], act["opacities"], act["scales"], act["rotations"], None, bg, 1.0,
         cams["viewmatrix"], cams["projmatrix"], cams["tanfovx"], cams["tanfovy"], cams["image_height"],
-        cams["image_width"], n_cams=n)
+        cams["image_width"], n_cams=n, arena=arena, tanfov_dev=cams.get("tanfov_dev"))
     if n == 1:
         color, radii = color[None], radii[None]
-    loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True)
+    if arena is not None:
+        loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True, arena=arena)
+    else:
+        loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True)
+    if flat is not None:
+        raster.backward_flat(st, dL, flat, mode=flat_mode, scratch=None if arena is None else arena.bwd_scratch)
+        return loss_stats, flat, radii, st
     grads = raster.backward(st, dL, need_cov3D_grad=False)
     if stats is not None:
         g2 = grads["means2D"] if n > 1 else grads["means2D"][None]
         stats.accumulate_batch(radii.contiguous(), g2.contiguous())
     return loss_stats, grads, radii, st
+
+
+class StepGraph:
+    """A step captured once into a CUDA graph and replayed: `fn()` must issue only stream work on the current stream
+    (asynchronous forward through a RasterArena, fused loss, flat backward, exchange kernel, statistics, optimiser),
+    no host synchronisation and no host -> device copies of pageable memory.  The ~30 launches of a step then cost one
+    graph launch on the host and back-to-back kernel starts on the device -- what is left of the per-step constant
+    when a GPU holds 3-4 cameras.  Outputs are whatever tensors `fn` returns (static addresses: the arena's outputs,
+    the flat buffer); inputs are updated in place (parameters by the optimiser, cameras / targets by copy_)."""
+
+    def __init__(self, fn, warmup=2, device=None):
+        self.fn = fn
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):   # first calls set kernel attributes, size pinned staging, fill caches
+                fn()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = fn()
+
+    def replay(self):
+        self.graph.replay()
+        return self.out
 
 
 class HostFeed:

@@ -88,6 +88,12 @@ typedef struct gsb_raster_ctx {
   uint16_t* tile_keys_unsorted;       /* camera-local tile id per emitted instance */
   uint16_t* tile_keys_sorted;         /* sorted camera-local tile ids; NULL when one pass suffices */
   void* sort_temp;
+  /* capacity-guarded path (gsb_raster_forward_async): the binning buffer holds `capacity` instances; the instance
+   * count is only known on the device.  status (DEVICE int32[4]): [0] error code of the call (0, GSB_EPREFILTER,
+   * GSB_ENOMEM when the instances did not fit), [1] num_rendered, [2] instances that would have been needed.
+   * On the blocking path capacity == num_rendered. */
+  int64_t capacity;
+  int32_t* status;
 } gsb_raster_ctx;
 
 /* Library / build identification. */
@@ -111,6 +117,25 @@ int gsb_raster_forward(const gsb_raster_args* args, gsb_alloc_fn geom_alloc, gsb
                        gsb_alloc_fn image_alloc, void* user, float* out_color, float* out_depth,
                        int32_t* radii, gsb_raster_ctx* ctx, void* stream);
 
+/* Rasterizer::forward without the host in the loop (the reference blocks on a 4-byte
+ * D2H of num_rendered per call, cr/rasterizer_impl.cu:281-282).  The three state buffers are caller-owned arenas
+ * (>= gsb_geom_bytes / gsb_image_bytes / gsb_binning_bytes(capacity, ...) bytes, 256-B aligned, reusable from call
+ * to call); `capacity` bounds the (Gaussian, tile) instances.  Nothing synchronises and nothing is copied from
+ * pageable or pinned host memory, so the call can be captured into a CUDA graph: the per-camera scalars come from
+ * tanfov_dev (DEVICE float [n_cams][2] = tanfovx, tanfovy; args->tanfov*_host are ignored).  If the instances do not
+ * fit, ctx->status[0] becomes GSB_ENOMEM, ctx->status[2] the count that was needed, every tile list is empty (the
+ * images are pure background, all gradients zero) and nothing is written out of bounds: the caller reads the
+ * status words whenever it next synchronises and repeats the step with a larger arena.  ctx->num_rendered is -1
+ * (unknown on the host); ctx->status[1] holds it on the device. */
+int gsb_raster_forward_async(const gsb_raster_args* args, const float* tanfov_dev, char* geom, size_t geom_bytes,
+                             char* image, size_t image_bytes, char* binning, size_t binning_bytes, int64_t capacity,
+                             float* out_color, float* out_depth, int32_t* radii, gsb_raster_ctx* ctx, void* stream);
+
+/* Walked and composited (pixel, Gaussian) pairs of a forward state, per camera: counts (DEVICE uint64 [n_cams][2])
+ * = (sum over pixels of n_contrib, pairs with alpha >= 1/255 that were blended) -- B and B_alpha of the metric
+ * definition; a measurement entry point (re-runs the forward walk without writing images). */
+int gsb_raster_count_pairs(const gsb_raster_args* args, const gsb_raster_ctx* ctx, uint64_t* counts, void* stream);
+
 /* Re-blend an existing forward state with different colours: everything a forward call computes before the
  * blend (preprocess, sorts, instance lists, tile ranges) depends only on the geometry, opacities and cameras, so
  * a second render of the SAME Gaussians through the SAME cameras -- the segmentation render that follows every
@@ -131,6 +156,50 @@ int gsb_raster_forward_colors(const gsb_raster_args* a, const gsb_raster_ctx* ct
 int gsb_raster_backward(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                         float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot, void* stream);
+
+/* The backward of a camera-batched training step, written for the exchange: instead of separate gradient tables the
+ * step's whole per-Gaussian record goes into ONE row-major buffer flat [P][GSB_FLAT_WIDTH] that the multi-GPU
+ * exchange reduces in place and the optimiser consumes:
+ *   cols 0-2 dL/dmeans3D, 3-5 dL/dcolors, 6-9 dL/drotations, 10 dL/dopacity, 11-13 dL/dscales   (summed over cameras)
+ *   col 14  sum over the batch's cameras with radius > 0 of ||dL/dmean2D.xy||   (accumulate_mean_2d_gradients,
+ *           external.py:113-124: the norm is taken per camera, BEFORE any reduction)
+ *   col 15  number of the batch's cameras with radius > 0                       (visibility_count increment)
+ *   col 16  max over the batch's cameras of the radius                          (max_2d_radii, densify.py:154-162)
+ *   cols 17-19 dL/d(second colour table) -- the segmentation render of densify.py:136-150
+ * mode 0: first render of the iteration, every column written (17-19 zero).  mode 1: a second render of the same
+ * Gaussians with another colour table: cols 0-2, 6-13 are added to, 17-19 written, 3-5 and 14-16 left alone.
+ * scratch: gsb_backward_scratch_bytes(P, n_cams) bytes.  dL_dmean2D_out (optional, [n_cams][P][3]) receives the
+ * per-camera screen-space gradients like gsb_raster_backward. */
+#define GSB_FLAT_WIDTH 20
+#define GSB_FLAT_COL_GRADNORM 14
+#define GSB_FLAT_COL_VISCOUNT 15
+#define GSB_FLAT_COL_MAXRADIUS 16
+size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams);
+int gsb_raster_backward_flat(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                             void* scratch, float* flat, int32_t mode, float* dL_dmean2D_out, void* stream);
+
+/* DensificationVariables update from a (reduced) flat buffer: grad_accum += col 14, vis_count += col 15,
+ * max_2d_radii = max(max_2d_radii, col 16) (shared.py:20-26, densify.py:154-162, external.py:113-124). */
+int gsb_flat_apply_stats(int32_t P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
+                         void* stream);
+
+/* Multi-GPU exchange over NVLink peer memory (new; the reference has no distributed code).  One process per GPU;
+ * every rank allocates its exchange block with gsb_comm_alloc, exports it (64-byte CUDA IPC handle), the hosts swap
+ * handles (any side channel) and open the peers' blocks.  gsb_allreduce_flat then reduces `n_float4` 16-byte words
+ * of the block in place across `world` ranks in ONE kernel: rank r pulls slice r from every peer (P2P loads),
+ * reduces in rank order -- SUM, except component `max_comp` of every `row_float4`-th word counted from word
+ * `max_word`, which takes MAX (col 16 of a flat row) -- and pushes the result into every peer's block (P2P
+ * stores); ranks meet through flag words in the blocks themselves (release/acquire at system scope), no host
+ * involvement, graph-capturable.  All ranks end with bit-identical contents.  peers_host: HOST array of `world`
+ * device pointers (own block at index rank); every block is gsb_comm_bytes(payload_bytes) long, payload first. */
+#define GSB_COMM_MAX_RANKS 16
+size_t gsb_comm_bytes(size_t payload_bytes);
+int gsb_comm_alloc(size_t bytes, void** block, unsigned char* handle64);   /* cudaMalloc + zero + cudaIpcGetMemHandle */
+int gsb_comm_open(const unsigned char* handle64, void** peer_block);       /* cudaIpcOpenMemHandle (peer access) */
+int gsb_comm_close(void* peer_block);
+int gsb_comm_free(void* block);
+int gsb_allreduce_flat(int32_t rank, int32_t world, void* const* peers_host, size_t payload_bytes, int64_t n_float4,
+                       int32_t row_float4, int32_t max_word, int32_t max_comp, void* stream);
 
 /* Rasterizer::markVisible (cr/rasterizer.h:24-29, cr/rasterizer_impl.cu:141-153). present: uint8 [P]. */
 int gsb_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -43,6 +43,12 @@ class Oracle:
                                          C.c_int, C.c_float, C.c_float, _f, _f, _f, _f, C.c_void_p, C.c_void_p]
         l.gso_ssim_l1.argtypes = [C.c_int, C.c_int, C.c_int, _f, _f, C.c_float, C.c_float, _d, C.c_void_p]
         l.gso_densify_accumulate.argtypes = [C.c_int, _i, _f, _f, _f, _f, _u8]
+        l.gso_set_threads.restype = C.c_int
+        l.gso_set_threads.argtypes = [C.c_int]
+
+    def set_threads(self, n=0):
+        """OpenMP team size of the oracle's loops (n <= 0: query).  Returns the size in effect."""
+        return int(self.l.gso_set_threads(int(n)))
 
     # ---- forward ------------------------------------------------------------------------------
     def forward(self, means3D, colors, opacities, scales, rotations, bg, view, proj, tanfovx, tanfovy, H, W,

@@ -28,7 +28,7 @@ def worker(rank, world, port, n_cams, P, out_dir):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     mine = gd.shard_cameras(n_cams, rank, world)
-    acc = {k: torch.zeros(P, b - a) for k, (a, b) in gd.COLS.items() if b - a > 1 or k == "opacities"}
+    acc = {k: torch.zeros(P, gd.COLS[k][1] - gd.COLS[k][0]) for k in ("means3D", "colors", "rotations", "opacities", "scales")}
     st = {"mean_2d_gradients_accumulated": torch.zeros(P), "visibility_count": torch.zeros(P)}
     maxr = torch.zeros(P)
     for c in mine:
@@ -38,11 +38,13 @@ def worker(rank, world, port, n_cams, P, out_dir):
         for k in s:
             st[k] += s[k]
         maxr = torch.maximum(maxr, r)
-    flat = gd.pack(torch.zeros(P, gd.WIDTH), acc, st)
-    gd.allreduce(flat, maxr)
-    out = gd.unpack(flat)
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), maxr=maxr.numpy(), cams=np.array(mine),
-             **{k: v.numpy() for k, v in out.items()})
+    # one step's record: gradients, THIS step's statistic increments, this step's largest radius
+    flat = gd.pack(torch.zeros(P, gd.WIDTH), acc, st, maxr)
+    ex = gd.Exchange(P, "cpu")          # CPU tensors: the torch.distributed form of the exchange
+    ex.flat.copy_(flat)
+    out = gd.unpack(ex.allreduce())
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), maxr=out["max_2d_radii"].numpy(), cams=np.array(mine),
+             **{k: v.numpy() for k, v in out.items() if k not in ("max_2d_radii", "segmentation_colors")})
     dist.destroy_process_group()
 
 
