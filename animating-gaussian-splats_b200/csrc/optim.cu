@@ -115,11 +115,95 @@ adam_kernel(AdamArgs a, float w1, float beta2, float w2, float eps) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// The optimiser step of the first-frame loop straight from the (exchanged) flat step record: activation adjoint
+// (normalize / sigmoid / exp, the arithmetic of activate_bwd_kernel) + Adam (the arithmetic of adam_kernel) over
+// the six per-Gaussian tables in ONE launch, thread per Gaussian.  The step count lives on the device (graph
+// replays advance it; adam_tick_kernel), the bias corrections are evaluated in double per block.
+// ------------------------------------------------------------------------------------------------
+struct FlatAdamDev {
+  float* p[6]; float* m[6]; float* v[6];   // means, colors, segmentation colours, quaternions, opacity logits, log scales
+  double lr[6];
+};
+
+__global__ void adam_tick_kernel(long long* step) { *step += 1; }
+
+__global__ void __launch_bounds__(256)
+adam_flat_kernel(int P, FlatAdamDev a, const float* __restrict__ flat, const long long* __restrict__ step,
+                 double beta1, double beta2, float w1, float fbeta2, float w2, float eps) {
+  __shared__ float s_step_size[6], s_bc2_sqrt;
+  if (threadIdx.x == 0) {
+    const double t = (double)*step;
+    const double bc1 = 1.0 - pow(beta1, t), bc2 = 1.0 - pow(beta2, t);
+    for (int k = 0; k < 6; k++) s_step_size[k] = (float)(a.lr[k] / bc1);
+    s_bc2_sqrt = (float)sqrt(bc2);
+  }
+  __syncthreads();
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  const float4* row = reinterpret_cast<const float4*>(flat) + (size_t)i * (GSB_FLAT_WIDTH / 4);
+  const float4 r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2), r3 = __ldg(row + 3), r4 = __ldg(row + 4);
+  const float bc2s = s_bc2_sqrt;
+  auto upd = [&](int t, size_t o, float g) {
+    float m = a.m[t][o], v = a.v[t][o];
+    m = m + (g - m) * w1;
+    v = v * fbeta2 + w2 * g * g;
+    const float denom = sqrtf(v) / bc2s + eps;
+    a.p[t][o] = a.p[t][o] - s_step_size[t] * (m / denom);
+    a.m[t][o] = m;
+    a.v[t][o] = v;
+  };
+  const size_t i3 = 3 * (size_t)i, i4 = 4 * (size_t)i;
+  // activation adjoints first (they read the parameters the updates below overwrite)
+  const float4 q = reinterpret_cast<const float4*>(a.p[3])[i];
+  const float4 g = make_float4(r1.z, r1.w, r2.x, r2.y);
+  const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+  float4 dq;
+  if (n > 1e-12f) {
+    const float inv = 1.0f / n;
+    const float4 y = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+    const float dot = y.x * g.x + y.y * g.y + y.z * g.z + y.w * g.w;
+    dq = make_float4((g.x - y.x * dot) * inv, (g.y - y.y * dot) * inv, (g.z - y.z * dot) * inv, (g.w - y.w * dot) * inv);
+  } else {
+    dq = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);
+  }
+  const float sg = sigmoidf_(a.p[4][i]);
+  const float dlogit = r2.z * sg * (1.0f - sg);
+  const float dls0 = r2.w * expf(a.p[5][i3]), dls1 = r3.x * expf(a.p[5][i3 + 1]), dls2 = r3.y * expf(a.p[5][i3 + 2]);
+  upd(0, i3, r0.x); upd(0, i3 + 1, r0.y); upd(0, i3 + 2, r0.z);
+  upd(1, i3, r0.w); upd(1, i3 + 1, r1.x); upd(1, i3 + 2, r1.y);
+  upd(2, i3, r4.y); upd(2, i3 + 1, r4.z); upd(2, i3 + 2, r4.w);
+  upd(3, i4, dq.x); upd(3, i4 + 1, dq.y); upd(3, i4 + 2, dq.z); upd(3, i4 + 3, dq.w);
+  upd(4, (size_t)i, dlogit);
+  upd(5, i3, dls0); upd(5, i3 + 1, dls1); upd(5, i3 + 2, dls2);
+}
+
 }  // namespace gsb
 
 using namespace gsb;
 
 extern "C" {
+
+int gsb_adam_flat(const gsb_flat_adam_args* a, const float* flat, int64_t* step_dev, double beta1, double beta2, double eps,
+                  void* stream) {
+  if (!a || a->P < 0) return GSB_EINVAL;
+  if (a->P == 0) return GSB_OK;
+  if (!flat || !step_dev || ((uintptr_t)flat & 15u)) return GSB_EINVAL;
+  FlatAdamDev d;
+  for (int k = 0; k < 6; k++) {
+    if (!a->param[k] || !a->exp_avg[k] || !a->exp_avg_sq[k]) return GSB_EINVAL;
+    d.p[k] = a->param[k]; d.m[k] = a->exp_avg[k]; d.v[k] = a->exp_avg_sq[k]; d.lr[k] = a->lr[k];
+  }
+  if ((uintptr_t)d.p[3] & 15u) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_dev));
+  GSB_LAUNCH_CHECK();
+  adam_flat_kernel<<<(a->P + 255) / 256, 256, 0, st>>>(a->P, d, flat, reinterpret_cast<const long long*>(step_dev), beta1,
+                                                        beta2, (float)(1.0 - beta1), (float)beta2, (float)(1.0 - beta2),
+                                                        (float)eps);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
 
 int gsb_activate(int32_t P, const float* quats, const float* opacity_logits, const float* log_scales,
                  float* rotations, float* opacities, float* scales, void* stream) {

@@ -45,6 +45,10 @@ class _RasterizeGaussians(torch.autograd.Function):
             means3D, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs.bg, rs.scale_modifier,
             rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, rs.prefiltered,
             reuse_geometry=True)
+        # Like the reference (DGR/py:82-84) the inputs go through save_for_backward, so autograd's version check catches
+        # an in-place change between forward and backward (the kernels read them again through raw pointers), and the
+        # state lives as long as the graph does: backward may run more than once (retain_graph=True).
+        ctx.save_for_backward(means3D, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
         ctx.state = state
         ctx.num_rendered = state.num_rendered
         ctx.has_cov = cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0
@@ -54,8 +58,8 @@ class _RasterizeGaussians(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_out_color, _grad_radii, _grad_depth):
+        _ = ctx.saved_tensors   # raises if an input was modified in place since the forward
         g = _raster.backward(ctx.state, grad_out_color)
-        ctx.state = None
         empty = None
         grads = (
             g["means3D"],

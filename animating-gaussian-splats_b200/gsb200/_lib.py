@@ -51,6 +51,11 @@ class AdamGroup(C.Structure):
                 ("numel", C.c_int64), ("step", C.c_int64), ("lr", C.c_double)]
 
 
+class FlatAdamArgs(C.Structure):
+    _fields_ = [("P", C.c_int32), ("param", C.c_void_p * 6), ("exp_avg", C.c_void_p * 6), ("exp_avg_sq", C.c_void_p * 6),
+                ("lr", C.c_double * 6)]
+
+
 # name -> (restype, argtypes): every symbol include/gsb200.h declares
 SYMBOLS = {
     "gsb_version": (C.c_char_p, []),
@@ -101,6 +106,7 @@ SYMBOLS = {
     "gsb_activate": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
     "gsb_activate_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 10),
     "gsb_adam_step": (C.c_int, [C.c_int32, C.POINTER(AdamGroup), C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "gsb_adam_flat": (C.c_int, [C.POINTER(FlatAdamArgs), C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_void_p]),
     "gsb_rigidity_loss": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_void_p,
                                     C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64] +
                           [C.c_void_p] * 4),

@@ -109,7 +109,7 @@ def knn_squared_distances(points, k):
     """Squared distances to the k nearest neighbours, self excluded (shared.py:45-61, float64)."""
     from scipy.spatial import cKDTree
     pts = np.ascontiguousarray(points, np.float64)
-    d, idx = cKDTree(pts).query(pts, k=k + 1)
+    d, idx = cKDTree(pts).query(pts, k=k + 1, workers=-1)   # same result on all host cores
     return idx[:, 1:], d[:, 1:] ** 2
 
 

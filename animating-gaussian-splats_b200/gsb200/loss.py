@@ -11,7 +11,7 @@ import torch
 from . import _lib as L
 
 
-def _run(img, target, w_l1, w_ssim, want_grad, arena=None):
+def _run(img, target, w_l1, w_ssim, want_grad, arena=None, tag=""):
     L.require_cuda(img, "img")
     squeeze = img.ndim == 3
     x = (img[None] if squeeze else img).contiguous().float()
@@ -22,7 +22,7 @@ def _run(img, target, w_l1, w_ssim, want_grad, arena=None):
     lib = L.lib()
     if arena is not None:   # buffers that live with the arena: stable addresses, no allocation per step
         scratch = arena.output("ssim_scratch", (lib.gsb_ssim_scratch_bytes(n, H, W),), torch.uint8)
-        out = arena.output("loss_stats", (n, 3), torch.float32)
+        out = arena.output(tag + "loss_stats", (n, 3), torch.float32)
         grad = arena.output("dL_dimage", tuple(x.shape), torch.float32) if want_grad else None
     else:
         scratch = torch.empty(lib.gsb_ssim_scratch_bytes(n, H, W), dtype=torch.uint8, device=x.device)
@@ -77,8 +77,9 @@ def calc_ssim(img1, img2, window_size=11, size_average=True):
     return r[0] if img1.ndim == 3 else r.mean()
 
 
-def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None):
+def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None, tag=""):
     """Non-autograd fast path used by the training step: one call, returns (stats [n,3], dL/dimg or None).
-    arena (gsb200.raster.RasterArena): outputs and scratch live in the arena instead of fresh allocations."""
-    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena)
+    arena (gsb200.raster.RasterArena): outputs and scratch live in the arena instead of fresh allocations (`tag`
+    names the loss numbers of a second loss in the same step; dL/dimg and the scratch are consumed before it runs)."""
+    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena, tag)
     return out, (g[0] if (squeeze and g is not None) else g)

@@ -130,6 +130,76 @@ class FusedAdam(torch.optim.Optimizer):
         return loss
 
 
+def activate_into(params, out):
+    """The activations without autograd, into caller-owned tensors out = (rotations, opacities, scales) -- the form
+    a captured step uses (static addresses, one launch)."""
+    q, lg, ls = params["rotation_quaternions"].data, params["opacity_logits"].data, params["log_scales"].data
+    rot, opa, sca = out
+    with L.device_guard(q.device):
+        rc = L.lib().gsb_activate(q.size(0), L.ptr(q), L.ptr(lg), L.ptr(ls), L.ptr(rot), L.ptr(opa), L.ptr(sca), L.stream_ptr())
+    L.check(rc, "gsb_activate")
+    return out
+
+
+class FlatAdam:
+    """The optimiser step of the first-frame loop straight from the flat step record (gsb_adam_flat): activation
+    adjoint + Adam over the six per-Gaussian tables in one launch, step count on the device, so the call can sit
+    inside a captured step.  It works ON an optimizer built by create_optimizer (FusedAdam or torch.optim.Adam):
+    parameters, learning rates, betas / eps and the exp_avg / exp_avg_sq tensors are that optimizer's, so the densify
+    surgery of external.py:127-204 and a later optimizer.step() see a consistent state after sync_state()."""
+
+    TABLES = ("means", "colors", "segmentation_masks", "rotation_quaternions", "opacity_logits", "log_scales")
+
+    def __init__(self, optimizer):
+        groups = {g["name"]: g for g in optimizer.param_groups}
+        self.optimizer = optimizer
+        self.args = L.FlatAdamArgs()
+        self.keep = []
+        steps = set()
+        first = groups[self.TABLES[0]]
+        self.betas, self.eps = tuple(first["betas"]), float(first["eps"])
+        for k, name in enumerate(self.TABLES):
+            g = groups[name]
+            p = g["params"][0]
+            L.require_cuda(p, name)
+            if p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("FlatAdam needs contiguous float32 parameters")
+            if tuple(g["betas"]) != self.betas or float(g["eps"]) != self.eps:
+                raise RuntimeError("FlatAdam needs one (betas, eps) for all tables")
+            st = optimizer.state[p]
+            if len(st) == 0:
+                st["step"] = torch.tensor(0.0)
+                st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            steps.add(int(st["step"]))
+            self.args.param[k], self.args.exp_avg[k], self.args.exp_avg_sq[k] = p.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+            self.args.lr[k] = float(g["lr"])
+            self.keep += [p, st["exp_avg"], st["exp_avg_sq"]]
+        if len(steps) != 1:
+            raise RuntimeError(f"FlatAdam needs one step count for all tables, got {sorted(steps)}")
+        self.P = groups["means"]["params"][0].shape[0]
+        self.args.P = self.P
+        self.device = groups["means"]["params"][0].device
+        self.step_dev = torch.full((1,), steps.pop(), dtype=torch.int64, device=self.device)
+
+    def step(self, flat):
+        with L.device_guard(self.device):
+            rc = L.lib().gsb_adam_flat(C.byref(self.args), L.ptr(flat), L.ptr(self.step_dev), self.betas[0], self.betas[1],
+                                       self.eps, L.stream_ptr())
+        L.check(rc, "gsb_adam_flat")
+
+    def sync_state(self):
+        """Publish the device step count to the optimizer's per-parameter state (blocks) and bump the tensors' torch
+        version counters (the kernel wrote them through raw pointers)."""
+        n = int(self.step_dev.item())
+        for t in self.keep:
+            torch.autograd.graph.increment_version(t)
+        groups = {g["name"]: g for g in self.optimizer.param_groups}
+        for name in self.TABLES:
+            self.optimizer.state[groups[name]["params"][0]]["step"] = torch.tensor(float(n))
+        return n
+
+
 def create_optimizer(parameters, scene_radius):
     """densify.py:68-86 with the fused step."""
     learning_rates = {"means": 0.00016 * scene_radius, "colors": 0.0025, "segmentation_masks": 0.0,

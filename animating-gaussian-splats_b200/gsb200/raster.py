@@ -339,6 +339,40 @@ def backward(st, dL_dpix, need_cov3D_grad=True):
     return g
 
 
+def reblend(st, colors, arena=None, name="color2"):
+    """Blend an existing forward state again with another colour table (gsb_raster_forward_colors): the second render
+    of an iteration (densify.py:136-150) needs no preprocess, no sorts and no instance lists of its own.
+    -> (color [n,3,H,W] or [3,H,W], depth, RasterState sharing st's buffers, for backward / backward_flat)."""
+    P, n, H, W = st.args.P, st.args.n_cams, st.args.height, st.args.width
+    col = _f32c(colors, "colors_precomp")
+    st2 = RasterState()
+    st2.ctx = st.ctx
+    st2.geom, st2.binning, st2.img = st.geom, st.binning, st.img
+    st2.tan_x, st2.tan_y = st.tan_x, st.tan_y
+    st2.keep = list(st.keep) + [col]
+    a = L.RasterArgs()
+    C.memmove(C.byref(a), C.byref(st.args), C.sizeof(L.RasterArgs))
+    a.colors = L.ptr(col)
+    a.color_cam_stride = 0
+    st2.args = a
+    dev = col.device
+    if arena is not None:
+        color = arena.output(name, (n, 3, H, W), torch.float32)
+        depth = arena.output(name + "_depth", (n, 1, H, W), torch.float32)
+    else:
+        color = torch.empty((n, 3, H, W), dtype=torch.float32, device=dev)
+        depth = torch.empty((n, 1, H, W), dtype=torch.float32, device=dev)
+    if P > 0:
+        with L.device_guard(dev):
+            rc = L.lib().gsb_raster_forward_colors(C.byref(a), C.byref(st2.ctx), L.ptr(color), L.ptr(depth), L.stream_ptr())
+        L.check(rc, "gsb_raster_forward_colors")
+    else:
+        color.zero_(); depth.zero_()
+    if n == 1:
+        return color[0], depth[0], st2
+    return color, depth, st2
+
+
 def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None):
     """The step's backward in its exchange form (gsb_raster_backward_flat): the per-Gaussian record -- gradients,
     statistic increments, largest radius -- goes into `flat` [P, 20] (layout: gsb200.dist.COLS).  mode 0 writes every

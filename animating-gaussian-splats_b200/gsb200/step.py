@@ -152,8 +152,9 @@ class HostFeed:
             tgt.copy_(self.host_targets, non_blocking=True)
             self.ready[k % 2].record(self.copy_stream)
 
-    def step(self, cams, bg, stats=None, after=None, wait=True):
-        """One end-to-end step.  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
+    def step(self, cams, bg, stats=None, after=None, wait=True, flat=None, arena=None):
+        """One end-to-end step.  flat / arena: the exchange form and the host-free forward of timestep_step (`after`
+        then receives the flat record in place of the gradient dict).  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
         loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix) of this
         step.  wait=True blocks until it is filled.  wait=False returns at once -- the way a training loop that only
         logs the loss calls it: the host goes on to issue the next step while this one's backward still runs; the
@@ -166,7 +167,7 @@ class HostFeed:
         self._prefetch(k + 1)
         rot, opa, sca = optim.activate(raw)   # one launch (gsb_activate)
         act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
-        loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats)
+        loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats, flat=flat, arena=arena)
         if after is not None:
             after(loss_stats, grads, radii, st)
         out = self.loss_hosts[k % 2]

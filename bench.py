@@ -147,6 +147,44 @@ def render_targets(tgt_raw, cams_stacked, n, bg, dev):
 
 
 # ------------------------------------------------------------------------------------------------
+def _host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def full_record(act, cams, targets, bg, dev):
+    """The N = 1 result of the step over ALL cameras on this rank: the flat record the exchange must reproduce."""
+    from gsb200 import step as step_mod, dist as gd
+    flat = torch.zeros((act["means3D"].shape[0], gd.WIDTH), dtype=torch.float32, device=dev)
+    step_mod.timestep_step(act, cams, targets, bg, None, flat=flat)
+    return flat
+
+
+def record_parity(got, want):
+    """north_star tolerances on the exchanged record: gradients 1e-4 relative (absolute floor 1e-5 of the column's
+    largest magnitude -- float atomics are unordered), visibility counts and radii exact."""
+    from gsb200 import dist as gd
+    g, w = got.double(), want.double()
+    out = {"ok": True}
+    worst = 0.0
+    for k, (a, b) in gd.COLS.items():
+        if k in ("visibility_count", "max_2d_radii"):
+            eq = bool(torch.equal(got[:, a:b], want[:, a:b]))
+            out[k + "_exact"] = eq
+            out["ok"] = out["ok"] and eq
+            continue
+        d = (g[:, a:b] - w[:, a:b]).abs()
+        scale = torch.maximum(g[:, a:b].abs(), w[:, a:b].abs())
+        floor = 1e-5 * float(w[:, a:b].abs().max()) + 1e-30
+        rel = float((d / (scale + floor / 1e-4)).max())   # d <= 1e-4 * scale + floor  <=>  rel <= 1e-4
+        worst = max(worst, rel)
+        out["ok"] = out["ok"] and rel <= 1e-4
+    out["max_rel"] = worst
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     from gsb200 import _lib, raster, scene, step as step_mod, dist as gd
@@ -162,30 +200,34 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.lib()
+    use_graph = os.environ.get("GSB_BENCH_GRAPH", "1") != "0"
 
     g_raw, tgt_raw, cams = build_workload(args)
-    # camera -> rank.  N > 1: cost-balanced (gsb200.dist.shard_cameras with per-camera costs): every rank renders
-    # all cameras once, untimed, and estimates each camera's cost from its walked pairs and instance count (what a
-    # trainer takes from the previous timestep's renders); rank 0's numbers are broadcast so all ranks agree.
+    P = args.gaussians
+    bg = torch.zeros(3, device=dev)
+    # camera -> rank.  N > 1: cost-balanced (gsb200.dist.shard_cameras with per-camera costs): every rank runs the
+    # whole 27-camera step once, untimed -- its forward state gives the per-camera costs (what a trainer takes from the
+    # previous timestep's renders; rank 0's numbers are broadcast so all ranks agree) and its flat record is the N = 1
+    # answer that the exchanged record is checked against below.
     cam_costs = None
-    if world > 1 and os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
+    want_flat = None
+    if world > 1:
         all_sc = scene.stack_cameras(cams, dev)
         a0 = {k: v.to(dev).contiguous() for k, v in scene.activate(g_raw).items()}
-        _, _, _, st0 = raster.forward(a0["means3D"], a0["colors_precomp"], a0["opacities"], a0["scales"], a0["rotations"],
-                                      None, torch.zeros(3, device=dev), 1.0, all_sc["viewmatrix"], all_sc["projmatrix"],
-                                      all_sc["tanfovx"], all_sc["tanfovy"], all_sc["image_height"], all_sc["image_width"],
-                                      n_cams=args.cams)
-        ct = torch.tensor(gd.camera_costs(st0), dtype=torch.float64, device=dev)
-        dist.broadcast(ct, 0)
-        cam_costs = [float(x) for x in ct.cpu()]
-        del st0, a0, all_sc
+        all_targets = render_targets(tgt_raw, all_sc, args.cams, bg, dev)
+        want_flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev)
+        _, _, _, st0 = step_mod.timestep_step(a0, all_sc, all_targets, bg, None, flat=want_flat)
+        if os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
+            ct = torch.tensor(gd.camera_costs(st0), dtype=torch.float64, device=dev)
+            dist.broadcast(ct, 0)
+            cam_costs = [float(x) for x in ct.cpu()]
+        del st0, a0, all_sc, all_targets
     my_cam_ids = gd.shard_cameras(args.cams, rank, world, cam_costs)
     my_cams = [cams[i] for i in my_cam_ids]
     n_my = len(my_cams)
     sc = scene.stack_cameras(my_cams, dev)
-    bg = torch.zeros(3, device=dev)
+    sc["tanfov_dev"] = raster.tanfov_table(sc["tanfovx"], sc["tanfovy"], n_my, dev)
     targets = render_targets(tgt_raw, sc, n_my, bg, dev)
-    P = args.gaussians
 
     # host (pinned) copies for the end-to-end leg
     raw_keys = ["means", "colors", "rotation_quaternions", "opacity_logits", "log_scales"]
@@ -193,36 +235,62 @@ def run_ours(args):
     host_targets = targets.cpu().pin_memory()
     dev_raw = {k: torch.empty_like(v, device=dev) for k, v in host_raw.items()}
     dev_targets = torch.empty_like(targets)
-    loss_host = torch.empty((n_my, 3), dtype=torch.float32).pin_memory()
-
-    stats = step_mod.DensifyStats(P, dev)
-    # flat buffer for the one allreduce: 17 gradient floats + 2 summed statistics per Gaussian
-    flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev) if world > 1 else None
-
-    def activate():
-        return {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}
-
-    def one_step(act):
-        loss_stats, grads, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, stats)
-        if world > 1:
-            gd.pack(flat, grads, {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
-                                  "visibility_count": stats.visibility_count})
-            gd.allreduce(flat, stats.max_2d_radii)
-        return loss_stats, grads, st
-
     for k in raw_keys:
         dev_raw[k].copy_(host_raw[k])
     dev_targets.copy_(host_targets)
-    act = activate()
+    act = {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}
+
+    stats = step_mod.DensifyStats(P, dev)
+    # the step record ([P, 20]: gradients + this step's statistic increments + largest radius) lives in peer-mapped
+    # memory; the backward writes it, ONE kernel reduces it over the ranks in place
+    ex = gd.Exchange(P, dev)
+    # arena of the host-free forward: capacity from an untimed render of this rank's cameras
+    _, _, _, st_probe = step_mod.timestep_step(act, sc, dev_targets, bg, None)
+    R_probe = st_probe.num_rendered
+    del st_probe
+    arena = raster.RasterArena(dev).reserve(P, n_my, args.width, args.height, capacity=int(1.25 * R_probe) + 4096)
+
+    def one_step():
+        """The product step: forward -> fused loss -> backward into the flat record -> exchange -> statistics."""
+        loss_stats, flat, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
+        ex.allreduce()
+        stats.apply_flat(ex.flat)
+        return loss_stats, flat, st
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- N > 1: the exchanged record must equal the N = 1 record --------------------------------------
+    parity = None
+    loss_stats, flat, st = one_step()
+    torch.cuda.synchronize()
+    err, R_dev, _ = st.status()
+    if err != 0:
+        raise RuntimeError(f"asynchronous forward failed: status {err}")
+    if world > 1:
+        parity = record_parity(ex.flat, want_flat)
+        parity["transport"] = "one-kernel NVLink all-reduce over CUDA-IPC peer memory" if ex.mode == "nvlink" else ex.mode
+        ref0 = ex.flat.clone()
+        dist.broadcast(ref0, 0)
+        parity["replicas_bit_identical"] = bool(torch.equal(ref0, ex.flat))
+        ok = torch.tensor([1.0 if (parity["ok"] and parity["replicas_bit_identical"]) else 0.0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        parity["ok"] = bool(ok.item() == 1.0)
+        del want_flat, ref0
+        print(f"nccl_parity: {'ok' if parity['ok'] else 'FAILED'}, max_rel={parity['max_rel']:.3e}", file=sys.stderr)
+        if not parity["ok"]:
+            raise RuntimeError(f"exchanged record differs from the single-GPU record: {parity}")
+
+    graph = step_mod.StepGraph(one_step) if use_graph else None
+    run_step = graph.replay if graph is not None else one_step
+
     if args.profile_only:
         for _ in range(3):
-            one_step(act)
+            one_step()
+        for _ in range(3):
+            run_step()
         torch.cuda.synchronize()
         return
 
@@ -231,7 +299,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     for _ in range(max(args.warmup, 3)):
-        loss_stats, grads, st = one_step(act)
+        run_step()
     sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.begin()
@@ -239,7 +307,7 @@ def run_ours(args):
     e0.record()
     marks[0].record()
     for k in range(args.steps):
-        loss_stats, grads, st = one_step(act)
+        run_step()
         marks[k + 1].record()
     e1.record()
     sync_all()
@@ -251,55 +319,65 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
+    if st.status()[0] != 0:
+        raise RuntimeError("arena overflow inside the timed region")
+
+    def timed_loop(fn, iters=10):
+        fn()
+        sync_all()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        sync_all()
+        tt_ = torch.tensor([a.elapsed_time(b) / iters], dtype=torch.float64, device=dev)
+        own = float(tt_.item())
+        if world > 1:
+            dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+        timed_loop.own = own
+        return float(tt_.item())
+
+    # the same step issued launch by launch from Python (no graph): what the graph removes
+    ms_eager = timed_loop(one_step) if use_graph else ms_step
 
     # ---- N > 1: what the exchange costs (each piece timed alone, max over ranks) -----------------
     exchange = None
     if world > 1:
-        def timed_loop(fn, iters=10):
-            fn()
-            sync_all()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            for _ in range(iters):
-                fn()
-            b.record()
-            sync_all()
-            tt_ = torch.tensor([a.elapsed_time(b) / iters], dtype=torch.float64, device=dev)
-            own = float(tt_.item())
-            dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
-            timed_loop.own = own
-            return float(tt_.item())
-        sd = {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
-              "visibility_count": stats.visibility_count}
+        def local_step():
+            step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
+        g_local = step_mod.StepGraph(local_step) if use_graph else None
         exchange = {
-            "pack": timed_loop(lambda: gd.pack(flat, grads, sd)),
-            "allreduce_sum": timed_loop(lambda: dist.all_reduce(flat)),
-            "allreduce_max": timed_loop(lambda: dist.all_reduce(stats.max_2d_radii, op=dist.ReduceOp.MAX)),
-            "step_without_exchange": timed_loop(lambda: step_mod.timestep_step(act, sc, dev_targets, bg, stats)),
-            "bytes_sum": flat.numel() * 4, "bytes_max": stats.max_2d_radii.numel() * 4,
+            "allreduce_kernel": timed_loop(ex.allreduce),
+            "apply_stats": timed_loop(lambda: stats.apply_flat(ex.flat)),
+            "step_without_exchange": timed_loop(g_local.replay if g_local is not None else local_step),
+            "bytes": ex.flat.numel() * 4, "transport": parity["transport"],
         }
+        own_local = timed_loop.own
+        flat_n = torch.zeros_like(ex.flat)
+        exchange["nccl_allreduce_sum_same_bytes"] = timed_loop(lambda: dist.all_reduce(flat_n))
+        del flat_n
         per_rank = [None] * world
-        dist.all_gather_object(per_rank, {"rank": rank, "cameras": my_cam_ids, "step_without_exchange": timed_loop.own,
+        dist.all_gather_object(per_rank, {"rank": rank, "cameras": my_cam_ids, "step_without_exchange": own_local,
                                           "est_cost": None if cam_costs is None else sum(cam_costs[c] for c in my_cam_ids)})
         exchange["per_rank"] = per_rank
 
     # ---- end to end: host buffers in, loss out, every step ------------------------------------
     # gsb200.step.HostFeed: each step's inputs (raw parameter tables + target images, pinned host memory) are
     # copied host -> device (double-buffered, the copy of step k+1 overlaps step k), activations + step run on
-    # the device, the per-camera loss numbers come back to pinned host memory; one stream sync per step.
+    # the device, the per-camera loss numbers come back to pinned host memory; gradients stay on the device (the
+    # optimiser consumes them there), only the 3 loss numbers per camera return to the host.
     feed = step_mod.HostFeed(host_raw, host_targets, dev)
     E2E_BLOCKING = os.environ.get("GSB_BENCH_E2E_BLOCKING", "0") == "1"
 
-    def after(loss_stats, grads, radii, st_):
-        if world > 1:
-            gd.pack(flat, grads, {"mean_2d_gradients_accumulated": stats.mean_2d_gradients_accumulated,
-                                  "visibility_count": stats.visibility_count})
-            gd.allreduce(flat, stats.max_2d_radii)
+    def after(loss_stats_, flat_, radii_, st_):
+        ex.allreduce()
+        stats.apply_flat(ex.flat)
 
     def e2e_step():
         # non-blocking: the loss numbers are copied to pinned host memory every step, the host does not wait for
         # them before issuing the next step (a training loop only logs them); GSB_BENCH_E2E_BLOCKING=1 waits
-        feed.step(sc, bg, stats, after, wait=E2E_BLOCKING)
+        feed.step(sc, bg, None, after, wait=E2E_BLOCKING, flat=ex.flat, arena=arena)
 
     e2e_step()
     sync_all()
@@ -324,7 +402,7 @@ def run_ours(args):
     reps = 3
     buf = (C.c_float * len(_lib.PROFILE_STAGES))()
     for _ in range(reps):
-        loss_stats, grads, st = one_step(act)
+        loss_stats, flat, st = one_step()
         torch.cuda.synchronize()
         lib.gsb_profile_read(buf, len(_lib.PROFILE_STAGES))
         stage_acc += np.array(list(buf))
@@ -332,15 +410,18 @@ def run_ours(args):
     stages = {k: float(v / reps) for k, v in zip(_lib.PROFILE_STAGES, stage_acc) if not k.endswith("_begin")}
 
     # ---- workload statistics ---------------------------------------------------------------------
-    tt = st.tensors()
-    walked = int(tt["n_contrib"].long().sum().item())             # sum over pixels of n_contrib
+    pairs = raster.count_pairs(st).sum(dim=0)                     # (walked = sum of n_contrib, composited)
+    walked, blended = int(pairs[0].item()), int(pairs[1].item())
     R = st.num_rendered
-    cnt = torch.tensor([walked, R], dtype=torch.float64, device=dev)
+    tile_bits = int(st.ctx.tile_bits)
+    cnt = torch.tensor([walked, R, blended], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(cnt)
-    walked_all, R_all = int(cnt[0].item()), int(cnt[1].item())
+    walked_all, R_all, blended_all = int(cnt[0].item()), int(cnt[1].item()), int(cnt[2].item())
+    peak_mem = torch.cuda.max_memory_allocated(dev)
 
     if rank != 0:
+        ex.close()
         if world > 1:
             dist.destroy_process_group()
         return
@@ -349,25 +430,38 @@ def run_ours(args):
     traffic = {}
     try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
         if (args.gaussians, args.cams, args.width, args.height, world) == (300_000, 27, 640, 360, 1):
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-                traffic = json.load(f)["kernels"]
+            for name in ("r2_traffic.json", "r1_traffic.json"):
+                fp = os.path.join(ROOT, "profiles", name)
+                if os.path.exists(fp):
+                    with open(fp) as f:
+                        traffic = json.load(f)["kernels"]
+                    break
     except Exception:
         traffic = {}
     tr = lambda name: (traffic.get(name, {}).get("dram_bytes_per_launch") if traffic else None)
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
     fp32_peak_tflops = n_sm * 128 * 2 * sm_max_mhz * 1e6 / 1e12
-    # dominant kernel: backward blend.  Algorithmic work: 70 FP32 flop per walked pair.
+    peak_note = f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)"
+    # dominant kernel: backward blend.  SURVEY 8(d): 70 FP32 flop per CONTRIBUTING pair (alpha >= 1/255 and blended,
+    # counted on the GPU by gsb_raster_count_pairs); the walked-pair figure (sum of n_contrib) is kept beside it.
     bwd_ms = stages["render_bwd"]
-    achieved = (walked * 70.0) / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else 0.0
+    ach = lambda pairs_, flop, ms_: (pairs_ * flop) / (ms_ * 1e-3) / 1e12 if ms_ > 0 else 0.0
+    achieved = ach(blended, 70.0, bwd_ms)
     roofline = {"kernel": "render_bwd2_kernel", "bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops,
                 "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops, "traffic": tr("render_bwd2_kernel"),
-                "peak_source": f"{n_sm} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_src} sm_max_mhz)",
-                "ms": bwd_ms, "pairs": walked}
+                "peak_source": peak_note, "ms": bwd_ms, "pairs": blended,
+                "pairs_definition": "contributing (pixel, Gaussian) pairs B_alpha, 70 flop each (SURVEY 8d)",
+                "frac_walked": ach(walked, 70.0, bwd_ms) / fp32_peak_tflops, "walked_pairs": walked}
+    fwd_ms = stages["render_fwd"]
+    roofline_fwd = {"kernel": "render_fwd_kernel", "bound": "fp32", "achieved": ach(walked, 24.0, fwd_ms),
+                    "peak": fp32_peak_tflops, "unit": "TFLOP/s", "frac": ach(walked, 24.0, fwd_ms) / fp32_peak_tflops,
+                    "traffic": tr("render_fwd_kernel"), "peak_source": peak_note, "ms": fwd_ms, "pairs": walked,
+                    "pairs_definition": "walked pairs B = sum of n_contrib, 24 flop each (SURVEY 8d)"}
     # the HBM-bound kernel with the most bytes: the instance sort (segmented onesweep on 16-bit camera-local
     # tile ids).  Algorithmic bytes per pass: the histogram reads the key (2); the scatter reads key (2) + payload (4)
     # and writes the payload (4) (+ the key (2) when another pass follows).  DESIGN.md section 5.
-    tile_digit = int(os.environ.get("GSB_TILE_DIGIT", "0")) or (5 if st.ctx.tile_bits <= 5 else 8 if st.ctx.tile_bits <= 8 else 10 if st.ctx.tile_bits <= 10 else 8)
-    passes = (max(st.ctx.tile_bits, 1) + tile_digit - 1) // tile_digit
+    tile_digit = int(os.environ.get("GSB_TILE_DIGIT", "0")) or (5 if tile_bits <= 5 else 8 if tile_bits <= 8 else 10 if tile_bits <= 10 else 8)
+    passes = (max(tile_bits, 1) + tile_digit - 1) // tile_digit
     depth_digit = 11 if os.environ.get("GSB_DEPTH_DIGIT") == "11" else 8
     gpasses = (32 + depth_digit - 1) // depth_digit
     sort_bytes = R * (12 * passes + (2 * passes if passes > 1 else 0))
@@ -378,9 +472,12 @@ def run_ours(args):
                     "unit": "GB/s", "ms": sort_ms, "instances": R,
                     "traffic": tr("seg_sort_instances"), "algorithmic_bytes": sort_bytes}
     roofline_hbm["frac"] = roofline_hbm["achieved"] / hbm_peak
-    # preprocess, depth sort (setup + 3 kernels per pass), scan, setup, key emission, instance sort (3 per pass),
-    # ranges, blend fwd, ssim fwd/finalize/bwd, blend bwd, preprocess bwd, densify statistics
-    launches = 1 + (1 + 3 * gpasses) + 1 + 1 + 1 + 3 * passes + 1 + 1 + 3 + 1 + 1 + 1
+    # cam params, preprocess, depth sort (setup + 3 kernels per pass), scan, setup, key emission, instance sort (3 per
+    # pass), ranges, (heaviest-first tile order for short launches), blend fwd, ssim fwd/finalize/bwd, blend bwd,
+    # preprocess bwd (writes the flat record), exchange kernel (N > 1), statistics from the record
+    tiles_total = ((args.width + 15) // 16) * ((args.height + 15) // 16) * n_my
+    launches = (1 + 1 + (1 + 3 * gpasses) + 1 + 1 + 1 + 3 * passes + 1 + (1 if tiles_total < 12 * 148 * 6 else 0) + 1 + 3 + 1 + 1 +
+                (1 if world > 1 else 0) + 1)
 
     out = {
         "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",
@@ -392,43 +489,53 @@ def run_ours(args):
                    "cameras_per_rank": n_my, "parallelism": f"camera-sharded dp{world}",
                    "camera_assignment": ("round-robin" if cam_costs is None else
                                          "cost-balanced (LPT on per-camera walked pairs + instances of an untimed calibration render)"),
+                   "step_issue": ("one CUDA graph per step (gsb200.step.StepGraph): host-free forward through a reused arena, "
+                                  "flat step record, exchange kernel, statistics") if use_graph else "launch by launch from Python",
                    "l2": "per-step working set (state + instance lists) is several hundred MB > 126 MB L2; no explicit flush"},
         "blends_per_sec": 2.0 * walked_all / (ms_step * 1e-3), "walked_pairs_per_step": walked_all,
-        "num_rendered_per_step": R_all,
+        "contributing_pairs_per_step": blended_all, "num_rendered_per_step": R_all,
         "e2e": {"value": args.cams / (ms_e2e * 1e-3), "unit": "iters/s", "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches * args.steps,
-        "stage_ms": stages, "roofline": roofline, "roofline_hbm": roofline_hbm, "clocks": clocks,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "returns": "the per-camera loss numbers only (3 floats per camera); gradients and statistics stay on the "
+                           "device, where the optimiser and the densify step consume them"},
+        "gpu_launches": launches * args.steps, "ms_per_step_eager": ms_eager, "peak_memory_bytes": int(peak_mem),
+        "stage_ms": stages, "roofline": roofline, "roofline_fwd": roofline_fwd, "roofline_hbm": roofline_hbm, "clocks": clocks,
     }
     if exchange is not None:
         out["exchange_ms"] = exchange
+    if parity is not None:
+        out["nccl_parity"] = parity
+    extras = os.environ.get("GSB_BENCH_EXTRAS", "1") != "0"
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, g_raw, cams, host_targets)
     if world == 1 and not args.no_reference_cuda:
         out["reference_cuda"] = reference_cuda(args, act, my_cams, dev_targets, bg, dev)
-        try:
-            out["densify_loop_shape"] = {
-                "what": "densify.py:201-248 shape: 1 camera/iteration, colour + segmentation render, 2x L1/SSIM, "
-                        "backward, densify statistics, torch Adam; through the drop-in Python surface",
-                "unit": "iters/s", "ours": densify_shaped(args, "ours"),
-                "reference_cuda": densify_shaped(args, "reference_cuda")}
-        except Exception as ex:  # never lose the headline line to the extra measurement
-            out["densify_loop_shape"] = {"error": repr(ex)[:300]}
-        try:
-            out["rigidity_loss"] = rigidity_shaped(args)
-        except Exception as ex:
-            out["rigidity_loss"] = {"error": repr(ex)[:300]}
-        try:
-            out["deformation_forward"] = deformation_shaped(args)
-        except Exception as ex:
-            out["deformation_forward"] = {"error": repr(ex)[:300]}
-        try:
-            out["train_step_shape"] = train_step_shaped(args)
-        except Exception as ex:
-            out["train_step_shape"] = {"error": repr(ex)[:300]}
+    # free the headline step's buffers before the extra legs
+    del graph, feed, arena
+    ex.close()
+    torch.cuda.empty_cache()
+    if world == 1 and not args.no_reference_cuda and extras:
+        for key, fn in (("c4_forward_throughput", lambda: c4_forward(args)),
+                        ("densify_loop_shape", lambda: densify_loop_leg(args)),
+                        ("densify_event", lambda: densify_event_leg(args)),
+                        ("rigidity_loss", lambda: rigidity_shaped(args)),
+                        ("deformation_forward", lambda: deformation_shaped(args)),
+                        ("train_step_shape", lambda: train_step_shaped(args))):
+            try:
+                out[key] = fn()
+            except Exception as ex_:  # never lose the headline line to an extra measurement
+                out[key] = {"error": repr(ex_)[:300]}
+            torch.cuda.empty_cache()
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def densify_loop_leg(args):
+    return {"what": "densify.py:201-248 shape: 1 camera/iteration, colour + segmentation render, 2x L1/SSIM, "
+                    "backward, densify statistics, Adam",
+            "unit": "iters/s", "ours": densify_shaped(args, "ours"), "ours_graph": densify_shaped(args, "ours_graph"),
+            "reference_cuda": densify_shaped(args, "reference_cuda")}
 
 
 def deformation_shaped(args, hidden=256, blocks=4, iters=10):
@@ -729,6 +836,7 @@ def cpu_baseline(args, g_raw, cams, host_targets, budget_s=12.0):
     import oracle_lib
     from gsb200 import scene
     o = oracle_lib.load()
+    threads = o.set_threads(_host_threads())   # explicit: launchers export OMP_NUM_THREADS=1
     act_np = {k: v.numpy() for k, v in scene.activate(g_raw).items()}
     n_avail = min(len(cams), host_targets.size(0))
     done = 0
@@ -737,9 +845,9 @@ def cpu_baseline(args, g_raw, cams, host_targets, budget_s=12.0):
         cpu_step(o, act_np, cams[done], host_targets[done].numpy(), args.height, args.width)
         done += 1
     dt = time.perf_counter() - t0
-    return {"value": done / dt, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port",
+    return {"value": done / dt, "unit": "iters/s", "cores": threads, "kind": "port",
             "sample": f"cameras 0..{done - 1} of the workload ({args.gaussians} gaussians, {args.width}x{args.height}): "
-                      f"fwd + L1/SSIM + bwd on the C oracle (OpenMP), {done} iterations in {dt:.1f} s"}
+                      f"fwd + L1/SSIM + bwd on the C oracle (OpenMP, {threads} threads), {done} iterations in {dt:.1f} s"}
 
 
 def run_reference(args):
@@ -752,6 +860,9 @@ def run_reference(args):
     import oracle_lib
     from gsb200 import scene
     o = oracle_lib.load()
+    # torch.distributed.run exports OMP_NUM_THREADS=1 and libgomp read it when torch loaded it: set the team size
+    # explicitly to the cores this process may use, and report the number actually in effect
+    threads = o.set_threads(_host_threads())
     g_raw, tgt_raw, cams = build_workload(args)
     act_np = {k: v.numpy() for k, v in scene.activate(g_raw).items()}
     tgt_np = {k: v.numpy() for k, v in scene.activate(tgt_raw).items()}
@@ -768,7 +879,7 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / args.steps
     v = 1.0 / dt
     sample = (f"camera 0 of the workload ({args.gaussians} gaussians, {W}x{H}) per step: fwd + L1/SSIM + bwd on the "
-              f"C oracle (OpenMP); the reference has no CPU path for the rasterizer")
+              f"C oracle (OpenMP, {threads} threads); the reference has no CPU path for the rasterizer")
     print(json.dumps({
         "impl": "reference", "metric": "train iters/sec (one iter = one camera fwd + L1/SSIM + bwd; 27 cameras per step)",
         "value": v, "unit": "iters/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1),
@@ -777,7 +888,7 @@ def run_reference(args):
         "config": {"workload": f"Panoptic-shaped timestep: {args.gaussians} gaussians, {args.cams} cameras "
                                f"{W}x{H}, fwd + L1/SSIM + bwd + densify stats (BASELINE.json configs[1])",
                    "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "iters/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -800,9 +911,10 @@ def torch_ssim_l1(img, target):
     return 0.8 * (img - target).abs().mean() + 0.2 * (1.0 - ssim)
 
 
-def reference_cuda(args, act, cams, targets, bg, dev, passes=2):
+def reference_cuda(args, act, cams, targets, bg, dev, passes=10):
     """The unmodified reference CUDA extension (oracle/_ref) on the same GPU, same inputs, its own
-    per-camera call pattern: forward -> torch L1/SSIM -> autograd -> backward, camera by camera."""
+    per-camera call pattern: forward -> torch L1/SSIM -> autograd -> backward, camera by camera.  Timed like the
+    headline: warm-up, >= 10 passes over the cameras, CUDA events, its own clock / throttle sample."""
     import oracle_lib
     import helpers
     ref = oracle_lib.load_reference_ext()
@@ -817,17 +929,156 @@ def reference_cuda(args, act, cams, targets, bg, dev, passes=2):
             loss.backward()
             helpers.ref_backward(ref, act, cam, bg, dev, fw, img.grad)
 
-    one_pass()
+    sampler = ClockSampler(dev.index or 0)
+    sampler.start()
+    for _ in range(2):
+        one_pass()
     torch.cuda.synchronize()
+    passes = max(passes, 10)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.begin()
     e0.record()
     for _ in range(passes):
         one_pass()
     e1.record()
     torch.cuda.synchronize()
+    sampler.end()
     ms = e0.elapsed_time(e1) / passes
-    return {"value": len(cams) / (ms * 1e-3), "unit": "iters/s", "ms_per_step": ms,
-            "what": "unmodified reference extension (sm_100a build, CUB sort) + stock torch L1/SSIM, camera by camera"}
+    return {"value": len(cams) / (ms * 1e-3), "unit": "iters/s", "ms_per_step": ms, "passes": passes, "warmup_passes": 2,
+            "clocks": sampler.stop(),
+            "what": "unmodified reference extension (sm_100a build, CUB sort) + stock torch L1/SSIM, camera by camera; "
+                    "per-kernel breakdown: profiles/r2_reference_stages.md"}
+
+
+def c4_forward(args, gaussians=1_000_000, n_cams=8, W=1920, H=1080, iters=10):
+    """BASELINE.json configs[3]: 1 M Gaussians, 1920x1080, 8 cameras, forward-only render throughput.  8160 tiles per
+    camera > 1024, so the instance sort takes the path only this config exercises: two 8-bit passes on the 16-bit
+    camera-local tile ids + tile_ranges_seg_kernel.  "ours": all 8 cameras in one host-free batched call replayed
+    from a CUDA graph; "reference_cuda": the unmodified extension camera by camera on the same B200."""
+    import ctypes as C
+    import helpers
+    import oracle_lib
+    from gsb200 import _lib, raster, scene, step as step_mod
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = scene.make_gaussians(gaussians, seed=1)
+    cams = scene.make_cameras(n_cams, W, H, seed=1)
+    a = {k: v.to(dev).contiguous() for k, v in scene.activate(g).items()}
+    sc = scene.stack_cameras(cams, dev)
+    td = raster.tanfov_table(sc["tanfovx"], sc["tanfovy"], n_cams, dev)
+    bg = torch.zeros(3, device=dev)
+
+    def fwd(**kw):
+        return raster.forward(a["means3D"], a["colors_precomp"], a["opacities"], a["scales"], a["rotations"], None, bg, 1.0,
+                              sc["viewmatrix"], sc["projmatrix"], sc["tanfovx"], sc["tanfovy"], H, W, n_cams=n_cams, **kw)
+
+    color_sync, _, _, st = fwd()
+    R = st.num_rendered
+    tile_bits = int(st.ctx.tile_bits)
+    cam0 = color_sync[0].clone()
+    del st, color_sync
+    arena = raster.RasterArena(dev).reserve(gaussians, n_cams, W, H, capacity=int(1.1 * R) + 4096)
+    graph = step_mod.StepGraph(lambda: fwd(arena=arena, tanfov_dev=td))
+
+    def timed(fn, n):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    ms = timed(graph.replay, iters)
+    color, _, _, st = graph.out
+    if st.status()[0] != 0:
+        raise RuntimeError("arena overflow in the C4 leg")
+    lib = _lib.lib()
+    lib.gsb_profile_enable(1)
+    buf = (C.c_float * len(_lib.PROFILE_STAGES))()
+    acc = np.zeros(len(_lib.PROFILE_STAGES))
+    for _ in range(3):
+        fwd(arena=arena, tanfov_dev=td)
+        torch.cuda.synchronize()
+        lib.gsb_profile_read(buf, len(_lib.PROFILE_STAGES))
+        acc += np.array(list(buf))
+    lib.gsb_profile_enable(0)
+    stages = {k: float(v / 3) for k, v in zip(_lib.PROFILE_STAGES, acc) if not k.endswith("_begin") and v > 0}
+    pairs = raster.count_pairs(st).sum(dim=0)
+    hbm_peak, sm_max_mhz, _ = peaks()
+    digit = 8
+    passes = (tile_bits + digit - 1) // digit
+    # per pass: histogram reads the key (2 B); scatter reads key + payload (6 B), writes payload (4 B) and the key (2 B;
+    # the last pass too: tile_ranges_seg_kernel needs the sorted ids); then the ranges kernel reads the sorted ids (2 B)
+    sort_bytes = R * 14 * passes
+    out = {"what": f"{gaussians} Gaussians, {n_cams} cameras {W}x{H}, forward only (BASELINE.json configs[3])",
+           "ms_per_pass": ms, "renders_per_s": n_cams / (ms * 1e-3), "num_rendered": R, "tile_bits": tile_bits,
+           "sort_bits_reference": 32 + int(oracle_lib.load().higher_msb(((W + 15) // 16) * ((H + 15) // 16))),
+           "walked_pairs": int(pairs[0]), "contributing_pairs": int(pairs[1]),
+           "blends_per_sec_fwd": float(pairs[0]) / (ms * 1e-3), "stage_ms": stages,
+           "roofline_hbm": {"kernel": f"(seg_tile_hist + seg_chunk_scan + seg_scatter)<u16,{digit}> x{passes} (two-pass instance sort)",
+                            "bound": "hbm", "algorithmic_bytes": sort_bytes, "ms": stages.get("sort"),
+                            "achieved": sort_bytes / (stages["sort"] * 1e-3) / 1e9 if stages.get("sort") else None,
+                            "peak": hbm_peak, "unit": "GB/s",
+                            "frac": sort_bytes / (stages["sort"] * 1e-3) / 1e9 / hbm_peak if stages.get("sort") else None},
+           "roofline_fwd": {"kernel": "render_fwd_kernel", "bound": "fp32", "ms": stages.get("render_fwd"),
+                            "frac": (float(pairs[0]) * 24.0 / (stages["render_fwd"] * 1e-3) / 1e12) /
+                                    (torch.cuda.get_device_properties(dev).multi_processor_count * 256 * sm_max_mhz * 1e-6)
+                            if stages.get("render_fwd") else None}}
+    ref = oracle_lib.load_reference_ext()
+    if ref is not None:
+        def ref_pass():
+            for cam in cams:
+                helpers.ref_forward(ref, a, cam, bg, dev)
+        fw0 = helpers.ref_forward(ref, a, cams[0], bg, dev)
+        out["max_abs_diff_camera0"] = float((fw0["color"] - cam0).abs().max())
+        del fw0
+        ms_ref = timed(ref_pass, 5)
+        out["reference_cuda"] = {"ms_per_pass": ms_ref, "renders_per_s": n_cams / (ms_ref * 1e-3)}
+        out["speedup_vs_reference_cuda"] = ms_ref / ms
+    return out
+
+
+def densify_event_leg(args):
+    """One densify event (external.py:211-314: clone / split / remove parents / prune over the six tables and both
+    Adam moments) at 300 k, 1 M and 2 M Gaussians: ms per event and the achieved bandwidth against SURVEY 8(d)'s
+    2 x 204 B per surviving Gaussian."""
+    import time
+    from gsb200 import densify as gdens, optim as goptim, scene
+    dev = torch.device("cuda", torch.cuda.current_device())
+    hbm_peak, _, _ = peaks()
+    res = {"what": "densify_gaussians at i = 1000: ~12% cloned, ~8% split, 3% pruned; wall clock around the call with "
+                   "device synchronisation (the call reads row counts back)", "unit": "ms per event"}
+    for P in (300_000, 1_000_000, 2_000_000):
+        gen = torch.Generator().manual_seed(P)
+        raw = {"means": torch.randn(P, 3, generator=gen), "colors": torch.rand(P, 3, generator=gen),
+               "segmentation_masks": torch.rand(P, 3, generator=gen), "rotation_quaternions": torch.randn(P, 4, generator=gen),
+               "opacity_logits": torch.randn(P, 1, generator=gen) * 1.5 + 2.0,
+               "log_scales": torch.log(torch.where(torch.rand(P, 1, generator=gen) < 0.4, 0.02, 0.002) * torch.ones(P, 3))}
+        times = []
+        for rep in range(3):
+            params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in raw.items()}
+            opt = goptim.FusedAdam([{"params": [v], "name": k, "lr": 1e-4} for k, v in params.items()], lr=0.0, eps=1e-15)
+            for v in params.values():
+                v.grad = torch.zeros_like(v)
+            opt.step()
+            hot = (torch.rand(P, generator=gen) < 0.2).float().to(dev)
+            dv = gdens.DensificationVariables(visibility_count=torch.ones(P, device=dev),
+                                              mean_2d_gradients_accumulated=hot * 0.001, max_2d_radii=torch.zeros(P, device=dev),
+                                              gaussian_is_visible_mask=torch.zeros(P, dtype=torch.bool, device=dev))
+            dv.means_2d = type("G", (), {"grad": torch.zeros(P, 3, device=dev)})()
+            torch.manual_seed(0)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                gdens.densify_gaussians(params, dv, 1.0, opt, 1000)
+            torch.cuda.synchronize()
+            times.append((time.perf_counter() - t0) * 1e3)
+            after = params["means"].shape[0]
+            del params, opt, dv
+        ms = min(times)
+        res[str(P)] = {"ms": ms, "after": after, "algorithmic_bytes": 2 * 204 * after,
+                       "achieved_gbs": 2 * 204 * after / (ms * 1e-3) / 1e9, "frac_of_hbm": 2 * 204 * after / (ms * 1e-3) / 1e9 / hbm_peak}
+    return res
 
 
 def densify_shaped(args, impl, iters=30, warm=5):
@@ -846,6 +1097,45 @@ def densify_shaped(args, impl, iters=30, warm=5):
     seg_targets = (targets > 0.5).float()
     params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in g_raw.items()}
     groups = [{"params": [v], "name": k, "lr": 1e-4} for k, v in params.items()]
+    if impl == "ours_graph":
+        # the same iteration with the host out of the loop: gsb200.first_frame.FirstFrameEngine with one view slot --
+        # fused activations, host-free forward, segmentation re-blend on the same geometry, flat record, statistics and
+        # activation adjoint + Adam from the record, all replayed from one CUDA graph; the camera of the iteration is
+        # copied into the slot (device to device) before each replay
+        from gsb200 import first_frame, optim as goptim
+        opt = goptim.FusedAdam(groups, lr=0.0, eps=1e-15)
+        eng = first_frame.FirstFrameEngine(params, opt, 1, args.width, args.height, dev)
+        one_cam = [{"viewmatrix": sc["viewmatrix"][i:i + 1], "projmatrix": sc["projmatrix"][i:i + 1],
+                    "tanfovx": [sc["tanfovx"][i]], "tanfovy": [sc["tanfovy"][i]]} for i in range(args.cams)]
+        td = [torch.tensor([[sc["tanfovx"][i], sc["tanfovy"][i]]], dtype=torch.float32, device=dev) for i in range(args.cams)]
+        eng.set_views(one_cam[0], targets[0:1], seg_targets[0:1])
+        eng.rebuild()
+        # arena sized for the most expensive camera, not just camera 0
+        eng.rebuild(capacity=2 * eng.arena.capacity)
+
+        def one_g(it):
+            i = it % args.cams
+            eng.cams["viewmatrix"].copy_(one_cam[i]["viewmatrix"].reshape(1, 4, 4))
+            eng.cams["projmatrix"].copy_(one_cam[i]["projmatrix"].reshape(1, 4, 4))
+            eng.cams["tanfov_dev"].copy_(td[i])
+            eng.images.copy_(targets[i:i + 1])
+            eng.masks.copy_(seg_targets[i:i + 1])
+            eng.step(check_every=0)
+
+        for it in range(warm):
+            one_g(it)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for it in range(iters):
+            one_g(warm + it)
+        e1.record()
+        torch.cuda.synchronize()
+        ok = eng.state.status()[0] == 0
+        eng.close()
+        if not ok:
+            raise RuntimeError("arena overflow in the densify-shaped graph loop")
+        return iters / (e0.elapsed_time(e1) * 1e-3)
     if impl == "ours":   # the fused step of gsb200.optim (one launch over all tables); the reference arm keeps torch's
         from gsb200 import optim as goptim
         opt = goptim.FusedAdam(groups, lr=0.0, eps=1e-15)

@@ -275,6 +275,22 @@ typedef struct gsb_adam_group {
 int gsb_adam_step(int32_t n_groups, const gsb_adam_group* groups_host, double beta1, double beta2, double eps,
                   void* stream);
 
+/* One optimiser step of the first-frame loop straight from the (exchanged) flat step record of
+ * gsb_raster_backward_flat: the adjoint of create_render_arguments (shared.py:29-42: normalize / sigmoid / exp,
+ * evaluated on the raw parameters) + torch.optim.Adam's update (densify.py:68-86) over the six per-Gaussian tables
+ * in ONE launch.  Table order: means [P][3] (cols 0-2), colors [P][3] (3-5), segmentation colours [P][3] (17-19),
+ * rotation_quaternions [P][4] (6-9 through the normalisation), opacity_logits [P] (10 through the sigmoid),
+ * log_scales [P][3] (11-13 through the exponential).  *step_dev (DEVICE int64) is the number of updates applied so
+ * far; the call increments it on the device and uses the new value for the bias corrections, so it can be replayed
+ * from a CUDA graph. */
+typedef struct gsb_flat_adam_args {
+  int32_t P;
+  float* param[6]; float* exp_avg[6]; float* exp_avg_sq[6];
+  double lr[6];
+} gsb_flat_adam_args;
+int gsb_adam_flat(const gsb_flat_adam_args* args, const float* flat, int64_t* step_dev, double beta1, double beta2,
+                  double eps, void* stream);
+
 /* Rigidity loss of the per-timestep step (train.py:317-351 with quat_mult :301-308, weighted_l2_loss_v2 :311-315,
  * build_rotation external.py:27-47): loss = mean_ij sqrt(w_ij |R_i^T (mean_nbr(i,j) - mean_i) - prev_offset_ij|^2
  * + 1e-20), R_i from normalize(quats_i) (x) prev_inv_rot_i, over F foreground Gaussians x K neighbours.

@@ -94,6 +94,53 @@ def test_seg_sort_u32_depth_keys(n_seg, P, digit_bits, iota):
     _seg_sort_case(32, n_seg * P, [P] * n_seg, 32, digit_bits, iota)
 
 
+def _seg_sort_keys(keys, seg_lens, end_bit, digit_bits, key_bits=16):
+    """Given keys (no random draw): segmented sort against a stable torch sort per segment."""
+    L, lib = _lib()
+    n = keys.numel()
+    kdt = torch.int16 if key_bits == 16 else torch.int32
+    kin_t = keys.to(kdt)
+    vals = torch.arange(n, dtype=torch.int32, device="cuda").flip(0).contiguous()
+    seg = torch.tensor([0] + list(torch.tensor(seg_lens).cumsum(0)), dtype=torch.int32, device="cuda")
+    n_seg = len(seg_lens)
+    passes = (end_bit + digit_bits - 1) // digit_bits
+    ko = torch.empty_like(kin_t) if passes > 1 else None
+    vo = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    temp = torch.empty(lib.gsb_seg_sort_temp_bytes(n, n_seg, key_bits // 8, end_bit, digit_bits), dtype=torch.uint8, device="cuda")
+    fn = lib.gsb_seg_sort_u16 if key_bits == 16 else lib.gsb_seg_sort_u32
+    L.check(fn(n, n_seg, L.ptr(seg), L.ptr(kin_t), L.ptr(ko), L.ptr(vals), L.ptr(vo), end_bit, digit_bits, L.ptr(temp),
+               L.stream_ptr()), "seg_sort")
+    torch.cuda.synchronize()
+    segc = seg.cpu().tolist()
+    for s in range(n_seg):
+        a, b = segc[s], segc[s + 1]
+        if a < b:
+            order = torch.sort(keys[a:b], stable=True).indices
+            assert torch.equal(vo[a:b], vals[a:b][order]), (s, a, b)
+            if ko is not None:
+                assert torch.equal(ko[a:b], kin_t[a:b][order]), (s, a, b)
+
+
+@pytest.mark.parametrize("digit_bits,end_bit", [(10, 10), (8, 13), (5, 10)])
+def test_seg_sort_fully_skewed_keys(digit_bits, end_bit):
+    """Every instance of a camera in ONE tile (one digit value holds the whole segment: 16-bit per-warp counters and
+    per-tile u16 rows at their limits, every lane of every warp colliding on one counter), one different tile per
+    camera, and a camera whose instances alternate between the two extreme tile ids."""
+    top = (1 << end_bit) - 1
+    lens = [70_001, 4096 * 16, 33_333, 5, 131_072]
+    parts = [torch.full((lens[0],), 0, dtype=torch.int64), torch.full((lens[1],), top, dtype=torch.int64),
+             torch.full((lens[2],), 517 & top, dtype=torch.int64), torch.full((lens[3],), 1, dtype=torch.int64),
+             torch.arange(lens[4], dtype=torch.int64) % 2 * top]
+    _seg_sort_keys(torch.cat(parts).cuda(), lens, end_bit, digit_bits)
+
+
+def test_seg_sort_depth_keys_all_equal():
+    """u32 depth keys with one value per camera (a wall of Gaussians at one depth): order must stay the input order."""
+    P = 50_000
+    keys = torch.cat([torch.full((P,), 0x3F800000, dtype=torch.int64), torch.full((P,), 0xFFFFFFFF, dtype=torch.int64)]).cuda()
+    _seg_sort_keys(keys, [P, P], 32, 8, key_bits=32)
+
+
 def test_seg_sort_large_one_pass():
     """C2-like instance sort shape: a few long segments, 10-bit digits, one pass, payload only."""
     lens = [1_500_000, 0, 2_300_001, 999_999]

@@ -167,3 +167,85 @@ def test_batched_iteration_matches_sum_of_single_camera_iterations(tmp_path):
         bad, worst = helpers.grad_close(helpers.to_np(params[k].grad), helpers.to_np(want[k]), rel=2e-4, floor=2e-6)
         assert bad == 0, (k, bad, worst)
     assert torch.allclose(stats.mean_2d_gradients_accumulated, want_acc, rtol=1e-4, atol=1e-9)
+
+
+def test_engine_step_equals_batched_iteration_plus_fused_adam(tmp_path):
+    """FirstFrameEngine (flat record -> statistics -> activation adjoint + Adam in one kernel) against the same
+    iteration through the separate pieces: batched_iteration (two timestep_steps + autograd activations) + FusedAdam."""
+    from gsb200 import first_frame, io as gio, optim as goptim, step as gstep
+    _make_sequence(tmp_path, n_cams=3, W=64, H=48, P=1500)
+    dev = torch.device("cuda")
+    meta = gio.load_dataset_metadata(tmp_path)
+    radius = gio.get_scene_radius(meta)
+    views = gio.load_timestep_views(meta, 0, tmp_path, device=dev)
+    cams, images, masks = gio.stack_views(views)
+
+    def fresh():
+        params = gio.initialize_parameters(tmp_path, device=dev)
+        with torch.no_grad():
+            g = torch.Generator(device="cuda").manual_seed(5)
+            params["rotation_quaternions"].add_(0.3 * torch.randn(params["rotation_quaternions"].shape, device=dev, generator=g))
+            params["log_scales"].add_(0.2 * torch.randn(params["log_scales"].shape, device=dev, generator=g))
+        return params, goptim.create_optimizer(params, radius)
+
+    pa, oa = fresh()
+    stats = gstep.DensifyStats(1500, dev)
+    for _ in range(3):
+        first_frame.batched_iteration(pa, cams, images, masks, torch.zeros(3, device=dev), stats)
+        oa.step()
+        oa.zero_grad(set_to_none=True)
+    for graph in (False, True):
+        pb, ob = fresh()
+        eng = first_frame.FirstFrameEngine(pb, ob, 3, 64, 48, dev, graph=False)
+        eng.set_views(cams, images, masks)
+        eng.rebuild()
+        if graph:   # capture without the warm-up steps of StepGraph: build the graph by hand around one iteration
+            eng._iteration(); eng._iteration()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                eng._iteration()
+            g.replay()
+        else:
+            for _ in range(3):
+                eng.step(check_every=0)
+        torch.cuda.synchronize()
+        assert eng.adam.sync_state() == 3
+        for k, lr in (("means", 0.00016 * radius), ("colors", 0.0025), ("opacity_logits", 0.05), ("log_scales", 0.001),
+                      ("rotation_quaternions", 0.001)):
+            d = (pa[k].data - pb[k].data).abs()
+            assert float(d.max()) < 0.05 * lr * 3 + 1e-7, (graph, k, float(d.max()), float(d.mean()))
+            sa, sb = oa.state[pa[k]], ob.state[pb[k]]
+            assert torch.allclose(sa["exp_avg"], sb["exp_avg"], rtol=2e-3, atol=1e-9 + 1e-4 * float(sa["exp_avg"].abs().max())), k
+        assert torch.equal(pa["segmentation_masks"].data, pb["segmentation_masks"].data)
+        assert torch.equal(eng.stats.visibility_count, stats.visibility_count)
+        assert torch.equal(eng.stats.max_2d_radii, stats.max_2d_radii)
+        assert torch.allclose(eng.stats.mean_2d_gradients_accumulated, stats.mean_2d_gradients_accumulated, rtol=1e-3, atol=1e-9)
+        eng.close()
+
+
+def test_run_first_frame_crosses_densify_events(tmp_path):
+    """The captured loop through two densify events (compressed schedule): row counts change, the engine is rebuilt for
+    the new count, the loss falls, Adam's step count survives the surgery."""
+    from gsb200 import first_frame, io as gio, optim as goptim
+    _make_sequence(tmp_path, n_cams=3, W=64, H=48, P=1500)
+    dev = torch.device("cuda")
+    meta = gio.load_dataset_metadata(tmp_path)
+    radius = gio.get_scene_radius(meta)
+    params = gio.initialize_parameters(tmp_path, device=dev)
+    opt = goptim.create_optimizer(params, radius)
+    cams, images, masks = gio.stack_views(gio.load_timestep_views(meta, 0, tmp_path, device=dev))
+    idx = list(range(0, 60)) + [440 + j for j in range(61)] + [540 + j for j in range(61)]   # ..., 500, ..., 600
+    log = []
+    params, timeline = first_frame.run_first_frame(params, opt, radius, cams, images, masks, len(idx), dev,
+                                                   log=lambda d: log.append((float(d["loss/image"]), d["gaussian_count"])),
+                                                   iteration_index=lambda k: idx[k])
+    assert [e["i"] for e in timeline] == [500, 600]
+    assert timeline[0]["before"] == 1500 and timeline[0]["after"] != 1500
+    assert params["means"].shape[0] == timeline[-1]["after"]
+    n = params["means"].shape[0]
+    assert all(params[k].shape[0] == n for k in gio.PARAMETER_KEYS[:6])
+    first, last = np.mean([l for l, _ in log[:20]]), np.mean([l for l, _ in log[-20:]])
+    assert last < 0.9 * first, (first, last)
+    steps = {int(opt.state[params[k]]["step"]) for k in gio.PARAMETER_KEYS[:6]}
+    assert len(steps) == 1 and steps.pop() >= len(idx)
