@@ -108,7 +108,9 @@ def test_flat_backward_matches_separate_tables():
     assert torch.allclose(u["mean_2d_gradients_accumulated"], stats.mean_2d_gradients_accumulated, rtol=1e-5, atol=1e-9)
     assert float(u["segmentation_colors"].abs().max()) == 0.0
     vis = (radii > 0)[..., None].expand(n, P, 3)
-    assert torch.allclose(m2d[vis], grads["means2D"][vis], rtol=1e-5, atol=1e-9) and float(m2d[~vis].abs().max()) == 0.0
+    bad, worst = helpers.grad_close(helpers.to_np(m2d[vis]), helpers.to_np(grads["means2D"][vis]), rel=1e-5, floor=1e-6)
+    assert bad == 0, (bad, worst)
+    assert float(m2d[~vis].abs().max()) == 0.0
     # statistics from the record (gsb_flat_apply_stats) == the per-camera kernel, twice in a row
     s2 = step.DensifyStats(P, dev)
     s2.apply_flat(flat); s2.apply_flat(flat)

@@ -131,6 +131,8 @@ def test_prefiltered_violation_raises():
     _, a, cams = helpers.scene_inputs(2000, 64, 64, seed=6, device=dev)
     cam = cams[0]
     bg = torch.zeros(3, device=dev)
+    # in_frustum only objects to p_view.z <= 0.2 (cr/auxiliary.h:150-161): put a few Gaussians behind the camera
+    a["means3D"][:5] = 1.5 * cam["campos"].to(dev) + 0.01 * a["means3D"][:5]
     call = lambda pre: raster.forward(a["means3D"], a["colors_precomp"], a["opacities"], a["scales"], a["rotations"], None,
                                       bg, 1.0, cam["viewmatrix"].to(dev), cam["projmatrix"].to(dev), cam["tanfovx"],
                                       cam["tanfovy"], 64, 64, prefiltered=pre)
@@ -140,7 +142,8 @@ def test_prefiltered_violation_raises():
         call(True)
     color, _, _, _ = call(False)                # the device is still usable
     assert torch.isfinite(color).all()
-    vis = radii > 0                             # and the promise holds for the visible subset
+    vis = torch.ones_like(radii, dtype=torch.bool)   # and the promise holds once those Gaussians are filtered out
+    vis[:5] = False
     sub = {k: v[vis].contiguous() for k, v in a.items()}
     c2, _, r2, _ = raster.forward(sub["means3D"], sub["colors_precomp"], sub["opacities"], sub["scales"], sub["rotations"],
                                   None, bg, 1.0, cam["viewmatrix"].to(dev), cam["projmatrix"].to(dev), cam["tanfovx"],
