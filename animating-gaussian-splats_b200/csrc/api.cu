@@ -439,7 +439,8 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
 }
 
 size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams) {
-  // raw first moments [n_cams][P][3] | raw second moments [n_cams][P][4] | dL/dopacity [P] | dL/dcolor [P][3]
+  // raw second moments [n_cams][P][4] (read as float4: first, so they stay 16-byte aligned for any P) | raw first
+  // moments [n_cams][P][3] | dL/dopacity [P] | dL/dcolor [P][3]
   return align_up(((size_t)P * n_cams * 7 + (size_t)P * 4) * sizeof(float), 256);
 }
 
@@ -453,9 +454,9 @@ int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx
   if (((uintptr_t)flat & 15u) || ((uintptr_t)scratch & 15u)) return GSB_EINVAL;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const size_t n = (size_t)a->P * a->n_cams;
-  float* m1 = reinterpret_cast<float*>(scratch);
-  float* m2 = m1 + 3 * n;
-  float* dop = m2 + 4 * n;
+  float* m2 = reinterpret_cast<float*>(scratch);
+  float* m1 = m2 + 4 * n;
+  float* dop = m1 + 3 * n;
   float* dcol = dop + a->P;
   prof_mark(PF_BWD_BEGIN, st);
   GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * 4) * sizeof(float), st));   // one fill for all four

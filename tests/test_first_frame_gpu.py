@@ -82,9 +82,10 @@ def _stock_loop(root, iterations, seed, ref):
         return im, radii, a["means2D"]
 
     for i in range(iterations):
-        if not buf:
-            buf.extend(views)
-        view = buf.pop(rng.randint(0, len(buf) - 1))
+        # densify.py:108-111 as the reference behaves: its local rebinding leaves the caller's buffer empty, so every
+        # iteration draws uniformly with replacement from all views
+        draw = buf if buf else list(views)
+        view = draw.pop(rng.randint(0, len(draw) - 1))
         im, radii, m2d = render(view, params["colors"])
         l_img = bench.torch_ssim_l1(im, view.image)
         sg, _, _ = render(view, params["segmentation_masks"])
