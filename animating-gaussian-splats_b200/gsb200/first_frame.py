@@ -276,10 +276,11 @@ def densify_batched(sequence_path, step_count, log=None, device="cuda", export=T
 
 
 def run_first_frame(parameters, optimizer, scene_radius, cams, images, masks, step_count, device, log=None, graph=True,
-                    on_event=None, iteration_index=None):
+                    on_event=None, iteration_index=None, max_gaussians=None):
     """The loop of densify_batched on tensors already in memory (bench.py's C5 leg feeds it a synthetic sequence).
     iteration_index(k) -> the reference iteration number i of step k (default k): lets a bounded run visit every
-    densify event of external.py:218-221 (i = 500, 600, ..., 5000) with fewer optimiser steps in between."""
+    densify event of external.py:218-221 (i = 500, 600, ..., 5000) with fewer optimiser steps in between.
+    max_gaussians: stop after the event that leaves more rows than this (the reference's schedule has no cap)."""
     import time
     n = images.shape[0]
     eng = FirstFrameEngine(parameters, optimizer, n, images.shape[3], images.shape[2], device, graph=graph)
@@ -311,6 +312,8 @@ def run_first_frame(parameters, optimizer, scene_radius, cams, images, masks, st
                              "event_ms": (t1 - t0) * 1e3, "rebuild_ms": (t2 - t1) * 1e3})
             if on_event is not None:
                 on_event(i, t1 - t0, parameters["means"].shape[0])
+            if max_gaussians is not None and parameters["means"].shape[0] > max_gaussians:
+                break
     eng.check()
     eng.adam.sync_state()
     eng.close()

@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--height", type=int, default=360)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-reference-cuda", action="store_true")
+    ap.add_argument("--no-c5", action="store_true", help="skip the sequence + densify leg (BASELINE.json configs[4])")
     ap.add_argument("--profile-only", action="store_true", help="one warm step + 2 steps, for ncu")
     return ap.parse_args()
 
@@ -419,6 +420,21 @@ def run_ours(args):
         dist.all_reduce(cnt)
     walked_all, R_all, blended_all = int(cnt[0].item()), int(cnt[1].item()), int(cnt[2].item())
     peak_mem = torch.cuda.max_memory_allocated(dev)
+    extras = os.environ.get("GSB_BENCH_EXTRAS", "1") != "0"
+
+    # ---- C5: the sequence + densify config, on all ranks (after the headline measurements) ------------------
+    c5 = None
+    if extras and not args.no_c5:
+        del graph
+        graph = None
+        torch.cuda.empty_cache()
+        try:
+            c5 = c5_sequence(args, world, rank, dev)
+        except Exception as ex_:
+            import traceback
+            traceback.print_exc(file=sys.stderr)
+            c5 = {"error": repr(ex_)[:300]}
+        torch.cuda.empty_cache()
 
     if rank != 0:
         ex.close()
@@ -505,7 +521,8 @@ def run_ours(args):
         out["exchange_ms"] = exchange
     if parity is not None:
         out["nccl_parity"] = parity
-    extras = os.environ.get("GSB_BENCH_EXTRAS", "1") != "0"
+    if c5 is not None:
+        out["c5_sequence"] = c5
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, g_raw, cams, host_targets)
     if world == 1 and not args.no_reference_cuda:
@@ -529,6 +546,189 @@ def run_ours(args):
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_event=6, timesteps=20, steps_per_timestep=3,
+                views_per_step=5, cap=2_600_000):
+    """BASELINE.json configs[4]: a synthetic 150-timestep sequence; first-frame optimisation with the reference's
+    densify schedule (external.py:211-314: events at i = 500, 600, ..., 5000, opacity reset at 3000) growing the
+    cloud from 150 k Gaussians, camera-sharded over the ranks with ONE exchange per step (gsb200.first_frame:
+    FirstFrameEngine / run_first_frame), then train.py-shaped timesteps (train.py:728-776: DeformationNetwork ->
+    5 sampled views -> rigidity -> Adam) on the densified cloud with the views sharded over the ranks.
+    Bounded: every densify event of the schedule is visited, with `steps_per_event` optimiser steps in front of each
+    (the reference runs 100), and `timesteps` of the 150 timesteps are trained with `steps_per_timestep` steps each.
+    Collective: every rank calls it."""
+    import math
+    import random
+    import time
+    import torch.distributed as dist
+    from gsb200 import scene, raster, dist as gd, first_frame, optim as goptim, deform, rigidity as R, timestep_train as tt
+    T_total = 150
+    W, H, n_cams = args.width, args.height, args.cams
+    torch.cuda.reset_peak_memory_stats(dev)
+    t_begin = time.perf_counter()
+    # ---- the sequence: ground-truth Gaussians that move rigidly (+ a little noise); images are their renders ------
+    gt = scene.make_gaussians(P_gt, seed=11)
+    gt["opacity_logits"] = gt["opacity_logits"].abs() + 0.5
+    cams = scene.make_cameras(n_cams, W, H, seed=11)
+    mine = gd.shard_cameras(n_cams, rank, world)
+    sc = scene.stack_cameras([cams[i] for i in mine], dev)
+    bg = torch.zeros(3, device=dev)
+    gt_act = {k: v.to(dev).contiguous() for k, v in scene.activate(gt).items()}
+    gt_seg = gt["segmentation_masks"].to(dev).contiguous()
+    rng = np.random.default_rng(5)
+    noise_dir = torch.from_numpy(rng.normal(0, 1, size=(P_gt, 3)).astype(np.float32)).to(dev)
+
+    def gt_means(t):
+        ang = 0.15 * math.sin(2 * math.pi * t / T_total)
+        c, s_ = math.cos(ang), math.sin(ang)
+        rot = torch.tensor([[c, -s_, 0.0], [s_, c, 0.0], [0.0, 0.0, 1.0]], device=dev)
+        return (gt_act["means3D"] @ rot.T + 0.002 * math.sin(2 * math.pi * t / 37.0) * noise_dir).contiguous()
+
+    def render_gt(t, sub_sc, n, colors):
+        a = dict(gt_act, means3D=gt_means(t))
+        col, _, _, _ = raster.forward(a["means3D"], colors, a["opacities"], a["scales"], a["rotations"], None, bg, 1.0,
+                                      sub_sc["viewmatrix"], sub_sc["projmatrix"], sub_sc["tanfovx"], sub_sc["tanfovy"], H, W,
+                                      n_cams=n)
+        return (col if n > 1 else col[None]).clone()
+
+    images = render_gt(0, sc, len(mine), gt_act["colors_precomp"]).clamp(0, 1)
+    masks = (render_gt(0, sc, len(mine), gt_seg) > 0.5).float()
+    # ---- initial cloud: a noisy subsample of the ground truth, initialised like densify.py:22-57 --------------------
+    sel = torch.from_numpy(rng.choice(P_gt, size=P0, replace=False))
+    init = scene.make_gaussians(P0, seed=12)   # only for the log_scales rule (3-NN distances); means replaced below
+    means0 = gt["means"][sel] + torch.from_numpy(rng.normal(0, 0.01, size=(P0, 3)).astype(np.float32))
+    from scipy.spatial import cKDTree
+    d, _ = cKDTree(means0.numpy()).query(means0.numpy(), k=4, workers=-1)
+    ls = np.log(np.sqrt(np.clip((d[:, 1:] ** 2).mean(-1), 1e-7, None)))[:, None].astype(np.float32)
+    quat = torch.zeros(P0, 4); quat[:, 0] = 1.0
+    raw = {"means": means0, "colors": gt["colors"][sel].clone(), "segmentation_masks": gt["segmentation_masks"][sel].clone(),
+           "rotation_quaternions": quat, "opacity_logits": torch.zeros(P0, 1), "log_scales": torch.from_numpy(np.tile(ls, (1, 3)))}
+    params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in raw.items()}
+    cam_centers = np.stack([np.linalg.inv(c["viewmatrix"][0].numpy().T)[:3, 3] for c in cams])
+    scene_radius = 1.1 * float(np.max(np.linalg.norm(cam_centers - cam_centers.mean(0), axis=1)))   # densify.py:60-65
+    opt = goptim.create_optimizer(params, scene_radius)
+    setup_s = time.perf_counter() - t_begin
+
+    # ---- phase 1: first-frame optimisation through every densify event of the schedule -------------------------
+    idx = []
+    for e in range(500, 5001, 100):
+        idx += [e - steps_per_event + 1 + j for j in range(steps_per_event)]
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    # the schedule has no cap of its own: the run stops densifying once the cloud has outgrown `cap`
+    _, timeline = first_frame.run_first_frame(params, opt, scene_radius, sc, images, masks, len(idx), dev,
+                                              iteration_index=lambda k: idx[k], max_gaussians=cap)
+    torch.cuda.synchronize(dev)
+    counts = [(0, P0)] + [(e["i"], e["after"]) for e in timeline]
+    stop = {"at": timeline[-1]["i"] if (timeline and timeline[-1]["after"] > cap) else None}
+    phase1_s = time.perf_counter() - t0
+    P1 = params["means"].shape[0]
+    events = len(counts) - 1
+    steps1 = events * steps_per_event if stop["at"] is not None else len(idx)
+    # a clean timing of the optimiser step at the final size (graph replays, no events in between)
+    eng = first_frame.FirstFrameEngine(params, opt, len(mine), W, H, dev)
+    eng.set_views(sc, images, masks)
+    eng.rebuild()
+    for _ in range(3):
+        eng.step(check_every=0)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        eng.step(check_every=0)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    tms = torch.tensor([e0.elapsed_time(e1) / 10], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    final_step_ms = float(tms.item())
+    eng.check()
+    eng.adam.sync_state()
+    # replicas must be bit-identical after all the events
+    identical = True
+    if world > 1:
+        for k in ("means", "opacity_logits", "log_scales"):
+            ref = params[k].data.clone()
+            dist.broadcast(ref, 0)
+            identical = identical and bool(torch.equal(ref, params[k].data))
+        flag = torch.tensor([1.0 if identical else 0.0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        identical = bool(flag.item() == 1.0)
+    eng.close()
+    del eng
+    torch.cuda.empty_cache()
+
+    # ---- phase 2: train.py-shaped timesteps on the densified cloud, views sharded over the ranks ---------------------
+    init_p = {k: v.data.detach().contiguous() for k, v in params.items()}
+    t1 = time.perf_counter()
+    ninfo = R.create_neighbor_info(init_p, k=20)
+    knn_s = time.perf_counter() - t1
+    enc0 = deform.normalize_and_encode_means_and_rotations(init_p)
+    fg_prev = R.create_foreground_info(init_p, ninfo.indices)
+    enc_prev = enc0
+    torch.manual_seed(0)
+    net = deform.DeformationNetwork(256, 4, precise=True).to(dev)
+    nopt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    ex = gd.Exchange(P1, dev)
+    all_sc = scene.stack_cameras(cams, dev)
+    prng = random.Random(0)
+    ts_list = [1 + (k * (T_total - 2)) // max(timesteps - 1, 1) for k in range(timesteps)]
+    train_ms = []
+    losses = []
+    for t in ts_list:
+        picks = sorted(prng.sample(range(n_cams), views_per_step))
+        my_picks = picks[rank::world]
+        if my_picks:
+            sub = {"viewmatrix": all_sc["viewmatrix"][my_picks].contiguous(), "projmatrix": all_sc["projmatrix"][my_picks].contiguous(),
+                   "tanfovx": [all_sc["tanfovx"][i] for i in my_picks], "tanfovy": [all_sc["tanfovy"][i] for i in my_picks],
+                   "image_width": W, "image_height": H}
+            tgt = render_gt(t, sub, len(my_picks), gt_act["colors_precomp"]).clamp(0, 1)
+        else:
+            sub, tgt = None, None
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(steps_per_timestep):
+            loss, enc_t, fg_t = tt.train_step(net, nopt, init_p, enc0, enc_prev, fg_prev, ninfo, (sub, tgt), t, T_total,
+                                              exchange=ex, view_count=views_per_step)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        enc_prev, fg_prev = enc_t, fg_t
+        tm = torch.tensor([e0.elapsed_time(e1) / steps_per_timestep], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        train_ms.append(float(tm.item()))
+        losses.append(float(loss))
+    ex.close()
+    peak = torch.tensor([float(torch.cuda.max_memory_allocated(dev))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(peak, op=dist.ReduceOp.MAX)
+    ev_ms = [e["event_ms"] for e in timeline] if timeline else []
+    rb_ms = [e["rebuild_ms"] for e in timeline] if timeline else []
+    return {
+        "what": f"synthetic {T_total}-timestep sequence, {n_cams} cameras {W}x{H}: first-frame optimisation from {P0} Gaussians "
+                f"through the densify schedule of external.py:211-314 ({steps_per_event} optimiser steps before each of the "
+                f"events at i = 500..5000; the reference runs 100), then {timesteps} train.py-shaped timesteps x "
+                f"{steps_per_timestep} steps ({views_per_step} sampled views, DeformationNetwork 256 x 4, rigidity K = 20) "
+                f"(BASELINE.json configs[4])",
+        "n_gpus": world, "gaussians_start": P0, "gaussians_end": P1, "densify_events": events,
+        "stopped_at_event": stop["at"], "gaussian_count_over_events": counts,
+        "first_frame": {"optimiser_steps": steps1, "seconds_wall": phase1_s,
+                        "iters_per_s_wall": steps1 * n_cams / phase1_s,
+                        "ms_per_step_at_final_size": final_step_ms, "iters_per_s_at_final_size": n_cams / (final_step_ms * 1e-3),
+                        "ms_per_densify_event_mean": float(np.mean(ev_ms)) if ev_ms else None,
+                        "ms_per_densify_event_max": float(np.max(ev_ms)) if ev_ms else None,
+                        "ms_per_rebuild_mean": float(np.mean(rb_ms)) if rb_ms else None,
+                        "replicas_bit_identical": identical},
+        "timesteps": {"count": timesteps, "ms_per_step_mean": float(np.mean(train_ms)), "ms_per_step_first": train_ms[0],
+                      "steps_per_s": 1e3 / float(np.mean(train_ms)), "loss_first": losses[0], "loss_last": losses[-1],
+                      "knn_seconds": knn_s, "network": "replicated on every rank (3xTF32 forward, TF32 backward); views sharded"},
+        "peak_memory_bytes_per_gpu": int(peak.item()), "setup_seconds": setup_s,
+    }
 
 
 def densify_loop_leg(args):
