@@ -696,35 +696,58 @@ int launch_ranges_from_hist(int n_cams, int tiles_per_cam, int log_nb, const uin
 }
 
 // identifyTileRanges on sorted camera-local tile ids (multi-pass sorts: > 1024 tiles per camera).
-// ranges pre-zeroed by the caller.
+// ranges pre-zeroed by the caller.  A thread owns 8 consecutive instances (one 16-byte load of their ids + the id in
+// front of them); the segment table sits in shared memory, the camera of the thread's first instance comes from one
+// binary search there and advances with the instances (the first version searched global memory once per instance
+// and read every id twice: 1.05 ms for C4's 249 M instances).
+constexpr int TR_ITEMS = 8;
 __global__ void __launch_bounds__(256)
 tile_ranges_seg_kernel(uint32_t R_upper, int n_cams, int tiles_per_cam, const uint32_t* __restrict__ seg_start,
                        const uint16_t* __restrict__ keys, uint2* __restrict__ ranges) {
-  const uint32_t i = blockIdx.x * 256u + threadIdx.x;
-  const uint32_t R = seg_start[n_cams];
-  if (i >= R || i >= R_upper) return;
-  int cam = 0;  // camera of instance i: last c with seg_start[c] <= i
+  __shared__ uint32_t s_seg[GSB_MAX_CAMS + 2];
+  for (int c = threadIdx.x; c <= n_cams; c += 256) s_seg[c] = seg_start[c];
+  __syncthreads();
+  const uint32_t R = min(s_seg[n_cams], R_upper);
+  const uint32_t base = (blockIdx.x * 256u + threadIdx.x) * TR_ITEMS;
+  if (base >= R) return;
+  uint32_t k[TR_ITEMS];
+  if (base + TR_ITEMS <= R) {
+    const uint4 v = *reinterpret_cast<const uint4*>(keys + base);
+    k[0] = v.x & 0xFFFFu; k[1] = v.x >> 16; k[2] = v.y & 0xFFFFu; k[3] = v.y >> 16;
+    k[4] = v.z & 0xFFFFu; k[5] = v.z >> 16; k[6] = v.w & 0xFFFFu; k[7] = v.w >> 16;
+  } else {
+#pragma unroll
+    for (int j = 0; j < TR_ITEMS; j++) k[j] = base + j < R ? keys[base + j] : 0u;
+  }
+  uint32_t prev = base > 0 ? keys[base - 1] : 0u;
+  int cam = 0;  // camera of instance `base`: last c with seg_start[c] <= base
   for (int lo = 0, hi = n_cams; lo < hi;) {
     const int mid = (lo + hi + 1) >> 1;
-    if (seg_start[mid] <= i) { lo = mid; cam = mid; } else hi = mid - 1;
+    if (s_seg[mid] <= base) { lo = mid; cam = mid; } else hi = mid - 1;
   }
-  const uint32_t cur = keys[i];
-  uint2* rg = ranges + (size_t)cam * tiles_per_cam;
-  const bool first = (i == seg_start[cam]);
-  if (first) rg[cur].x = i;
-  else {
-    const uint32_t prev = keys[i - 1];
-    if (prev != cur) { rg[prev].y = i; rg[cur].x = i; }
+#pragma unroll
+  for (int j = 0; j < TR_ITEMS; j++) {
+    const uint32_t i = base + j;
+    if (i >= R) break;
+    while (i >= s_seg[cam + 1]) cam++;   // also steps over cameras without instances
+    const uint32_t cur = k[j];
+    uint2* rg = ranges + (size_t)cam * tiles_per_cam;
+    if (i == s_seg[cam]) rg[cur].x = i;
+    else if (prev != cur) { rg[prev].y = i; rg[cur].x = i; }
+    if (i + 1 == s_seg[cam + 1]) rg[cur].y = i + 1;
+    prev = cur;
   }
-  if (i + 1 == seg_start[cam + 1]) rg[cur].y = i + 1;
 }
 
 int launch_tile_ranges_seg(int64_t R, int n_cams, int tiles_per_cam, const uint32_t* seg_start, const uint16_t* keys,
                            uint32_t* ranges, cudaStream_t st) {
   GSB_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)n_cams * tiles_per_cam * 8, st));
   if (R <= 0) return GSB_OK;
-  tile_ranges_seg_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>((uint32_t)R, n_cams, tiles_per_cam, seg_start, keys,
-                                                                      reinterpret_cast<uint2*>(ranges));
+  if (n_cams > GSB_MAX_CAMS) return GSB_EINVAL;
+  const int64_t per_block = 256 * TR_ITEMS;
+  tile_ranges_seg_kernel<<<(unsigned)((R + per_block - 1) / per_block), 256, 0, st>>>((uint32_t)R, n_cams, tiles_per_cam,
+                                                                                   seg_start, keys,
+                                                                                   reinterpret_cast<uint2*>(ranges));
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

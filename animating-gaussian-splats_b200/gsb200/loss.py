@@ -44,10 +44,12 @@ class _L1SSIM(torch.autograd.Function):
         # gradient of the requested scalar: l1 -> (1,0), ssim -> (0,-1) in (w_l1, w_ssim) terms
         gw = {"loss": (w_l1, w_ssim), "ssim": (0.0, -1.0), "l1": (1.0, 0.0)}[which]
         need = img.requires_grad
-        out, _, squeeze = _run(img, target, w_l1, w_ssim, False)
-        grad = None
+        # ONE launch chain: the l1 and ssim columns do not depend on the weights, and for "loss" the gradient weights
+        # are the mix weights, so the run that produces the gradient also produces the value that is returned
         if need:
-            _, grad, _ = _run(img, target, gw[0], gw[1], True)
+            out, grad, squeeze = _run(img, target, gw[0], gw[1], True)
+        else:
+            out, grad, squeeze = _run(img, target, w_l1, w_ssim, False)
         ctx.save_for_backward(grad)
         ctx.squeeze = squeeze
         col = {"l1": 0, "ssim": 1, "loss": 2}[which]
