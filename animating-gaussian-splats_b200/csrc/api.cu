@@ -448,7 +448,11 @@ int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx
                              float* flat, int32_t mode, float* dL_dmean2D_out, void* stream) {
   if (!a || !ctx) return GSB_EINVAL;
   if (a->P == 0) return GSB_OK;
-  if (!dL_dpix || !scratch || !flat || (mode != 0 && mode != 1) || a->color_cam_stride != 0) return GSB_EINVAL;
+  const int part = mode & ~0xFF;
+  mode &= 0xFF;
+  if (!scratch || !flat || mode < 0 || mode > 2 || a->color_cam_stride != 0) return GSB_EINVAL;
+  if (part != 0 && part != GSB_FLAT_BLEND_ONLY && part != GSB_FLAT_FINISH_ONLY) return GSB_EINVAL;
+  if (!dL_dpix && part != GSB_FLAT_FINISH_ONLY) return GSB_EINVAL;
   if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height)
     return GSB_EINVAL;
   if (((uintptr_t)flat & 15u) || ((uintptr_t)scratch & 15u)) return GSB_EINVAL;
@@ -458,13 +462,16 @@ int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx
   float* m1 = m2 + 4 * n;
   float* dop = m1 + 3 * n;
   float* dcol = dop + a->P;
-  prof_mark(PF_BWD_BEGIN, st);
-  GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * 4) * sizeof(float), st));   // one fill for all four
-  prof_mark(PF_BWD_ZERO, st);
   int rc;
-  if (ctx->num_rendered != 0)
-    if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st))) return rc;
-  prof_mark(PF_RENDER_BWD, st);
+  if (part != GSB_FLAT_FINISH_ONLY) {
+    prof_mark(PF_BWD_BEGIN, st);
+    GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * 4) * sizeof(float), st));   // one fill for all four
+    prof_mark(PF_BWD_ZERO, st);
+    if (ctx->num_rendered != 0)
+      if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st))) return rc;
+    prof_mark(PF_RENDER_BWD, st);
+    if (part == GSB_FLAT_BLEND_ONLY) return GSB_OK;
+  }
   GeomExtras gx;
   GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
   if ((rc = launch_preprocess_bwd(*a, gx.cams, *ctx, m1, m2, nullptr, nullptr, nullptr, nullptr, st, flat, mode, dop, dcol,

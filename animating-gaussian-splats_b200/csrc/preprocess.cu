@@ -473,6 +473,15 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
       row[2] = make_float4(gq.z, gq.w, dop, gs[0]);
       row[3] = make_float4(gs[1], gs[2], st_norm, st_cnt);
       row[4] = make_float4(st_rad, 0.f, 0.f, 0.f);
+    } else if (flat_mode == 2) {
+      // another camera group of the same step (rendered concurrently on its own stream): everything adds up
+      float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4];
+      r0.x += gm[0]; r0.y += gm[1]; r0.z += gm[2]; r0.w += c0;
+      r1.x += c1; r1.y += c2; r1.z += gq.x; r1.w += gq.y;
+      r2.x += gq.z; r2.y += gq.w; r2.z += dop; r2.w += gs[0];
+      r3.x += gs[1]; r3.y += gs[2]; r3.z += st_norm; r3.w += st_cnt;
+      r4.x = fmaxf(r4.x, st_rad);
+      row[0] = r0; row[1] = r1; row[2] = r2; row[3] = r3; row[4] = r4;
     } else {
       // second render of the iteration (another colour table): geometry gradients add up, colours go to 17-19
       float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];

@@ -373,11 +373,17 @@ def reblend(st, colors, arena=None, name="color2"):
     return color, depth, st2
 
 
-def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None):
+_FLAT_PART = {"all": 0, "blend": 0x100, "finish": 0x200}
+
+
+def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, part="all"):
     """The step's backward in its exchange form (gsb_raster_backward_flat): the per-Gaussian record -- gradients,
     statistic increments, largest radius -- goes into `flat` [P, 20] (layout: gsb200.dist.COLS).  mode 0 writes every
     column; mode 1 (a second render of the same Gaussians with another colour table) adds the geometry gradients and
-    writes the colour gradient into cols 17-19.  scratch: uint8 tensor of gsb_backward_scratch_bytes (allocated here if
+    writes the colour gradient into cols 17-19; mode 2 (another camera group of the same step) adds to every column
+    (col 16: max).  part: "blend" runs only the per-tile backward into `scratch`, "finish" only the per-Gaussian pass
+    from `scratch` into flat (dL_dpix may be None) -- for callers that overlap several groups on streams.
+    scratch: uint8 tensor of gsb_backward_scratch_bytes (allocated here if
     None).  means2D_out: optional [n, P, 3] for the per-camera screen-space gradients."""
     a, c = st.args, st.ctx
     P, n = a.P, a.n_cams
@@ -389,12 +395,14 @@ def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None):
     lib = L.lib()
     if scratch is None:
         scratch = torch.empty(lib.gsb_backward_scratch_bytes(P, n), dtype=torch.uint8, device=flat.device)
-    dpix = dL_dpix.contiguous()
-    if dpix.dtype != torch.float32:
-        dpix = dpix.float()
+    dpix = None
+    if dL_dpix is not None:
+        dpix = dL_dpix.contiguous()
+        if dpix.dtype != torch.float32:
+            dpix = dpix.float()
     with L.device_guard(flat.device):
-        rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat), int(mode),
-                                          L.ptr(means2D_out), L.stream_ptr())
+        rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat),
+                                          int(mode) | _FLAT_PART[part], L.ptr(means2D_out), L.stream_ptr())
     L.check(rc, "gsb_raster_backward_flat")
     return flat
 

@@ -84,6 +84,71 @@ def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2, flat
     return loss_stats, grads, radii, st
 
 
+class CameraGroups:
+    """A rank's cameras as several batches that run CONCURRENTLY (one CUDA stream each): forward -> loss -> per-tile
+    backward of every group overlap, so the few long tiles that end one group's blend kernels run beside another
+    group's bulk instead of alone on the GPU -- what limits a step when a GPU holds only 3-4 cameras.  The short
+    per-Gaussian passes that write the flat record are ordered on the calling stream (group 0 writes, the others
+    add).  Every group owns an arena; capture the whole step() into a StepGraph: the fork / join becomes parallel
+    branches of the graph."""
+
+    def __init__(self, cams, targets, n_groups, P, device, capacities=None):
+        n = targets.shape[0]
+        self.dev = torch.device(device)
+        n_groups = max(1, min(int(n_groups), n))
+        bounds = [round(g * n / n_groups) for g in range(n_groups + 1)]
+        self.groups = []
+        W, H = cams["image_width"], cams["image_height"]
+        for g in range(n_groups):
+            ix = list(range(bounds[g], bounds[g + 1]))
+            sub = {"viewmatrix": cams["viewmatrix"][ix].contiguous(), "projmatrix": cams["projmatrix"][ix].contiguous(),
+                   "tanfovx": [cams["tanfovx"][i] for i in ix], "tanfovy": [cams["tanfovy"][i] for i in ix],
+                   "image_width": W, "image_height": H}
+            sub["tanfov_dev"] = raster.tanfov_table(sub["tanfovx"], sub["tanfovy"], len(ix), self.dev)
+            self.groups.append({"ix": ix, "cams": sub, "targets": targets[ix].contiguous(), "arena": raster.RasterArena(self.dev),
+                                "stream": torch.cuda.Stream(device=self.dev) if g > 0 else None})
+        self.P = P
+        self.capacities = capacities
+
+    def reserve(self, act, bg, slack=1.25):
+        """Size every group's arena from one blocking render of its cameras."""
+        for g in self.groups:
+            n = len(g["ix"])
+            c = g["cams"]
+            _, _, _, st = raster.forward(act["means3D"], act["colors_precomp"], act["opacities"], act["scales"], act["rotations"],
+                                         None, bg, 1.0, c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"],
+                                         c["image_height"], c["image_width"], n_cams=n)
+            g["arena"].reserve(self.P, n, c["image_width"], c["image_height"], int(slack * st.num_rendered) + 4096)
+        return self
+
+    def step(self, act, bg, flat, w_l1=0.8, w_ssim=0.2):
+        """-> (list of per-group loss numbers [n_g, 3], flat, list of RasterStates)."""
+        cur = torch.cuda.current_stream(self.dev)
+        outs = []
+        for g in self.groups:
+            s = g["stream"]
+            if s is not None:
+                s.wait_stream(cur)
+            with torch.cuda.stream(s if s is not None else cur):
+                n = len(g["ix"])
+                c = g["cams"]
+                color, _, radii, st = raster.forward(act["means3D"], act["colors_precomp"], act["opacities"], act["scales"],
+                                                     act["rotations"], None, bg, 1.0, c["viewmatrix"], c["projmatrix"],
+                                                     c["tanfovx"], c["tanfovy"], c["image_height"], c["image_width"], n_cams=n,
+                                                     arena=g["arena"], tanfov_dev=c["tanfov_dev"])
+                if n == 1:
+                    color = color[None]
+                loss_stats, dL = loss_mod.l1_ssim_fused(color, g["targets"], w_l1, w_ssim, grad=True, arena=g["arena"])
+                raster.backward_flat(st, dL, flat, mode=0, scratch=g["arena"].bwd_scratch, part="blend")
+                outs.append((loss_stats, st))
+        for k, g in enumerate(self.groups):   # join, then the short passes that touch flat, in order
+            if g["stream"] is not None:
+                cur.wait_stream(g["stream"])
+        for k, g in enumerate(self.groups):
+            raster.backward_flat(outs[k][1], None, flat, mode=0 if k == 0 else 2, scratch=g["arena"].bwd_scratch, part="finish")
+        return [o[0] for o in outs], flat, [o[1] for o in outs]
+
+
 class StepGraph:
     """A step captured once into a CUDA graph and replayed: `fn()` must issue only stream work on the current stream
     (asynchronous forward through a RasterArena, fused loss, flat backward, exchange kernel, statistics, optimiser),

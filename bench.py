@@ -251,9 +251,18 @@ def run_ours(args):
     del st_probe
     arena = raster.RasterArena(dev).reserve(P, n_my, args.width, args.height, capacity=int(1.25 * R_probe) + 4096)
 
+    # few cameras per GPU (N > 1): render them as concurrent groups so that one group's long tiles overlap another's
+    # bulk (gsb200.step.CameraGroups); GSB_BENCH_GROUPS overrides (1 = one batch)
+    n_groups = int(os.environ.get("GSB_BENCH_GROUPS", "0")) or (min(n_my, 4) if n_my <= 8 else 1)
+    cg = step_mod.CameraGroups(sc, dev_targets, n_groups, P, dev).reserve(act, bg) if n_groups > 1 else None
+
     def one_step():
         """The product step: forward -> fused loss -> backward into the flat record -> exchange -> statistics."""
-        loss_stats, flat, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
+        if cg is not None:
+            loss_stats, flat, sts = cg.step(act, bg, ex.flat)
+            st = sts[0]
+        else:
+            loss_stats, flat, radii, st = step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
         ex.allreduce()
         stats.apply_flat(ex.flat)
         return loss_stats, flat, st
@@ -346,7 +355,10 @@ def run_ours(args):
     exchange = None
     if world > 1:
         def local_step():
-            step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
+            if cg is not None:
+                cg.step(act, bg, ex.flat)
+            else:
+                step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
         g_local = step_mod.StepGraph(local_step) if use_graph else None
         exchange = {
             "allreduce_kernel": timed_loop(ex.allreduce),
@@ -402,8 +414,8 @@ def run_ours(args):
     stage_acc = np.zeros(len(_lib.PROFILE_STAGES))
     reps = 3
     buf = (C.c_float * len(_lib.PROFILE_STAGES))()
-    for _ in range(reps):
-        loss_stats, flat, st = one_step()
+    for _ in range(reps):   # the rank's cameras as ONE batch: the stage events of concurrent groups would interleave
+        loss_stats, flat, radii_, st = step_mod.timestep_step(act, sc, dev_targets, bg, None, flat=ex.flat, arena=arena)
         torch.cuda.synchronize()
         lib.gsb_profile_read(buf, len(_lib.PROFILE_STAGES))
         stage_acc += np.array(list(buf))
@@ -505,6 +517,7 @@ def run_ours(args):
                    "cameras_per_rank": n_my, "parallelism": f"camera-sharded dp{world}",
                    "camera_assignment": ("round-robin" if cam_costs is None else
                                          "cost-balanced (LPT on per-camera walked pairs + instances of an untimed calibration render)"),
+                   "camera_groups": n_groups,
                    "step_issue": ("one CUDA graph per step (gsb200.step.StepGraph): host-free forward through a reused arena, "
                                   "flat step record, exchange kernel, statistics") if use_graph else "launch by launch from Python",
                    "l2": "per-step working set (state + instance lists) is several hundred MB > 126 MB L2; no explicit flush"},
@@ -1129,6 +1142,10 @@ def reference_cuda(args, act, cams, targets, bg, dev, passes=10):
             loss.backward()
             helpers.ref_backward(ref, act, cam, bg, dev, fw, img.grad)
 
+    if os.environ.get("GSB_REF_PROFILE") == "1":   # tools/prof_r2.sh: one warm pass + one pass under ncu
+        one_pass(); torch.cuda.synchronize()
+        one_pass(); torch.cuda.synchronize()
+        return {"profile_only": True}
     sampler = ClockSampler(dev.index or 0)
     sampler.start()
     for _ in range(2):

@@ -168,12 +168,19 @@ int gsb_raster_backward(const gsb_raster_args* args, const gsb_raster_ctx* ctx, 
  *   cols 17-19 dL/d(second colour table) -- the segmentation render of densify.py:136-150
  * mode 0: first render of the iteration, every column written (17-19 zero).  mode 1: a second render of the same
  * Gaussians with another colour table: cols 0-2, 6-13 are added to, 17-19 written, 3-5 and 14-16 left alone.
+ * mode 2: another camera group of the SAME step (a caller that renders its cameras as several batches on concurrent
+ * streams, so that one batch's long tiles overlap another's bulk): every column is added to, col 16 maximised.
+ * Adding GSB_FLAT_BLEND_ONLY runs only the per-tile blend backward (into scratch), GSB_FLAT_FINISH_ONLY only the
+ * per-Gaussian pass from scratch into flat -- the two halves of one call, so that a caller can run the blends of
+ * several groups concurrently and order only the short passes that touch flat.
  * scratch: gsb_backward_scratch_bytes(P, n_cams) bytes.  dL_dmean2D_out (optional, [n_cams][P][3]) receives the
  * per-camera screen-space gradients like gsb_raster_backward. */
 #define GSB_FLAT_WIDTH 20
 #define GSB_FLAT_COL_GRADNORM 14
 #define GSB_FLAT_COL_VISCOUNT 15
 #define GSB_FLAT_COL_MAXRADIUS 16
+#define GSB_FLAT_BLEND_ONLY 0x100
+#define GSB_FLAT_FINISH_ONLY 0x200
 size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams);
 int gsb_raster_backward_flat(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
                              void* scratch, float* flat, int32_t mode, float* dL_dmean2D_out, void* stream);

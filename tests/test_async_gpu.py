@@ -227,3 +227,26 @@ def test_exchange_kernel_two_processes(tmp_path, world):
         for r in range(world):
             assert np.array_equal(got[r][f"arr_{it}"], got[0][f"arr_{it}"]), (it, r)
         assert np.array_equal(got[0][f"arr_{it}"], want), it
+
+
+@pytest.mark.parametrize("n_groups", [2, 3])
+def test_camera_groups_equal_one_batch(n_groups):
+    """The rank's cameras as concurrent groups (streams, one arena each, flat record written by group 0 and added to by
+    the others) == the same cameras as one batch; also through a captured graph (fork / join as graph branches)."""
+    from gsb200 import raster, step
+    dev, g, a, cams, sc, bg, targets = _setup(n=3)
+    P = a["means3D"].shape[0]
+    flat_one = torch.zeros((P, 20), device=dev)
+    loss_one, _, _, _ = step.timestep_step(a, sc, targets, bg, None, flat=flat_one)
+    cg = step.CameraGroups(sc, targets, n_groups, P, dev).reserve(a, bg)
+    flat = torch.full((P, 20), float("nan"), device=dev)
+    for graph in (None, step.StepGraph(lambda: cg.step(a, bg, flat))):
+        flat.fill_(float("nan"))
+        losses, _, sts = cg.step(a, bg, flat) if graph is None else graph.replay()
+        torch.cuda.synchronize()
+        assert all(s.status()[0] == 0 for s in sts)
+        assert torch.allclose(torch.cat(losses), loss_one, rtol=0, atol=1e-6)
+        bad, worst = helpers.grad_close(helpers.to_np(flat[:, :15]), helpers.to_np(flat_one[:, :15]), rel=1e-4, floor=1e-5)
+        assert bad == 0, (n_groups, bad, worst)
+        assert torch.equal(flat[:, 15:17], flat_one[:, 15:17])
+        assert float(flat[:, 17:].abs().max()) == 0.0

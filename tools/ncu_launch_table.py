@@ -1,0 +1,31 @@
+#!/usr/bin/env python
+"""Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel: launches, total and mean duration,
+share of the listed time.  usage: ncu_launch_table.py launches.csv ["title"] > profiles/xxx.md"""
+import csv
+import re
+import sys
+from collections import OrderedDict
+
+rows = list(csv.reader(l for l in open(sys.argv[1]) if l.startswith('"')))
+H = rows[0]
+ki, mi, vi, ui = H.index("Kernel Name"), H.index("Metric Name"), H.index("Metric Value"), H.index("Metric Unit")
+agg = OrderedDict()
+for r in rows[1:]:
+    if r[mi] != "gpu__time_duration.sum":
+        continue
+    name = re.sub(r"\(.*", "", r[ki]).replace("void ", "")
+    name = re.sub(r"<.*", "", name) if len(name) > 70 else name
+    v = float(r[vi].replace(",", ""))
+    v *= {"ns": 1e-3, "us": 1.0, "usecond": 1.0, "nsecond": 1e-3, "ms": 1e3, "msecond": 1e3}.get(r[ui], 1.0)
+    a = agg.setdefault(name, [0, 0.0])
+    a[0] += 1
+    a[1] += v
+total = sum(a[1] for a in agg.values())
+if len(sys.argv) > 2:
+    print(f"# {sys.argv[2]}\n")
+print(f"{sum(a[0] for a in agg.values())} launches, {total / 1e3:.3f} ms of kernel time (ncu per-launch durations: cold caches, "
+      "serialised launches -- shares, not absolute step times)\n")
+print("| kernel | launches | total [us] | mean [us] | share |")
+print("|---|---|---|---|---|")
+for name, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+    print(f"| `{name}` | {n} | {t:.1f} | {t / n:.2f} | {100 * t / total:.1f}% |")
