@@ -185,10 +185,11 @@ __device__ __forceinline__ TileCoord tile_coord(const uint32_t* __restrict__ ord
 // COUNT: the measurement variant behind gsb_raster_count_pairs -- the same walk, no image outputs; per camera it
 // adds up the walked pairs (sum of n_contrib) and the pairs actually composited (alpha >= 1/255 and not the
 // terminating entry): the B and B_alpha of SURVEY.md section 8(d).
-// MASK: entries carry the 8-bit patch mask of tile_cull_keep<true> (which of the tile's eight 8x4 patches the splat's
-// alpha >= 1/255 ellipse can reach); a warp skips an entry that cannot reach its patch with one shared load and a bit
-// test instead of the 9-instruction power evaluation (the backward has always done so).
-template <bool COUNT, bool MASK>
+// (The patch mask of the backward -- a warp skips entries whose alpha >= 1/255 ellipse cannot reach its 8x4 patch --
+// was measured SLOWER here: 1.40 vs 1.21 ms at C2, 3.10 vs 2.64 ms at C4.  The forward's per-entry cost for a warp
+// that rejects is already only the 9-instruction power evaluation, and the mask's square roots and divisions in the
+// staging phase plus one more branch per entry cost more than they save.)
+template <bool COUNT>
 __global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_FWD_MINB)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                   const uint32_t* __restrict__ point_list, int W, int H, int P,
@@ -240,7 +241,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       id = point_list[range.x + progress];
       xy = means2D[cam_off + id];
       co = conic_opacity[cam_off + id];
-      keep = tile_cull_keep<MASK>(xy.x, xy.y, co, tx0, ty0, thr);
+      keep = tile_cull_keep<false>(xy.x, xy.y, co, tx0, ty0, thr);
     }
     int slot;
     const int n = compact_slot(keep, tid, s_wcnt, slot);
@@ -253,7 +254,6 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
     for (int j = 0; !done && j < n; j++) {
       const float4 a = s_a[j];
-      if (MASK && !((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;   // warp-uniform: cannot reach this patch
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
       const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
@@ -313,9 +313,7 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  static const int use_mask = [] { const char* e = getenv("GSB_FWD_MASK"); return e ? atoi(e) : 1; }();
-  auto kern = use_mask ? render_fwd_kernel<false, true> : render_fwd_kernel<false, false>;
-  kern<<<tiles_total, block, 0, st>>>(
+  render_fwd_kernel<false><<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
       reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, c.final_T, c.n_contrib, out_color,
@@ -328,7 +326,7 @@ int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsign
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   GSB_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * 2 * (size_t)a.n_cams, st));
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  render_fwd_kernel<true, false><<<tiles_total, block, 0, st>>>(
+  render_fwd_kernel<true><<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), nullptr, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
       reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, nullptr, nullptr, nullptr, nullptr,

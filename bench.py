@@ -562,7 +562,7 @@ def run_ours(args):
 
 
 def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_event=6, timesteps=20, steps_per_timestep=3,
-                views_per_step=5, cap=2_600_000):
+                views_per_step=5, cap=2_600_000, init_noise=0.01, steps_after_reset=None, gt_scale=None):
     """BASELINE.json configs[4]: a synthetic 150-timestep sequence; first-frame optimisation with the reference's
     densify schedule (external.py:211-314: events at i = 500, 600, ..., 5000, opacity reset at 3000) growing the
     cloud from 150 k Gaussians, camera-sharded over the ranks with ONE exchange per step (gsb200.first_frame:
@@ -581,8 +581,9 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     torch.cuda.reset_peak_memory_stats(dev)
     t_begin = time.perf_counter()
     # ---- the sequence: ground-truth Gaussians that move rigidly (+ a little noise); images are their renders ------
-    gt = scene.make_gaussians(P_gt, seed=11)
+    gt = scene.make_gaussians(P_gt, seed=11, scale_override=gt_scale)
     gt["opacity_logits"] = gt["opacity_logits"].abs() + 0.5
+    steps_after_reset = steps_after_reset or 2 * steps_per_event
     cams = scene.make_cameras(n_cams, W, H, seed=11)
     mine = gd.shard_cameras(n_cams, rank, world)
     sc = scene.stack_cameras([cams[i] for i in mine], dev)
@@ -610,7 +611,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     # ---- initial cloud: a noisy subsample of the ground truth, initialised like densify.py:22-57 --------------------
     sel = torch.from_numpy(rng.choice(P_gt, size=P0, replace=False))
     init = scene.make_gaussians(P0, seed=12)   # only for the log_scales rule (3-NN distances); means replaced below
-    means0 = gt["means"][sel] + torch.from_numpy(rng.normal(0, 0.01, size=(P0, 3)).astype(np.float32))
+    means0 = gt["means"][sel] + torch.from_numpy(rng.normal(0, init_noise, size=(P0, 3)).astype(np.float32))
     from scipy.spatial import cKDTree
     d, _ = cKDTree(means0.numpy()).query(means0.numpy(), k=4, workers=-1)
     ls = np.log(np.sqrt(np.clip((d[:, 1:] ** 2).mean(-1), 1e-7, None)))[:, None].astype(np.float32)
@@ -625,8 +626,9 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
 
     # ---- phase 1: first-frame optimisation through every densify event of the schedule -------------------------
     idx = []
-    for e in range(500, 5001, 100):
-        idx += [e - steps_per_event + 1 + j for j in range(steps_per_event)]
+    for e in range(500, 5001, 100):   # after the opacity reset at 3000 the opacities need steps to come back before the
+        n_e = steps_per_event if e <= 3000 else steps_after_reset   # final prune at 5000 (threshold 0.25): twice as many there
+        idx += [e - n_e + 1 + j for j in range(n_e)]
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
     # the schedule has no cap of its own: the run stops densifying once the cloud has outgrown `cap`
@@ -638,7 +640,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     phase1_s = time.perf_counter() - t0
     P1 = params["means"].shape[0]
     events = len(counts) - 1
-    steps1 = events * steps_per_event if stop["at"] is not None else len(idx)
+    steps1 = sum(1 for i in idx if stop["at"] is None or i <= stop["at"])
     # a clean timing of the optimiser step at the final size (graph replays, no events in between)
     eng = first_frame.FirstFrameEngine(params, opt, len(mine), W, H, dev)
     eng.set_views(sc, images, masks)
@@ -725,7 +727,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     return {
         "what": f"synthetic {T_total}-timestep sequence, {n_cams} cameras {W}x{H}: first-frame optimisation from {P0} Gaussians "
                 f"through the densify schedule of external.py:211-314 ({steps_per_event} optimiser steps before each of the "
-                f"events at i = 500..5000; the reference runs 100), then {timesteps} train.py-shaped timesteps x "
+                f"events at i = 500..3000, {steps_after_reset} after the opacity reset; the reference runs 100), then {timesteps} train.py-shaped timesteps x "
                 f"{steps_per_timestep} steps ({views_per_step} sampled views, DeformationNetwork 256 x 4, rigidity K = 20) "
                 f"(BASELINE.json configs[4])",
         "n_gpus": world, "gaussians_start": P0, "gaussians_end": P1, "densify_events": events,
