@@ -251,9 +251,11 @@ def run_ours(args):
     del st_probe
     arena = raster.RasterArena(dev).reserve(P, n_my, args.width, args.height, capacity=int(1.25 * R_probe) + 4096)
 
-    # few cameras per GPU (N > 1): render them as concurrent groups so that one group's long tiles overlap another's
-    # bulk (gsb200.step.CameraGroups); GSB_BENCH_GROUPS overrides (1 = one batch)
-    n_groups = int(os.environ.get("GSB_BENCH_GROUPS", "0")) or (min(n_my, 4) if n_my <= 8 else 1)
+    # GSB_BENCH_GROUPS=k: render the rank's cameras as k concurrent groups (gsb200.step.CameraGroups)
+    # measured at 3 and 4 cameras per GPU: SLOWER than one batch (1.14-1.35 vs 0.95-1.02 ms): each group pays the
+    # launch-bound per-batch kernels (depth sort, scan, set-up) again, which costs more than the overlapped tails save;
+    # one batch is the default
+    n_groups = int(os.environ.get("GSB_BENCH_GROUPS", "0")) or 1
     cg = step_mod.CameraGroups(sc, dev_targets, n_groups, P, dev).reserve(act, bg) if n_groups > 1 else None
 
     def one_step():
