@@ -210,19 +210,24 @@ def run_ours(args):
     # whole 27-camera step once, untimed -- its forward state gives the per-camera costs (what a trainer takes from the
     # previous timestep's renders; rank 0's numbers are broadcast so all ranks agree) and its flat record is the N = 1
     # answer that the exchanged record is checked against below.
+    raw_keys = ["means", "colors", "rotation_quaternions", "opacity_logits", "log_scales"]
+    host_raw = {k: g_raw[k].contiguous().pin_memory() for k in raw_keys}
+    dev_raw = {k: torch.empty_like(v, device=dev) for k, v in host_raw.items()}
+    for k in raw_keys:
+        dev_raw[k].copy_(host_raw[k])
+    act = {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}   # the activated tables every leg below uses
     cam_costs = None
     want_flat = None
     if world > 1:
         all_sc = scene.stack_cameras(cams, dev)
-        a0 = {k: v.to(dev).contiguous() for k, v in scene.activate(g_raw).items()}
         all_targets = render_targets(tgt_raw, all_sc, args.cams, bg, dev)
         want_flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev)
-        _, _, _, st0 = step_mod.timestep_step(a0, all_sc, all_targets, bg, None, flat=want_flat)
+        _, _, _, st0 = step_mod.timestep_step(act, all_sc, all_targets, bg, None, flat=want_flat)
         if os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
             ct = torch.tensor(gd.camera_costs(st0), dtype=torch.float64, device=dev)
             dist.broadcast(ct, 0)
             cam_costs = [float(x) for x in ct.cpu()]
-        del st0, a0, all_sc, all_targets
+        del st0, all_sc, all_targets
     my_cam_ids = gd.shard_cameras(args.cams, rank, world, cam_costs)
     my_cams = [cams[i] for i in my_cam_ids]
     n_my = len(my_cams)
@@ -231,15 +236,9 @@ def run_ours(args):
     targets = render_targets(tgt_raw, sc, n_my, bg, dev)
 
     # host (pinned) copies for the end-to-end leg
-    raw_keys = ["means", "colors", "rotation_quaternions", "opacity_logits", "log_scales"]
-    host_raw = {k: g_raw[k].contiguous().pin_memory() for k in raw_keys}
     host_targets = targets.cpu().pin_memory()
-    dev_raw = {k: torch.empty_like(v, device=dev) for k, v in host_raw.items()}
     dev_targets = torch.empty_like(targets)
-    for k in raw_keys:
-        dev_raw[k].copy_(host_raw[k])
     dev_targets.copy_(host_targets)
-    act = {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}
 
     stats = step_mod.DensifyStats(P, dev)
     # the step record ([P, 20]: gradients + this step's statistic increments + largest radius) lives in peer-mapped
