@@ -19,11 +19,12 @@
 // staging copy: the producer (preprocess_bwd_kernel<FLAT>) writes straight into the mapped block.  Flag words carry a
 // per-block epoch that the kernel itself advances, so launches can be replayed from a CUDA graph.
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace gsb {
 
-constexpr int COMM_MAX_BLOCKS = 256;   // flag slots per block of the exchange
+constexpr int COMM_MAX_BLOCKS = 512;   // flag slots per block of the exchange
 constexpr int COMM_SLOT_WORDS = 64;    // ready[16] | done[16] | epoch | error | pad
 constexpr int COMM_THREADS = 512;
 constexpr unsigned long long COMM_TIMEOUT_NS = 10ull * 1000 * 1000 * 1000;
@@ -75,7 +76,7 @@ __device__ __forceinline__ float4 comm_combine(float4 a, float4 b, int max_comp)
 
 // WORLD > 0: compile-time rank count (loads fully unrolled, all in flight); WORLD == 0: run-time count (<= 16)
 template <int WORLD>
-__global__ void __launch_bounds__(COMM_THREADS)
+__global__ void __launch_bounds__(COMM_THREADS, (WORLD >= 8 || WORLD == 0) ? 1 : 2)
 allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off, long long n4, int row4, int max_word,
                       int max_comp) {
   const int world = WORLD > 0 ? WORLD : world_rt;
@@ -102,25 +103,46 @@ allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off,
     long long i = lo + (long long)b * COMM_THREADS + tid;
     int phase = (int)(((i - max_word) % row4 + row4) % row4);   // 0: word i holds the MAX component
     const int step = (int)(stride % row4);
-    for (; i < hi; i += stride) {
-      const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
-      float4 acc;
-      if (WORLD > 0) {
-        float4 v[WORLD > 0 ? WORLD : 1];
+    if (WORLD > 0) {
+      // two words per thread and iteration: 2 x WORLD independent 16-byte peer loads in flight before the first add
+      for (; i < hi; i += 2 * stride) {
+        const long long i2 = i + stride;
+        const bool two = i2 < hi;
+        int phase2 = phase + step;
+        if (phase2 >= row4) phase2 -= row4;
+        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
+        const int mc2 = (max_comp >= 0 && i2 >= max_word && phase2 == 0) ? max_comp : -1;
+        float4 v[WORLD > 0 ? WORLD : 1], w[WORLD > 0 ? WORLD : 1];
 #pragma unroll
         for (int q = 0; q < WORLD; q++) v[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i);
-        acc = v[0];
+        if (two) {
+#pragma unroll
+          for (int q = 0; q < WORLD; q++) w[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i2);
+        }
+        float4 acc = v[0];
 #pragma unroll
         for (int q = 1; q < WORLD; q++) acc = comm_combine(acc, v[q], mc);
-      } else {
-        acc = ld_peer(reinterpret_cast<const float4*>(peers.p[0]) + i);
-        for (int q = 1; q < world; q++) acc = comm_combine(acc, ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i), mc);
-      }
 #pragma unroll
-      for (int q = 0; q < (WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS); q++)
-        if (q < world) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
-      phase += step;
-      if (phase >= row4) phase -= row4;
+        for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
+        if (two) {
+          float4 acc2 = w[0];
+#pragma unroll
+          for (int q = 1; q < WORLD; q++) acc2 = comm_combine(acc2, w[q], mc2);
+#pragma unroll
+          for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(peers.p[q])[i2] = acc2;
+        }
+        phase = phase2 + step;
+        if (phase >= row4) phase -= row4;
+      }
+    } else {
+      for (; i < hi; i += stride) {
+        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
+        float4 acc = ld_peer(reinterpret_cast<const float4*>(peers.p[0]) + i);
+        for (int q = 1; q < world; q++) acc = comm_combine(acc, ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i), mc);
+        for (int q = 0; q < world; q++) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
+        phase += step;
+        if (phase >= row4) phase -= row4;
+      }
     }
   }
   __syncthreads();
@@ -148,7 +170,9 @@ int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payloa
   GSB_CUDA_CHECK(cudaGetDevice(&dev));
   GSB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const long long per_rank = (n_float4 + world - 1) / world;
-  int grid = (int)std::min<long long>(std::min(sms, COMM_MAX_BLOCKS), (per_rank + COMM_THREADS - 1) / COMM_THREADS);
+  static const int per_sm = [] { const char* e = getenv("GSB_COMM_BLOCKS_PER_SM"); return e ? std::max(1, atoi(e)) : 0; }();
+  const int bps = per_sm ? per_sm : (world == 2 || world == 4 ? 2 : 1);   // what the launch bounds of the instance allow
+  int grid = (int)std::min<long long>(std::min(bps * sms, COMM_MAX_BLOCKS), (per_rank + 2 * COMM_THREADS - 1) / (2 * COMM_THREADS));
   if (grid < 1) grid = 1;
 #define GSB_AR_CASE(W)                                                                                             \
   case W:                                                                                                          \
