@@ -268,7 +268,7 @@ static int forward_impl(const gsb_raster_args* a, FwdBuffers& fb, float* out_col
   int rc;
   if (fb.async) {
     // per-camera scalars computed on the device from the caller's table: nothing host-resident enters the stream
-    if ((rc = launch_cam_params(a->n_cams, a->width, a->height, fb.tanfov_dev, cams_dev, st))) return rc;
+    if ((rc = launch_cam_params(a->n_cams, a->width, a->height, fb.tanfov_dev, a->entries, cams_dev, st))) return rc;
   } else {
     // per-camera scalars: focal = dim / (2 tanfov) (cr/rasterizer_impl.cu:222-223)
     if ((rc = stage_reserve(64 + sizeof(CamParams) * (size_t)a->n_cams))) return rc;
@@ -279,8 +279,11 @@ static int forward_impl(const gsb_raster_args* a, FwdBuffers& fb, float* out_col
       cams_host[i].tanfovy = a->tanfovy_host[i];
       cams_host[i].focal_y = (float)a->height / (2.0f * a->tanfovy_host[i]);
       cams_host[i].focal_x = (float)a->width / (2.0f * a->tanfovx_host[i]);
+      cams_host[i].row0 = 0; cams_host[i].row1 = ctx->tiles_y; cams_host[i].split_slot = -1; cams_host[i].count_vis = 1;
     }
     GSB_CUDA_CHECK(cudaMemcpyAsync(cams_dev, cams_host, sizeof(CamParams) * (size_t)a->n_cams, cudaMemcpyHostToDevice, st));
+    if (a->entries)   // tile-band sharding: the entry fields come from the caller's device table
+      if ((rc = launch_cam_params(a->n_cams, a->width, a->height, nullptr, a->entries, cams_dev, st))) return rc;
   }
   GSB_CUDA_CHECK(cudaMemsetAsync(err_dev, 0, 16, st));
 
@@ -326,7 +329,7 @@ static int forward_impl(const gsb_raster_args* a, FwdBuffers& fb, float* out_col
   carve_binning(bin, ctx->capacity, ctx->tile_bits, a->n_cams, ctx, &bx);
 
   prof_mark(PF_D2H, st);
-  if ((rc = launch_duplicate_with_keys(*ctx, st))) return rc;
+  if ((rc = launch_duplicate_with_keys(*ctx, cams_dev, st))) return rc;
   prof_mark(PF_DUPKEYS, st);
   const TileSortPlan plan = tile_sort_plan(ctx->tile_bits);
   const uint32_t* tile_hist = nullptr;
@@ -445,12 +448,13 @@ size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams) {
 }
 
 int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix, void* scratch,
-                             float* flat, int32_t mode, float* dL_dmean2D_out, void* stream) {
+                             float* flat, int32_t flat_stride, int32_t mode, float* dL_dmean2D_out, void* stream) {
   if (!a || !ctx) return GSB_EINVAL;
   if (a->P == 0) return GSB_OK;
   const int part = mode & ~0xFF;
   mode &= 0xFF;
   if (!scratch || !flat || mode < 0 || mode > 2 || a->color_cam_stride != 0) return GSB_EINVAL;
+  if (flat_stride < GSB_FLAT_WIDTH || (flat_stride & 3)) return GSB_EINVAL;
   if (part != 0 && part != GSB_FLAT_BLEND_ONLY && part != GSB_FLAT_FINISH_ONLY) return GSB_EINVAL;
   if (!dL_dpix && part != GSB_FLAT_FINISH_ONLY) return GSB_EINVAL;
   if (a->P != ctx->P || a->n_cams != ctx->n_cams || a->width != ctx->width || a->height != ctx->height)
@@ -475,16 +479,18 @@ int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx
   GeomExtras gx;
   GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
   if ((rc = launch_preprocess_bwd(*a, gx.cams, *ctx, m1, m2, nullptr, nullptr, nullptr, nullptr, st, flat, mode, dop, dcol,
-                                  dL_dmean2D_out)))
+                                  dL_dmean2D_out, flat_stride)))
     return rc;
   prof_mark(PF_PREPROCESS_BWD, st);
   return GSB_OK;
 }
 
-int gsb_flat_apply_stats(int32_t P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
-                         void* stream) {
+int gsb_flat_apply_stats(int32_t P, const float* flat, int32_t flat_stride, float* grad_accum, float* vis_count,
+                         float* max_2d_radii, void* stream) {
   if (P < 0 || (P > 0 && (!flat || !grad_accum || !vis_count))) return GSB_EINVAL;
-  return launch_flat_apply_stats(P, flat, grad_accum, vis_count, max_2d_radii, reinterpret_cast<cudaStream_t>(stream));
+  if (flat_stride < GSB_FLAT_WIDTH || (flat_stride & 3)) return GSB_EINVAL;
+  return launch_flat_apply_stats(P, flat, flat_stride, grad_accum, vis_count, max_2d_radii,
+                                 reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t gsb_comm_bytes(size_t payload_bytes) { return comm_bytes(payload_bytes); }

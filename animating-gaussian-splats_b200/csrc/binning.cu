@@ -172,7 +172,8 @@ __global__ void __launch_bounds__(256)
 duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_t* __restrict__ gauss_order,
                            const float2* __restrict__ means2D, const int32_t* __restrict__ radii,
                            const uint32_t* __restrict__ offsets, uint16_t* __restrict__ tile_keys,
-                           uint32_t* __restrict__ vals, const uint32_t* __restrict__ n_emit) {
+                           uint32_t* __restrict__ vals, const uint32_t* __restrict__ n_emit,
+                           const CamParams* __restrict__ cams) {
   const long long slot = (long long)blockIdx.x * 256 + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
   uint32_t end = 0, start = 0, x0 = 0, y0 = 0, w = 1, gidx = 0;
@@ -189,6 +190,9 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
       const float2 xy = means2D[o];
       uint32_t x1, y1;
       tile_rect_dup(xy.x, xy.y, rad, gx, gy, x0, y0, x1, y1);
+      const uint32_t r0 = (uint32_t)cams[cam].row0, r1 = (uint32_t)cams[cam].row1;   // tile-band sharding
+      y0 = min(max(y0, r0), r1);
+      y1 = min(max(y1, r0), r1);
       w = x1 - x0;
       start = end - w * (y1 - y0);
       if (w == 0) w = 1;
@@ -243,12 +247,12 @@ duplicate_with_keys_kernel(long long total, int P, int gx, int gy, const uint32_
   }
 }
 
-int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st) {
+int launch_duplicate_with_keys(const gsb_raster_ctx& c, const CamParams* cams_dev, cudaStream_t st) {
   const long long total = (long long)c.n_cams * c.P;
   if (total <= 0 || c.capacity <= 0) return GSB_OK;
   duplicate_with_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
       total, c.P, c.tiles_x, c.tiles_y, c.gauss_order, reinterpret_cast<const float2*>(c.means2D), c.radii,
-      c.point_offsets, c.tile_keys_unsorted, c.point_list_unsorted, c.seg_start + c.n_cams);
+      c.point_offsets, c.tile_keys_unsorted, c.point_list_unsorted, c.seg_start + c.n_cams, cams_dev);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

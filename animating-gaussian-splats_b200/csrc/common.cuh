@@ -47,13 +47,17 @@ void set_last_error(const char* what, cudaError_t e);
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Host launchers implemented across the .cu files (all asynchronous on `st`).
-struct CamParams {  // per-camera scalars that live in a small device table
+struct CamParams {  // per-entry scalars that live in a small device table
   float tanfovx, tanfovy, focal_x, focal_y;
+  int row0, row1;          // tile rows the entry renders (tile-band sharding); whole camera: 0, tiles_y
+  int split_slot;          // >= 0: the camera's rows are shared with another rank (gsb_raster_args.entries)
+  int count_vis;           // this entry counts the camera in the visibility / radius statistics
 };
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                       int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st);
-int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, CamParams* cams_dev, cudaStream_t st);
+int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, const int32_t* entries, CamParams* cams_dev,
+                      cudaStream_t st);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // flat != nullptr: the exchange form (gsb_raster_backward_flat): rows of GSB_FLAT_WIDTH floats instead of the
 // separate tables; dL_dopacity / dL_dcolor are then the blend's camera-summed tables (inputs), flat_mode 0 | 1
@@ -61,9 +65,9 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat = nullptr, int flat_mode = 0,
                           const float* dL_dopacity = nullptr, const float* dL_dcolor = nullptr,
-                          float* dL_dmean2D_out = nullptr);
-int launch_flat_apply_stats(int P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
-                            cudaStream_t st);
+                          float* dL_dmean2D_out = nullptr, int flat_stride = GSB_FLAT_WIDTH);
+int launch_flat_apply_stats(int P, const float* flat, int flat_stride, float* grad_accum, float* vis_count,
+                            float* max_2d_radii, cudaStream_t st);
 int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payload_bytes, int64_t n_float4, int row_float4,
                           int max_word, int max_comp, cudaStream_t st);
 size_t comm_bytes(size_t payload_bytes);
@@ -71,7 +75,7 @@ size_t comm_bytes(size_t payload_bytes);
 size_t scan_scratch_bytes(int64_t n);
 int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void* scratch, cudaStream_t st,
                               const uint32_t* perm = nullptr, int perm_block = 0);
-int launch_duplicate_with_keys(const gsb_raster_ctx& c, cudaStream_t st);
+int launch_duplicate_with_keys(const gsb_raster_ctx& c, const CamParams* cams_dev, cudaStream_t st);
 size_t sort_temp_bytes(int64_t n);
 int launch_sort_pairs(int64_t n, const uint64_t* kin, uint64_t* kout, const uint32_t* vin, uint32_t* vout,
                       int end_bit, void* temp, cudaStream_t st);

@@ -129,7 +129,7 @@ struct FlatAdamDev {
 __global__ void adam_tick_kernel(long long* step) { *step += 1; }
 
 __global__ void __launch_bounds__(256)
-adam_flat_kernel(int P, FlatAdamDev a, const float* __restrict__ flat, const long long* __restrict__ step,
+adam_flat_kernel(int P, FlatAdamDev a, const float* __restrict__ flat, int flat_stride, const long long* __restrict__ step,
                  double beta1, double beta2, float w1, float fbeta2, float w2, float eps) {
   __shared__ float s_step_size[6], s_bc2_sqrt;
   if (threadIdx.x == 0) {
@@ -141,7 +141,7 @@ adam_flat_kernel(int P, FlatAdamDev a, const float* __restrict__ flat, const lon
   __syncthreads();
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= P) return;
-  const float4* row = reinterpret_cast<const float4*>(flat) + (size_t)i * (GSB_FLAT_WIDTH / 4);
+  const float4* row = reinterpret_cast<const float4*>(flat) + (size_t)i * (flat_stride / 4);
   const float4 r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2), r3 = __ldg(row + 3), r4 = __ldg(row + 4);
   const float bc2s = s_bc2_sqrt;
   auto upd = [&](int t, size_t o, float g) {
@@ -184,9 +184,9 @@ using namespace gsb;
 
 extern "C" {
 
-int gsb_adam_flat(const gsb_flat_adam_args* a, const float* flat, int64_t* step_dev, double beta1, double beta2, double eps,
-                  void* stream) {
-  if (!a || a->P < 0) return GSB_EINVAL;
+int gsb_adam_flat(const gsb_flat_adam_args* a, const float* flat, int32_t flat_stride, int64_t* step_dev, double beta1,
+                  double beta2, double eps, void* stream) {
+  if (!a || a->P < 0 || flat_stride < GSB_FLAT_WIDTH || (flat_stride & 3)) return GSB_EINVAL;
   if (a->P == 0) return GSB_OK;
   if (!flat || !step_dev || ((uintptr_t)flat & 15u)) return GSB_EINVAL;
   FlatAdamDev d;
@@ -198,7 +198,7 @@ int gsb_adam_flat(const gsb_flat_adam_args* a, const float* flat, int64_t* step_
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_dev));
   GSB_LAUNCH_CHECK();
-  adam_flat_kernel<<<(a->P + 255) / 256, 256, 0, st>>>(a->P, d, flat, reinterpret_cast<const long long*>(step_dev), beta1,
+  adam_flat_kernel<<<(a->P + 255) / 256, 256, 0, st>>>(a->P, d, flat, flat_stride, reinterpret_cast<const long long*>(step_dev), beta1,
                                                         beta2, (float)(1.0 - beta1), (float)beta2, (float)(1.0 - beta2),
                                                         (float)eps);
   GSB_LAUNCH_CHECK();

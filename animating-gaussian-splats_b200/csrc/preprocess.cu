@@ -212,8 +212,13 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
 
     uint32_t x0, y0, x1, y1;
     tile_rect(pix_x, pix_y, rad, gx, gy, x0, y0, x1, y1);
-    const uint32_t area = (x1 - x0) * (y1 - y0);
+    uint32_t area = (x1 - x0) * (y1 - y0);
     if (area == 0) break;
+    // tile-band sharding: the Gaussian stays visible (its state is the whole camera's) but instances are only
+    // emitted for the tile rows this entry renders
+    y0 = min(max(y0, (uint32_t)cp.row0), (uint32_t)cp.row1);
+    y1 = min(max(y1, (uint32_t)cp.row0), (uint32_t)cp.row1);
+    area = (x1 - x0) * (y1 - y0);
 
     depths[o] = tz;
     means2D[o] = make_float2(pix_x, pix_y);
@@ -299,7 +304,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       const float* __restrict__ dL_dconic, float* __restrict__ dL_dmean3D,
                       float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot,
                       float* __restrict__ flat, int flat_mode, const float* __restrict__ dL_dopacity,
-                      const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out) {
+                      const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out, int flat_stride) {
   extern __shared__ float s_mats[];  // [n_cams][32]: view then proj
   for (int i = threadIdx.x; i < n_cams * 32; i += blockDim.x) {
     const int cam = i >> 5, k = i & 31;
@@ -316,6 +321,9 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
   float gc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   bool any = false;
   float st_norm = 0.f, st_cnt = 0.f, st_rad = 0.f;   // FLAT: statistic increments of this batch
+  float4* const frow = FLAT ? reinterpret_cast<float4*>(flat) + (size_t)idx * (flat_stride / 4) : nullptr;
+  if (FLAT && flat_mode == 0)   // split-camera slots: zero unless one of this batch's entries owns the slot
+    for (int k = GSB_FLAT_WIDTH / 4; k < flat_stride / 4; k++) frow[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   // the 3D covariance does not depend on the camera: one row per Gaussian (cov_cam_stride is 0)
   float cov3D[6];
   {
@@ -345,9 +353,18 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float g2x = -(0.5f * W) * (con.x * rs1 + con.y * rs2);
     const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
     if (FLAT) {
-      st_norm += sqrtf(g2x * g2x + g2y * g2y);   // torch.norm of the first two components, one term per camera
-      st_cnt += 1.0f;
-      st_rad = fmaxf(st_rad, (float)rad);
+      if (cp.split_slot >= 0) {
+        // rows of this camera are rendered elsewhere too: the norm belongs to the SUMMED gradient (after the exchange)
+        float* slot = flat + (size_t)idx * flat_stride + GSB_FLAT_WIDTH + 2 * cp.split_slot;
+        if (flat_mode == 0) { slot[0] = g2x; slot[1] = g2y; }
+        else if (flat_mode == 2) { slot[0] += g2x; slot[1] += g2y; }
+      } else {
+        st_norm += sqrtf(g2x * g2x + g2y * g2y);   // torch.norm of the first two components, one term per camera
+      }
+      if (cp.count_vis) {
+        st_cnt += 1.0f;
+        st_rad = fmaxf(st_rad, (float)rad);
+      }
       if (dL_dmean2D_out) { dL_dmean2D_out[3 * o] = g2x; dL_dmean2D_out[3 * o + 1] = g2y; dL_dmean2D_out[3 * o + 2] = 0.f; }
     } else {
       dL_dmean2D[3 * o] = g2x;
@@ -464,7 +481,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
 #undef D
   }
   if (FLAT) {
-    float4* row = reinterpret_cast<float4*>(flat) + (size_t)idx * (GSB_FLAT_WIDTH / 4);
+    float4* row = frow;
     const float dop = dL_dopacity[idx];
     const float c0 = dL_dcolor[3 * (size_t)idx], c1 = dL_dcolor[3 * (size_t)idx + 1], c2 = dL_dcolor[3 * (size_t)idx + 2];
     if (flat_mode == 0) {
@@ -502,13 +519,18 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
 
 // DensificationVariables += the statistic columns of a (reduced) flat buffer
 __global__ void __launch_bounds__(256)
-flat_apply_stats_kernel(int P, const float* __restrict__ flat, float* __restrict__ grad_accum,
+flat_apply_stats_kernel(int P, const float* __restrict__ flat, int flat_stride, float* __restrict__ grad_accum,
                         float* __restrict__ vis_count, float* __restrict__ max_2d_radii) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= P) return;
-  const float* row = flat + (size_t)i * GSB_FLAT_WIDTH;
-  const float2 nc = *reinterpret_cast<const float2*>(row + GSB_FLAT_COL_GRADNORM);
+  const float* row = flat + (size_t)i * flat_stride;
+  float2 nc = *reinterpret_cast<const float2*>(row + GSB_FLAT_COL_GRADNORM);
   const float mr = row[GSB_FLAT_COL_MAXRADIUS];
+  // split cameras (tile-band sharding): the norm of the camera's summed screen-space gradient
+  for (int k = GSB_FLAT_WIDTH; k + 1 < flat_stride; k += 2) {
+    const float2 g = *reinterpret_cast<const float2*>(row + k);
+    nc.x += sqrtf(g.x * g.x + g.y * g.y);
+  }
   if (nc.y > 0.f) {
     grad_accum[i] += nc.x;
     vis_count[i] += nc.y;
@@ -516,29 +538,42 @@ flat_apply_stats_kernel(int P, const float* __restrict__ flat, float* __restrict
   if (max_2d_radii) max_2d_radii[i] = fmaxf(max_2d_radii[i], mr);
 }
 
-int launch_flat_apply_stats(int P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
-                            cudaStream_t st) {
+int launch_flat_apply_stats(int P, const float* flat, int flat_stride, float* grad_accum, float* vis_count,
+                            float* max_2d_radii, cudaStream_t st) {
   if (P <= 0) return GSB_OK;
-  flat_apply_stats_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, flat, grad_accum, vis_count, max_2d_radii);
+  flat_apply_stats_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, flat, flat_stride, grad_accum, vis_count, max_2d_radii);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
 
 // per-camera scalars on the device (asynchronous forward): focal = dim / (2 tanfov), the same two FP32 operations
 // the host performs on the blocking path (cr/rasterizer_impl.cu:222-223), so the bits agree
-__global__ void cam_params_kernel(int n_cams, int W, int H, const float* __restrict__ tanfov, CamParams* __restrict__ out) {
+// tanfov == nullptr: the host already wrote the four scalars (blocking path); only the entry fields are filled in
+__global__ void cam_params_kernel(int n_cams, int W, int H, const float* __restrict__ tanfov,
+                                  const int32_t* __restrict__ entries, CamParams* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_cams) return;
-  CamParams c;
-  c.tanfovx = tanfov[2 * i];
-  c.tanfovy = tanfov[2 * i + 1];
-  c.focal_y = __fdiv_rn((float)H, __fmul_rn(2.0f, c.tanfovy));
-  c.focal_x = __fdiv_rn((float)W, __fmul_rn(2.0f, c.tanfovx));
+  CamParams c = out[i];
+  if (tanfov) {
+    c.tanfovx = tanfov[2 * i];
+    c.tanfovy = tanfov[2 * i + 1];
+    c.focal_y = __fdiv_rn((float)H, __fmul_rn(2.0f, c.tanfovy));
+    c.focal_x = __fdiv_rn((float)W, __fmul_rn(2.0f, c.tanfovx));
+  }
+  const int gy = (H + GSB_TILE - 1) / GSB_TILE;
+  c.row0 = 0; c.row1 = gy; c.split_slot = -1; c.count_vis = 1;
+  if (entries) {
+    c.row0 = min(max(entries[4 * i], 0), gy);
+    c.row1 = min(max(entries[4 * i + 1], c.row0), gy);
+    c.split_slot = entries[4 * i + 2];
+    c.count_vis = entries[4 * i + 3] != 0;
+  }
   out[i] = c;
 }
 
-int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, CamParams* cams_dev, cudaStream_t st) {
-  cam_params_kernel<<<(n_cams + 127) / 128, 128, 0, st>>>(n_cams, W, H, tanfov_dev, cams_dev);
+int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, const int32_t* entries, CamParams* cams_dev,
+                      cudaStream_t st) {
+  cam_params_kernel<<<(n_cams + 127) / 128, 128, 0, st>>>(n_cams, W, H, tanfov_dev, entries, cams_dev);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -546,7 +581,7 @@ int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, CamPara
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat, int flat_mode,
-                          const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out) {
+                          const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out, int flat_stride) {
   if (a.P <= 0) return GSB_OK;
   const size_t smem = (size_t)a.n_cams * 32 * sizeof(float);
   if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
@@ -556,13 +591,13 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, c.cov3D, (size_t)0, reinterpret_cast<const float4*>(c.conic_opacity),
         dL_dmean2D, dL_dconic, nullptr, nullptr, nullptr, nullptr, flat, flat_mode, dL_dopacity, dL_dcolor,
-        dL_dmean2D_out);
+        dL_dmean2D_out, flat_stride);
   } else {
     preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, smem, st>>>(
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
         reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
-        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr);
+        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr, GSB_FLAT_WIDTH);
   }
   GSB_LAUNCH_CHECK();
   return GSB_OK;

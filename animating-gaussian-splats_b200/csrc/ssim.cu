@@ -42,8 +42,9 @@ static SsimWindow make_window() {
 // maps backward).  A warp owns halo rows warp, warp + 8, ...; a lane the columns lane and lane + 32, so there
 // is no index arithmetic per element and all global loads of the block are in flight before the first store.
 // The two pad columns of each row are zeroed (they are loaded by the 16-byte row loads, never used).
+// Rows outside [ylo, yhi) read as zero (the image border, or the edge of a band's derivative maps).
 template <int N>
-__device__ __forceinline__ void load_halos(const float* const (&src)[N], int H, int W, int x0, int y0,
+__device__ __forceinline__ void load_halos(const float* const (&src)[N], int ylo, int yhi, int W, int x0, int y0,
                                            float (*const (&dst)[N])[SS_PX], unsigned tid) {
   const int lane = tid & 31, warp = tid >> 5;
   const int xa = x0 - SS_R + lane, xb = xa + 32;
@@ -55,7 +56,7 @@ __device__ __forceinline__ void load_halos(const float* const (&src)[N], int H, 
   for (int i = 0; i < ROWS; i++) {
     const int r = warp + 8 * i;
     const int y = y0 + r - SS_R;
-    const bool rok = r < SS_HH && y >= 0 && y < H;
+    const bool rok = r < SS_HH && y >= ylo && y < yhi;
     const size_t ro = (size_t)(rok ? y : 0) * W;
 #pragma unroll
     for (int n = 0; n < N; n++) {
@@ -92,7 +93,7 @@ __device__ __forceinline__ void load16(const float* row, float (&v)[16]) {
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ target, SsimWindow win,
                 double* __restrict__ accum /* [n][2] */, float* __restrict__ maps /* [3][planes][H][W] or null */,
-                size_t plane_count) {
+                size_t plane_count, const int32_t* __restrict__ rows /* [n][4] or null: bands */) {
   __shared__ __align__(16) float s_x[SS_HH][SS_PX];
   __shared__ __align__(16) float s_y[SS_HH][SS_PX];
   __shared__ __align__(16) float s_h[5][SS_HH][SS_PH];
@@ -101,10 +102,13 @@ ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __rest
   const size_t plane = blockIdx.z;  // image * 3 + channel
   const size_t HW = (size_t)H * W;
   const int x0 = blockIdx.x * SS_TW, y0 = blockIdx.y * SS_TH;
+  int ly0 = 0, ly1 = H;   // pixel rows that enter the loss
+  if (rows) { ly0 = max(rows[4 * (plane / 3)], 0); ly1 = min(rows[4 * (plane / 3) + 1], H); }
+  if (y0 >= ly1 || y0 + SS_TH <= ly0) return;   // block-uniform
   {
     const float* const src[2] = {img + plane * HW, target + plane * HW};
     float (*const dst[2])[SS_PX] = {s_x, s_y};
-    load_halos<2>(src, H, W, x0, y0, dst, tid);
+    load_halos<2>(src, 0, H, W, x0, y0, dst, tid);
   }
   __syncthreads();
   for (int item = tid; item < SS_ROW_ITEMS; item += SS_THREADS) {
@@ -159,7 +163,7 @@ ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __rest
 #pragma unroll
   for (int o = 0; o < 4; o++) {
     const int y = y0 + ty0 + o;
-    if (x < W && y < H) {
+    if (x < W && y >= ly0 && y < ly1) {
       const float mu1 = f[0][o], mu2 = f[1][o], e11 = f[2][o], e22 = f[3][o], e12 = f[4][o];
       const float c1 = 0.0001f, c2 = 0.0009f;  // 0.01^2, 0.03^2 (external.py:96-97)
       const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
@@ -197,30 +201,39 @@ ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __rest
   }
 }
 
-__global__ void ssim_finalize_kernel(int n, double inv_count, float w_l1, float w_ssim,
-                                     const double* __restrict__ accum, float* __restrict__ loss_out) {
+__global__ void ssim_finalize_kernel(int n, int H, double inv_count, float w_l1, float w_ssim,
+                                     const double* __restrict__ accum, const int32_t* __restrict__ rows,
+                                     float* __restrict__ loss_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double l1 = accum[2 * i] * inv_count, ss = accum[2 * i + 1] * inv_count;
+  double frac = 1.0;   // a band's share of the constant in (1 - ssim), so that the bands of an image add up
+  if (rows) frac = (double)max(min(rows[4 * i + 1], H) - max(rows[4 * i], 0), 0) / (double)H;
   loss_out[3 * i] = (float)l1;
   loss_out[3 * i + 1] = (float)ss;
-  loss_out[3 * i + 2] = (float)((double)w_l1 * l1 + (double)w_ssim * (1.0 - ss));
+  loss_out[3 * i + 2] = (float)((double)w_l1 * l1 + (double)w_ssim * (frac - ss));
 }
 
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ target, SsimWindow win,
                 const float* __restrict__ maps, size_t plane_count, float k_l1, float k_ssim,
-                float* __restrict__ dL_dimg) {
+                float* __restrict__ dL_dimg, const int32_t* __restrict__ rows) {
   __shared__ __align__(16) float s_m[3][SS_HH][SS_PX];
   __shared__ __align__(16) float s_h[3][SS_HH][SS_PH];
   const unsigned tid = threadIdx.x;
   const size_t plane = blockIdx.z;
   const size_t HW = (size_t)H * W;
   const int x0 = blockIdx.x * SS_TW, y0 = blockIdx.y * SS_TH;
+  int ly0 = 0, ly1 = H, wy0 = 0, wy1 = H;   // loss rows (the maps exist there), rows of dL/dimg to write
+  if (rows) {
+    const int32_t* r = rows + 4 * (plane / 3);
+    ly0 = max(r[0], 0); ly1 = min(r[1], H); wy0 = max(r[2], 0); wy1 = min(r[3], H);
+  }
+  if (y0 >= wy1 || y0 + SS_TH <= wy0) return;   // block-uniform
   {
     const float* const src[3] = {maps + plane * HW, maps + (plane_count + plane) * HW, maps + (2 * plane_count + plane) * HW};
     float (*const dst[3])[SS_PX] = {s_m[0], s_m[1], s_m[2]};
-    load_halos<3>(src, H, W, x0, y0, dst, tid);
+    load_halos<3>(src, ly0, ly1, W, x0, y0, dst, tid);
   }
   __syncthreads();
   for (int item = tid; item < SS_ROW_ITEMS; item += SS_THREADS) {
@@ -260,11 +273,12 @@ ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __rest
 #pragma unroll
   for (int o = 0; o < 4; o++) {
     const int y = y0 + ty0 + o;
-    if (x >= W || y >= H) continue;
+    if (x >= W || y < wy0 || y >= wy1) continue;
     const size_t off = plane * HW + (size_t)y * W + x;
     const float xv = __ldg(img + off), yv = __ldg(target + off);
     const float d = xv - yv;
-    const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);  // torch l1_loss backward: sign(0) = 0
+    float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);  // torch l1_loss backward: sign(0) = 0
+    if (y < ly0 || y >= ly1) sgn = 0.f;                       // outside the band's loss rows
     const float g = b[0][o] + 2.f * xv * b[1][o] + yv * b[2][o];
     dL_dimg[off] = k_l1 * sgn - k_ssim * g;
   }
@@ -275,24 +289,25 @@ size_t ssim_scratch_bytes(int n, int H, int W) {
 }
 
 int launch_ssim_l1(int n, int H, int W, const float* img, const float* target, float w_l1, float w_ssim,
-                   float grad_scale, float* loss_out, float* dL_dimg, void* scratch, cudaStream_t st) {
+                   float grad_scale, float* loss_out, float* dL_dimg, void* scratch, cudaStream_t st,
+                   const int32_t* rows = nullptr) {
   static const SsimWindow win = make_window();
   double* accum = reinterpret_cast<double*>(scratch);
   float* maps = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + align_up((size_t)n * 2 * sizeof(double), 256));
   GSB_CUDA_CHECK(cudaMemsetAsync(accum, 0, (size_t)n * 2 * sizeof(double), st));
   dim3 grid((W + SS_TW - 1) / SS_TW, (H + SS_TH - 1) / SS_TH, n * 3), block(SS_THREADS);
   const size_t planes = (size_t)n * 3;
-  ssim_fwd_kernel<<<grid, block, 0, st>>>(H, W, img, target, win, accum, dL_dimg ? maps : nullptr, planes);
+  ssim_fwd_kernel<<<grid, block, 0, st>>>(H, W, img, target, win, accum, dL_dimg ? maps : nullptr, planes, rows);
   GSB_LAUNCH_CHECK();
   const double inv_count = 1.0 / ((double)3 * H * W);
   if (loss_out) {
-    ssim_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, inv_count, w_l1, w_ssim, accum, loss_out);
+    ssim_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, H, inv_count, w_l1, w_ssim, accum, rows, loss_out);
     GSB_LAUNCH_CHECK();
   }
   if (dL_dimg) {
     ssim_bwd_kernel<<<grid, block, 0, st>>>(H, W, img, target, win, maps, planes,
                                             (float)(grad_scale * w_l1 * inv_count),
-                                            (float)(grad_scale * w_ssim * inv_count), dL_dimg);
+                                            (float)(grad_scale * w_ssim * inv_count), dL_dimg, rows);
     GSB_LAUNCH_CHECK();
   }
   return GSB_OK;
@@ -309,5 +324,12 @@ int gsb_ssim_l1(int32_t n, int32_t height, int32_t width, const float* img, cons
   if (n <= 0 || height <= 0 || width <= 0 || !img || !target || !scratch) return GSB_EINVAL;
   return gsb::launch_ssim_l1(n, height, width, img, target, w_l1, w_ssim, grad_scale, loss_out, dL_dimg, scratch,
                              reinterpret_cast<cudaStream_t>(stream));
+}
+int gsb_ssim_l1_rows(int32_t n, int32_t height, int32_t width, const float* img, const float* target, const int32_t* rows,
+                     float w_l1, float w_ssim, float grad_scale, float* loss_out, float* dL_dimg, void* scratch,
+                     void* stream) {
+  if (n <= 0 || height <= 0 || width <= 0 || !img || !target || !scratch) return GSB_EINVAL;
+  return gsb::launch_ssim_l1(n, height, width, img, target, w_l1, w_ssim, grad_scale, loss_out, dL_dimg, scratch,
+                             reinterpret_cast<cudaStream_t>(stream), rows);
 }
 }

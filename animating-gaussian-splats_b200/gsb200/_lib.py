@@ -27,7 +27,7 @@ class RasterArgs(C.Structure):
         ("tanfovx_host", C.POINTER(C.c_float)), ("tanfovy_host", C.POINTER(C.c_float)),
         ("background", C.c_void_p), ("means3D", C.c_void_p), ("colors", C.c_void_p), ("opacities", C.c_void_p),
         ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
-        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("entries", C.c_void_p),
     ]
 
 
@@ -75,8 +75,10 @@ SYMBOLS = {
     "gsb_raster_count_pairs": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p]),
     "gsb_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_raster_backward_flat": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p, C.c_void_p,
-                                           C.c_int32, C.c_void_p, C.c_void_p]),
-    "gsb_flat_apply_stats": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
+                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "gsb_flat_apply_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 4),
+    "gsb_ssim_l1_rows": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
+                                   C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsb_comm_bytes": (C.c_size_t, [C.c_size_t]),
     "gsb_comm_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
     "gsb_comm_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
@@ -106,7 +108,8 @@ SYMBOLS = {
     "gsb_activate": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
     "gsb_activate_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 10),
     "gsb_adam_step": (C.c_int, [C.c_int32, C.POINTER(AdamGroup), C.c_double, C.c_double, C.c_double, C.c_void_p]),
-    "gsb_adam_flat": (C.c_int, [C.POINTER(FlatAdamArgs), C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "gsb_adam_flat": (C.c_int, [C.POINTER(FlatAdamArgs), C.c_void_p, C.c_int32, C.c_void_p, C.c_double, C.c_double, C.c_double,
+                                C.c_void_p]),
     "gsb_rigidity_loss": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_void_p,
                                     C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64] +
                           [C.c_void_p] * 4),

@@ -11,7 +11,7 @@ import torch
 from . import _lib as L
 
 
-def _run(img, target, w_l1, w_ssim, want_grad, arena=None, tag=""):
+def _run(img, target, w_l1, w_ssim, want_grad, arena=None, tag="", rows=None):
     L.require_cuda(img, "img")
     squeeze = img.ndim == 3
     x = (img[None] if squeeze else img).contiguous().float()
@@ -29,8 +29,14 @@ def _run(img, target, w_l1, w_ssim, want_grad, arena=None, tag=""):
         out = torch.empty((n, 3), dtype=torch.float32, device=x.device)
         grad = torch.empty_like(x) if want_grad else None
     with L.device_guard(x.device):
-        rc = lib.gsb_ssim_l1(n, H, W, L.ptr(x), L.ptr(y), float(w_l1), float(w_ssim), 1.0, L.ptr(out), L.ptr(grad),
-                             L.ptr(scratch), L.stream_ptr())
+        if rows is not None:
+            if rows.dtype != torch.int32 or tuple(rows.shape) != (n, 4) or not rows.is_cuda or not rows.is_contiguous():
+                raise RuntimeError("rows must be a contiguous int32 CUDA tensor [n, 4]")
+            rc = lib.gsb_ssim_l1_rows(n, H, W, L.ptr(x), L.ptr(y), L.ptr(rows), float(w_l1), float(w_ssim), 1.0, L.ptr(out),
+                                      L.ptr(grad), L.ptr(scratch), L.stream_ptr())
+        else:
+            rc = lib.gsb_ssim_l1(n, H, W, L.ptr(x), L.ptr(y), float(w_l1), float(w_ssim), 1.0, L.ptr(out), L.ptr(grad),
+                                 L.ptr(scratch), L.stream_ptr())
     L.check(rc, "gsb_ssim_l1")
     return out, grad, squeeze
 
@@ -79,9 +85,10 @@ def calc_ssim(img1, img2, window_size=11, size_average=True):
     return r[0] if img1.ndim == 3 else r.mean()
 
 
-def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None, tag=""):
+def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None, tag="", rows=None):
     """Non-autograd fast path used by the training step: one call, returns (stats [n,3], dL/dimg or None).
     arena (gsb200.raster.RasterArena): outputs and scratch live in the arena instead of fresh allocations (`tag`
-    names the loss numbers of a second loss in the same step; dL/dimg and the scratch are consumed before it runs)."""
-    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena, tag)
+    names the loss numbers of a second loss in the same step; dL/dimg and the scratch are consumed before it runs).
+    rows (int32 [n, 4] = loss_y0, loss_y1, write_y0, write_y1): image bands of tile-band sharding (gsb_ssim_l1_rows)."""
+    out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena, tag, rows)
     return out, (g[0] if (squeeze and g is not None) else g)

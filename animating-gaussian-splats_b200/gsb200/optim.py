@@ -184,8 +184,8 @@ class FlatAdam:
 
     def step(self, flat):
         with L.device_guard(self.device):
-            rc = L.lib().gsb_adam_flat(C.byref(self.args), L.ptr(flat), L.ptr(self.step_dev), self.betas[0], self.betas[1],
-                                       self.eps, L.stream_ptr())
+            rc = L.lib().gsb_adam_flat(C.byref(self.args), L.ptr(flat), int(flat.shape[1]), L.ptr(self.step_dev), self.betas[0],
+                                       self.betas[1], self.eps, L.stream_ptr())
         L.check(rc, "gsb_adam_flat")
 
     def sync_state(self):

@@ -210,13 +210,15 @@ def _as_list(x, n):
 
 def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, scale_modifier, viewmatrix,
             projmatrix, tanfovx, tanfovy, image_height, image_width, prefiltered=False, n_cams=1,
-            colors_per_camera=False, reuse_geometry=False, arena=None, tanfov_dev=None):
+            colors_per_camera=False, reuse_geometry=False, arena=None, tanfov_dev=None, entries=None):
     """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim.
     reuse_geometry: allow this call to take (and to leave behind) pre-blend state, see "Geometry reuse" above; the
     drop-in autograd node passes True, the batched step does not (every step there has new parameters).
     arena (RasterArena, reserved by the caller): the asynchronous form -- no host synchronisation, no allocation,
     CUDA-graph capturable; outputs live in the arena; tanfov_dev = tanfov_table(...) (built here if None, which
-    costs a host -> device copy and is therefore not capturable)."""
+    costs a host -> device copy and is therefore not capturable).
+    entries (int32 CUDA tensor [n_cams, 4] = tile_row0, tile_row1, split_slot, count_visibility): tile-band sharding --
+    every batch entry renders only those tile rows of its camera (include/gsb200.h: gsb_raster_args.entries)."""
     global _geom_cache, geom_cache_hits
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # DGR/rasterize_points.cu:56-58
@@ -249,6 +251,11 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
     a.background, a.means3D, a.colors, a.opacities = L.ptr(bgc), L.ptr(m3), L.ptr(col), L.ptr(opa)
     a.scales, a.rotations, a.cov3D_precomp = L.ptr(sca), L.ptr(rot), L.ptr(cov)
     a.viewmatrix, a.projmatrix = L.ptr(vm), L.ptr(pm)
+    if entries is not None:
+        if entries.dtype != torch.int32 or tuple(entries.shape) != (n_cams, 4) or not entries.is_cuda or not entries.is_contiguous():
+            raise RuntimeError("entries must be a contiguous int32 CUDA tensor [n_cams, 4]")
+        st.keep.append(entries)
+        a.entries = L.ptr(entries)
     st.args = a
     st.ctx = L.RasterCtx()
 
@@ -389,8 +396,9 @@ def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, par
     P, n = a.P, a.n_cams
     if P == 0:
         return flat
-    if flat.dtype != torch.float32 or tuple(flat.shape) != (P, L.FLAT_WIDTH) or not flat.is_contiguous():
-        raise RuntimeError(f"flat must be a contiguous float32 [P, {L.FLAT_WIDTH}] tensor")
+    if (flat.dtype != torch.float32 or flat.ndim != 2 or flat.shape[0] != P or flat.shape[1] < L.FLAT_WIDTH or flat.shape[1] % 4
+            or not flat.is_contiguous()):
+        raise RuntimeError(f"flat must be a contiguous float32 [P, {L.FLAT_WIDTH} + 4 k] tensor")
     L.require_cuda(flat, "flat")
     lib = L.lib()
     if scratch is None:
@@ -401,7 +409,7 @@ def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, par
         if dpix.dtype != torch.float32:
             dpix = dpix.float()
     with L.device_guard(flat.device):
-        rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat),
+        rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat), int(flat.shape[1]),
                                           int(mode) | _FLAT_PART[part], L.ptr(means2D_out), L.stream_ptr())
     L.check(rc, "gsb_raster_backward_flat")
     return flat

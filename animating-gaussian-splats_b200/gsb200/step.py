@@ -48,7 +48,7 @@ class DensifyStats:
         ranks' cameras): accum += col 14, count += col 15, max_2d_radii = max(., col 16).  One launch."""
         P = flat.shape[0]
         with L.device_guard(flat.device):
-            rc = L.lib().gsb_flat_apply_stats(P, L.ptr(flat), L.ptr(self.mean_2d_gradients_accumulated),
+            rc = L.lib().gsb_flat_apply_stats(P, L.ptr(flat), int(flat.shape[1]), L.ptr(self.mean_2d_gradients_accumulated),
                                               L.ptr(self.visibility_count), L.ptr(self.max_2d_radii), L.stream_ptr())
         L.check(rc, "gsb_flat_apply_stats")
 
@@ -67,13 +67,12 @@ def timestep_step(act, cams, targets, bg, stats=None, w_l1=0.8, w_ssim=0.2, flat
     color, depth, radii, st = raster.forward(
         act["means3D"], act["colors_precomp"], act["opacities"], act["scales"], act["rotations"], None, bg, 1.0,
         cams["viewmatrix"], cams["projmatrix"], cams["tanfovx"], cams["tanfovy"], cams["image_height"],
-        cams["image_width"], n_cams=n, arena=arena, tanfov_dev=cams.get("tanfov_dev"))
+        cams["image_width"], n_cams=n, arena=arena, tanfov_dev=cams.get("tanfov_dev"), entries=cams.get("entries"))
     if n == 1:
         color, radii = color[None], radii[None]
-    if arena is not None:
-        loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True, arena=arena)
-    else:
-        loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True)
+    # cams["entries"] / cams["rows"]: tile-band sharding (gsb200.dist.shard_bands): the entries render bands of their
+    # cameras, the loss covers the bands' own pixel rows
+    loss_stats, dL = loss_mod.l1_ssim_fused(color, targets, w_l1, w_ssim, grad=True, arena=arena, rows=cams.get("rows"))
     if flat is not None:
         raster.backward_flat(st, dL, flat, mode=flat_mode, scratch=None if arena is None else arena.bwd_scratch)
         return loss_stats, flat, radii, st

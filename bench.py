@@ -563,7 +563,7 @@ def run_ours(args):
 
 
 def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_event=6, timesteps=20, steps_per_timestep=3,
-                views_per_step=5, cap=2_600_000, init_noise=0.01, steps_after_reset=None, gt_scale=None):
+                views_per_step=5, cap=2_600_000, init_noise=0.01, steps_after_reset=None, gt_scale=None, color_noise=0.0):
     """BASELINE.json configs[4]: a synthetic 150-timestep sequence; first-frame optimisation with the reference's
     densify schedule (external.py:211-314: events at i = 500, 600, ..., 5000, opacity reset at 3000) growing the
     cloud from 150 k Gaussians, camera-sharded over the ranks with ONE exchange per step (gsb200.first_frame:
@@ -617,7 +617,10 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     d, _ = cKDTree(means0.numpy()).query(means0.numpy(), k=4, workers=-1)
     ls = np.log(np.sqrt(np.clip((d[:, 1:] ** 2).mean(-1), 1e-7, None)))[:, None].astype(np.float32)
     quat = torch.zeros(P0, 4); quat[:, 0] = 1.0
-    raw = {"means": means0, "colors": gt["colors"][sel].clone(), "segmentation_masks": gt["segmentation_masks"][sel].clone(),
+    col0 = gt["colors"][sel].clone()
+    if color_noise > 0:
+        col0 = (col0 + torch.from_numpy(rng.normal(0, color_noise, size=(P0, 3)).astype(np.float32))).clamp(0, 1)
+    raw = {"means": means0, "colors": col0, "segmentation_masks": gt["segmentation_masks"][sel].clone(),
            "rotation_quaternions": quat, "opacity_logits": torch.zeros(P0, 1), "log_scales": torch.from_numpy(np.tile(ls, (1, 3)))}
     params = {k: torch.nn.Parameter(v.to(dev).contiguous().requires_grad_(True)) for k, v in raw.items()}
     cam_centers = np.stack([np.linalg.inv(c["viewmatrix"][0].numpy().T)[:3, 3] for c in cams])

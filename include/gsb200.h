@@ -54,6 +54,15 @@ typedef struct gsb_raster_args {
   const float* cov3D_precomp;/* [P][6] or NULL */
   const float* viewmatrix;   /* [n_cams][16] */
   const float* projmatrix;   /* [n_cams][16] */
+  /* Tile-band sharding (new; NULL = every entry is a whole camera).  DEVICE int32 [n_cams][4] per batch entry:
+   * (tile_row0, tile_row1, split_slot, count_visibility).  The entry renders only the tile rows [tile_row0, tile_row1) of
+   * its camera: instance lists exist for those tiles only, all other tiles are empty (background).  Per-Gaussian
+   * state (radii, means2D, conics) is the whole camera's, so a Gaussian's gradients are the sums over the rendered
+   * tiles.  split_slot >= 0 marks a camera whose rows are shared with another rank: gsb_raster_backward_flat then
+   * writes the entry's screen-space gradient into the extra columns 20 + 2 slot, 21 + 2 slot of the flat record instead
+   * of adding its norm to col 14 (the norm must be taken of the camera's SUMMED gradient, after the exchange), and
+   * only the entry with count_visibility != 0 counts the camera in cols 15 / 16. */
+  const int32_t* entries;
 } gsb_raster_args;
 
 /* Saved state of one forward call: replaces the (geomBuffer, binningBuffer, imgBuffer, num_rendered)
@@ -173,6 +182,8 @@ int gsb_raster_backward(const gsb_raster_args* args, const gsb_raster_ctx* ctx, 
  * Adding GSB_FLAT_BLEND_ONLY runs only the per-tile blend backward (into scratch), GSB_FLAT_FINISH_ONLY only the
  * per-Gaussian pass from scratch into flat -- the two halves of one call, so that a caller can run the blends of
  * several groups concurrently and order only the short passes that touch flat.
+ * flat_stride: floats per row, a multiple of 4, >= GSB_FLAT_WIDTH; columns from 20 on are the split-camera slots of
+ * tile-band sharding (gsb_raster_args.entries), zero where this batch has nothing to say.
  * scratch: gsb_backward_scratch_bytes(P, n_cams) bytes.  dL_dmean2D_out (optional, [n_cams][P][3]) receives the
  * per-camera screen-space gradients like gsb_raster_backward. */
 #define GSB_FLAT_WIDTH 20
@@ -183,12 +194,14 @@ int gsb_raster_backward(const gsb_raster_args* args, const gsb_raster_ctx* ctx, 
 #define GSB_FLAT_FINISH_ONLY 0x200
 size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams);
 int gsb_raster_backward_flat(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
-                             void* scratch, float* flat, int32_t mode, float* dL_dmean2D_out, void* stream);
+                             void* scratch, float* flat, int32_t flat_stride, int32_t mode, float* dL_dmean2D_out,
+                             void* stream);
 
 /* DensificationVariables update from a (reduced) flat buffer: grad_accum += col 14, vis_count += col 15,
- * max_2d_radii = max(max_2d_radii, col 16) (shared.py:20-26, densify.py:154-162, external.py:113-124). */
-int gsb_flat_apply_stats(int32_t P, const float* flat, float* grad_accum, float* vis_count, float* max_2d_radii,
-                         void* stream);
+ * max_2d_radii = max(max_2d_radii, col 16) (shared.py:20-26, densify.py:154-162, external.py:113-124); every
+ * split-camera slot (cols 20 + 2 j, 21 + 2 j < flat_stride) adds the norm of its summed gradient to grad_accum. */
+int gsb_flat_apply_stats(int32_t P, const float* flat, int32_t flat_stride, float* grad_accum, float* vis_count,
+                         float* max_2d_radii, void* stream);
 
 /* Multi-GPU exchange over NVLink peer memory (new; the reference has no distributed code).  One process per GPU;
  * every rank allocates its exchange block with gsb_comm_alloc, exports it (64-byte CUDA IPC handle), the hosts swap
@@ -220,6 +233,14 @@ size_t gsb_ssim_scratch_bytes(int32_t n, int32_t height, int32_t width);
 int gsb_ssim_l1(int32_t n, int32_t height, int32_t width, const float* img, const float* target,
                 float w_l1, float w_ssim, float grad_scale, float* loss_out, float* dL_dimg,
                 void* scratch, void* stream);
+/* The same for image BANDS (tile-band sharding): rows = DEVICE int32 [n][4] per image (loss_y0, loss_y1, write_y0,
+ * write_y1).  Only the pixel rows [loss_y0, loss_y1) enter the two means (still normalised by the whole image's
+ * 3 H W, so the bands of an image add up to its loss; the third number is w_l1 l1 + w_ssim ((loss_y1 - loss_y0) / H - ssim));
+ * the image must be valid on [loss_y0 - 5, loss_y1 + 5), and dL_dimg is written on [write_y0, write_y1) (zero
+ * beyond loss +- 5) -- the rows of the tiles the band's rasterizer backward reads. */
+int gsb_ssim_l1_rows(int32_t n, int32_t height, int32_t width, const float* img, const float* target, const int32_t* rows,
+                     float w_l1, float w_ssim, float grad_scale, float* loss_out, float* dL_dimg, void* scratch,
+                     void* stream);
 
 /* Densification statistics: update_max_2d_radii_and_visibility_mask (densify.py:154-162) fused with
  * accumulate_mean_2d_gradients (external.py:113-124).  radii [P], grad_means2D [P][3]. */
@@ -295,8 +316,8 @@ typedef struct gsb_flat_adam_args {
   float* param[6]; float* exp_avg[6]; float* exp_avg_sq[6];
   double lr[6];
 } gsb_flat_adam_args;
-int gsb_adam_flat(const gsb_flat_adam_args* args, const float* flat, int64_t* step_dev, double beta1, double beta2,
-                  double eps, void* stream);
+int gsb_adam_flat(const gsb_flat_adam_args* args, const float* flat, int32_t flat_stride, int64_t* step_dev, double beta1,
+                  double beta2, double eps, void* stream);
 
 /* Rigidity loss of the per-timestep step (train.py:317-351 with quat_mult :301-308, weighted_l2_loss_v2 :311-315,
  * build_rotation external.py:27-47): loss = mean_ij sqrt(w_ij |R_i^T (mean_nbr(i,j) - mean_i) - prev_offset_ij|^2
