@@ -69,6 +69,102 @@ def camera_costs(state):
     return [float(x) for x in cost.cpu()]
 
 
+# ------------------------------------------------------------------------------------------------
+# Tile-band sharding (SURVEY.md 8(e) "finer option"): the unit of work is a tile ROW of a camera, so 27 cameras (or
+# train.py's 5) divide evenly over any number of ranks.  Legal because the loss is a plain sum over views and, inside
+# a view, over pixels (train.py:402-418; L1 and the SSIM map are means over pixels).  A rank renders the tile rows of
+# its band plus one halo row on each side (the 11x11 SSIM window reaches 5 pixels across), evaluates the loss on its
+# own pixel rows only, and back-propagates through everything it rendered; the ranks' records add up to the whole
+# camera's.  The one non-additive quantity is the densification statistic -- the NORM of a camera's screen-space
+# gradient (external.py:113-124) -- so a camera whose rows are split travels as its two gradient components in an extra
+# column pair of the flat record and the norm is taken after the exchange (gsb_flat_apply_stats).
+# ------------------------------------------------------------------------------------------------
+def tile_row_costs(state):
+    """Cost of every tile row of every camera of a rendered batch: [n_cams][tiles_y] floats (same model as
+    camera_costs, the per-camera constant spread over the rows)."""
+    c = state.ctx
+    n, H, W, gy = c.n_cams, c.height, c.width, c.tiles_y
+    nc = state._view(c.n_contrib, state.img, torch.int32, (n, H, W)).long().sum(dim=2)          # per pixel row
+    pad = gy * 16 - H
+    if pad:
+        nc = torch.cat([nc, torch.zeros((n, pad), dtype=nc.dtype, device=nc.device)], dim=1)
+    walked = nc.view(n, gy, 16).sum(dim=2).double()
+    seg = state._view(c.seg_start, state.geom, torch.int32, (n + 1,)).long()
+    inst = (seg[1:] - seg[:-1]).double()
+    share = walked / walked.sum(dim=1, keepdim=True).clamp_min(1.0)
+    cost = COST_PER_PAIR_MS * walked + (COST_PER_INSTANCE_MS * inst)[:, None] * share + COST_PER_CAMERA_MS / gy
+    return [[float(x) for x in row] for row in cost.cpu()]
+
+
+def shard_bands(row_costs, world):
+    """Contiguous cost-balanced partition of the (camera, tile row) sequence.  row_costs [n_cams][tiles_y] (every rank
+    must pass the same numbers).  -> (bands, split_slots): bands[rank] = [(camera, row0, row1), ...] with at most two
+    partial cameras per rank; split_slots = {camera: slot} for the cameras whose rows ended up on more than one rank."""
+    n_cams, gy = len(row_costs), len(row_costs[0])
+    flat_cost = [float(c) for row in row_costs for c in row]
+    total = sum(flat_cost)
+    cuts, run, k = [0], 0.0, 1
+    for i, c in enumerate(flat_cost):   # unit i goes to the rank whose share its midpoint falls into
+        mid = run + 0.5 * c
+        while k < world and mid >= k * total / world:
+            cuts.append(i)
+            k += 1
+        run += c
+    while len(cuts) < world:
+        cuts.append(len(flat_cost))
+    cuts.append(len(flat_cost))
+    bands = []
+    for r in range(world):
+        a, b = cuts[r], cuts[r + 1]
+        mine = []
+        cam = a // gy
+        while cam * gy < b:
+            r0, r1 = max(a - cam * gy, 0), min(b - cam * gy, gy)
+            if r1 > r0:
+                mine.append((cam, r0, r1))
+            cam += 1
+        bands.append(mine)
+    owners = {}
+    for r, mine in enumerate(bands):
+        for cam, r0, r1 in mine:
+            owners.setdefault(cam, []).append(r)
+    split = [cam for cam in sorted(owners) if len(owners[cam]) > 1]
+    return bands, {cam: j for j, cam in enumerate(split)}
+
+
+def flat_width(n_split):
+    """Floats per row of the flat record with n_split split-camera column pairs (a multiple of 4)."""
+    return WIDTH + 4 * ((2 * n_split + 3) // 4)
+
+
+def band_tables(mine, split_slots, tiles_y, height, device):
+    """Device tables of one rank's bands: entries [n, 4] for raster.forward (RENDER rows = band +- one halo tile row,
+    split slot, whether this entry counts the camera's visibility: the band that starts at row 0 does) and rows [n, 4]
+    for the loss (loss pixel rows, rows of dL/dimage to write = the rendered rows)."""
+    ent, rows = [], []
+    for cam, r0, r1 in mine:
+        h0, h1 = max(r0 - 1, 0), min(r1 + 1, tiles_y)
+        ent.append([h0, h1, split_slots.get(cam, -1), 1 if r0 == 0 else 0])
+        rows.append([16 * r0, min(16 * r1, height), 16 * h0, min(16 * h1, height)])
+    return (torch.tensor(ent, dtype=torch.int32, device=device).contiguous(),
+            torch.tensor(rows, dtype=torch.int32, device=device).contiguous())
+
+
+def band_batch(cams, targets, mine, split_slots, device):
+    """One rank's batch under tile-band sharding: `cams` = gsb200.scene.stack_cameras / gsb200.io.stack_views tables of ALL
+    cameras, targets [n_cams, 3, H, W] (or None), mine = shard_bands(...)[0][rank].  -> (cams dict for
+    gsb200.step.timestep_step incl. "entries" / "rows" / "tanfov_dev", targets of the batch's cameras)."""
+    from . import raster
+    ix = [cam for cam, _, _ in mine]
+    H, W = cams["image_height"], cams["image_width"]
+    sub = {"viewmatrix": cams["viewmatrix"][ix].contiguous(), "projmatrix": cams["projmatrix"][ix].contiguous(),
+           "tanfovx": [cams["tanfovx"][i] for i in ix], "tanfovy": [cams["tanfovy"][i] for i in ix],
+           "image_width": W, "image_height": H}
+    sub["tanfov_dev"] = raster.tanfov_table(sub["tanfovx"], sub["tanfovy"], len(ix), device)
+    sub["entries"], sub["rows"] = band_tables(mine, split_slots, (H + 15) // 16, H, device)
+    return sub, (targets[ix].contiguous() if targets is not None else None)
+
+
 def pack(flat, grads, stats_delta=None, max_radii=None):
     """Slice-copy form of the flat record for tensors that were NOT produced by gsb_raster_backward_flat (the gloo
     tests, callers holding separate gradient tables): gradients, THIS step's statistic increments (not running
@@ -124,14 +220,17 @@ class Exchange:
 
     world == 1 (or no process group): a plain device buffer, allreduce() does nothing."""
 
-    def __init__(self, P, device, group=None):
+    def __init__(self, P, device, group=None, width=WIDTH):
         self.P, self.device, self.group = int(P), torch.device(device), group
+        self.width = int(width)   # > 20: split-camera column pairs of tile-band sharding (flat_width)
+        if self.width < WIDTH or self.width % 4:
+            raise ValueError("flat width must be 20 + 4 k")
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.mode = os.environ.get("GSB_EXCHANGE", "nvlink") if (self.world > 1 and self.device.type == "cuda") else "local"
         self.block = None
         self.peer_blocks = []
-        self.payload = self.P * WIDTH * 4
+        self.payload = self.P * self.width * 4
         if self.mode == "nvlink":
             lib = L.lib()
             self.nbytes = lib.gsb_comm_bytes(self.payload)
@@ -152,11 +251,11 @@ class Exchange:
                     L.check(lib.gsb_comm_open(h, C.byref(p)), "gsb_comm_open")
                 self.peer_blocks.append(p.value)
                 self.ptrs[r] = p.value
-            self._mem = _DevMem(self.block, self.P * WIDTH)
-            self.flat = torch.as_tensor(self._mem, device=self.device).view(self.P, WIDTH)
+            self._mem = _DevMem(self.block, self.P * self.width)
+            self.flat = torch.as_tensor(self._mem, device=self.device).view(self.P, self.width)
             dist.barrier(group=group)   # every rank has mapped every block before anyone launches
         else:
-            self.flat = torch.zeros((self.P, WIDTH), dtype=torch.float32, device=self.device)
+            self.flat = torch.zeros((self.P, self.width), dtype=torch.float32, device=self.device)
 
     def allreduce(self):
         if self.world == 1:
@@ -164,8 +263,8 @@ class Exchange:
         if self.mode != "nvlink":
             return allreduce(self.flat, self.group)
         with L.device_guard(self.device):
-            rc = L.lib().gsb_allreduce_flat(self.rank, self.world, self.ptrs, self.payload, self.P * (WIDTH // 4), WIDTH // 4,
-                                            MAX_COL // 4, MAX_COL % 4, L.stream_ptr())
+            rc = L.lib().gsb_allreduce_flat(self.rank, self.world, self.ptrs, self.payload, self.P * (self.width // 4),
+                                            self.width // 4, MAX_COL // 4, MAX_COL % 4, L.stream_ptr())
         L.check(rc, "gsb_allreduce_flat")
         return self.flat
 
