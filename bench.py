@@ -168,6 +168,11 @@ def record_parity(got, want):
     largest magnitude -- float atomics are unordered), visibility counts and radii exact."""
     from gsb200 import dist as gd
     g, w = got.double(), want.double()
+    if got.shape[1] > gd.WIDTH:   # tile-band sharding: split cameras carry their summed 2-D gradient, the norm is taken here
+        g = g[:, :gd.WIDTH].clone()
+        for j in range((got.shape[1] - gd.WIDTH) // 2):
+            g[:, 14] += torch.sqrt(got[:, gd.WIDTH + 2 * j].double() ** 2 + got[:, gd.WIDTH + 2 * j + 1].double() ** 2)
+        got = got[:, :gd.WIDTH]
     out = {"ok": True}
     worst = 0.0
     for k, (a, b) in gd.COLS.items():
@@ -218,22 +223,43 @@ def run_ours(args):
     act = {k: v.contiguous() for k, v in scene.activate(dev_raw).items()}   # the activated tables every leg below uses
     cam_costs = None
     want_flat = None
+    bands = split = None
+    full_counts = None
+    use_bands = world > 1 and os.environ.get("GSB_BENCH_BANDS", "1") != "0"
     if world > 1:
         all_sc = scene.stack_cameras(cams, dev)
         all_targets = render_targets(tgt_raw, all_sc, args.cams, bg, dev)
         want_flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev)
         _, _, _, st0 = step_mod.timestep_step(act, all_sc, all_targets, bg, None, flat=want_flat)
-        if os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
+        full_counts = raster.count_pairs(st0).sum(dim=0).tolist() + [st0.num_rendered]
+        if use_bands:
+            # tile-band sharding: the unit is a tile row of a camera, cut where the cumulative cost crosses k / N
+            rc_ = torch.tensor(gd.tile_row_costs(st0), dtype=torch.float64, device=dev)
+            dist.broadcast(rc_, 0)
+            bands, split = gd.shard_bands([[float(x) for x in row] for row in rc_.cpu()], world)
+        elif os.environ.get("GSB_BENCH_ROUND_ROBIN", "0") != "1":
             ct = torch.tensor(gd.camera_costs(st0), dtype=torch.float64, device=dev)
             dist.broadcast(ct, 0)
             cam_costs = [float(x) for x in ct.cpu()]
-        del st0, all_sc, all_targets
-    my_cam_ids = gd.shard_cameras(args.cams, rank, world, cam_costs)
+        del st0
+    if use_bands:
+        mine = bands[rank]
+        my_cam_ids = [c for c, _, _ in mine]
+        sc, targets = gd.band_batch(all_sc, all_targets, mine, split, dev)
+        targets = targets.clone()
+        n_my = len(mine)
+        flat_w = gd.flat_width(len(split))
+    else:
+        my_cam_ids = gd.shard_cameras(args.cams, rank, world, cam_costs)
+        mine = None
+        n_my = len(my_cam_ids)
+        sc = scene.stack_cameras([cams[i] for i in my_cam_ids], dev)
+        sc["tanfov_dev"] = raster.tanfov_table(sc["tanfovx"], sc["tanfovy"], n_my, dev)
+        targets = render_targets(tgt_raw, sc, n_my, bg, dev)
+        flat_w = gd.WIDTH
     my_cams = [cams[i] for i in my_cam_ids]
-    n_my = len(my_cams)
-    sc = scene.stack_cameras(my_cams, dev)
-    sc["tanfov_dev"] = raster.tanfov_table(sc["tanfovx"], sc["tanfovy"], n_my, dev)
-    targets = render_targets(tgt_raw, sc, n_my, bg, dev)
+    if world > 1:
+        del all_sc, all_targets
 
     # host (pinned) copies for the end-to-end leg
     host_targets = targets.cpu().pin_memory()
@@ -243,7 +269,7 @@ def run_ours(args):
     stats = step_mod.DensifyStats(P, dev)
     # the step record ([P, 20]: gradients + this step's statistic increments + largest radius) lives in peer-mapped
     # memory; the backward writes it, ONE kernel reduces it over the ranks in place
-    ex = gd.Exchange(P, dev)
+    ex = gd.Exchange(P, dev, width=flat_w)
     # arena of the host-free forward: capacity from an untimed render of this rank's cameras
     _, _, _, st_probe = step_mod.timestep_step(act, sc, dev_targets, bg, None)
     R_probe = st_probe.num_rendered
@@ -372,7 +398,7 @@ def run_ours(args):
         exchange["nccl_allreduce_sum_same_bytes"] = timed_loop(lambda: dist.all_reduce(flat_n))
         del flat_n
         per_rank = [None] * world
-        dist.all_gather_object(per_rank, {"rank": rank, "cameras": my_cam_ids, "step_without_exchange": own_local,
+        dist.all_gather_object(per_rank, {"rank": rank, "cameras": my_cam_ids, "bands": mine, "step_without_exchange": own_local,
                                           "est_cost": None if cam_costs is None else sum(cam_costs[c] for c in my_cam_ids)})
         exchange["per_rank"] = per_rank
 
@@ -432,6 +458,9 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(cnt)
     walked_all, R_all, blended_all = int(cnt[0].item()), int(cnt[1].item()), int(cnt[2].item())
+    rendered_walked = walked_all   # what the ranks actually walked (bands: the halo rows are rendered twice)
+    if full_counts is not None:    # the metric's pair counts are those of the N = 1 step
+        walked_all, blended_all, R_all = int(full_counts[0]), int(full_counts[1]), int(full_counts[2])
     peak_mem = torch.cuda.max_memory_allocated(dev)
     extras = os.environ.get("GSB_BENCH_EXTRAS", "1") != "0"
 
@@ -516,8 +545,12 @@ def run_ours(args):
         "config": {"workload": f"Panoptic-shaped timestep: {P} gaussians, {args.cams} cameras {args.width}x{args.height}, "
                                "fwd + L1/SSIM + bwd + densify stats (BASELINE.json configs[1])",
                    "cameras_per_rank": n_my, "parallelism": f"camera-sharded dp{world}",
-                   "camera_assignment": ("round-robin" if cam_costs is None else
+                   "camera_assignment": ("tile-band sharding: contiguous cost-balanced partition of the (camera, tile row) sequence, "
+                                         "one halo tile row per band edge, loss on the band's own pixel rows "
+                                         f"({len(split)} split cameras, flat record {flat_w} floats wide)" if use_bands else
+                                         "round-robin" if cam_costs is None else
                                          "cost-balanced (LPT on per-camera walked pairs + instances of an untimed calibration render)"),
+                   "walked_pairs_rendered_incl_halo": rendered_walked,
                    "camera_groups": n_groups,
                    "step_issue": ("one CUDA graph per step (gsb200.step.StepGraph): host-free forward through a reused arena, "
                                   "flat step record, exchange kernel, statistics") if use_graph else "launch by launch from Python",
