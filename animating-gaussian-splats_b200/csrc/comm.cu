@@ -104,34 +104,33 @@ allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off,
     int phase = (int)(((i - max_word) % row4 + row4) % row4);   // 0: word i holds the MAX component
     const int step = (int)(stride % row4);
     if (WORLD > 0) {
-      // two words per thread and iteration: 2 x WORLD independent 16-byte peer loads in flight before the first add
-      for (; i < hi; i += 2 * stride) {
-        const long long i2 = i + stride;
-        const bool two = i2 < hi;
-        int phase2 = phase + step;
-        if (phase2 >= row4) phase2 -= row4;
-        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
-        const int mc2 = (max_comp >= 0 && i2 >= max_word && phase2 == 0) ? max_comp : -1;
-        float4 v[WORLD > 0 ? WORLD : 1], w[WORLD > 0 ? WORLD : 1];
+      // software pipeline: the peer loads of word k + 1 are issued before the reduction and the peer stores of word
+      // k, so the inbound (pull) and outbound (push) directions of the links are busy at the same time (a first
+      // version loaded everything, then stored everything: each direction idle half the time)
+      float4 v[WORLD > 0 ? WORLD : 1];
+      if (i < hi) {
 #pragma unroll
         for (int q = 0; q < WORLD; q++) v[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i);
-        if (two) {
+      }
+      while (i < hi) {
+        const long long nx = i + stride;
+        const bool has = nx < hi;
+        float4 w[WORLD > 0 ? WORLD : 1];
+        if (has) {
 #pragma unroll
-          for (int q = 0; q < WORLD; q++) w[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i2);
+          for (int q = 0; q < WORLD; q++) w[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + nx);
         }
+        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
         float4 acc = v[0];
 #pragma unroll
         for (int q = 1; q < WORLD; q++) acc = comm_combine(acc, v[q], mc);
 #pragma unroll
         for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
-        if (two) {
-          float4 acc2 = w[0];
+        if (!has) break;
 #pragma unroll
-          for (int q = 1; q < WORLD; q++) acc2 = comm_combine(acc2, w[q], mc2);
-#pragma unroll
-          for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(peers.p[q])[i2] = acc2;
-        }
-        phase = phase2 + step;
+        for (int q = 0; q < WORLD; q++) v[q] = w[q];
+        i = nx;
+        phase += step;
         if (phase >= row4) phase -= row4;
       }
     } else {
@@ -172,7 +171,7 @@ int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payloa
   const long long per_rank = (n_float4 + world - 1) / world;
   static const int per_sm = [] { const char* e = getenv("GSB_COMM_BLOCKS_PER_SM"); return e ? std::max(1, atoi(e)) : 0; }();
   const int bps = per_sm ? per_sm : (world == 2 || world == 4 ? 2 : 1);   // what the launch bounds of the instance allow
-  int grid = (int)std::min<long long>(std::min(bps * sms, COMM_MAX_BLOCKS), (per_rank + 2 * COMM_THREADS - 1) / (2 * COMM_THREADS));
+  int grid = (int)std::min<long long>(std::min(bps * sms, COMM_MAX_BLOCKS), (per_rank + 4 * COMM_THREADS - 1) / (4 * COMM_THREADS));   // >= 4 pipelined words per thread
   if (grid < 1) grid = 1;
 #define GSB_AR_CASE(W)                                                                                             \
   case W:                                                                                                          \
