@@ -6,12 +6,12 @@
 // peers have mapped (CUDA IPC, gsb_comm_alloc / gsb_comm_open), and the reduction is a two-shot all-reduce written
 // directly against those mappings:
 //
-//   meet      every block b of every rank tells block b of every peer "my buffer is complete" (st.release.sys on a
-//             flag word in the peer's block) and waits for the same from all of them (ld.acquire.sys);
-//   reduce    rank r owns slice r: it loads that slice from every peer's buffer (P2P loads, all in flight before the
-//             first add), reduces in rank order and stores the result into every peer's buffer (P2P stores) -- the
-//             reduce-scatter and the all-gather of a ring/tree library collapse into one pass, the NVSwitch carries
-//             (world - 1) / world of the buffer in each direction per GPU;
+//   scatter   rank r stores its part of every other rank's slice into that rank's staging rows (P2P stores);
+//   meet      per block, release / acquire on flag words in the blocks themselves (st.release.sys / ld.acquire.sys);
+//   reduce    rank r owns slice r: it sums its own part and the staged rows in rank order (local loads) and stores
+//             the result into every peer's buffer (P2P stores) -- the reduce-scatter and the all-gather of a ring /
+//             tree library collapse into one launch, the NVSwitch carries (world - 1) / world of the buffer in each
+//             direction per GPU and phase, every byte as a posted store;
 //   leave     "my slice is everywhere" to every peer, wait for all of them: when the kernel ends the local buffer
 //             holds the complete result and no peer reads or writes it any more, so the next step may overwrite it.
 //
@@ -29,8 +29,11 @@ constexpr int COMM_SLOT_WORDS = 64;    // ready[16] | done[16] | epoch | error |
 constexpr int COMM_THREADS = 512;
 constexpr unsigned long long COMM_TIMEOUT_NS = 10ull * 1000 * 1000 * 1000;
 
+// block layout: payload | staging (one row of ceil(n / world) words per rank: <= payload + 16 world bytes) | flags
+static size_t comm_stage_bytes(size_t payload_bytes) { return align_up(payload_bytes + 16 * GSB_COMM_MAX_RANKS, 256); }
 size_t comm_bytes(size_t payload_bytes) {
-  return align_up(payload_bytes, 256) + (size_t)COMM_MAX_BLOCKS * COMM_SLOT_WORDS * sizeof(uint32_t);
+  return align_up(payload_bytes, 256) + comm_stage_bytes(payload_bytes) +
+         (size_t)COMM_MAX_BLOCKS * COMM_SLOT_WORDS * sizeof(uint32_t);
 }
 
 struct CommPeers { char* p[GSB_COMM_MAX_RANKS]; };
@@ -74,11 +77,21 @@ __device__ __forceinline__ float4 comm_combine(float4 a, float4 b, int max_comp)
   return r;
 }
 
-// WORLD > 0: compile-time rank count (loads fully unrolled, all in flight); WORLD == 0: run-time count (<= 16)
+// WORLD > 0: compile-time rank count (loops over the peers fully unrolled); WORLD == 0: run-time count (<= 16).
+//
+// Push form.  A first version PULLED slice r from every peer with P2P loads; at 8 GPUs it moved 24 MB in 91 us
+// (~230 GB/s per direction): remote loads pay a round trip each and the links' read tracking limits how many are
+// outstanding.  Here every byte crosses NVLink as a posted STORE:
+//   scatter   rank r copies its part of slice q into peer q's staging area (row r), for every q != r;
+//   meet      release / acquire on the flag words, per block: block b of every rank handles the same words of every
+//             slice, so block b of rank q only needs the blocks b of its peers;
+//   reduce    rank r sums its own part and the world - 1 staged rows of slice r in rank order (local loads, MAX for
+//             the radius component) and stores the result into every peer's buffer;
+//   leave     second release / acquire: when the kernel ends the local buffer is complete and nobody writes it.
 template <int WORLD>
 __global__ void __launch_bounds__(COMM_THREADS, (WORLD >= 8 || WORLD == 0) ? 1 : 2)
-allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off, long long n4, int row4, int max_word,
-                      int max_comp) {
+allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t stage_off, size_t flags_off, long long n4,
+                      long long slice_cap, int row4, int max_word, int max_comp) {
   const int world = WORLD > 0 ? WORLD : world_rt;
   const int b = blockIdx.x, G = gridDim.x;
   const unsigned tid = threadIdx.x;
@@ -88,60 +101,49 @@ allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off,
   if (tid == 0) { s_epoch = my_slot[32] + 1u; s_fail = 0; }
   __syncthreads();
   const uint32_t epoch = s_epoch;
+  const float4* mine = reinterpret_cast<const float4*>(peers.p[rank]);
+  const long long stride = (long long)G * COMM_THREADS;
+  const long long first = (long long)b * COMM_THREADS + tid;
 
-  // meet: my buffer is complete (this kernel follows its producer on the stream); wait for every peer's
+  // scatter: my contribution to every other rank's slice goes into that rank's staging row `rank`
+  for (long long o = first; o < slice_cap; o += stride) {
+#pragma unroll
+    for (int q = 0; q < (WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS); q++) {
+      if (q >= world || q == rank) continue;
+      const long long lo = n4 * q / world, hi = n4 * (q + 1) / world;
+      if (lo + o < hi)
+        (reinterpret_cast<float4*>(peers.p[q] + stage_off) + (size_t)rank * slice_cap)[o] = mine[lo + o];
+    }
+  }
+  __syncthreads();
   if (tid < (unsigned)world) {
     uint32_t* peer_slot = reinterpret_cast<uint32_t*>(peers.p[tid] + flags_off) + (size_t)b * COMM_SLOT_WORDS;
-    st_release_sys(peer_slot + rank, epoch);
+    st_release_sys(peer_slot + rank, epoch);   // release: ordered after this block's stores (bar.sync above)
     if (!comm_wait(my_slot + tid, epoch)) s_fail = 1;
   }
   __syncthreads();
 
   if (!s_fail) {
     const long long lo = n4 * rank / world, hi = n4 * (rank + 1) / world;
-    const long long stride = (long long)G * COMM_THREADS;
-    long long i = lo + (long long)b * COMM_THREADS + tid;
+    const float4* stage = reinterpret_cast<const float4*>(peers.p[rank] + stage_off);
+    long long i = lo + first;
     int phase = (int)(((i - max_word) % row4 + row4) % row4);   // 0: word i holds the MAX component
     const int step = (int)(stride % row4);
-    if (WORLD > 0) {
-      // software pipeline: the peer loads of word k + 1 are issued before the reduction and the peer stores of word
-      // k, so the inbound (pull) and outbound (push) directions of the links are busy at the same time (a first
-      // version loaded everything, then stored everything: each direction idle half the time)
-      float4 v[WORLD > 0 ? WORLD : 1];
-      if (i < hi) {
+    for (; i < hi; i += stride) {
+      const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
+      float4 v[WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS];
 #pragma unroll
-        for (int q = 0; q < WORLD; q++) v[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i);
-      }
-      while (i < hi) {
-        const long long nx = i + stride;
-        const bool has = nx < hi;
-        float4 w[WORLD > 0 ? WORLD : 1];
-        if (has) {
+      for (int q = 0; q < (WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS); q++)
+        if (q < world) v[q] = (q == rank) ? mine[i] : ld_peer(stage + (size_t)q * slice_cap + (i - lo));
+      float4 acc = v[0];
 #pragma unroll
-          for (int q = 0; q < WORLD; q++) w[q] = ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + nx);
-        }
-        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
-        float4 acc = v[0];
+      for (int q = 1; q < (WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS); q++)
+        if (q < world) acc = comm_combine(acc, v[q], mc);
 #pragma unroll
-        for (int q = 1; q < WORLD; q++) acc = comm_combine(acc, v[q], mc);
-#pragma unroll
-        for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
-        if (!has) break;
-#pragma unroll
-        for (int q = 0; q < WORLD; q++) v[q] = w[q];
-        i = nx;
-        phase += step;
-        if (phase >= row4) phase -= row4;
-      }
-    } else {
-      for (; i < hi; i += stride) {
-        const int mc = (max_comp >= 0 && i >= max_word && phase == 0) ? max_comp : -1;
-        float4 acc = ld_peer(reinterpret_cast<const float4*>(peers.p[0]) + i);
-        for (int q = 1; q < world; q++) acc = comm_combine(acc, ld_peer(reinterpret_cast<const float4*>(peers.p[q]) + i), mc);
-        for (int q = 0; q < world; q++) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
-        phase += step;
-        if (phase >= row4) phase -= row4;
-      }
+      for (int q = 0; q < (WORLD > 0 ? WORLD : GSB_COMM_MAX_RANKS); q++)
+        if (q < world) reinterpret_cast<float4*>(peers.p[q])[i] = acc;
+      phase += step;
+      if (phase >= row4) phase -= row4;
     }
   }
   __syncthreads();
@@ -149,7 +151,7 @@ allreduce_flat_kernel(CommPeers peers, int rank, int world_rt, size_t flags_off,
   // leave: my slice is in every peer's buffer; wait until every peer's slice is in mine
   if (tid < (unsigned)world) {
     uint32_t* peer_slot = reinterpret_cast<uint32_t*>(peers.p[tid] + flags_off) + (size_t)b * COMM_SLOT_WORDS;
-    st_release_sys(peer_slot + 16 + rank, epoch);   // release: ordered after this block's stores (bar.sync above)
+    st_release_sys(peer_slot + 16 + rank, epoch);
     if (!comm_wait(my_slot + 16 + tid, epoch)) s_fail = 1;
   }
   __syncthreads();
@@ -164,7 +166,10 @@ int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payloa
   if (world == 1 || n_float4 == 0) return GSB_OK;
   CommPeers cp;
   for (int i = 0; i < GSB_COMM_MAX_RANKS; i++) cp.p[i] = i < world ? reinterpret_cast<char*>(peers[i]) : nullptr;
-  const size_t flags_off = align_up(payload_bytes, 256);
+  const size_t stage_off = align_up(payload_bytes, 256);
+  const size_t flags_off = stage_off + comm_stage_bytes(payload_bytes);
+  const long long slice_cap = (n_float4 + world - 1) / world;
+  if ((size_t)slice_cap * world * 16 > comm_stage_bytes(payload_bytes)) return GSB_EINVAL;
   int dev = 0, sms = 148;
   GSB_CUDA_CHECK(cudaGetDevice(&dev));
   GSB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -175,16 +180,16 @@ int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payloa
   if (grid < 1) grid = 1;
 #define GSB_AR_CASE(W)                                                                                             \
   case W:                                                                                                          \
-    allreduce_flat_kernel<W><<<grid, COMM_THREADS, 0, st>>>(cp, rank, world, flags_off, (long long)n_float4, row_float4, \
-                                                             max_word, max_comp);                                  \
+    allreduce_flat_kernel<W><<<grid, COMM_THREADS, 0, st>>>(cp, rank, world, stage_off, flags_off, (long long)n_float4, \
+                                                             slice_cap, row_float4, max_word, max_comp);           \
     break
   switch (world) {
     GSB_AR_CASE(2);
     GSB_AR_CASE(4);
     GSB_AR_CASE(8);
     default:
-      allreduce_flat_kernel<0><<<grid, COMM_THREADS, 0, st>>>(cp, rank, world, flags_off, (long long)n_float4, row_float4,
-                                                              max_word, max_comp);
+      allreduce_flat_kernel<0><<<grid, COMM_THREADS, 0, st>>>(cp, rank, world, stage_off, flags_off, (long long)n_float4,
+                                                              slice_cap, row_float4, max_word, max_comp);
   }
 #undef GSB_AR_CASE
   GSB_LAUNCH_CHECK();

@@ -206,11 +206,11 @@ int gsb_flat_apply_stats(int32_t P, const float* flat, int32_t flat_stride, floa
 /* Multi-GPU exchange over NVLink peer memory (new; the reference has no distributed code).  One process per GPU;
  * every rank allocates its exchange block with gsb_comm_alloc, exports it (64-byte CUDA IPC handle), the hosts swap
  * handles (any side channel) and open the peers' blocks.  gsb_allreduce_flat then reduces `n_float4` 16-byte words
- * of the block in place across `world` ranks in ONE kernel: rank r pulls slice r from every peer (P2P loads),
- * reduces in rank order -- SUM, except component `max_comp` of every `row_float4`-th word counted from word
- * `max_word`, which takes MAX (col 16 of a flat row) -- and pushes the result into every peer's block (P2P
- * stores); ranks meet through flag words in the blocks themselves (release/acquire at system scope), no host
- * involvement, graph-capturable.  All ranks end with bit-identical contents.  peers_host: HOST array of `world`
+ * of the block in place across `world` ranks in ONE kernel: every rank pushes its part of slice q into rank q's
+ * staging rows (P2P stores), rank r reduces slice r in rank order -- SUM, except component `max_comp` of every
+ * `row_float4`-th word counted from word `max_word`, which takes MAX (col 16 of a flat row) -- and pushes the result
+ * into every peer's block (P2P stores); ranks meet through flag words in the blocks themselves (release/acquire at
+ * system scope), no host involvement, graph-capturable.  All ranks end with bit-identical contents.  peers_host: HOST array of `world`
  * device pointers (own block at index rank); every block is gsb_comm_bytes(payload_bytes) long, payload first. */
 #define GSB_COMM_MAX_RANKS 16
 size_t gsb_comm_bytes(size_t payload_bytes);
