@@ -199,6 +199,7 @@ class HostFeed:
         self.loss_hosts = [torch.empty((host_targets.size(0), 3), dtype=torch.float32).pin_memory() for _ in range(2)]
         self.loss_host = self.loss_hosts[0]
         self.done = [torch.cuda.Event(), torch.cuda.Event()]   # step k's kernels and loss read-back finished
+        self.graphs, self.act_out = [None, None], [None, None]
         self.k = 0
         self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_raw.values()) + \
             host_targets.numel() * host_targets.element_size()
@@ -216,9 +217,11 @@ class HostFeed:
             tgt.copy_(self.host_targets, non_blocking=True)
             self.ready[k % 2].record(self.copy_stream)
 
-    def step(self, cams, bg, stats=None, after=None, wait=True, flat=None, arena=None):
+    def step(self, cams, bg, stats=None, after=None, wait=True, flat=None, arena=None, graph=False):
         """One end-to-end step.  flat / arena: the exchange form and the host-free forward of timestep_step (`after`
-        then receives the flat record in place of the gradient dict).  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
+        then receives the flat record in place of the gradient dict).  graph=True (needs flat and arena): activations
+        + step + `after` are captured once per buffer half and replayed, so the host issues two copies, one graph
+        launch and the loss read-back per step; cams / bg / after must then be the same objects every step.  `after(loss_stats, grads, radii, state)` runs on the compute stream before the
         loss read-back (e.g. the multi-GPU exchange).  Returns the pinned [n,3] loss buffer (l1, ssim, mix) of this
         step.  wait=True blocks until it is filled.  wait=False returns at once -- the way a training loop that only
         logs the loss calls it: the host goes on to issue the next step while this one's backward still runs; the
@@ -227,13 +230,34 @@ class HostFeed:
         k = self.k
         raw, tgt = self.bufs[k % 2]
         cur = torch.cuda.current_stream(self.dev)
+        if graph and (flat is None or arena is None):
+            raise RuntimeError("HostFeed.step(graph=True) needs the flat record and an arena (host-free step)")
+        if graph and self.graphs[k % 2] is None:
+            if self.act_out[k % 2] is None:
+                self.act_out[k % 2] = (torch.empty_like(raw["rotation_quaternions"]), torch.empty_like(raw["opacity_logits"]),
+                                       torch.empty_like(raw["log_scales"]))
+            out_a = self.act_out[k % 2]
+
+            def body():
+                rot, opa, sca = optim.activate_into(raw, out_a)
+                act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
+                r = timestep_step(act, cams, tgt, bg, stats, flat=flat, arena=arena)
+                if after is not None:
+                    after(*r)
+                return r
+
+            cur.wait_event(self.ready[k % 2])   # the half's first copy must have landed before the warm-up runs read it
+            self.graphs[k % 2] = StepGraph(body, device=self.dev)
         cur.wait_event(self.ready[k % 2])
         self._prefetch(k + 1)
-        rot, opa, sca = optim.activate(raw)   # one launch (gsb_activate)
-        act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
-        loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats, flat=flat, arena=arena)
-        if after is not None:
-            after(loss_stats, grads, radii, st)
+        if graph:
+            loss_stats, grads, radii, st = self.graphs[k % 2].replay()
+        else:
+            rot, opa, sca = optim.activate(raw)   # one launch (gsb_activate)
+            act = {"means3D": raw["means"], "colors_precomp": raw["colors"], "rotations": rot, "opacities": opa, "scales": sca}
+            loss_stats, grads, radii, st = timestep_step(act, cams, tgt, bg, stats, flat=flat, arena=arena)
+            if after is not None:
+                after(loss_stats, grads, radii, st)
         out = self.loss_hosts[k % 2]
         out.copy_(loss_stats, non_blocking=True)
         self.done[k % 2].record(cur)

@@ -225,7 +225,11 @@ def run_ours(args):
     want_flat = None
     bands = split = None
     full_counts = None
-    use_bands = world > 1 and os.environ.get("GSB_BENCH_BANDS", "1") != "0"
+    # tile-band sharding is built and parity-checked (GSB_BENCH_BANDS=1) but whole cameras are the default here: at 27
+    # cameras x 300 k Gaussians every extra batch entry costs ~0.06 ms of per-Gaussian work and the split-camera columns
+    # widen the exchanged record (24 -> 43 MB at N = 8), which together outweigh the better balance (1.276 vs 1.265 ms
+    # at N = 8, 2.879 vs 2.889 ms at N = 2); bands are what lets FEWER cameras than ranks use every GPU
+    use_bands = world > 1 and os.environ.get("GSB_BENCH_BANDS", "1" if args.cams < world else "0") != "0"
     if world > 1:
         all_sc = scene.stack_cameras(cams, dev)
         all_targets = render_targets(tgt_raw, all_sc, args.cams, bg, dev)
@@ -417,9 +421,10 @@ def run_ours(args):
     def e2e_step():
         # non-blocking: the loss numbers are copied to pinned host memory every step, the host does not wait for
         # them before issuing the next step (a training loop only logs them); GSB_BENCH_E2E_BLOCKING=1 waits
-        feed.step(sc, bg, None, after, wait=E2E_BLOCKING, flat=ex.flat, arena=arena)
+        feed.step(sc, bg, None, after, wait=E2E_BLOCKING, flat=ex.flat, arena=arena, graph=use_graph)
 
-    e2e_step()
+    for _ in range(3):   # both buffer halves captured (every rank captures at the same steps: the warm-ups run the exchange)
+        e2e_step()
     sync_all()
     sampler.begin()
     e0.record()
