@@ -104,24 +104,34 @@ scan_u32_kernel(long long n, const uint32_t* in, uint32_t* out,
   }
   const uint32_t thread_excl = warp_off + inc - run;
 
-  // decoupled look-back by thread 0 (tiles are few: n / 2048)
-  if (threadIdx.x == 0) {
+  // decoupled look-back by warp 0: 32 predecessors per round trip (a first version walked them one at a time from
+  // thread 0 -- ~17 dependent L2 round trips per tile, which made the kernel latency-bound at 0.17 of HBM speed)
+  if (warp == 0) {
     uint32_t prefix = 0;
     if (tile == 0) {
-      st_relaxed_u64(status, (2ull << 32) | block_total);
+      if (lane == 0) st_relaxed_u64(status, (2ull << 32) | block_total);
     } else {
-      st_relaxed_u64(status + tile, (1ull << 32) | block_total);
-      long long p = (long long)tile - 1;
+      if (lane == 0) st_relaxed_u64(status + tile, (1ull << 32) | block_total);
+      long long p = (long long)tile - 1;   // nearest predecessor not yet accounted for
       while (true) {
-        unsigned long long s = ld_relaxed_u64(status + p);
-        while ((s >> 32) == 0) s = ld_relaxed_u64(status + p);
-        prefix += (uint32_t)s;
-        if ((s >> 32) == 2) break;
-        p--;
+        const long long idx = p - (long long)lane;
+        unsigned long long sv = (2ull << 32);   // in front of tile 0: an inclusive prefix of 0
+        if (idx >= 0) {
+          sv = ld_relaxed_u64(status + idx);
+          while ((sv >> 32) == 0) sv = ld_relaxed_u64(status + idx);
+        }
+        const unsigned incl = __ballot_sync(0xffffffffu, (sv >> 32) == 2);
+        const int first = incl ? __ffs(incl) - 1 : 31;          // lanes 0..first are needed
+        uint32_t v = ((int)lane <= first) ? (uint32_t)sv : 0u;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        prefix += v;
+        if (incl) break;
+        p -= 32;
       }
-      st_relaxed_u64(status + tile, (2ull << 32) | (uint32_t)(prefix + block_total));
+      if (lane == 0) st_relaxed_u64(status + tile, (2ull << 32) | (uint32_t)(prefix + block_total));
     }
-    s_prefix = prefix;
+    if (lane == 0) s_prefix = prefix;
   }
   __syncthreads();
   const uint32_t add = s_prefix + thread_excl;
