@@ -477,10 +477,19 @@ def run_ours(args):
         torch.cuda.empty_cache()
         try:
             c5 = c5_sequence(args, world, rank, dev)
+            torch.cuda.empty_cache()
+            # The reference's schedule grows this synthetic cloud by ~3% per event (150 k -> ~420 k before the final
+            # prune), not to the ~2 M of BASELINE.json configs[4]; the 2 M operating point is measured from a cloud of
+            # that size: optimiser steps, two densify events, three timesteps.
+            big = c5_sequence(args, world, rank, dev, P0=2_000_000, P_gt=2_400_000, gt_scale=0.006, steps_per_event=4,
+                              events=(500, 600), timesteps=3, steps_per_timestep=2)
+            c5["at_2M_gaussians"] = {k: big[k] for k in ("gaussians_start", "gaussians_end", "gaussian_count_over_events",
+                                                          "first_frame", "timesteps", "peak_memory_bytes_per_gpu",
+                                                          "setup_seconds")}
         except Exception as ex_:
             import traceback
             traceback.print_exc(file=sys.stderr)
-            c5 = {"error": repr(ex_)[:300]}
+            c5 = dict(c5 or {}, error=repr(ex_)[:300])
         torch.cuda.empty_cache()
 
     if rank != 0:
@@ -601,7 +610,8 @@ def run_ours(args):
 
 
 def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_event=6, timesteps=20, steps_per_timestep=3,
-                views_per_step=5, cap=2_600_000, init_noise=0.01, steps_after_reset=None, gt_scale=None, color_noise=0.0):
+                views_per_step=5, cap=2_600_000, init_noise=0.01, steps_after_reset=None, gt_scale=None, color_noise=0.0,
+                events=None):
     """BASELINE.json configs[4]: a synthetic 150-timestep sequence; first-frame optimisation with the reference's
     densify schedule (external.py:211-314: events at i = 500, 600, ..., 5000, opacity reset at 3000) growing the
     cloud from 150 k Gaussians, camera-sharded over the ranks with ONE exchange per step (gsb200.first_frame:
@@ -649,7 +659,6 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     masks = (render_gt(0, sc, len(mine), gt_seg) > 0.5).float()
     # ---- initial cloud: a noisy subsample of the ground truth, initialised like densify.py:22-57 --------------------
     sel = torch.from_numpy(rng.choice(P_gt, size=P0, replace=False))
-    init = scene.make_gaussians(P0, seed=12)   # only for the log_scales rule (3-NN distances); means replaced below
     means0 = gt["means"][sel] + torch.from_numpy(rng.normal(0, init_noise, size=(P0, 3)).astype(np.float32))
     from scipy.spatial import cKDTree
     d, _ = cKDTree(means0.numpy()).query(means0.numpy(), k=4, workers=-1)
@@ -668,7 +677,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
 
     # ---- phase 1: first-frame optimisation through every densify event of the schedule -------------------------
     idx = []
-    for e in range(500, 5001, 100):   # after the opacity reset at 3000 the opacities need steps to come back before the
+    for e in (events if events is not None else range(500, 5001, 100)):   # after the opacity reset at 3000 the opacities need steps to come back before the
         n_e = steps_per_event if e <= 3000 else steps_after_reset   # final prune at 5000 (threshold 0.25): twice as many there
         idx += [e - n_e + 1 + j for j in range(n_e)]
     torch.cuda.synchronize(dev)
