@@ -126,20 +126,109 @@ split_rows_kernel(int P, int S, const uint8_t* __restrict__ sel, const int32_t* 
   }
 }
 
-// Packs the step's exchange buffer [P][16] in one pass: means3D(3) colours(3) rotations(4) opacity(1)
-// scales(3) grad-norm accumulator(1) visibility count(1)  (gsb200/dist.py COLS).
+// ------------------------------------------------------------------------------------------------
+// One densify event as one pass over the Gaussians (external.py:211-314).  The reference appends clones, appends
+// split children, compacts away the split parents and compacts again for the prune -- every step a torch.cat /
+// boolean-mask re-allocation of all six tables and both Adam moments.  Every row of the FINAL tables is a function of
+// exactly one source row, and whether it survives can be decided from that source row alone:
+//   original i     survives iff not split and not pruned                       -> [0, K0)
+//   clone of i     survives iff cloned and not pruned (a copy of the row)      -> [K0, K0 + K1)
+//   children of i  survive iff split and not pruned with log_scale - log 1.6   -> [K0 + K1, +K2) and [.., +K2)
+// (order inside each group = source order, which is what cat + stable mask indexing leave).  plan: flags + four
+// 0/1 columns; their inclusive scans are the ranks; apply: thread per source row writes its 0-4 output rows of all
+// 18 tables.  SURVEY.md 8(d): <= 2 x 204 B per surviving Gaussian.
+// ------------------------------------------------------------------------------------------------
+enum { DF_ORIG = 1, DF_CLONE = 2, DF_CHILD = 4, DF_SPLIT = 8 };
+
 __global__ void __launch_bounds__(256)
-pack_flat_kernel(int P, const float* __restrict__ g_means, const float* __restrict__ g_colors,
-                 const float* __restrict__ g_rot, const float* __restrict__ g_opac, const float* __restrict__ g_scales,
-                 const float* __restrict__ accum, const float* __restrict__ count, float4* __restrict__ flat) {
+densify_plan_kernel(int P, const float* __restrict__ grad_accum, const float* __restrict__ vis_count,
+                    const float* __restrict__ opacity_logits, const float* __restrict__ log_scales, float grad_thr,
+                    float clone_max_scale, float prune_opacity, int prune_big, float big_scale,
+                    uint8_t* __restrict__ flags, uint32_t* __restrict__ cols /* [4][P] */) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= P) return;
-  const size_t j = (size_t)i;
-  const float4 q = reinterpret_cast<const float4*>(g_rot)[j];
-  flat[4 * j + 0] = make_float4(g_means[3 * j], g_means[3 * j + 1], g_means[3 * j + 2], g_colors[3 * j]);
-  flat[4 * j + 1] = make_float4(g_colors[3 * j + 1], g_colors[3 * j + 2], q.x, q.y);
-  flat[4 * j + 2] = make_float4(q.z, q.w, g_opac[j], g_scales[3 * j]);
-  flat[4 * j + 3] = make_float4(g_scales[3 * j + 1], g_scales[3 * j + 2], accum ? accum[j] : 0.f, count ? count[j] : 0.f);
+  float avg = grad_accum[i] / vis_count[i];          // external.py:224-225: NaN (0 / 0) -> 0
+  if (avg != avg) avg = 0.f;
+  const float s0 = expf(log_scales[3 * (size_t)i]), s1 = expf(log_scales[3 * (size_t)i + 1]), s2 = expf(log_scales[3 * (size_t)i + 2]);
+  const float max_s = fmaxf(s0, fmaxf(s1, s2));
+  const bool hot = avg >= grad_thr;
+  const bool clone = hot && max_s <= clone_max_scale;   // external.py:232-238
+  const bool split = hot && max_s > clone_max_scale;    // external.py:241-250 (clones carry a padded gradient of 0)
+  const float op = 1.0f / (1.0f + expf(-opacity_logits[i]));
+  const bool low = op < prune_opacity;                  // external.py:290-296
+  const bool prune_row = low || (prune_big && max_s > big_scale);
+  // the children's scales as the reference forms them: exp(log(exp(ls) / 1.6))
+  const float c0 = expf(logf(s0 * (1.0f / 1.6f))), c1 = expf(logf(s1 * (1.0f / 1.6f))), c2 = expf(logf(s2 * (1.0f / 1.6f)));
+  const bool prune_child = low || (prune_big && fmaxf(c0, fmaxf(c1, c2)) > big_scale);
+  const unsigned f = ((!split && !prune_row) ? DF_ORIG : 0) | ((clone && !prune_row) ? DF_CLONE : 0) |
+                     ((split && !prune_child) ? DF_CHILD : 0) | (split ? DF_SPLIT : 0);
+  flags[i] = (uint8_t)f;
+  cols[i] = (f & DF_ORIG) ? 1u : 0u;
+  cols[(size_t)P + i] = (f & DF_CLONE) ? 1u : 0u;
+  cols[2 * (size_t)P + i] = (f & DF_CHILD) ? 1u : 0u;
+  cols[3 * (size_t)P + i] = (f & DF_SPLIT) ? 1u : 0u;
+}
+
+__global__ void densify_totals_kernel(int P, const uint32_t* __restrict__ cols, int32_t* __restrict__ totals) {
+  if (threadIdx.x < 4) totals[threadIdx.x] = (int32_t)cols[(size_t)threadIdx.x * P + P - 1];   // inclusive scans
+}
+
+struct DensifyTables {
+  const float* src[18];   // means, colors, segmentation colours, quaternions, opacity logits, log scales; then their
+  float* dst[18];         // exp_avg (6) and exp_avg_sq (6) in the same order
+};
+__constant__ const int kRowFloats[6] = {3, 3, 3, 4, 1, 3};
+
+__global__ void __launch_bounds__(256)
+densify_apply_kernel(int P, const uint8_t* __restrict__ flags, const uint32_t* __restrict__ cols, int K0, int K1, int K2, int S,
+                     DensifyTables t, const float* __restrict__ samples) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= P) return;
+  const unsigned f = flags[i];
+  if (!(f & (DF_ORIG | DF_CLONE | DF_CHILD))) return;
+  auto copy_row = [&](int table, size_t dst_row, bool zero) {
+    const int w = kRowFloats[table % 6];
+    const float* s = t.src[table] + (size_t)i * w;
+    float* d = t.dst[table] + dst_row * w;
+    for (int k = 0; k < w; k++) d[k] = zero ? 0.f : s[k];
+  };
+  if (f & DF_ORIG) {
+    const size_t r = cols[i] - 1u;
+    for (int tb = 0; tb < 18; tb++) copy_row(tb, r, false);
+  }
+  if (f & DF_CLONE) {   // cat_params_to_optimizer: the row is appended, its Adam moments start at zero
+    const size_t r = (size_t)K0 + cols[(size_t)P + i] - 1u;
+    for (int tb = 0; tb < 18; tb++) copy_row(tb, r, tb >= 6);
+  }
+  if (f & DF_CHILD) {   // external.py:251-271
+    const size_t ra = (size_t)K0 + K1 + cols[2 * (size_t)P + i] - 1u, rb = ra + K2;
+    const size_t sj = cols[3 * (size_t)P + i] - 1u;   // row of the split draw: rank among ALL split rows
+    for (int tb = 0; tb < 18; tb++) {
+      copy_row(tb, ra, tb >= 6);
+      copy_row(tb, rb, tb >= 6);
+    }
+    float4 q = reinterpret_cast<const float4*>(t.src[3])[i];
+    const float norm = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);  // build_rotation, external.py:27-46
+    q.x /= norm; q.y /= norm; q.z /= norm; q.w /= norm;
+    const float rr = q.x, x = q.y, y = q.z, z = q.w;
+    const float R00 = 1.f - 2.f * (y * y + z * z), R01 = 2.f * (x * y - rr * z), R02 = 2.f * (x * z + rr * y);
+    const float R10 = 2.f * (x * y + rr * z), R11 = 1.f - 2.f * (x * x + z * z), R12 = 2.f * (y * z - rr * x);
+    const float R20 = 2.f * (x * z - rr * y), R21 = 2.f * (y * z + rr * x), R22 = 1.f - 2.f * (x * x + y * y);
+    const float mx = t.src[0][3 * (size_t)i], my = t.src[0][3 * (size_t)i + 1], mz = t.src[0][3 * (size_t)i + 2];
+    float ls[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) ls[k] = logf(expf(t.src[5][3 * (size_t)i + k]) * (1.0f / 1.6f));
+#pragma unroll
+    for (int rep = 0; rep < 2; rep++) {
+      const size_t j = (size_t)rep * S + sj, r = rep ? rb : ra;
+      const float sx = samples[3 * j], sy = samples[3 * j + 1], sz = samples[3 * j + 2];
+      t.dst[0][3 * r] = mx + (R00 * sx + R01 * sy + R02 * sz);
+      t.dst[0][3 * r + 1] = my + (R10 * sx + R11 * sy + R12 * sz);
+      t.dst[0][3 * r + 2] = mz + (R20 * sx + R21 * sy + R22 * sz);
+#pragma unroll
+      for (int k = 0; k < 3; k++) t.dst[5][3 * r + k] = ls[k];
+    }
+  }
 }
 
 }  // namespace gsb
@@ -171,15 +260,54 @@ int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii
   return GSB_OK;
 }
 
-int gsb_pack_flat(int32_t P, const float* g_means3D, const float* g_colors, const float* g_rotations,
-                  const float* g_opacities, const float* g_scales, const float* grad_accum, const float* vis_count,
-                  float* flat, void* stream) {
-  if (P < 0) return GSB_EINVAL;
+size_t gsb_densify_plan_scratch_bytes(int32_t P) {
+  // flags u8 [P] | four 0/1 -> rank columns u32 [4][P] | scan scratch
+  const size_t n = (size_t)(P > 0 ? P : 1);
+  return align_up(n, 256) + align_up(16 * n, 256) + scan_scratch_bytes((int64_t)n) + 256;
+}
+
+int gsb_densify_plan(int32_t P, const float* grad_accum, const float* vis_count, const float* opacity_logits,
+                     const float* log_scales, float grad_threshold, float clone_max_scale, float prune_opacity,
+                     int32_t prune_big, float big_scale, void* scratch, int32_t* totals_dev, void* stream) {
+  if (P < 0 || !scratch || !totals_dev) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (P == 0) { GSB_CUDA_CHECK(cudaMemsetAsync(totals_dev, 0, 16, st)); return GSB_OK; }
+  if (!grad_accum || !vis_count || !opacity_logits || !log_scales) return GSB_EINVAL;
+  char* base = reinterpret_cast<char*>(scratch);
+  uint8_t* flags = reinterpret_cast<uint8_t*>(base);
+  uint32_t* cols = reinterpret_cast<uint32_t*>(base + align_up((size_t)P, 256));
+  void* scan_scratch = base + align_up((size_t)P, 256) + align_up(16 * (size_t)P, 256);
+  densify_plan_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, grad_accum, vis_count, opacity_logits, log_scales, grad_threshold,
+                                                       clone_max_scale, prune_opacity, prune_big, big_scale, flags, cols);
+  GSB_LAUNCH_CHECK();
+  for (int k = 0; k < 4; k++) {
+    uint32_t* c = cols + (size_t)k * P;
+    int rc = launch_inclusive_scan_u32(P, c, c, scan_scratch, st);
+    if (rc) return rc;
+  }
+  densify_totals_kernel<<<1, 32, 0, st>>>(P, cols, totals_dev);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_densify_apply(int32_t P, const void* scratch, const int32_t* totals_host, const float* const* src18,
+                      float* const* dst18, const float* samples, void* stream) {
+  if (P < 0 || !scratch || !totals_host || !src18 || !dst18) return GSB_EINVAL;
   if (P == 0) return GSB_OK;
-  if (!g_means3D || !g_colors || !g_rotations || !g_opacities || !g_scales || !flat) return GSB_EINVAL;
-  pack_flat_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      P, g_means3D, g_colors, g_rotations, g_opacities, g_scales, grad_accum, vis_count,
-      reinterpret_cast<float4*>(flat));
+  const int K0 = totals_host[0], K1 = totals_host[1], K2 = totals_host[2], S = totals_host[3];
+  if (K0 < 0 || K1 < 0 || K2 < 0 || S < K2 || (S > 0 && !samples)) return GSB_EINVAL;
+  if (K0 + K1 + 2 * K2 == 0) return GSB_OK;
+  DensifyTables t;
+  for (int k = 0; k < 18; k++) {
+    if (!src18[k] || !dst18[k]) return GSB_EINVAL;
+    t.src[k] = src18[k]; t.dst[k] = dst18[k];
+  }
+  if ((uintptr_t)t.src[3] & 15u) return GSB_EINVAL;
+  const char* base = reinterpret_cast<const char*>(scratch);
+  const uint8_t* flags = reinterpret_cast<const uint8_t*>(base);
+  const uint32_t* cols = reinterpret_cast<const uint32_t*>(base + align_up((size_t)P, 256));
+  densify_apply_kernel<<<(P + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(P, flags, cols, K0, K1, K2, S, t,
+                                                                                         samples);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

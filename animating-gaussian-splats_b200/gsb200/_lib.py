@@ -92,7 +92,11 @@ SYMBOLS = {
                               C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsb_densify_accumulate": (C.c_int, [C.c_int32] + [C.c_void_p] * 7),
     "gsb_densify_accumulate_batch": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 7),
-    "gsb_pack_flat": (C.c_int, [C.c_int32] + [C.c_void_p] * 9),
+    "gsb_densify_plan_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "gsb_densify_plan": (C.c_int, [C.c_int32] + [C.c_void_p] * 4 + [C.c_float, C.c_float, C.c_float, C.c_int32, C.c_float,
+                                   C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsb_densify_apply": (C.c_int, [C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                    C.c_void_p, C.c_void_p]),
     "gsb_densify_accumulate_masked": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
     "gsb_split_rows": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 9),
     "gsb_scan_scratch_bytes": (C.c_size_t, [C.c_int32]),

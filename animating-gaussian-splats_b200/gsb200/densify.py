@@ -4,10 +4,11 @@ Drop-in names: DensificationVariables (shared.py:20-26), update_max_2d_radii_and
 (densify.py:154-162), accumulate_mean_2d_gradients (external.py:113-124), densify_gaussians
 (external.py:211-314, same arguments: parameter dict, DensificationVariables, scene radius, torch Adam
 optimizer, iteration).  The row surgery the reference performs with boolean-mask indexing and torch.cat
-over every parameter and Adam-moment tensor is done here by a mask scan (exclusive rank, one launch
-chain per mask) and order-preserving row gathers through the C ABI; the split transform is one kernel.
-The thresholds are cheap elementwise torch expressions; the only host syncs are the row counts that
-size the new tensors (the reference syncs for the same reason inside its mask indexing).
+over every parameter and Adam-moment tensor -- four re-allocations of 18 tables per event -- is ONE pass here:
+every final row is a function of one source row, so a plan kernel decides per source row which of its up to four
+output rows survive, four scans rank them, and one apply kernel writes all 18 new tables (gsb_densify_plan /
+gsb_densify_apply).  The one host synchronisation per event is the read-back of four row counts that size the new
+tensors (the reference synchronises inside every mask indexing).
 """
 import ctypes as C
 from dataclasses import dataclass
@@ -54,54 +55,50 @@ def accumulate_mean_2d_gradients(densification_variables):
     L.check(rc, "gsb_densify_accumulate_masked")
 
 
-class _Mask:
-    """A row mask with its exclusive rank and count (gsb_mask_scan)."""
-
-    def __init__(self, mask):
-        self.mask = mask.contiguous()
-        P = self.mask.numel()
-        dev = mask.device
-        self.rank = torch.empty(P, dtype=torch.int32, device=dev)
-        cnt = torch.zeros(1, dtype=torch.int32, device=dev)
-        lib = L.lib()
-        scratch = torch.empty(lib.gsb_scan_scratch_bytes(max(P, 1)), dtype=torch.uint8, device=dev)
-        with L.device_guard(dev):
-            rc = lib.gsb_mask_scan(P, L.ptr(self.mask), L.ptr(self.rank), L.ptr(cnt), L.ptr(scratch), _stream())
-        L.check(rc, "gsb_mask_scan")
-        self.count = int(cnt.item())   # sizes the new tensors: the one host sync per mask
-
-    def gather_into(self, src, dst):
-        """dst[rank[i]] = src[i] for selected rows; dst is a [count, row] view."""
-        if self.count == 0:
-            return
-        src = src.contiguous()
-        row = src[0].numel()
-        with L.device_guard(src.device):
-            rc = L.lib().gsb_gather_rows(src.shape[0], L.ptr(self.mask), L.ptr(self.rank), L.ptr(src), L.ptr(dst),
-                                         row, _stream())
-        L.check(rc, "gsb_gather_rows")
-
-
-def _append_selected(t, m, repeat=1):
-    """torch.cat((t, t[mask].repeat(repeat, 1))) without the intermediate tensors."""
-    N = t.shape[0]
-    out = torch.empty((N + repeat * m.count,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
-    out[:N].copy_(t)
-    for r in range(repeat):
-        m.gather_into(t, out[N + r * m.count: N + (r + 1) * m.count])
-    return out
-
-
-def _append_zeros(t, n):
-    out = torch.zeros((t.shape[0] + n,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
-    out[: t.shape[0]].copy_(t)
-    return out
-
-
-def _compact(t, keep):
-    out = torch.empty((keep.count,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
-    keep.gather_into(t, out)
-    return out
+def _fused_event(tables, stats, scene_radius, i, samples):
+    """Clone / split / remove parents / prune as one plan + one apply launch chain over all 18 tables
+    (gsb_densify_plan / gsb_densify_apply); one read-back of four row counts sizes the new tables."""
+    lib = L.lib()
+    p0 = tables["means"][0]
+    dev, P = p0.device, p0.shape[0]
+    src = []
+    for j in range(3):
+        for k in KEYS:
+            t = tables[k][j]
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.float().contiguous()
+                tables[k][j] = t
+            src.append(t)
+    scratch = torch.empty(lib.gsb_densify_plan_scratch_bytes(P), dtype=torch.uint8, device=dev)
+    totals = torch.zeros(4, dtype=torch.int32, device=dev)
+    thr = 0.25 if i == 5000 else 0.005                      # external.py:290-296
+    with L.device_guard(dev):
+        rc = lib.gsb_densify_plan(P, L.ptr(stats["mean_2d_gradients_accumulated"].contiguous()),
+                                  L.ptr(stats["visibility_count"].contiguous()), L.ptr(src[4]), L.ptr(src[5]), 0.0002,
+                                  0.01 * scene_radius, thr, 1 if i >= 3000 else 0, 0.1 * scene_radius, L.ptr(scratch),
+                                  L.ptr(totals), _stream())
+    L.check(rc, "gsb_densify_plan")
+    K0, K1, K2, S = (int(x) for x in totals.cpu())          # the event's one host synchronisation
+    N = K0 + K1 + 2 * K2
+    if S > 0:
+        if samples is None:   # the reference's draw (external.py:258-261): same shapes, same generator consumption
+            flags = scratch[:P]
+            stds = torch.exp(src[5])[(flags & 8) != 0].repeat(2, 1)
+            samples = torch.normal(mean=torch.zeros_like(stds), std=stds)
+        samples = samples.contiguous().float()
+    dst = [torch.empty((N,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t in src]
+    arr_t = C.c_void_p * 18
+    hs = (C.c_int32 * 4)(K0, K1, K2, S)
+    with L.device_guard(dev):
+        rc = lib.gsb_densify_apply(P, L.ptr(scratch), hs, arr_t(*[t.data_ptr() if t.numel() else None for t in src]),
+                                   arr_t(*[t.data_ptr() if t.numel() else None for t in dst]), L.ptr(samples) if S > 0 else None,
+                                   _stream()) if (P > 0 and N > 0) else 0
+    L.check(rc, "gsb_densify_apply")
+    for j in range(3):
+        for n_, k in enumerate(KEYS):
+            tables[k][j] = dst[6 * j + n_]
+    for k in _STATS:
+        stats[k] = torch.zeros(N, dtype=torch.float32, device=dev)
 
 
 def densify_step(tables, stats, visible, means2d_grad, scene_radius, i, samples=None):
@@ -114,60 +111,8 @@ def densify_step(tables, stats, visible, means2d_grad, scene_radius, i, samples=
                                 stats["max_2d_radii"], visible)
     dv.means_2d = type("G", (), {"grad": means2d_grad})()
     accumulate_mean_2d_gradients(dv)
-    dev = visible.device
-    grad_thr = 0.0002
     if i >= 500 and i % 100 == 0:
-        avg = stats["mean_2d_gradients_accumulated"] / stats["visibility_count"]
-        avg = torch.where(avg.isnan(), torch.zeros_like(avg), avg)
-        max_s = torch.exp(tables["log_scales"][0]).max(dim=1).values
-        hot = avg >= grad_thr
-        # clone (external.py:232-238): appended after the existing rows, Adam moments extended with zeros
-        clone = _Mask(hot & (max_s <= 0.01 * scene_radius))
-        N0 = avg.shape[0]
-        # split candidates are evaluated on the N0 + C rows; clones carry padded gradient 0 (external.py:241-250)
-        split_mask = torch.zeros(N0 + clone.count, dtype=torch.bool, device=dev)
-        split_mask[:N0] = hot & (max_s > 0.01 * scene_radius)
-        for k in KEYS:
-            p, m, v = tables[k]
-            tables[k] = [_append_selected(p, clone), _append_zeros(m, clone.count), _append_zeros(v, clone.count)]
-        split = _Mask(split_mask)
-        S = split.count
-        N1 = N0 + clone.count
-        if samples is None:
-            stds = torch.exp(tables["log_scales"][0])[split_mask].repeat(2, 1)
-            samples = torch.normal(mean=torch.zeros_like(stds), std=stds)
-        samples = samples.contiguous().float()
-        new = {}
-        for k in KEYS:
-            new[k] = _append_selected(tables[k][0], split, repeat=2)
-        if S > 0:
-            with L.device_guard(dev):
-                rc = L.lib().gsb_split_rows(N1, S, L.ptr(split.mask), L.ptr(split.rank), L.ptr(tables["means"][0]),
-                                            L.ptr(tables["rotation_quaternions"][0].contiguous()),
-                                            L.ptr(tables["log_scales"][0]), L.ptr(samples),
-                                            L.ptr(new["means"][N1:]), L.ptr(new["log_scales"][N1:]), _stream())
-            L.check(rc, "gsb_split_rows")
-        for k in KEYS:
-            tables[k] = [new[k], _append_zeros(tables[k][1], 2 * S), _append_zeros(tables[k][2], 2 * S)]
-        n_pts = N1 + 2 * S
-        # remove the split parents (external.py:280-288); statistics restart from zero (external.py:273-279)
-        keep = torch.ones(n_pts, dtype=torch.bool, device=dev)
-        keep[:N1] = ~split_mask
-        keep = _Mask(keep)
-        for k in KEYS:
-            tables[k] = [_compact(t, keep) for t in tables[k]]
-        for k in _STATS:
-            stats[k] = torch.zeros(keep.count, dtype=torch.float32, device=dev)
-        # prune (external.py:290-302)
-        thr = 0.25 if i == 5000 else 0.005
-        to_remove = (torch.sigmoid(tables["opacity_logits"][0]) < thr).squeeze(-1)
-        if i >= 3000:
-            to_remove = to_remove | (torch.exp(tables["log_scales"][0]).max(dim=1).values > 0.1 * scene_radius)
-        keep = _Mask(~to_remove)
-        for k in KEYS:
-            tables[k] = [_compact(t, keep) for t in tables[k]]
-        for k in _STATS:
-            stats[k] = torch.zeros(keep.count, dtype=torch.float32, device=dev)
+        _fused_event(tables, stats, scene_radius, i, samples)
     if i > 0 and i % 3000 == 0:  # opacity reset (external.py:306-314): logit(0.01), moments zeroed
         p = tables["opacity_logits"][0]
         v = torch.log((torch.ones_like(p) * 0.01) / (1 - torch.ones_like(p) * 0.01))

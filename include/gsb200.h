@@ -253,13 +253,6 @@ int gsb_densify_accumulate_batch(int32_t P, int32_t n_cams, const int32_t* radii
                                  float* max_2d_radii, float* grad_accum, float* vis_count, uint8_t* visible,
                                  void* stream);
 
-/* Multi-GPU exchange buffer (new; the reference has no distributed code): flat [P][16] =
- * dL_dmeans3D(3) dL_dcolors(3) dL_drotations(4) dL_dopacity(1) dL_dscales(3) grad-norm accumulator(1)
- * visibility count(1) in one pass, ready for ONE allreduce.  grad_accum / vis_count may be NULL (zeros). */
-int gsb_pack_flat(int32_t P, const float* g_means3D, const float* g_colors, const float* g_rotations,
-                  const float* g_opacities, const float* g_scales, const float* grad_accum, const float* vis_count,
-                  float* flat, void* stream);
-
 /* accumulate_mean_2d_gradients (external.py:113-124) taking the visibility mask (uint8 [P]) like the reference. */
 int gsb_densify_accumulate_masked(int32_t P, const uint8_t* visible, const float* grad_means2D, float* grad_accum,
                                   float* vis_count, void* stream);
@@ -279,6 +272,26 @@ size_t gsb_scan_scratch_bytes(int32_t n);
 int gsb_mask_scan(int32_t P, const uint8_t* keep, int32_t* dst_index, int32_t* count_out, void* scratch, void* stream);
 int gsb_gather_rows(int32_t P, const uint8_t* keep, const int32_t* dst_index, const float* src, float* dst,
                     int32_t row_floats, void* stream);
+
+/* One densify event -- clone, split (n = 2), removal of the split parents, prune (external.py:211-314 with
+ * cat_params_to_optimizer / remove_points, external.py:127-204) -- as ONE pass over the Gaussians instead of four
+ * re-allocations of every table.  gsb_densify_plan decides, per source row, which of its up to four output rows
+ * survive (original / clone / two split children) and ranks them (order = the reference's: originals, clones,
+ * first children, second children, each in source order); totals_dev (DEVICE int32 [4]) receives the numbers of
+ * surviving originals, clones, child pairs and of ALL split rows (the split draw of external.py:261 has 2 x that
+ * many rows).  Thresholds: mean accumulated gradient >= grad_threshold; clone when max scale <= clone_max_scale else
+ * split; prune sigmoid(opacity) < prune_opacity or (prune_big and max scale > big_scale).  The caller reads the four
+ * totals (its one synchronisation), allocates the new tables (K0 + K1 + 2 K2 rows) and calls gsb_densify_apply with
+ * src18 / dst18 = HOST arrays of the 18 table pointers: means [.,3], colors [.,3], segmentation colours [.,3],
+ * quaternions [.,4], opacity logits [.,1], log scales [.,3], then their exp_avg and their exp_avg_sq in the same
+ * order (new rows get zero moments), and samples [2 S][3].  scratch: gsb_densify_plan_scratch_bytes(P), shared by
+ * both calls. */
+size_t gsb_densify_plan_scratch_bytes(int32_t P);
+int gsb_densify_plan(int32_t P, const float* grad_accum, const float* vis_count, const float* opacity_logits,
+                     const float* log_scales, float grad_threshold, float clone_max_scale, float prune_opacity,
+                     int32_t prune_big, float big_scale, void* scratch, int32_t* totals_dev, void* stream);
+int gsb_densify_apply(int32_t P, const void* scratch, const int32_t* totals_host, const float* const* src18,
+                      float* const* dst18, const float* samples, void* stream);
 
 /* create_render_arguments (shared.py:29-42), the three activations in one launch:
  * rotations = normalize(quats) [P][4] (torch.nn.functional.normalize: q / max(||q||, 1e-12)),

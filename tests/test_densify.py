@@ -121,17 +121,3 @@ def test_accumulate_batch_equals_sequential():
     b.accumulate_batch(radii, grad)
     for k in ("visibility_count", "mean_2d_gradients_accumulated", "max_2d_radii", "gaussian_is_visible_mask"):
         assert torch.equal(getattr(a, k), getattr(b, k)), k
-
-
-@pytest.mark.gpu
-def test_pack_flat_matches_slice_copies():
-    from gsb200 import dist as gd
-    P = 3001
-    g = torch.Generator().manual_seed(1)
-    r = lambda *s: torch.randn(*s, generator=g)
-    grads = {"means3D": r(P, 3), "colors": r(P, 3), "rotations": r(P, 4), "opacities": r(P, 1), "scales": r(P, 3)}
-    st = {"mean_2d_gradients_accumulated": r(P).abs(), "visibility_count": r(P).abs()}
-    want = gd.pack(torch.zeros(P, gd.WIDTH), grads, st)
-    got = gd.pack(torch.zeros(P, gd.WIDTH, device="cuda"), {k: v.cuda() for k, v in grads.items()},
-                  {k: v.cuda() for k, v in st.items()})
-    assert torch.equal(got.cpu(), want)
