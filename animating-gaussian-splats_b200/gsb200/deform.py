@@ -7,15 +7,18 @@ interchangeable with the reference's nn.Module in both directions.
 
 Per layer: ONE tcgen05 GEMM whose epilogue also accumulates the BatchNorm batch statistics, then ONE pass that
 normalises, adds the residual and applies GELU.  BatchNorm always uses batch statistics and updates its running
-buffers, because the reference never leaves training mode.  `precise=True` selects the 3xTF32 split (FP32-level
-accuracy); the default is plain TF32 (what torch does with allow_tf32).
+buffers, because the reference never leaves training mode.  `precise=True` (the default) selects the 3xTF32 split
+(FP32-level accuracy: the reference never enables allow_tf32, so its nn.Linear layers are FP32 products);
+`precise=False` is an opt-in fast mode in plain TF32 (what torch computes with allow_tf32), forward and backward.
 
 Training: when gradients are enabled the forward runs inside ONE autograd node (_DeformFn) that keeps the per-block
 activations (x, z1, a, z2 and the BatchNorm sums) and whose backward is built from the same pieces: dX = dY W on the
 forward GEMM with the transposed weight, dW = dY^T X on the MN-major tcgen05 weight-gradient kernel, and the two-pass
-BatchNorm / GELU adjoint (gsb_bn_gelu_backward).  The backward GEMMs run in TF32 (like torch with allow_tf32), also
-when the forward uses the 3xTF32 split.  The 7-wide output layer's two backward products stay on torch.mm: 7 is not a
-tensor-core tile, and they are 2% of the backward's bytes.
+BatchNorm / GELU adjoint (gsb_bn_gelu_backward).  With precise=True the input gradients run on the 3xTF32 layer and
+the weight gradients are FP32 products (torch.mm with TF32 off: a 3xTF32 form of the MN-major weight-gradient kernel
+would have to materialise hi / lo splits of both operands, which costs what the FP32 product costs); with
+precise=False both run in TF32 on the tcgen05 kernels.  The 7-wide output layer's two backward products stay on
+torch.mm: 7 is not a tensor-core tile, and they are 2% of the backward's bytes.
 """
 import torch
 from torch import nn
@@ -70,7 +73,7 @@ class ResidualBlock(nn.Module):   # parameter container with the reference's nam
 
 
 class DeformationNetwork(nn.Module):
-    def __init__(self, hidden_dimension, residual_block_count, precise=False):
+    def __init__(self, hidden_dimension, residual_block_count, precise=True):
         super().__init__()
         if hidden_dimension % 4 or hidden_dimension > 256:
             raise ValueError("hidden_dimension must be a multiple of 4 and at most 256 on the tcgen05 path")
@@ -164,6 +167,24 @@ class _DeformFn(torch.autograd.Function):
         net, x, keep, last = ctx.net, ctx.x, ctx.keep, ctx.last
         d_out = d_out.contiguous().float()
         grads = {}
+        # precise (the default, = the reference's FP32 matmuls): input gradients on the 3xTF32 tcgen05 layer, weight
+        # gradients as FP32 products; precise=False: both in plain TF32 on the tcgen05 kernels (what torch computes
+        # with allow_tf32) -- an opt-in fast mode
+        precise = net.precise
+
+        def dx(g, w):
+            return linear(g, w.detach().t().contiguous(), None, precise=precise)
+
+        def dw(g, a):
+            if not precise:
+                return linear_wgrad(g, a)
+            prev = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = False
+            try:
+                return g.t() @ a
+            finally:
+                torch.backends.cuda.matmul.allow_tf32 = prev
+
         # output layer (7 columns): plain torch products
         w_out = net.fc_out.weight.detach()
         grads[net.fc_out.weight] = d_out.t() @ last
@@ -172,14 +193,14 @@ class _DeformFn(torch.autograd.Function):
         for block, (identity, z1, st1, a, z2, st2) in zip(reversed(list(net.residual_blocks)), reversed(keep)):
             dz2, g2, dgam2, dbet2 = net._bn_bwd(dh, z2, st2, block.bn2, identity)
             grads[block.bn2.weight], grads[block.bn2.bias] = dgam2, dbet2
-            grads[block.fc2.weight] = linear_wgrad(dz2, a)
-            da = linear(dz2, block.fc2.weight.detach().t().contiguous(), None)
+            grads[block.fc2.weight] = dw(dz2, a)
+            da = dx(dz2, block.fc2.weight)
             dz1, _, dgam1, dbet1 = net._bn_bwd(da, z1, st1, block.bn1, None)
             grads[block.bn1.weight], grads[block.bn1.bias] = dgam1, dbet1
-            grads[block.fc1.weight] = linear_wgrad(dz1, identity)
-            dh = linear(dz1, block.fc1.weight.detach().t().contiguous(), None)
+            grads[block.fc1.weight] = dw(dz1, identity)
+            dh = dx(dz1, block.fc1.weight)
             dh += g2                                     # the residual branch
-        grads[net.fc_in.weight] = linear_wgrad(dh, x)
+        grads[net.fc_in.weight] = dw(dh, x)
         grads[net.fc_in.bias] = dh.sum(0)
         ctx.keep = ctx.last = ctx.x = None
         plist = net._parameter_list()

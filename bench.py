@@ -792,7 +792,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
                         "replicas_bit_identical": identical},
         "timesteps": {"count": timesteps, "ms_per_step_mean": float(np.mean(train_ms)), "ms_per_step_first": train_ms[0],
                       "steps_per_s": 1e3 / float(np.mean(train_ms)), "loss_first": losses[0], "loss_last": losses[-1],
-                      "knn_seconds": knn_s, "network": "replicated on every rank (3xTF32 forward, TF32 backward); views sharded"},
+                      "knn_seconds": knn_s, "network": "replicated on every rank (precise mode: 3xTF32 forward / input gradients, FP32 weight gradients); views sharded"},
         "peak_memory_bytes_per_gpu": int(peak.item()), "setup_seconds": setup_s,
     }
 
@@ -869,7 +869,7 @@ def deformation_shaped(args, hidden=256, blocks=4, iters=10):
     for precise in (False, True):
         net = deform.DeformationNetwork(hidden, blocks, precise=precise).to(dev)
         net.load_state_dict(stock.state_dict())
-        res["fwd_bwd_ours_3xtf32_fwd" if precise else "fwd_bwd_ours_tf32"] = timed(
+        res["fwd_bwd_ours_precise" if precise else "fwd_bwd_ours_tf32"] = timed(
             lambda: train(lambda: net(init, network_input=x), net))
     for name, flag in (("fwd_bwd_torch_fp32", False), ("fwd_bwd_torch_tf32", True)):
         torch.backends.cuda.matmul.allow_tf32 = flag
@@ -945,11 +945,12 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
                    f"{views} of {args.cams} cameras {args.width}x{args.height}, rigidity K={neighbours}, Adam",
            "unit": "ms per step", "ours": timed(ours)}
     res["ours_steps_per_s"] = 1e3 / res["ours"]
-    res["network_matmuls"] = "3xTF32 forward (FP32-level), TF32 backward"
+    res["network_matmuls"] = ("precise (default): 3xTF32 forward and input gradients, FP32 weight gradients -- compare with "
+                              "`stock` (torch FP32); ours_tf32: TF32 everywhere (opt-in fast mode)")
     torch.manual_seed(0)
     net = deform.DeformationNetwork(hidden, blocks, precise=False).to(dev)
     opt = torch.optim.Adam(net.parameters(), lr=1e-4)
-    res["ours_tf32_forward"] = timed(ours)
+    res["ours_tf32"] = timed(ours)
     ref = oracle_lib.load_reference_ext()
     if ref is None:
         return res

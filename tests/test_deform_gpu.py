@@ -104,11 +104,13 @@ def test_update_gaussian_cloud_parameters_shapes():
     assert torch.isfinite(out["means"]).all() and not torch.equal(out["means"], p["means"])
 
 
+@pytest.mark.parametrize("precise", [True, False])
 @pytest.mark.parametrize("rows,h,blocks", [(20_000, 128, 2), (5000, 64, 1), (100_000, 256, 3)])
-def test_backward_matches_stock_torch(rows, h, blocks):
-    """Gradients of every parameter and of the [N,7] input through the tcgen05 backward (TF32 products) against torch
-    autograd on the same architecture in FP32: 3e-2 of each gradient's RMS (BatchNorm's 1/std carries the TF32 rounding
-    of the forward into every later layer, as in the forward test)."""
+def test_backward_matches_stock_torch(rows, h, blocks, precise):
+    """Gradients of every parameter and of the [N,7] input against torch autograd on the same architecture in FP32.
+    precise=True (the default: 3xTF32 forward and input gradients, FP32 weight gradients -- the reference's precision):
+    2e-3 of each gradient's RMS; precise=False (TF32 everywhere, the opt-in fast mode): 3e-2 (BatchNorm's 1/std carries
+    the TF32 rounding of the forward into every later layer, as in the forward test)."""
     from gsb200 import deform
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.manual_seed(rows % 11)
@@ -117,7 +119,8 @@ def test_backward_matches_stock_torch(rows, h, blocks):
         for m in ref.modules():
             if isinstance(m, nn.BatchNorm1d):
                 m.weight.uniform_(0.5, 1.5); m.bias.normal_(0, 0.3)
-    ours = deform.DeformationNetwork(h, blocks, precise=True).cuda()
+    ours = deform.DeformationNetwork(h, blocks, precise=precise).cuda()
+    assert deform.DeformationNetwork(h, blocks).precise is True
     ours.load_state_dict(ref.state_dict())
     x = torch.randn(rows, 192, device="cuda")
     init_a = torch.randn(rows, 7, device="cuda", requires_grad=True)
@@ -132,7 +135,7 @@ def test_backward_matches_stock_torch(rows, h, blocks):
         assert p.grad is not None, name
         rms = q.grad.pow(2).mean().sqrt().item() + 1e-12
         err = (p.grad - q.grad).abs().max().item() / rms
-        assert err < 3e-2, (name, err)
+        assert err < (2e-3 if precise else 3e-2), (name, precise, err)
 
 
 def test_training_steps_follow_stock_torch():
