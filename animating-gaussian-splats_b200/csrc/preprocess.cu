@@ -111,11 +111,14 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
   __shared__ __align__(16) float s_mean[768];
   __shared__ __align__(16) float s_scale[768];
   __shared__ float s_V[16], s_Pm[16];
+  __shared__ CamParams s_cp;   // the block's camera: one load per block instead of 32 bytes per thread
   const int cam = blockIdx.y;
   const int block_first = blockIdx.x * 256;
   const int idx = block_first + threadIdx.x;
   if (threadIdx.x < 16) s_V[threadIdx.x] = viewmatrix[16 * cam + threadIdx.x];
   else if (threadIdx.x < 32) s_Pm[threadIdx.x - 16] = projmatrix[16 * cam + threadIdx.x - 16];
+  else if (threadIdx.x < 40)
+    reinterpret_cast<int*>(&s_cp)[threadIdx.x - 32] = reinterpret_cast<const int*>(cams + cam)[threadIdx.x - 32];
   stage3(means3D, P, block_first, s_mean);
   if (scales) stage3(scales, P, block_first, s_scale);
   __syncthreads();
@@ -159,7 +162,7 @@ preprocess_fwd_kernel(int P, int W, int H, int gx, int gy, float mod, int prefil
     }
 
     // computeCov2D (cr/forward.cu:74-113)
-    const CamParams cp = cams[cam];
+    const CamParams cp = s_cp;
     const float tx_ = xform_row(V, 0, mx, my, mz);
     const float ty_ = xform_row(V, 1, mx, my, mz);
     const float limx = MUL(cp.tanfovx, 1.3f);
@@ -305,11 +308,17 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot,
                       float* __restrict__ flat, int flat_mode, const float* __restrict__ dL_dopacity,
                       const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out, int flat_stride) {
-  extern __shared__ float s_mats[];  // [n_cams][32]: view then proj
+  extern __shared__ float s_mats[];  // [n_cams][32]: view then proj; FLAT: then int [n_cams][2] = split slot, count flag
   for (int i = threadIdx.x; i < n_cams * 32; i += blockDim.x) {
     const int cam = i >> 5, k = i & 31;
     s_mats[i] = (k < 16) ? viewmatrix[16 * cam + k] : projmatrix[16 * cam + k - 16];
   }
+  int* const s_entry = reinterpret_cast<int*>(s_mats + 32 * n_cams);
+  if (FLAT)
+    for (int i = threadIdx.x; i < n_cams; i += blockDim.x) {
+      s_entry[2 * i] = cams[i].split_slot;
+      s_entry[2 * i + 1] = cams[i].count_vis;
+    }
   __shared__ __align__(16) float s_mean[768];
   stage3(means3D, P, blockIdx.x * 256, s_mean);
   __syncthreads();
@@ -342,7 +351,9 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     any = true;
     const float* view = s_mats + 32 * cam;
     const float* proj = view + 16;
-    const CamParams cp = cams[cam];
+    // the four scalars only (one 16-byte load): the entry fields of the FLAT form sit in shared memory
+    const float4 cp4 = __ldg(reinterpret_cast<const float4*>(cams + cam));
+    struct { float tanfovx, tanfovy, focal_x, focal_y; } cp = {cp4.x, cp4.y, cp4.z, cp4.w};
     const float h_x = cp.focal_x, h_y = cp.focal_y;
     // the blend kernel leaves raw pixel moments of w = dL/dG * G: (S1, S2) in dL_dmean2D, (S1 dx, S1 dy, -, S2 dy)
     // in dL_dconic; their linear maps to the gradients (cr/backward.cu:536-548) are applied here, once per Gaussian
@@ -353,15 +364,16 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float g2x = -(0.5f * W) * (con.x * rs1 + con.y * rs2);
     const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
     if (FLAT) {
-      if (cp.split_slot >= 0) {
+      const int split_slot = s_entry[2 * cam];
+      if (split_slot >= 0) {
         // rows of this camera are rendered elsewhere too: the norm belongs to the SUMMED gradient (after the exchange)
-        float* slot = flat + (size_t)idx * flat_stride + GSB_FLAT_WIDTH + 2 * cp.split_slot;
+        float* slot = flat + (size_t)idx * flat_stride + GSB_FLAT_WIDTH + 2 * split_slot;
         if (flat_mode == 0) { slot[0] = g2x; slot[1] = g2y; }
         else if (flat_mode == 2) { slot[0] += g2x; slot[1] += g2y; }
       } else {
         st_norm += sqrtf(g2x * g2x + g2y * g2y);   // torch.norm of the first two components, one term per camera
       }
-      if (cp.count_vis) {
+      if (s_entry[2 * cam + 1]) {
         st_cnt += 1.0f;
         st_rad = fmaxf(st_rad, (float)rad);
       }
@@ -583,7 +595,7 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat, int flat_mode,
                           const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out, int flat_stride) {
   if (a.P <= 0) return GSB_OK;
-  const size_t smem = (size_t)a.n_cams * 32 * sizeof(float);
+  const size_t smem = (size_t)a.n_cams * (32 * sizeof(float) + (flat ? 2 * sizeof(int) : 0));
   if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
   if (flat) {
     if (!dL_dopacity || !dL_dcolor || !a.scales || !a.rotations) return GSB_EINVAL;
