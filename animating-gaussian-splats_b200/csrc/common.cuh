@@ -53,6 +53,7 @@ struct CamParams {  // per-entry scalars that live in a small device table
   int split_slot;          // >= 0: the camera's rows are shared with another rank (gsb_raster_args.entries)
   int count_vis;           // this entry counts the camera in the visibility / radius statistics
 };
+static_assert(sizeof(CamParams) == 32, "kernels copy a CamParams as eight 32-bit words / read its first 16 bytes");
 
 int launch_preprocess(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                       int32_t* radii_out, uint32_t* gauss_keys_in, int* err_flag_dev, cudaStream_t st);
