@@ -227,7 +227,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f;
   float D = 15.0f;  // median depth default (cr/forward.cu:308)
-  uint32_t blended = 0;
+  uint32_t blended = 0, evaluated = 0, staged = 0;   // COUNT only
+  float slots = 0.f;
 
   for (int i = 0; i < rounds; i++) {
     if (__syncthreads_count(done) == GSB_BLOCK_SIZE) break;
@@ -252,7 +253,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                                depths[cam_off + id]);
     }
     __syncthreads();
+    if (COUNT && tid == 0) staged += (uint32_t)n;
     for (int j = 0; !done && j < n; j++) {
+      if (COUNT) { evaluated++; slots += 32.0f / (float)__popc(__activemask()); }   // 32 lane slots per warp iteration
       const float4 a = s_a[j];
       const float4 co2 = s_co[j];
       const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
@@ -274,15 +277,19 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
 
   if (COUNT) {
-    unsigned long long w = last_contributor, b = blended;
+    // per camera: walked pairs (sum of n_contrib), composited pairs, evaluated pairs (inner-loop iterations of live
+    // pixels), lane slots issued (32 per warp iteration: evaluated / slots = lane utilisation), entries staged after
+    // tile culling, entries listed
+    unsigned long long v[4] = {last_contributor, blended, evaluated, (unsigned long long)(slots + 0.5f)};
 #pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
-      w += __shfl_xor_sync(0xffffffffu, w, s);
-      b += __shfl_xor_sync(0xffffffffu, b, s);
-    }
-    if ((tid & 31u) == 0) {
-      atomicAdd(pair_counts + 2 * cam, w);
-      atomicAdd(pair_counts + 2 * cam + 1, b);
+    for (int s = 16; s >= 1; s >>= 1)
+#pragma unroll
+      for (int k = 0; k < 4; k++) v[k] += __shfl_xor_sync(0xffffffffu, v[k], s);
+    if ((tid & 31u) == 0)
+      for (int k = 0; k < 4; k++) atomicAdd(pair_counts + 6 * cam + k, v[k]);
+    if (tid == 0) {
+      atomicAdd(pair_counts + 6 * cam + 4, (unsigned long long)staged);
+      atomicAdd(pair_counts + 6 * cam + 5, (unsigned long long)total);
     }
     return;
   }
@@ -324,7 +331,7 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
 
 int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsigned long long* counts, cudaStream_t st) {
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
-  GSB_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * 2 * (size_t)a.n_cams, st));
+  GSB_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * 6 * (size_t)a.n_cams, st));
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
   render_fwd_kernel<true><<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), nullptr, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,

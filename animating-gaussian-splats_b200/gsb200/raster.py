@@ -416,11 +416,12 @@ def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, par
 
 
 def count_pairs(st):
-    """(walked, composited) (pixel, Gaussian) pairs per camera of a forward state: int64 tensor [n_cams, 2].
-    walked = sum of n_contrib (B of SURVEY.md 8(d)); composited = pairs with alpha >= 1/255 that were blended (B_alpha)."""
+    """Work counters per camera of a forward state: int64 tensor [n_cams, 6] = walked pairs (sum of n_contrib, B of
+    SURVEY.md 8(d)), composited pairs (alpha >= 1/255 and blended, B_alpha), pairs the forward's inner loop evaluated,
+    lane slots it issued (evaluated / slots = lane utilisation), list entries staged after tile culling, list entries."""
     n = st.args.n_cams
     dev = st.geom.device
-    counts = torch.zeros((n, 2), dtype=torch.int64, device=dev)
+    counts = torch.zeros((n, 6), dtype=torch.int64, device=dev)
     with L.device_guard(dev):
         rc = L.lib().gsb_raster_count_pairs(C.byref(st.args), C.byref(st.ctx), L.ptr(counts), L.stream_ptr())
     L.check(rc, "gsb_raster_count_pairs")

@@ -235,7 +235,7 @@ def run_ours(args):
         all_targets = render_targets(tgt_raw, all_sc, args.cams, bg, dev)
         want_flat = torch.zeros((P, gd.WIDTH), dtype=torch.float32, device=dev)
         _, _, _, st0 = step_mod.timestep_step(act, all_sc, all_targets, bg, None, flat=want_flat)
-        full_counts = raster.count_pairs(st0).sum(dim=0).tolist() + [st0.num_rendered]
+        full_counts = raster.count_pairs(st0).sum(dim=0).tolist()[:2] + [st0.num_rendered]
         if use_bands:
             # tile-band sharding: the unit is a tile row of a camera, cut where the cumulative cost crosses k / N
             rc_ = torch.tensor(gd.tile_row_costs(st0), dtype=torch.float64, device=dev)
@@ -457,6 +457,8 @@ def run_ours(args):
     # ---- workload statistics ---------------------------------------------------------------------
     pairs = raster.count_pairs(st).sum(dim=0)                     # (walked = sum of n_contrib, composited)
     walked, blended = int(pairs[0].item()), int(pairs[1].item())
+    fwd_work = {"evaluated_pairs": int(pairs[2]), "lane_slots": int(pairs[3]), "lane_utilisation": float(pairs[2]) / max(float(pairs[3]), 1.0),
+                "entries_staged": int(pairs[4]), "entries_listed": int(pairs[5])}
     R = st.num_rendered
     tile_bits = int(st.ctx.tile_bits)
     cnt = torch.tensor([walked, R, blended], dtype=torch.float64, device=dev)
@@ -576,7 +578,7 @@ def run_ours(args):
                 "returns": "the per-camera loss numbers only (3 floats per camera); gradients and statistics stay on the "
                            "device, where the optimiser and the densify step consume them"},
         "gpu_launches": launches * args.steps, "ms_per_step_eager": ms_eager, "peak_memory_bytes": int(peak_mem),
-        "stage_ms": stages, "roofline": roofline, "roofline_fwd": roofline_fwd, "roofline_hbm": roofline_hbm, "clocks": clocks,
+        "forward_work": fwd_work, "stage_ms": stages, "roofline": roofline, "roofline_fwd": roofline_fwd, "roofline_hbm": roofline_hbm, "clocks": clocks,
     }
     if exchange is not None:
         out["exchange_ms"] = exchange

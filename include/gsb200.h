@@ -140,9 +140,10 @@ int gsb_raster_forward_async(const gsb_raster_args* args, const float* tanfov_de
                              char* image, size_t image_bytes, char* binning, size_t binning_bytes, int64_t capacity,
                              float* out_color, float* out_depth, int32_t* radii, gsb_raster_ctx* ctx, void* stream);
 
-/* Walked and composited (pixel, Gaussian) pairs of a forward state, per camera: counts (DEVICE uint64 [n_cams][2])
- * = (sum over pixels of n_contrib, pairs with alpha >= 1/255 that were blended) -- B and B_alpha of the metric
- * definition; a measurement entry point (re-runs the forward walk without writing images). */
+/* Work counters of a forward state, per camera: counts (DEVICE uint64 [n_cams][6]) = (sum over pixels of n_contrib,
+ * pairs with alpha >= 1/255 that were blended -- B and B_alpha of the metric definition --, pairs the inner loop
+ * evaluated for live pixels, lane slots it issued (32 per warp iteration), list entries staged after tile culling,
+ * list entries); a measurement entry point (re-runs the forward walk without writing images). */
 int gsb_raster_count_pairs(const gsb_raster_args* args, const gsb_raster_ctx* ctx, uint64_t* counts, void* stream);
 
 /* Re-blend an existing forward state with different colours: everything a forward call computes before the
