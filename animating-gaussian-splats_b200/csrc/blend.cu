@@ -189,7 +189,10 @@ __device__ __forceinline__ TileCoord tile_coord(const uint32_t* __restrict__ ord
 // was measured SLOWER here: 1.40 vs 1.21 ms at C2, 3.10 vs 2.64 ms at C4.  The forward's per-entry cost for a warp
 // that rejects is already only the 9-instruction power evaluation, and the mask's square roots and divisions in the
 // staging phase plus one more branch per entry cost more than they save.)
-template <bool COUNT>
+// TWO: a second colour table (the segmentation colours of densify.py:136-150) is blended in the same walk into a
+// second image: the two renders of a first-frame iteration share every alpha, T and termination decision, so the
+// second one costs three more FMAs per composited pair instead of a second pass over the lists.
+template <bool COUNT, bool TWO>
 __global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_FWD_MINB)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                   const uint32_t* __restrict__ point_list, int W, int H, int P,
@@ -197,10 +200,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float4* __restrict__ conic_opacity, const float* __restrict__ depths,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
-                  unsigned long long* __restrict__ pair_counts) {
+                  unsigned long long* __restrict__ pair_counts, const float* __restrict__ colors2,
+                  float* __restrict__ out_color2) {
   __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position + 1)
   __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_cd[GSB_BLOCK_SIZE];  // r, g, b, depth
+  __shared__ float4 s_c2[TWO ? GSB_BLOCK_SIZE : 1];  // r, g, b of the second table
   __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
 
   const TileCoord tc = tile_coord(order, tiles_x, tiles_pc);
@@ -226,6 +231,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float T = 1.0f;
   uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  float E0 = 0.f, E1 = 0.f, E2 = 0.f;   // TWO: the second image
   float D = 15.0f;  // median depth default (cr/forward.cu:308)
   uint32_t blended = 0, evaluated = 0, staged = 0;   // COUNT only
   float slots = 0.f;
@@ -251,6 +257,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       s_co[slot] = co;
       s_cd[slot] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
                                depths[cam_off + id]);
+      if (TWO) s_c2[slot] = make_float4(colors2[3 * (size_t)id], colors2[3 * (size_t)id + 1], colors2[3 * (size_t)id + 2], 0.f);
     }
     __syncthreads();
     if (COUNT && tid == 0) staged += (uint32_t)n;
@@ -269,6 +276,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       C0 = FMA(T, MUL(alpha, cd.x), C0);
       C1 = FMA(T, MUL(alpha, cd.y), C1);
       C2 = FMA(T, MUL(alpha, cd.z), C2);
+      if (TWO) {
+        const float4 c2 = s_c2[j];
+        E0 = FMA(T, MUL(alpha, c2.x), E0);
+        E1 = FMA(T, MUL(alpha, c2.y), E1);
+        E2 = FMA(T, MUL(alpha, c2.z), E2);
+      }
       if (T > 0.5f && test_T < 0.5f) D = cd.w;
       T = test_T;
       last_contributor = __float_as_uint(a.w);
@@ -307,6 +320,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     oc[pid] = FMA(bg[0], T, C0);
     oc[HW + pid] = FMA(bg[1], T, C1);
     oc[2 * HW + pid] = FMA(bg[2], T, C2);
+    if (TWO) {
+      float* o2 = out_color2 + (size_t)te.cam * 3 * HW;
+      o2[pid] = FMA(bg[0], T, E0);
+      o2[HW + pid] = FMA(bg[1], T, E1);
+      o2[2 * HW + pid] = FMA(bg[2], T, E2);
+    }
     out_depth[te.cam * HW + pid] = D;
   }
 }
@@ -320,11 +339,13 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  render_fwd_kernel<false><<<tiles_total, block, 0, st>>>(
+  if (a.colors2 && (!a.out_color2 || a.color_cam_stride != 0)) return GSB_EINVAL;
+  auto kern = a.colors2 ? render_fwd_kernel<false, true> : render_fwd_kernel<false, false>;
+  kern<<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
       reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, c.final_T, c.n_contrib, out_color,
-      out_depth, nullptr);
+      out_depth, nullptr, a.colors2, a.out_color2);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
@@ -333,11 +354,11 @@ int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsign
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   GSB_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * 6 * (size_t)a.n_cams, st));
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  render_fwd_kernel<true><<<tiles_total, block, 0, st>>>(
+  render_fwd_kernel<true, false><<<tiles_total, block, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), nullptr, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       reinterpret_cast<const float2*>(c.means2D), a.colors, a.color_cam_stride,
       reinterpret_cast<const float4*>(c.conic_opacity), c.depths, a.background, nullptr, nullptr, nullptr, nullptr,
-      counts);
+      counts, nullptr, nullptr);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

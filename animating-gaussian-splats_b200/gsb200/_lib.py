@@ -28,6 +28,7 @@ class RasterArgs(C.Structure):
         ("background", C.c_void_p), ("means3D", C.c_void_p), ("colors", C.c_void_p), ("opacities", C.c_void_p),
         ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
         ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("entries", C.c_void_p),
+        ("colors2", C.c_void_p), ("out_color2", C.c_void_p),
     ]
 
 

@@ -63,6 +63,13 @@ typedef struct gsb_raster_args {
    * of adding its norm to col 14 (the norm must be taken of the camera's SUMMED gradient, after the exchange), and
    * only the entry with count_visibility != 0 counts the camera in cols 15 / 16. */
   const int32_t* entries;
+  /* Two colour tables in one walk (new; NULL = one render).  colors2 [P][3]: a second colour table of the SAME
+   * Gaussians -- the segmentation colours that densify.py:136-150 renders right after the colours, through the same
+   * camera -- blended by the same forward pass into out_color2 [n_cams][3][H][W] (the two renders share every alpha,
+   * transmittance and termination decision, so each image equals its own render).  gsb_raster_backward_flat then takes
+   * the second image's gradient as dL_dpix2 and back-propagates both in one walk. */
+  const float* colors2;
+  float* out_color2;
 } gsb_raster_args;
 
 /* Saved state of one forward call: replaces the (geomBuffer, binningBuffer, imgBuffer, num_rendered)
