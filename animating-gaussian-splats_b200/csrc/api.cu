@@ -443,12 +443,15 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
 
 size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams) {
   // raw second moments [n_cams][P][4] (read as float4: first, so they stay 16-byte aligned for any P) | raw first
-  // moments [n_cams][P][3] | dL/dopacity [P] | dL/dcolor [P][3]
-  return align_up(((size_t)P * n_cams * 7 + (size_t)P * 4) * sizeof(float), 256);
+  // moments [n_cams][P][3] | dL/dopacity [P] | dL/dcolor [P][3] | dL/dcolor of a second table [P][3]
+  return align_up(((size_t)P * n_cams * 7 + (size_t)P * 7) * sizeof(float), 256);
 }
 
-int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix, void* scratch,
-                             float* flat, int32_t flat_stride, int32_t mode, float* dL_dmean2D_out, void* stream) {
+}  // extern "C"
+
+static int backward_flat_impl(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                              const float* dL_dpix2, void* scratch, float* flat, int32_t flat_stride, int32_t mode,
+                              float* dL_dmean2D_out, void* stream) {
   if (!a || !ctx) return GSB_EINVAL;
   if (a->P == 0) return GSB_OK;
   const int part = mode & ~0xFF;
@@ -466,23 +469,39 @@ int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx
   float* m1 = m2 + 4 * n;
   float* dop = m1 + 3 * n;
   float* dcol = dop + a->P;
+  float* dcol2 = dL_dpix2 ? dcol + 3 * (size_t)a->P : nullptr;
+  if (dL_dpix2 && (mode != 0 || part != 0 || !a->colors2)) return GSB_EINVAL;
   int rc;
   if (part != GSB_FLAT_FINISH_ONLY) {
     prof_mark(PF_BWD_BEGIN, st);
-    GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * 4) * sizeof(float), st));   // one fill for all four
+    GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * (dL_dpix2 ? 7 : 4)) * sizeof(float), st));   // one fill
     prof_mark(PF_BWD_ZERO, st);
     if (ctx->num_rendered != 0)
-      if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st))) return rc;
+      if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st, dL_dpix2, dcol2))) return rc;
     prof_mark(PF_RENDER_BWD, st);
     if (part == GSB_FLAT_BLEND_ONLY) return GSB_OK;
   }
   GeomExtras gx;
   GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
   if ((rc = launch_preprocess_bwd(*a, gx.cams, *ctx, m1, m2, nullptr, nullptr, nullptr, nullptr, st, flat, mode, dop, dcol,
-                                  dL_dmean2D_out, flat_stride)))
+                                  dL_dmean2D_out, flat_stride, dcol2)))
     return rc;
   prof_mark(PF_PREPROCESS_BWD, st);
   return GSB_OK;
+}
+
+extern "C" {
+
+int gsb_raster_backward_flat(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix, void* scratch,
+                             float* flat, int32_t flat_stride, int32_t mode, float* dL_dmean2D_out, void* stream) {
+  return backward_flat_impl(a, ctx, dL_dpix, nullptr, scratch, flat, flat_stride, mode, dL_dmean2D_out, stream);
+}
+
+int gsb_raster_backward_flat2(const gsb_raster_args* a, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                              const float* dL_dpix2, void* scratch, float* flat, int32_t flat_stride,
+                              float* dL_dmean2D_out, void* stream) {
+  if (!dL_dpix2) return GSB_EINVAL;
+  return backward_flat_impl(a, ctx, dL_dpix, dL_dpix2, scratch, flat, flat_stride, 0, dL_dmean2D_out, stream);
 }
 
 int gsb_flat_apply_stats(int32_t P, const float* flat, int32_t flat_stride, float* grad_accum, float* vis_count,

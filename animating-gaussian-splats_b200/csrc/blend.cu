@@ -399,6 +399,31 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
   v[0] += __shfl_xor_sync(full, v[0], 1);
 }
 
+// Sum 4 values over the 32 lanes with 5 shuffles; afterwards every lane of the group 8 k .. 8 k + 7 holds the full
+// warp sum of component k.
+__device__ __forceinline__ float warp_reduce4(float (&v)[4], unsigned lane) {
+  const unsigned full = 0xffffffffu;
+  {
+    const bool up = lane & 16u;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float send = up ? v[i] : v[i + 2];
+      const float keep = up ? v[i + 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(full, send, 16);
+    }
+  }
+  {
+    const bool up = lane & 8u;
+    const float send = up ? v[0] : v[1];
+    const float keep = up ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(full, send, 8);
+  }
+  v[0] += __shfl_xor_sync(full, v[0], 4);
+  v[0] += __shfl_xor_sync(full, v[0], 2);
+  v[0] += __shfl_xor_sync(full, v[0], 1);
+  return v[0];
+}
+
 __global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_BWD_MINB)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                   const uint32_t* __restrict__ point_list, int W, int H, int P,
@@ -580,10 +605,16 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 struct BwdPixel {
   float T, ar0, ar1, ar2, dpx0, dpx1, dpx2, nTf_bg, pfy;
   int last;
+  float br0, br1, br2, dq0, dq1, dq2;   // TWO: accum_rec and dL/dpixel of the second image
 };
 
+// TWO: the pixel belongs to two images blended from two colour tables in one walk (render_fwd_kernel<.., TWO>): alpha, T
+// and the decisions are shared, dL/dalpha is the sum over both images' channels, the second table's colour gradient
+// goes to w[1..3] (w[0] carries the opacity term g_op).
+template <bool TWO>
 __device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, float G, float dx, float dy, float4 ci,
-                                          float opac, float (&v)[8], float& g_op) {
+                                          float4 ci2, float opac, float (&v)[8], float (&w)[4]) {
+  float& g_op = w[0];
   if (!valid) return;
   const float om = 1.f - alpha;
   float rcp;
@@ -601,6 +632,18 @@ __device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, 
   v[0] = fmaf(dchannel_dcolor, s.dpx0, v[0]);
   v[1] = fmaf(dchannel_dcolor, s.dpx1, v[1]);
   v[2] = fmaf(dchannel_dcolor, s.dpx2, v[2]);
+  if (TWO) {
+    const float e0 = ci2.x - s.br0, e1 = ci2.y - s.br1, e2 = ci2.z - s.br2;
+    dL_dalpha = fmaf(e0, s.dq0, dL_dalpha);
+    dL_dalpha = fmaf(e1, s.dq1, dL_dalpha);
+    dL_dalpha = fmaf(e2, s.dq2, dL_dalpha);
+    s.br0 = fmaf(alpha, e0, s.br0);
+    s.br1 = fmaf(alpha, e1, s.br1);
+    s.br2 = fmaf(alpha, e2, s.br2);
+    w[1] = fmaf(dchannel_dcolor, s.dq0, w[1]);
+    w[2] = fmaf(dchannel_dcolor, s.dq1, w[2]);
+    w[3] = fmaf(dchannel_dcolor, s.dq2, w[3]);
+  }
   dL_dalpha = fmaf(dL_dalpha, s.T, s.nTf_bg * rcp);
   const float g = G * dL_dalpha;
   g_op += g;
@@ -617,17 +660,21 @@ __device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, 
 #define GSB_BWD2_MINB 6
 #endif
 
-__global__ void __launch_bounds__(128, GSB_BWD2_MINB)
+template <bool TWO>
+__global__ void __launch_bounds__(128, TWO ? 5 : GSB_BWD2_MINB)
 render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                    const uint32_t* __restrict__ point_list, int W, int H, int P,
                    const float* __restrict__ bg, const float2* __restrict__ means2D,
                    const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,
                    const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                    const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
-                   float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
+                   float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
+                   const float* __restrict__ colors2, const float* __restrict__ dL_dpixels2,
+                   float* __restrict__ dL_dcolor2) {
   __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold | patch mask, bits(list position)
   __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
+  __shared__ float4 s_c2[TWO ? GSB_BLOCK_SIZE : 1];  // r, g, b of the second colour table
   __shared__ int s_wcnt[8];
   __shared__ int s_block_last;
   __shared__ int s_patch_last[8];
@@ -667,22 +714,34 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     float bg_dot = 0.f;
     bg_dot += b0 * s.dpx0; bg_dot += b1 * s.dpx1; bg_dot += b2 * s.dpx2;
     s.ar0 = s.ar1 = s.ar2 = 0.f;
+    s.br0 = s.br1 = s.br2 = 0.f;
+    s.dq0 = s.dq1 = s.dq2 = 0.f;
+    if (TWO) {
+      if (inside) {
+        const float* dq = dL_dpixels2 + (size_t)cam * 3 * HW;
+        s.dq0 = dq[pid]; s.dq1 = dq[HW + pid]; s.dq2 = dq[2 * HW + pid];
+      }
+      bg_dot += b0 * s.dq0; bg_dot += b1 * s.dq1; bg_dot += b2 * s.dq2;   // both images sit on the same background
+    }
     s.nTf_bg = -T_final * bg_dot;
     s.pfy = (float)py;
   };
   init(A, pyA);
   init(B, pyB);
 
+  // writer lanes: the eight values of warp_reduce8 end in lanes 0, 4, ..., 28; the four values of the second
+  // reduction (opacity term, TWO: the second table's colour gradient) in lanes 1, 9, 17, 25
   float* lane_base;
   unsigned lane_stride;
   {
     const unsigned comp = lane >> 2;
     if (lane == 1) { lane_base = dL_dopacity; lane_stride = 1; }
+    else if (TWO && (lane & 7u) == 1u) { lane_base = dL_dcolor2 + ((lane >> 3) - 1u); lane_stride = 3; }
     else if (comp < 3) { lane_base = dcol_tab + comp; lane_stride = 3; }
     else if (comp < 5) { lane_base = dL_dmean2D + 3 * cam_off + (comp - 3); lane_stride = 3; }
     else { lane_base = dL_dconic + 4 * cam_off + (comp == 7 ? 3 : comp - 5); lane_stride = 4; }
   }
-  const bool lane_writes = ((lane & 3u) == 0) || lane == 1;
+  const bool lane_writes = ((lane & 3u) == 0) || lane == 1 || (TWO && (lane & 7u) == 1u);
 
   int lastA = A.last, lastB = B.last;
 #pragma unroll
@@ -755,6 +814,9 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
         s_co[slot[h]] = co[h];
         s_ci[slot[h]] = make_float4(col_tab[3 * (size_t)id[h]], col_tab[3 * (size_t)id[h] + 1],
                                     col_tab[3 * (size_t)id[h] + 2], __uint_as_float(id[h]));
+        if (TWO)
+          s_c2[slot[h]] = make_float4(colors2[3 * (size_t)id[h]], colors2[3 * (size_t)id[h] + 1],
+                                      colors2[3 * (size_t)id[h] + 2], 0.f);
       }
     __syncthreads();
     for (int j = 0; j < n; j++) {
@@ -782,35 +844,54 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
       const bool validA = preA && !(alphaA < 1.0f / 255.0f), validB = preB && !(alphaB < 1.0f / 255.0f);
       if (!__any_sync(0xffffffffu, validA || validB)) continue;
 
-      float v[8];
-      float g_op = 0.f;
+      float v[8], w[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int k = 0; k < 8; k++) v[k] = 0.f;
       const float4 ci = s_ci[j];
-      bwd_pixel(A, validA, alphaA, GA, dx, dyA, ci, co2.w, v, g_op);
-      bwd_pixel(B, validB, alphaB, GB, dx, dyB, ci, co2.w, v, g_op);
+      const float4 ci2 = TWO ? s_c2[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+      bwd_pixel<TWO>(A, validA, alphaA, GA, dx, dyA, ci, ci2, co2.w, v, w);
+      bwd_pixel<TWO>(B, validB, alphaB, GB, dx, dyB, ci, ci2, co2.w, v, w);
       warp_reduce8(v, lane);
+      float extra;
+      if (TWO) {
+        extra = warp_reduce4(w, lane);   // lanes 8 k .. 8 k + 7 hold component k
+      } else {
+        extra = w[0];
 #pragma unroll
-      for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
+        for (int s = 16; s >= 1; s >>= 1) extra += __shfl_xor_sync(0xffffffffu, extra, s);
+      }
       const uint32_t id2 = __float_as_uint(ci.w);
-      const float val = (lane == 1) ? g_op : v[0];
+      const float val = ((lane & 3u) == 1u) ? extra : v[0];
       if (lane_writes && val != 0.f) atomicAdd(lane_base + id2 * lane_stride, val);
     }
   }
 }
 
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
-                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st) {
+                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st, const float* dL_dpix2,
+                      float* dL_dcolor2) {
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
   static const int two_px = [] { const char* e = getenv("GSB_BWD_2PX"); return e ? atoi(e) : 1; }();
-  if (two_px) {
-    render_bwd2_kernel<<<tiles_total, 128, 0, st>>>(
+  if (dL_dpix2) {   // both images of a two-table forward in one walk
+    if (!a.colors2 || !dL_dcolor2 || a.color_cam_stride != 0) return GSB_EINVAL;
+    render_bwd2_kernel<true><<<tiles_total, 128, 0, st>>>(
         reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
         a.background,
         reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
-        a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+        a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, a.colors2,
+        dL_dpix2, dL_dcolor2);
+    GSB_LAUNCH_CHECK();
+    return GSB_OK;
+  }
+  if (two_px) {
+    render_bwd2_kernel<false><<<tiles_total, 128, 0, st>>>(
+        reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
+        a.background,
+        reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
+        a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, nullptr,
+        nullptr, nullptr);
     GSB_LAUNCH_CHECK();
     return GSB_OK;
   }

@@ -66,7 +66,8 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat = nullptr, int flat_mode = 0,
                           const float* dL_dopacity = nullptr, const float* dL_dcolor = nullptr,
-                          float* dL_dmean2D_out = nullptr, int flat_stride = GSB_FLAT_WIDTH);
+                          float* dL_dmean2D_out = nullptr, int flat_stride = GSB_FLAT_WIDTH,
+                          const float* dL_dcolor2 = nullptr);
 int launch_flat_apply_stats(int P, const float* flat, int flat_stride, float* grad_accum, float* vis_count,
                             float* max_2d_radii, cudaStream_t st);
 int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payload_bytes, int64_t n_float4, int row_float4,
@@ -103,6 +104,7 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
                       cudaStream_t st);
 int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsigned long long* counts, cudaStream_t st);
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
-                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st);
+                      float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st,
+                      const float* dL_dpix2 = nullptr, float* dL_dcolor2 = nullptr);
 
 }  // namespace gsb

@@ -307,7 +307,8 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       const float* __restrict__ dL_dconic, float* __restrict__ dL_dmean3D,
                       float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot,
                       float* __restrict__ flat, int flat_mode, const float* __restrict__ dL_dopacity,
-                      const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out, int flat_stride) {
+                      const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out, int flat_stride,
+                      const float* __restrict__ dL_dcolor2) {
   extern __shared__ float s_mats[];  // [n_cams][32]: view then proj; FLAT: then int [n_cams][2] = split slot, count flag
   for (int i = threadIdx.x; i < n_cams * 32; i += blockDim.x) {
     const int cam = i >> 5, k = i & 31;
@@ -501,7 +502,10 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
       row[1] = make_float4(c1, c2, gq.x, gq.y);
       row[2] = make_float4(gq.z, gq.w, dop, gs[0]);
       row[3] = make_float4(gs[1], gs[2], st_norm, st_cnt);
-      row[4] = make_float4(st_rad, 0.f, 0.f, 0.f);
+      if (dL_dcolor2)   // two-table backward: the second colour table's gradient arrived in the same walk
+        row[4] = make_float4(st_rad, dL_dcolor2[3 * (size_t)idx], dL_dcolor2[3 * (size_t)idx + 1], dL_dcolor2[3 * (size_t)idx + 2]);
+      else
+        row[4] = make_float4(st_rad, 0.f, 0.f, 0.f);
     } else if (flat_mode == 2) {
       // another camera group of the same step (rendered concurrently on its own stream): everything adds up
       float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4];
@@ -593,7 +597,8 @@ int launch_cam_params(int n_cams, int W, int H, const float* tanfov_dev, const i
 int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, const gsb_raster_ctx& c,
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat, int flat_mode,
-                          const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out, int flat_stride) {
+                          const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out, int flat_stride,
+                          const float* dL_dcolor2) {
   if (a.P <= 0) return GSB_OK;
   const size_t smem = (size_t)a.n_cams * (32 * sizeof(float) + (flat ? 2 * sizeof(int) : 0));
   if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
@@ -603,13 +608,13 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, c.cov3D, (size_t)0, reinterpret_cast<const float4*>(c.conic_opacity),
         dL_dmean2D, dL_dconic, nullptr, nullptr, nullptr, nullptr, flat, flat_mode, dL_dopacity, dL_dcolor,
-        dL_dmean2D_out, flat_stride);
+        dL_dmean2D_out, flat_stride, dL_dcolor2);
   } else {
     preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, smem, st>>>(
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
         reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
-        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr, GSB_FLAT_WIDTH);
+        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr, GSB_FLAT_WIDTH, nullptr);
   }
   GSB_LAUNCH_CHECK();
   return GSB_OK;

@@ -77,6 +77,8 @@ SYMBOLS = {
     "gsb_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_raster_backward_flat": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "gsb_raster_backward_flat2": (C.c_int, [C.POINTER(RasterArgs), C.POINTER(RasterCtx), C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "gsb_flat_apply_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 4),
     "gsb_ssim_l1_rows": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
                                    C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -128,8 +128,12 @@ class FirstFrameEngine:
     exchange all ranks hold the same record, so parameters, Adam moments and statistics stay bit-identical.
     A densify event changes P: call rebuild() afterwards (new exchange block, arena, graph)."""
 
-    def __init__(self, parameters, optimizer, n_views, width, height, device, graph=True):
+    def __init__(self, parameters, optimizer, n_views, width, height, device, graph=True, two_table=True):
         self.parameters, self.optimizer = parameters, optimizer
+        # two_table: colours and segmentation colours are blended by ONE forward walk and back-propagated by ONE
+        # backward walk (gsb_raster_args.colors2); False: colour render, then a re-blend of the same geometry with the
+        # segmentation colours and a second backward (the reference's two renders, densify.py:116-150)
+        self.two_table = two_table
         self.n, self.W, self.H, self.dev = int(n_views), int(width), int(height), torch.device(device)
         self.use_graph = graph
         n, dev = self.n, self.dev
@@ -195,12 +199,24 @@ class FirstFrameEngine:
         rot, opa, sca = goptim.activate_into(p, self.act_out)
         act = {"means3D": p["means"].data, "colors_precomp": p["colors"].data, "rotations": rot, "opacities": opa, "scales": sca}
         flat = self.ex.flat
-        loss_c, _, radii, st = gstep.timestep_step(act, self.cams, self.images, self.bg, None, flat=flat, arena=self.arena)
-        seg, _, st2 = raster.reblend(st, p["segmentation_masks"].data, arena=self.arena, name="seg")
-        if self.n == 1:
-            seg = seg[None]
-        loss_s, dLs = gloss.l1_ssim_fused(seg, self.masks, 3 * 0.8, 3 * 0.2, grad=True, arena=self.arena, tag="seg_")
-        raster.backward_flat(st2, dLs, flat, mode=1, scratch=self.arena.bwd_scratch)
+        if self.two_table:
+            c = self.cams
+            color, _, radii, st = raster.forward(act["means3D"], act["colors_precomp"], opa, sca, rot, None, self.bg, 1.0,
+                                                 c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], self.H, self.W,
+                                                 n_cams=self.n, arena=self.arena, tanfov_dev=c["tanfov_dev"],
+                                                 colors2=p["segmentation_masks"].data)
+            if self.n == 1:
+                color = color[None]
+            loss_c, dLc = gloss.l1_ssim_fused(color, self.images, 0.8, 0.2, grad=True, arena=self.arena)
+            loss_s, dLs = gloss.l1_ssim_fused(st.color2, self.masks, 3 * 0.8, 3 * 0.2, grad=True, arena=self.arena, tag="seg_")
+            raster.backward_flat(st, dLc, flat, scratch=self.arena.bwd_scratch, dL_dpix2=dLs)
+        else:
+            loss_c, _, radii, st = gstep.timestep_step(act, self.cams, self.images, self.bg, None, flat=flat, arena=self.arena)
+            seg, _, st2 = raster.reblend(st, p["segmentation_masks"].data, arena=self.arena, name="seg")
+            if self.n == 1:
+                seg = seg[None]
+            loss_s, dLs = gloss.l1_ssim_fused(seg, self.masks, 3 * 0.8, 3 * 0.2, grad=True, arena=self.arena, tag="seg_")
+            raster.backward_flat(st2, dLs, flat, mode=1, scratch=self.arena.bwd_scratch)
         self.ex.allreduce()
         self.stats.apply_flat(flat)
         self.adam.step(flat)

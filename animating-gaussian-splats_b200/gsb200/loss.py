@@ -23,7 +23,7 @@ def _run(img, target, w_l1, w_ssim, want_grad, arena=None, tag="", rows=None):
     if arena is not None:   # buffers that live with the arena: stable addresses, no allocation per step
         scratch = arena.output("ssim_scratch", (lib.gsb_ssim_scratch_bytes(n, H, W),), torch.uint8)
         out = arena.output(tag + "loss_stats", (n, 3), torch.float32)
-        grad = arena.output("dL_dimage", tuple(x.shape), torch.float32) if want_grad else None
+        grad = arena.output(tag + "dL_dimage", tuple(x.shape), torch.float32) if want_grad else None
     else:
         scratch = torch.empty(lib.gsb_ssim_scratch_bytes(n, H, W), dtype=torch.uint8, device=x.device)
         out = torch.empty((n, 3), dtype=torch.float32, device=x.device)
@@ -88,7 +88,7 @@ def calc_ssim(img1, img2, window_size=11, size_average=True):
 def l1_ssim_fused(img, target, w_l1=0.8, w_ssim=0.2, grad=True, arena=None, tag="", rows=None):
     """Non-autograd fast path used by the training step: one call, returns (stats [n,3], dL/dimg or None).
     arena (gsb200.raster.RasterArena): outputs and scratch live in the arena instead of fresh allocations (`tag`
-    names the loss numbers of a second loss in the same step; dL/dimg and the scratch are consumed before it runs).
+    names the loss numbers and dL/dimg of a second loss in the same step; the scratch is shared, the calls run in order).
     rows (int32 [n, 4] = loss_y0, loss_y1, write_y0, write_y1): image bands of tile-band sharding (gsb_ssim_l1_rows)."""
     out, g, squeeze = _run(img, target, w_l1, w_ssim, grad, arena, tag, rows)
     return out, (g[0] if (squeeze and g is not None) else g)

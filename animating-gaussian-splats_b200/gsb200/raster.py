@@ -16,7 +16,7 @@ from . import _lib as L
 class RasterState:
     """What the reference returns to Python as (num_rendered, geomBuffer, binningBuffer, imgBuffer)."""
 
-    __slots__ = ("ctx", "args", "geom", "binning", "img", "keep", "tan_x", "tan_y", "_status")
+    __slots__ = ("ctx", "args", "geom", "binning", "img", "keep", "tan_x", "tan_y", "_status", "color2")
 
     @property
     def num_rendered(self):
@@ -210,7 +210,7 @@ def _as_list(x, n):
 
 def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, scale_modifier, viewmatrix,
             projmatrix, tanfovx, tanfovy, image_height, image_width, prefiltered=False, n_cams=1,
-            colors_per_camera=False, reuse_geometry=False, arena=None, tanfov_dev=None, entries=None):
+            colors_per_camera=False, reuse_geometry=False, arena=None, tanfov_dev=None, entries=None, colors2=None):
     """-> (color [n,3,H,W] or [3,H,W], depth, radii, RasterState).  Single camera squeezes the batch dim.
     reuse_geometry: allow this call to take (and to leave behind) pre-blend state, see "Geometry reuse" above; the
     drop-in autograd node passes True, the batched step does not (every step there has new parameters).
@@ -218,7 +218,9 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
     CUDA-graph capturable; outputs live in the arena; tanfov_dev = tanfov_table(...) (built here if None, which
     costs a host -> device copy and is therefore not capturable).
     entries (int32 CUDA tensor [n_cams, 4] = tile_row0, tile_row1, split_slot, count_visibility): tile-band sharding --
-    every batch entry renders only those tile rows of its camera (include/gsb200.h: gsb_raster_args.entries)."""
+    every batch entry renders only those tile rows of its camera (include/gsb200.h: gsb_raster_args.entries).
+    colors2 ([P, 3]): a second colour table blended in the same walk; its image is left in state.color2 ([n, 3, H, W])
+    and backward_flat(..., dL_dpix2=) back-propagates both images at once."""
     global _geom_cache, geom_cache_hits
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # DGR/rasterize_points.cu:56-58
@@ -251,6 +253,15 @@ def forward(means3D, colors, opacities, scales, rotations, cov3D_precomp, bg, sc
     a.background, a.means3D, a.colors, a.opacities = L.ptr(bgc), L.ptr(m3), L.ptr(col), L.ptr(opa)
     a.scales, a.rotations, a.cov3D_precomp = L.ptr(sca), L.ptr(rot), L.ptr(cov)
     a.viewmatrix, a.projmatrix = L.ptr(vm), L.ptr(pm)
+    st.color2 = None
+    if colors2 is not None and P > 0:
+        c2 = _f32c(colors2, "colors2")
+        if colors_per_camera or tuple(c2.shape) != (P, 3):
+            raise RuntimeError("colors2 must be one [P, 3] table shared by the cameras")
+        st.color2 = (arena.output("color2", (n_cams, 3, H, W), torch.float32) if arena is not None
+                     else torch.empty((n_cams, 3, H, W), dtype=torch.float32, device=dev))
+        st.keep += [c2, st.color2]
+        a.colors2, a.out_color2 = L.ptr(c2), L.ptr(st.color2)
     if entries is not None:
         if entries.dtype != torch.int32 or tuple(entries.shape) != (n_cams, 4) or not entries.is_cuda or not entries.is_contiguous():
             raise RuntimeError("entries must be a contiguous int32 CUDA tensor [n_cams, 4]")
@@ -356,6 +367,7 @@ def reblend(st, colors, arena=None, name="color2"):
     st2.ctx = st.ctx
     st2.geom, st2.binning, st2.img = st.geom, st.binning, st.img
     st2.tan_x, st2.tan_y = st.tan_x, st.tan_y
+    st2.color2 = None
     st2.keep = list(st.keep) + [col]
     a = L.RasterArgs()
     C.memmove(C.byref(a), C.byref(st.args), C.sizeof(L.RasterArgs))
@@ -383,7 +395,7 @@ def reblend(st, colors, arena=None, name="color2"):
 _FLAT_PART = {"all": 0, "blend": 0x100, "finish": 0x200}
 
 
-def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, part="all"):
+def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, part="all", dL_dpix2=None):
     """The step's backward in its exchange form (gsb_raster_backward_flat): the per-Gaussian record -- gradients,
     statistic increments, largest radius -- goes into `flat` [P, 20] (layout: gsb200.dist.COLS).  mode 0 writes every
     column; mode 1 (a second render of the same Gaussians with another colour table) adds the geometry gradients and
@@ -408,6 +420,15 @@ def backward_flat(st, dL_dpix, flat, mode=0, scratch=None, means2D_out=None, par
         dpix = dL_dpix.contiguous()
         if dpix.dtype != torch.float32:
             dpix = dpix.float()
+    if dL_dpix2 is not None:   # both images of a two-table forward (colors2) in one walk
+        if st.color2 is None or mode != 0 or part != "all":
+            raise RuntimeError("dL_dpix2 needs a forward with colors2, mode 0 and part 'all'")
+        d2 = dL_dpix2.contiguous().float()
+        with L.device_guard(flat.device):
+            rc = lib.gsb_raster_backward_flat2(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(d2), L.ptr(scratch), L.ptr(flat),
+                                               int(flat.shape[1]), L.ptr(means2D_out), L.stream_ptr())
+        L.check(rc, "gsb_raster_backward_flat2")
+        return flat
     with L.device_guard(flat.device):
         rc = lib.gsb_raster_backward_flat(C.byref(a), C.byref(c), L.ptr(dpix), L.ptr(scratch), L.ptr(flat), int(flat.shape[1]),
                                           int(mode) | _FLAT_PART[part], L.ptr(means2D_out), L.stream_ptr())

@@ -205,6 +205,14 @@ int gsb_raster_backward_flat(const gsb_raster_args* args, const gsb_raster_ctx* 
                              void* scratch, float* flat, int32_t flat_stride, int32_t mode, float* dL_dmean2D_out,
                              void* stream);
 
+/* The backward of a two-table forward (gsb_raster_args.colors2): dL_dpix of the first image and dL_dpix2 of the second
+ * are back-propagated in ONE walk of the lists (they share alpha, T and every decision; dL/dalpha is the sum over both
+ * images' channels).  Writes every column of flat like mode 0, cols 17-19 = the second table's colour gradient: the
+ * result equals gsb_raster_backward_flat mode 0 on the first render followed by mode 1 on a second render. */
+int gsb_raster_backward_flat2(const gsb_raster_args* args, const gsb_raster_ctx* ctx, const float* dL_dpix,
+                              const float* dL_dpix2, void* scratch, float* flat, int32_t flat_stride,
+                              float* dL_dmean2D_out, void* stream);
+
 /* DensificationVariables update from a (reduced) flat buffer: grad_accum += col 14, vis_count += col 15,
  * max_2d_radii = max(max_2d_radii, col 16) (shared.py:20-26, densify.py:154-162, external.py:113-124); every
  * split-camera slot (cols 20 + 2 j, 21 + 2 j < flat_stride) adds the norm of its summed gradient to grad_accum. */

@@ -250,3 +250,36 @@ def test_camera_groups_equal_one_batch(n_groups):
         assert bad == 0, (n_groups, bad, worst)
         assert torch.equal(flat[:, 15:17], flat_one[:, 15:17])
         assert float(flat[:, 17:].abs().max()) == 0.0
+
+
+def test_two_table_walk_equals_two_renders():
+    """colors2: both images from one forward walk are bit-identical to two separate renders, and the one-walk backward
+    of both image gradients equals mode 0 on the first render + mode 1 on the second."""
+    from gsb200 import raster
+    dev, g, a, cams, sc, bg, targets = _setup()
+    n, P = 3, a["means3D"].shape[0]
+    seg = torch.rand((P, 3), generator=torch.Generator().manual_seed(9)).to(dev)
+    c1, d1, r1, st1 = _fwd(a, sc, bg, n)
+    c2, _, _, st2 = _fwd(dict(a, colors_precomp=seg), sc, bg, n)
+    c1, c2 = c1.clone(), c2.clone()
+    cf, df, rf, stf = _fwd(a, sc, bg, n, colors2=seg)
+    assert torch.equal(cf, c1) and torch.equal(stf.color2, c2) and torch.equal(df, d1) and torch.equal(rf, r1)
+    assert torch.equal(stf.tensors()["n_contrib"], st1.tensors()["n_contrib"])
+    dL1 = torch.randn(c1.shape, generator=torch.Generator().manual_seed(2)).to(dev)
+    dL2 = torch.randn(c1.shape, generator=torch.Generator().manual_seed(3)).to(dev)
+    want = torch.zeros((P, 20), device=dev)
+    raster.backward_flat(st1, dL1, want)
+    raster.backward_flat(st2, dL2, want, mode=1)
+    got = torch.full((P, 20), float("nan"), device=dev)
+    raster.backward_flat(stf, dL1, got, dL_dpix2=dL2)
+    torch.cuda.synchronize()
+    for a_, b_ in ((0, 14), (17, 20)):
+        bad, worst = helpers.grad_close(helpers.to_np(got[:, a_:b_]), helpers.to_np(want[:, a_:b_]), rel=1e-4, floor=1e-5)
+        assert bad == 0, (a_, bad, worst)
+    assert torch.equal(got[:, 15:17], want[:, 15:17])
+    assert torch.allclose(got[:, 14], want[:, 14], rtol=1e-5, atol=1e-9)
+    # the asynchronous path too
+    R = st1.num_rendered
+    arena = raster.RasterArena(dev).reserve(P, n, 200, 120, capacity=int(1.3 * R))
+    ca, _, _, sta = _fwd(a, sc, bg, n, arena=arena, colors2=seg)
+    assert torch.equal(ca, c1) and torch.equal(sta.color2, c2)
