@@ -443,8 +443,9 @@ int gsb_raster_backward(const gsb_raster_args* a, const gsb_raster_ctx* ctx, con
 
 size_t gsb_backward_scratch_bytes(int32_t P, int32_t n_cams) {
   // raw second moments [n_cams][P][4] (read as float4: first, so they stay 16-byte aligned for any P) | raw first
-  // moments [n_cams][P][3] | dL/dopacity [P] | dL/dcolor [P][3] | dL/dcolor of a second table [P][3]
-  return align_up(((size_t)P * n_cams * 7 + (size_t)P * 7) * sizeof(float), 256);
+  // moments [n_cams][P][3] | dL/dopacity [P] | dL/dcolor [P][3] | two-table backward: dL/dcolor of the second table
+  // [P][3] | first moments of the first image alone [n_cams][P][2]
+  return align_up(((size_t)P * n_cams * 9 + (size_t)P * 7) * sizeof(float), 256);
 }
 
 }  // extern "C"
@@ -470,21 +471,22 @@ static int backward_flat_impl(const gsb_raster_args* a, const gsb_raster_ctx* ct
   float* dop = m1 + 3 * n;
   float* dcol = dop + a->P;
   float* dcol2 = dL_dpix2 ? dcol + 3 * (size_t)a->P : nullptr;
+  float* m1f = dL_dpix2 ? dcol2 + 3 * (size_t)a->P : nullptr;
   if (dL_dpix2 && (mode != 0 || part != 0 || !a->colors2)) return GSB_EINVAL;
   int rc;
   if (part != GSB_FLAT_FINISH_ONLY) {
     prof_mark(PF_BWD_BEGIN, st);
-    GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * 7 + (size_t)a->P * (dL_dpix2 ? 7 : 4)) * sizeof(float), st));   // one fill
+    GSB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (n * (dL_dpix2 ? 9 : 7) + (size_t)a->P * (dL_dpix2 ? 7 : 4)) * sizeof(float), st));   // one fill
     prof_mark(PF_BWD_ZERO, st);
     if (ctx->num_rendered != 0)
-      if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st, dL_dpix2, dcol2))) return rc;
+      if ((rc = launch_render_bwd(*a, *ctx, dL_dpix, m1, m2, dop, dcol, st, dL_dpix2, dcol2, m1f))) return rc;
     prof_mark(PF_RENDER_BWD, st);
     if (part == GSB_FLAT_BLEND_ONLY) return GSB_OK;
   }
   GeomExtras gx;
   GeomLayout::carve(reinterpret_cast<char*>(ctx->depths), a->P, a->n_cams, nullptr, &gx);
   if ((rc = launch_preprocess_bwd(*a, gx.cams, *ctx, m1, m2, nullptr, nullptr, nullptr, nullptr, st, flat, mode, dop, dcol,
-                                  dL_dmean2D_out, flat_stride, dcol2)))
+                                  dL_dmean2D_out, flat_stride, dcol2, m1f)))
     return rc;
   prof_mark(PF_PREPROCESS_BWD, st);
   return GSB_OK;

@@ -399,31 +399,6 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
   v[0] += __shfl_xor_sync(full, v[0], 1);
 }
 
-// Sum 4 values over the 32 lanes with 5 shuffles; afterwards every lane of the group 8 k .. 8 k + 7 holds the full
-// warp sum of component k.
-__device__ __forceinline__ float warp_reduce4(float (&v)[4], unsigned lane) {
-  const unsigned full = 0xffffffffu;
-  {
-    const bool up = lane & 16u;
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-      const float send = up ? v[i] : v[i + 2];
-      const float keep = up ? v[i + 2] : v[i];
-      v[i] = keep + __shfl_xor_sync(full, send, 16);
-    }
-  }
-  {
-    const bool up = lane & 8u;
-    const float send = up ? v[0] : v[1];
-    const float keep = up ? v[1] : v[0];
-    v[0] = keep + __shfl_xor_sync(full, send, 8);
-  }
-  v[0] += __shfl_xor_sync(full, v[0], 4);
-  v[0] += __shfl_xor_sync(full, v[0], 2);
-  v[0] += __shfl_xor_sync(full, v[0], 1);
-  return v[0];
-}
-
 __global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_BWD_MINB)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
                   const uint32_t* __restrict__ point_list, int W, int H, int P,
@@ -605,15 +580,17 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 struct BwdPixel {
   float T, ar0, ar1, ar2, dpx0, dpx1, dpx2, nTf_bg, pfy;
   int last;
-  float br0, br1, br2, dq0, dq1, dq2;   // TWO: accum_rec and dL/dpixel of the second image
+  float br0, br1, br2, dq0, dq1, dq2, nTf_bgi;   // TWO: accum_rec / dL/dpixel of the second image, background term of the first
 };
 
 // TWO: the pixel belongs to two images blended from two colour tables in one walk (render_fwd_kernel<.., TWO>): alpha, T
 // and the decisions are shared, dL/dalpha is the sum over both images' channels, the second table's colour gradient
-// goes to w[1..3] (w[0] carries the opacity term g_op).
+// goes to w[1..3] (w[0] carries the opacity term g_op), and w[4..5] are the first moments of the FIRST image's share
+// alone: the densification statistic is the norm of the colour render's screen-space gradient, not of the sum
+// (densify.py:147-150 reads means_2d.grad of the colour render's carrier).
 template <bool TWO>
 __device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, float G, float dx, float dy, float4 ci,
-                                          float4 ci2, float opac, float (&v)[8], float (&w)[4]) {
+                                          float4 ci2, float opac, float (&v)[8], float (&w)[8]) {
   float& g_op = w[0];
   if (!valid) return;
   const float om = 1.f - alpha;
@@ -633,6 +610,9 @@ __device__ __forceinline__ void bwd_pixel(BwdPixel& s, bool valid, float alpha, 
   v[1] = fmaf(dchannel_dcolor, s.dpx1, v[1]);
   v[2] = fmaf(dchannel_dcolor, s.dpx2, v[2]);
   if (TWO) {
+    const float wgi = opac * (G * fmaf(dL_dalpha, s.T, s.nTf_bgi * rcp));   // the first image's share of opac * dL/dG * G
+    w[4] = fmaf(wgi, dx, w[4]);
+    w[5] = fmaf(wgi, dy, w[5]);
     const float e0 = ci2.x - s.br0, e1 = ci2.y - s.br1, e2 = ci2.z - s.br2;
     dL_dalpha = fmaf(e0, s.dq0, dL_dalpha);
     dL_dalpha = fmaf(e1, s.dq1, dL_dalpha);
@@ -670,7 +650,7 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
                    const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
                    float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
                    const float* __restrict__ colors2, const float* __restrict__ dL_dpixels2,
-                   float* __restrict__ dL_dcolor2) {
+                   float* __restrict__ dL_dcolor2, float* __restrict__ dL_dmean2D_first /* [n_cams][P][2] */) {
   __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold | patch mask, bits(list position)
   __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
   __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
@@ -716,6 +696,7 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     s.ar0 = s.ar1 = s.ar2 = 0.f;
     s.br0 = s.br1 = s.br2 = 0.f;
     s.dq0 = s.dq1 = s.dq2 = 0.f;
+    s.nTf_bgi = -T_final * bg_dot;
     if (TWO) {
       if (inside) {
         const float* dq = dL_dpixels2 + (size_t)cam * 3 * HW;
@@ -729,19 +710,21 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   init(A, pyA);
   init(B, pyB);
 
-  // writer lanes: the eight values of warp_reduce8 end in lanes 0, 4, ..., 28; the four values of the second
-  // reduction (opacity term, TWO: the second table's colour gradient) in lanes 1, 9, 17, 25
+  // writer lanes: after warp_reduce8 the four lanes 4 k .. 4 k + 3 hold component k.  Lane 4 k writes component k of
+  // the first group; lane 4 k + 1 component k of the second group (k = 0: the opacity term; TWO: k = 1..3 the second
+  // table's colour gradient, k = 4, 5 the first image's first moments)
   float* lane_base;
   unsigned lane_stride;
   {
     const unsigned comp = lane >> 2;
     if (lane == 1) { lane_base = dL_dopacity; lane_stride = 1; }
-    else if (TWO && (lane & 7u) == 1u) { lane_base = dL_dcolor2 + ((lane >> 3) - 1u); lane_stride = 3; }
+    else if (TWO && (lane & 3u) == 1u && comp < 4) { lane_base = dL_dcolor2 + (comp - 1u); lane_stride = 3; }
+    else if (TWO && (lane & 3u) == 1u) { lane_base = dL_dmean2D_first + 2 * cam_off + (comp & 1u); lane_stride = 2; }
     else if (comp < 3) { lane_base = dcol_tab + comp; lane_stride = 3; }
     else if (comp < 5) { lane_base = dL_dmean2D + 3 * cam_off + (comp - 3); lane_stride = 3; }
     else { lane_base = dL_dconic + 4 * cam_off + (comp == 7 ? 3 : comp - 5); lane_stride = 4; }
   }
-  const bool lane_writes = ((lane & 3u) == 0) || lane == 1 || (TWO && (lane & 7u) == 1u);
+  const bool lane_writes = ((lane & 3u) == 0) || lane == 1 || (TWO && (lane & 3u) == 1u && lane < 24u);
 
   int lastA = A.last, lastB = B.last;
 #pragma unroll
@@ -844,7 +827,7 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
       const bool validA = preA && !(alphaA < 1.0f / 255.0f), validB = preB && !(alphaB < 1.0f / 255.0f);
       if (!__any_sync(0xffffffffu, validA || validB)) continue;
 
-      float v[8], w[4] = {0.f, 0.f, 0.f, 0.f};
+      float v[8], w[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int k = 0; k < 8; k++) v[k] = 0.f;
       const float4 ci = s_ci[j];
@@ -854,7 +837,8 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
       warp_reduce8(v, lane);
       float extra;
       if (TWO) {
-        extra = warp_reduce4(w, lane);   // lanes 8 k .. 8 k + 7 hold component k
+        warp_reduce8(w, lane);   // lanes 4 k .. 4 k + 3 hold component k
+        extra = w[0];
       } else {
         extra = w[0];
 #pragma unroll
@@ -869,19 +853,19 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
 
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
                       float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st, const float* dL_dpix2,
-                      float* dL_dcolor2) {
+                      float* dL_dcolor2, float* dL_dmean2D_first) {
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
   dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
   static const int two_px = [] { const char* e = getenv("GSB_BWD_2PX"); return e ? atoi(e) : 1; }();
   if (dL_dpix2) {   // both images of a two-table forward in one walk
-    if (!a.colors2 || !dL_dcolor2 || a.color_cam_stride != 0) return GSB_EINVAL;
+    if (!a.colors2 || !dL_dcolor2 || !dL_dmean2D_first || a.color_cam_stride != 0) return GSB_EINVAL;
     render_bwd2_kernel<true><<<tiles_total, 128, 0, st>>>(
         reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
         a.background,
         reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
         a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, a.colors2,
-        dL_dpix2, dL_dcolor2);
+        dL_dpix2, dL_dcolor2, dL_dmean2D_first);
     GSB_LAUNCH_CHECK();
     return GSB_OK;
   }
@@ -891,7 +875,7 @@ int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const f
         a.background,
         reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
         a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, nullptr,
-        nullptr, nullptr);
+        nullptr, nullptr, nullptr);
     GSB_LAUNCH_CHECK();
     return GSB_OK;
   }

@@ -67,7 +67,7 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat = nullptr, int flat_mode = 0,
                           const float* dL_dopacity = nullptr, const float* dL_dcolor = nullptr,
                           float* dL_dmean2D_out = nullptr, int flat_stride = GSB_FLAT_WIDTH,
-                          const float* dL_dcolor2 = nullptr);
+                          const float* dL_dcolor2 = nullptr, const float* dL_dmean2D_first = nullptr);
 int launch_flat_apply_stats(int P, const float* flat, int flat_stride, float* grad_accum, float* vis_count,
                             float* max_2d_radii, cudaStream_t st);
 int launch_allreduce_flat(int rank, int world, void* const* peers, size_t payload_bytes, int64_t n_float4, int row_float4,
@@ -105,6 +105,6 @@ int launch_render_fwd(const gsb_raster_args& a, const gsb_raster_ctx& c, float* 
 int launch_count_pairs(const gsb_raster_args& a, const gsb_raster_ctx& c, unsigned long long* counts, cudaStream_t st);
 int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const float* dL_dpix, float* dL_dmean2D,
                       float* dL_dconic, float* dL_dopacity, float* dL_dcolor, cudaStream_t st,
-                      const float* dL_dpix2 = nullptr, float* dL_dcolor2 = nullptr);
+                      const float* dL_dpix2 = nullptr, float* dL_dcolor2 = nullptr, float* dL_dmean2D_first = nullptr);
 
 }  // namespace gsb

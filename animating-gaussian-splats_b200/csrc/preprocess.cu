@@ -308,7 +308,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
                       float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscale, float* __restrict__ dL_drot,
                       float* __restrict__ flat, int flat_mode, const float* __restrict__ dL_dopacity,
                       const float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean2D_out, int flat_stride,
-                      const float* __restrict__ dL_dcolor2) {
+                      const float* __restrict__ dL_dcolor2, const float* __restrict__ dL_dmean2D_first) {
   extern __shared__ float s_mats[];  // [n_cams][32]: view then proj; FLAT: then int [n_cams][2] = split slot, count flag
   for (int i = threadIdx.x; i < n_cams * 32; i += blockDim.x) {
     const int cam = i >> 5, k = i & 31;
@@ -365,20 +365,26 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float g2x = -(0.5f * W) * (con.x * rs1 + con.y * rs2);
     const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
     if (FLAT) {
+      float n2x = g2x, n2y = g2y;   // the gradient whose norm is the statistic: the first (colour) image's alone
+      if (dL_dmean2D_first) {
+        const float f1 = dL_dmean2D_first[2 * o], f2 = dL_dmean2D_first[2 * o + 1];
+        n2x = -(0.5f * W) * (con.x * f1 + con.y * f2);
+        n2y = -(0.5f * H) * (con.z * f2 + con.y * f1);
+      }
       const int split_slot = s_entry[2 * cam];
       if (split_slot >= 0) {
         // rows of this camera are rendered elsewhere too: the norm belongs to the SUMMED gradient (after the exchange)
         float* slot = flat + (size_t)idx * flat_stride + GSB_FLAT_WIDTH + 2 * split_slot;
-        if (flat_mode == 0) { slot[0] = g2x; slot[1] = g2y; }
-        else if (flat_mode == 2) { slot[0] += g2x; slot[1] += g2y; }
+        if (flat_mode == 0) { slot[0] = n2x; slot[1] = n2y; }
+        else if (flat_mode == 2) { slot[0] += n2x; slot[1] += n2y; }
       } else {
-        st_norm += sqrtf(g2x * g2x + g2y * g2y);   // torch.norm of the first two components, one term per camera
+        st_norm += sqrtf(n2x * n2x + n2y * n2y);   // torch.norm of the first two components, one term per camera
       }
       if (s_entry[2 * cam + 1]) {
         st_cnt += 1.0f;
         st_rad = fmaxf(st_rad, (float)rad);
       }
-      if (dL_dmean2D_out) { dL_dmean2D_out[3 * o] = g2x; dL_dmean2D_out[3 * o + 1] = g2y; dL_dmean2D_out[3 * o + 2] = 0.f; }
+      if (dL_dmean2D_out) { dL_dmean2D_out[3 * o] = n2x; dL_dmean2D_out[3 * o + 1] = n2y; dL_dmean2D_out[3 * o + 2] = 0.f; }
     } else {
       dL_dmean2D[3 * o] = g2x;
       dL_dmean2D[3 * o + 1] = g2y;
@@ -598,7 +604,7 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
                           float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcov3D,
                           float* dL_dscale, float* dL_drot, cudaStream_t st, float* flat, int flat_mode,
                           const float* dL_dopacity, const float* dL_dcolor, float* dL_dmean2D_out, int flat_stride,
-                          const float* dL_dcolor2) {
+                          const float* dL_dcolor2, const float* dL_dmean2D_first) {
   if (a.P <= 0) return GSB_OK;
   const size_t smem = (size_t)a.n_cams * (32 * sizeof(float) + (flat ? 2 * sizeof(int) : 0));
   if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
@@ -608,13 +614,13 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, c.cov3D, (size_t)0, reinterpret_cast<const float4*>(c.conic_opacity),
         dL_dmean2D, dL_dconic, nullptr, nullptr, nullptr, nullptr, flat, flat_mode, dL_dopacity, dL_dcolor,
-        dL_dmean2D_out, flat_stride, dL_dcolor2);
+        dL_dmean2D_out, flat_stride, dL_dcolor2, dL_dmean2D_first);
   } else {
     preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, smem, st>>>(
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
         reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
-        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr, GSB_FLAT_WIDTH, nullptr);
+        dL_dcov3D, dL_dscale, dL_drot, nullptr, 0, nullptr, nullptr, nullptr, GSB_FLAT_WIDTH, nullptr, nullptr);
   }
   GSB_LAUNCH_CHECK();
   return GSB_OK;
