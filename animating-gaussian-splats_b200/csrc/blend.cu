@@ -202,10 +202,13 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_color, float* __restrict__ out_depth,
                   unsigned long long* __restrict__ pair_counts, const float* __restrict__ colors2,
                   float* __restrict__ out_color2) {
-  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position + 1)
-  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
-  __shared__ float4 s_cd[GSB_BLOCK_SIZE];  // r, g, b, depth
-  __shared__ float4 s_c2[TWO ? GSB_BLOCK_SIZE : 1];  // r, g, b of the second table
+  // one array, so that the inner loop addresses all of an entry's records from ONE register with immediate offsets
+  // (as separate arrays every access recomputed its shared-window base: ~8 of the loop's 58 instructions)
+  __shared__ float4 s_stage[TWO ? 4 : 3][GSB_BLOCK_SIZE];
+  float4* const s_a = s_stage[0];    // x, y, early-reject power threshold, bits(list position + 1)
+  float4* const s_co = s_stage[1];   // conic a, b, c, opacity
+  float4* const s_cd = s_stage[2];   // r, g, b, depth
+  float4* const s_c2 = s_stage[TWO ? 3 : 2];   // TWO: r, g, b of the second table
   __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
 
   const TileCoord tc = tile_coord(order, tiles_x, tiles_pc);
@@ -271,7 +274,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const float alpha = fminf(0.99f, MUL(co2.w, expf(power)));
       if (alpha < 1.0f / 255.0f) continue;
       const float test_T = MUL(T, SUB(1.0f, alpha));
-      if (test_T < 0.0001f) { done = true; continue; }
+      if (test_T < 0.0001f) { done = true; break; }
       const float4 cd = s_cd[j];
       C0 = FMA(T, MUL(alpha, cd.x), C0);
       C1 = FMA(T, MUL(alpha, cd.y), C1);
@@ -651,10 +654,12 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
                    float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
                    const float* __restrict__ colors2, const float* __restrict__ dL_dpixels2,
                    float* __restrict__ dL_dcolor2, float* __restrict__ dL_dmean2D_first /* [n_cams][P][2] */) {
-  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold | patch mask, bits(list position)
-  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
-  __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
-  __shared__ float4 s_c2[TWO ? GSB_BLOCK_SIZE : 1];  // r, g, b of the second colour table
+  // one array: an entry's records are addressed from one register with immediate offsets (see render_fwd_kernel)
+  __shared__ float4 s_stage[TWO ? 4 : 3][GSB_BLOCK_SIZE];
+  float4* const s_a = s_stage[0];    // x, y, early-reject power threshold | patch mask, bits(list position)
+  float4* const s_co = s_stage[1];   // conic a, b, c, opacity
+  float4* const s_ci = s_stage[2];   // r, g, b, bits(id)
+  float4* const s_c2 = s_stage[TWO ? 3 : 2];   // TWO: r, g, b of the second colour table
   __shared__ int s_wcnt[8];
   __shared__ int s_block_last;
   __shared__ int s_patch_last[8];
