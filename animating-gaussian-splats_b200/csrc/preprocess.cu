@@ -296,7 +296,9 @@ __device__ __forceinline__ M3 m3_t(const M3& A) {
 // camera-summed opacity / colour gradients and the densification-statistic increments of this batch
 // (per-camera ||dL/dmean2D.xy|| summed over the visible cameras, their count, the largest radius), so that no
 // pack pass, no statistics launch and no separate gradient tables exist on the multi-GPU path.
-template <bool FLAT>
+// TWO (FLAT only): the batch was rendered with two colour tables in one walk: the second table's colour gradient fills
+// cols 17-19 and the statistic's norm is taken of the first image's screen-space gradient alone.
+template <bool FLAT, bool TWO>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* __restrict__ means3D,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -366,7 +368,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
     const float g2y = -(0.5f * H) * (con.z * rs2 + con.y * rs1);
     if (FLAT) {
       float n2x = g2x, n2y = g2y;   // the gradient whose norm is the statistic: the first (colour) image's alone
-      if (dL_dmean2D_first) {
+      if (TWO) {
         const float f1 = dL_dmean2D_first[2 * o], f2 = dL_dmean2D_first[2 * o + 1];
         n2x = -(0.5f * W) * (con.x * f1 + con.y * f2);
         n2y = -(0.5f * H) * (con.z * f2 + con.y * f1);
@@ -508,7 +510,7 @@ preprocess_bwd_kernel(int P, int n_cams, int W, int H, float mod, const float* _
       row[1] = make_float4(c1, c2, gq.x, gq.y);
       row[2] = make_float4(gq.z, gq.w, dop, gs[0]);
       row[3] = make_float4(gs[1], gs[2], st_norm, st_cnt);
-      if (dL_dcolor2)   // two-table backward: the second colour table's gradient arrived in the same walk
+      if (TWO)   // two-table backward: the second colour table's gradient arrived in the same walk
         row[4] = make_float4(st_rad, dL_dcolor2[3 * (size_t)idx], dL_dcolor2[3 * (size_t)idx + 1], dL_dcolor2[3 * (size_t)idx + 2]);
       else
         row[4] = make_float4(st_rad, 0.f, 0.f, 0.f);
@@ -610,13 +612,15 @@ int launch_preprocess_bwd(const gsb_raster_args& a, const CamParams* cams_dev, c
   if (a.n_cams > GSB_MAX_CAMS) return GSB_EINVAL;   // gsb_raster_forward refuses such batches as well
   if (flat) {
     if (!dL_dopacity || !dL_dcolor || !a.scales || !a.rotations) return GSB_EINVAL;
-    preprocess_bwd_kernel<true><<<(a.P + 255) / 256, 256, smem, st>>>(
+    if ((dL_dcolor2 != nullptr) != (dL_dmean2D_first != nullptr)) return GSB_EINVAL;
+    auto kern = dL_dcolor2 ? preprocess_bwd_kernel<true, true> : preprocess_bwd_kernel<true, false>;
+    kern<<<(a.P + 255) / 256, 256, smem, st>>>(
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, c.cov3D, (size_t)0, reinterpret_cast<const float4*>(c.conic_opacity),
         dL_dmean2D, dL_dconic, nullptr, nullptr, nullptr, nullptr, flat, flat_mode, dL_dopacity, dL_dcolor,
         dL_dmean2D_out, flat_stride, dL_dcolor2, dL_dmean2D_first);
   } else {
-    preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, smem, st>>>(
+    preprocess_bwd_kernel<false, false><<<(a.P + 255) / 256, 256, smem, st>>>(
         a.P, a.n_cams, a.width, a.height, a.scale_modifier, a.means3D, a.scales, a.rotations, a.viewmatrix,
         a.projmatrix, cams_dev, c.radii, a.cov3D_precomp ? a.cov3D_precomp : c.cov3D, (size_t)0,
         reinterpret_cast<const float4*>(c.conic_opacity), dL_dmean2D, dL_dconic, dL_dmean3D,
