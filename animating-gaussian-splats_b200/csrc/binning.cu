@@ -5,6 +5,7 @@
 // All integer work: results are bit-identical to the reference by construction (inclusive prefix
 // sum; *stable* ascending LSD sort on bits [0, end_bit)).
 #include <algorithm>
+#include <mutex>
 #include "common.cuh"
 
 namespace gsb {
@@ -156,6 +157,58 @@ int launch_inclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, void
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of the scan (gsb_inclusive_scan_u32_static): the ticket + tile status words live in a
+// file-scope device array instead of a caller buffer.  Every GPU that loads the library holds the array until exit.
+// In host code `g_scan_static` is only a stand-in for the symbol, NOT a device address: the address is taken once per
+// device with cudaGetSymbolAddress (that device current) and that pointer is what the kernel receives.
+// ------------------------------------------------------------------------------------------------
+constexpr int64_t SCAN_STATIC_MAX_ITEMS = (int64_t)GSB_SCAN_STATIC_MAX_ITEMS;
+constexpr size_t SCAN_STATIC_BYTES =
+    (16 + (size_t)((SCAN_STATIC_MAX_ITEMS + SCAN_TILE - 1) / SCAN_TILE) * sizeof(unsigned long long) + 255) / 256 * 256;
+static __device__ __align__(256) unsigned char g_scan_static[SCAN_STATIC_BYTES];
+
+constexpr int SCAN_STATIC_MAX_DEVICES = 64;
+static void* g_scan_static_ptr[SCAN_STATIC_MAX_DEVICES];   // device address of g_scan_static, per device ordinal
+static std::mutex g_scan_static_mu;
+
+static int scan_static_address(void** out) {
+  int dev = -1;
+  GSB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= SCAN_STATIC_MAX_DEVICES) return GSB_EINVAL;
+  std::lock_guard<std::mutex> lock(g_scan_static_mu);
+  if (!g_scan_static_ptr[dev]) {
+    void* p = nullptr;
+    GSB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_scan_static));
+    if (!p) return GSB_ECUDA;
+    g_scan_static_ptr[dev] = p;
+  }
+  *out = g_scan_static_ptr[dev];
+  return GSB_OK;
+}
+
+static int launch_inclusive_scan_u32_static(int64_t n, const uint32_t* in, uint32_t* out, cudaStream_t st) {
+  if (n <= 0) return GSB_OK;
+  if (n > SCAN_STATIC_MAX_ITEMS) {
+    set_last_error("gsb_inclusive_scan_u32_static: n exceeds GSB_SCAN_STATIC_MAX_ITEMS (use gsb_inclusive_scan_u32 "
+                   "with a caller scratch buffer)", cudaErrorInvalidValue);
+    return GSB_EINVAL;
+  }
+  void* scratch = nullptr;
+  const int rc = scan_static_address(&scratch);
+  if (rc) return rc;
+  // the array keeps the previous call's ticket and status words: clear what this call will use
+  return launch_inclusive_scan_u32(n, in, out, scratch, st, nullptr, 0);
+}
+}  // namespace gsb
+
+extern "C" int gsb_inclusive_scan_u32_static(int32_t n, const uint32_t* in, uint32_t* out, void* stream) {
+  if (n < 0 || (n > 0 && (!in || !out))) return GSB_EINVAL;
+  return gsb::launch_inclusive_scan_u32_static(n, in, out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+namespace gsb {
 
 // ------------------------------------------------------------------------------------------------
 // duplicateWithKeys (cr/rasterizer_impl.cu:70-111), warp-cooperative: a warp owns 32 consecutive

@@ -106,6 +106,7 @@ SYMBOLS = {
     "gsb_mask_scan": (C.c_int, [C.c_int32] + [C.c_void_p] * 5),
     "gsb_gather_rows": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "gsb_inclusive_scan_u32": (C.c_int, [C.c_int32] + [C.c_void_p] * 4),
+    "gsb_inclusive_scan_u32_static": (C.c_int, [C.c_int32] + [C.c_void_p] * 3),
     "gsb_sort_temp_bytes": (C.c_size_t, [C.c_int64]),
     "gsb_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                  C.c_void_p]),

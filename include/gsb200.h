@@ -422,6 +422,18 @@ int gsb_positional_encoding(int64_t rows, int32_t D, int32_t F, const float* x, 
 /* Debug / test accessors: the individual stages, so that tests can compare every intermediate
  * bit-for-bit. */
 int gsb_inclusive_scan_u32(int32_t n, const uint32_t* in, uint32_t* out, void* scratch, void* stream);
+/* Allocation-free variant of gsb_inclusive_scan_u32.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernel and same result, but the scan's scratch (ticket + tile status words) is a
+ * file-scope `static __device__` array inside the library -- gsb_scan_scratch_bytes(GSB_SCAN_STATIC_MAX_ITEMS) =
+ * 65 792 bytes, held by every GPU that loads the library until exit -- whose device address is taken once per device
+ * with cudaGetSymbolAddress.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine);
+ * the caller still passes `in` and `out`.  n > GSB_SCAN_STATIC_MAX_ITEMS returns GSB_EINVAL (gsb_last_error() says
+ * why).  Every call on a device shares the one array, which keeps the previous call's contents: the call clears the
+ * words it uses first (a cudaMemsetAsync on `stream`), and two calls that OVERLAP on the same GPU (different streams,
+ * or graphs replayed concurrently) race on it -- serialise them. */
+#define GSB_SCAN_STATIC_MAX_ITEMS (1 << 24)
+int gsb_inclusive_scan_u32_static(int32_t n, const uint32_t* in, uint32_t* out, void* stream);
 size_t gsb_sort_temp_bytes(int64_t n);
 int gsb_sort_pairs(int64_t n, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in,
                    uint32_t* vals_out, int32_t end_bit, void* temp, void* stream);
