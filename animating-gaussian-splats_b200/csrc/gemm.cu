@@ -343,12 +343,12 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 // whole range in TMEM (up to 2 x [128 x 256] FP32 = all 512 columns) and writes ONE partial [N, K]; a second kernel sums
 // the partials.  N, K multiples of 32, <= 256.
 // ------------------------------------------------------------------------------------------------
-constexpr int WG_BK = 32;   // reduction rows per stage
 
+template <int BK>
 __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t saddr) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)((WG_BK * 128) >> 4) << 16;   // leading byte offset: next block of 32 floats along M / N
+  d |= (uint64_t)((BK * 128) >> 4) << 16;      // leading byte offset: next block of 32 floats along M / N
   d |= (uint64_t)(512 >> 4) << 32;             // stride byte offset: next group of 4 reduction rows
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)1 << 61;                      // SWIZZLE_128B_BASE32B: the only MN-major layout for 32-bit operands
@@ -361,15 +361,22 @@ struct WgradParams {
   float* partial;   // [gridDim.x][N][K]
 };
 
-__global__ void __launch_bounds__(GM_THREADS, 1)
+// SPLIT (gsb_linear_wgrad_tf32x3): the 3xTF32 form.  Both operands stream, so both are split where they land: four
+// extra warps turn every landed stage in place into hi = x & ~0x1fff and write lo = x - hi into a second copy of the
+// stage (same swizzled offsets), and the issuer accumulates Ghi Xhi + Ghi Xlo + Glo Xhi.  BK = reduction rows per stage
+// (16 with SPLIT so that three double-size stages fit in shared memory at N = K = 256).
+template <bool SPLIT, int BK>
+__global__ void __launch_bounds__(GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), 1)
 wgrad_tf32_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_x, WgradParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES], empty_bar[GM_MAX_STAGES], acc_full;
+  __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES], empty_bar[GM_MAX_STAGES], split_bar[GM_MAX_STAGES], acc_full;
   __shared__ uint32_t tmem_base_s;
+  constexpr int WG_BK = BK;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int a_bytes = p.npad * 128, b_bytes = p.K * 128;
-  const int stage_bytes = a_bytes + b_bytes;
+  const int a_bytes = p.npad * (WG_BK * 4), b_bytes = p.K * (WG_BK * 4);
+  const int half_bytes = a_bytes + b_bytes;            // [A | B]; SPLIT: followed by [A_lo | B_lo]
+  const int stage_bytes = half_bytes * (SPLIT ? 2 : 1);
   const long long blocks = (p.rows + WG_BK - 1) / WG_BK;
   const long long b0 = blocks * blockIdx.x / gridDim.x, b1 = blocks * (blockIdx.x + 1) / gridDim.x;
   const int halves = p.npad / 128;
@@ -377,7 +384,11 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_consta
                         : halves * p.K <= 256 ? 256 : 512;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < p.stages; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&split_bar[s], GM_SPLIT_WARPS * 32);
+    }
     mbar_init(&acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -400,7 +411,7 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_consta
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* a = smem + (size_t)stage * stage_bytes;
         uint8_t* bt = a + a_bytes;
-        mbar_expect_tx(&full_bar[stage], (uint32_t)((p.N + p.K) * 128));
+        mbar_expect_tx(&full_bar[stage], (uint32_t)((p.N + p.K) * (WG_BK * 4)));
         for (int nb = 0; nb < p.N / 32; nb++) tma_load_2d(&map_g, &full_bar[stage], a + nb * (WG_BK * 128), nb * 32, (int)(b * WG_BK));
         for (int kb = 0; kb < p.K / 32; kb++) tma_load_2d(&map_x, &full_bar[stage], bt + kb * (WG_BK * 128), kb * 32, (int)(b * WG_BK));
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -414,22 +425,57 @@ wgrad_tf32_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       for (long long b = b0; b < b1; b++) {
-        mbar_wait(&full_bar[stage], phase);
+        mbar_wait(SPLIT ? &split_bar[stage] : &full_bar[stage], phase);
         tc_fence_after();
         const uint32_t a = smem_u32(smem + (size_t)stage * stage_bytes);
         const uint32_t bt = a + a_bytes;
 #pragma unroll
         for (int s = 0; s < WG_BK / GM_UMMA_K; s++) {
-          const uint64_t bd = umma_desc_mn_sw128(bt + s * 1024);
+          const uint64_t bd = umma_desc_mn_sw128<BK>(bt + s * 1024);
+          const uint64_t bdlo = umma_desc_mn_sw128<BK>(bt + half_bytes + s * 1024);
           for (int h = 0; h < halves; h++) {
-            const uint64_t ad = umma_desc_mn_sw128(a + h * (4 * WG_BK * 128) + s * 1024);
-            tc_mma_tf32(tmem_base + (uint32_t)(h * p.K), ad, bd, idesc, (b != b0 || s != 0) ? 1u : 0u);
+            const uint32_t ah = a + h * (4 * WG_BK * 128) + s * 1024;
+            const uint64_t ad = umma_desc_mn_sw128<BK>(ah);
+            const uint32_t d = tmem_base + (uint32_t)(h * p.K);
+            tc_mma_tf32(d, ad, bd, idesc, (b != b0 || s != 0) ? 1u : 0u);
+            if (SPLIT) {
+              tc_mma_tf32(d, ad, bdlo, idesc, 1u);
+              tc_mma_tf32(d, umma_desc_mn_sw128<BK>(ah + half_bytes), bd, idesc, 1u);
+            }
           }
         }
         tc_commit(&empty_bar[stage]);
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
       tc_commit(&acc_full);
+    }
+  } else if (warp >= 6) {
+    // ===== splitter (SPLIT only): G and X blocks of the landed stage -> hi (in place) + lo =====
+    const int tid = threadIdx.x - GM_THREADS;
+    const int a_f4 = p.N * (WG_BK * 4) / 16, b_f4 = p.K * (WG_BK * 4) / 16;   // the loaded parts (padding rows stay as they are)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long b = b0; b < b1; b++) {
+      mbar_wait(&full_bar[stage], phase);
+      uint8_t* base = smem + (size_t)stage * stage_bytes;
+      for (int part = 0; part < 2; part++) {
+        float4* hi = reinterpret_cast<float4*>(base + (part ? a_bytes : 0));
+        float4* lo = reinterpret_cast<float4*>(base + (part ? a_bytes : 0) + half_bytes);
+        const int n4 = part ? b_f4 : a_f4;
+        for (int o = tid; o < n4; o += GM_SPLIT_WARPS * 32) {
+          const float4 x = hi[o];
+          float4 h;
+          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
+          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
+          hi[o] = h;
+          lo[o] = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+      mbar_arrive(&split_bar[stage]);
+      if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
   } else {
     const int q = warp & 3;
@@ -610,8 +656,11 @@ int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_
 
 size_t gsb_linear_wgrad_scratch_bytes(int32_t N, int32_t K) { return (size_t)148 * 2 * N * K * sizeof(float); }
 
-int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
-                          float* dW, int32_t accumulate, void* scratch, void* stream) {
+}  // extern "C"
+
+template <bool SPLIT, int BK>
+static int launch_wgrad(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                        float* dW, int32_t accumulate, void* scratch, void* stream) {
   if (rows < 0 || N <= 0 || K <= 0 || N > 256 || K > 256 || (N & 31) || (K & 31) || rows > 0x7fffffffLL) return GSB_EINVAL;
   if (!dW || !scratch) return GSB_EINVAL;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -625,31 +674,42 @@ int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, in
   WgradParams p;
   p.rows = rows; p.N = N; p.K = K; p.npad = (N + 127) / 128 * 128;
   p.partial = reinterpret_cast<float*>(scratch);
-  const int stage_bytes = (p.npad + K) * 128;
+  const int stage_bytes = (p.npad + K) * (BK * 4) * (SPLIT ? 2 : 1);
   p.stages = (220 * 1024) / stage_bytes;
   if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
   if (p.stages < 2) return GSB_EINVAL;
   CUtensorMap mg, mx;
-  if (!make_map(&mg, G, rows, N, ldg, WG_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
-      !make_map(&mx, X, rows, K, ldx, WG_BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
+  if (!make_map(&mg, G, rows, N, ldg, BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
+      !make_map(&mx, X, rows, K, ldx, BK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) {
     set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
     return GSB_ECUDA;
   }
+  auto kern = wgrad_tf32_kernel<SPLIT, BK>;
   static bool attr_set = false;
   if (!attr_set) {
-    GSB_CUDA_CHECK(cudaFuncSetAttribute(wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    GSB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
-  const long long blocks = (rows + WG_BK - 1) / WG_BK;
-  int grid = sm_count() < 296 ? sm_count() : 296;
+  const long long blocks = (rows + BK - 1) / BK;
+  int grid = sm_count() < 296 ? sm_count() : 296;   // gsb_linear_wgrad_scratch_bytes holds 296 partials
   if (grid > blocks) grid = (int)blocks;
   const size_t smem = (size_t)p.stages * stage_bytes + 1024;
-  wgrad_tf32_kernel<<<grid, GM_THREADS, smem, st>>>(mg, mx, p);
+  kern<<<grid, GM_THREADS + (SPLIT ? GM_SPLIT_WARPS * 32 : 0), smem, st>>>(mg, mx, p);
   GSB_LAUNCH_CHECK();
   const long long n = (long long)N * K;
   wgrad_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(grid, n, p.partial, dW, accumulate);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
+}
+
+extern "C" {
+int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                          float* dW, int32_t accumulate, void* scratch, void* stream) {
+  return launch_wgrad<false, 32>(rows, N, K, G, ldg, X, ldx, dW, accumulate, scratch, stream);
+}
+int gsb_linear_wgrad_tf32x3(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                            float* dW, int32_t accumulate, void* scratch, void* stream) {
+  return launch_wgrad<true, 16>(rows, N, K, G, ldg, X, ldx, dW, accumulate, scratch, stream);
 }
 
 }  // extern "C"

@@ -182,6 +182,129 @@ bn_bwd_apply_kernel(long long rows, int N, const float* G, long long ldg, float*
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// The two backward products of a THIN dense layer (the network's output layer: 7 columns, train.py:80-110).  Seven is
+// not a tensor-core tile and both products are pure streaming: FP32 FMAs, every operand read once.
+//   thin_dx:    dX[rows, H] = G[rows, M] . W[M, H]            (M <= 8): writes rows x H x 4 B
+//   thin_wgrad: dW[M, H] = G^T . X[rows, H], db[M] = sum_rows G: reads rows x H x 4 B; per-block partial sums over a
+//               contiguous row range (FP32), summed over the blocks by a second kernel in double
+// ------------------------------------------------------------------------------------------------
+constexpr int THIN_MAX_M = 8;
+
+__global__ void __launch_bounds__(256)
+thin_dx_kernel(long long rows, int M, int H, const float* __restrict__ G, long long ldg, const float* __restrict__ W,
+               long long ldw, float* __restrict__ dX, long long ldx) {
+  extern __shared__ float s_w[];   // [M][H]
+  for (int i = threadIdx.x; i < M * H; i += 256) s_w[i] = W[(long long)(i / H) * ldw + (i % H)];
+  __syncthreads();
+  // a thread owns one group of 4 columns; 256 / (H / 4) rows per block pass (H <= 1024)
+  const int h4 = H >> 2, lanes = 256 / h4;
+  const int cg = threadIdx.x % h4, rl = threadIdx.x / h4;
+  if (rl >= lanes) return;
+  float4 w[THIN_MAX_M];
+#pragma unroll
+  for (int m = 0; m < THIN_MAX_M; m++)
+    w[m] = m < M ? *reinterpret_cast<const float4*>(s_w + m * H + 4 * cg) : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (long long r = (long long)blockIdx.x * lanes + rl; r < rows; r += (long long)gridDim.x * lanes) {
+    const float* g = G + r * ldg;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int m = 0; m < THIN_MAX_M; m++) {
+      if (m < M) {
+        const float gm = __ldg(g + m);
+        acc.x = fmaf(gm, w[m].x, acc.x); acc.y = fmaf(gm, w[m].y, acc.y); acc.z = fmaf(gm, w[m].z, acc.z); acc.w = fmaf(gm, w[m].w, acc.w);
+      }
+    }
+    *reinterpret_cast<float4*>(dX + r * ldx + 4 * cg) = acc;
+  }
+}
+
+constexpr int THIN_WG_ROWS = 64;   // rows of G staged per round
+
+__global__ void __launch_bounds__(256)
+thin_wgrad_kernel(long long rows, int M, int H, const float* __restrict__ G, long long ldg, const float* __restrict__ X,
+                  long long ldx, float* __restrict__ partial /* [gridDim.x][M + 1][H] */) {
+  __shared__ __align__(16) float s_g[THIN_WG_ROWS][THIN_MAX_M];
+  extern __shared__ float s_acc[];   // [M][H] + [THIN_MAX_M]: the block's sums over its row lanes
+  const int parts = gridDim.x;
+  const long long r0 = rows * blockIdx.x / parts, r1 = rows * (blockIdx.x + 1) / parts;
+  // a thread owns one group of 4 columns and every (256 / (H / 4))-th row of the block's range
+  const int h4 = H >> 2, lanes = 256 / h4;
+  const int cg = threadIdx.x % h4, rl = threadIdx.x / h4;
+  const bool active = rl < lanes;
+  for (int i = threadIdx.x; i < M * H + THIN_MAX_M; i += 256) s_acc[i] = 0.f;
+  float4 acc[THIN_MAX_M];
+#pragma unroll
+  for (int m = 0; m < THIN_MAX_M; m++) acc[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float gsum = 0.f;   // column threadIdx.x % 8 of G over the elements this thread stages (the bias gradient)
+  for (long long rb = r0; rb < r1; rb += THIN_WG_ROWS) {
+    const int nr = (int)((r1 - rb) < THIN_WG_ROWS ? (r1 - rb) : THIN_WG_ROWS);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < THIN_WG_ROWS * THIN_MAX_M / 256; k++) {
+      const int i = threadIdx.x + 256 * k;
+      const int r = i / THIN_MAX_M, m = i % THIN_MAX_M;
+      const float v = (r < nr && m < M) ? G[(rb + r) * ldg + m] : 0.f;
+      s_g[r][m] = v;
+      gsum += v;
+    }
+    __syncthreads();
+    if (active) {
+      const float* xp = X + rb * ldx + 4 * cg;
+#pragma unroll 4
+      for (int r = rl; r < nr; r += lanes) {
+        const float4 x = *reinterpret_cast<const float4*>(xp + (long long)r * ldx);
+        const float4 g0 = *reinterpret_cast<const float4*>(&s_g[r][0]);
+        const float4 g1 = *reinterpret_cast<const float4*>(&s_g[r][4]);
+        const float gm[THIN_MAX_M] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+        for (int m = 0; m < THIN_MAX_M; m++) {
+          acc[m].x = fmaf(gm[m], x.x, acc[m].x); acc[m].y = fmaf(gm[m], x.y, acc[m].y);
+          acc[m].z = fmaf(gm[m], x.z, acc[m].z); acc[m].w = fmaf(gm[m], x.w, acc[m].w);
+        }
+      }
+    }
+  }
+  if (active) {
+#pragma unroll
+    for (int m = 0; m < THIN_MAX_M; m++)
+      if (m < M) {
+        float* d = s_acc + m * H + 4 * cg;
+        atomicAdd(d, acc[m].x); atomicAdd(d + 1, acc[m].y); atomicAdd(d + 2, acc[m].z); atomicAdd(d + 3, acc[m].w);
+      }
+  }
+  gsum += __shfl_xor_sync(0xffffffffu, gsum, 8);
+  gsum += __shfl_xor_sync(0xffffffffu, gsum, 16);
+  if ((threadIdx.x & 31u) < THIN_MAX_M) atomicAdd(s_acc + M * H + (threadIdx.x & 7u), gsum);
+  __syncthreads();
+  float* out = partial + (size_t)blockIdx.x * (M + 1) * H;
+  for (int i = threadIdx.x; i < M * H; i += 256) out[i] = s_acc[i];
+  if (threadIdx.x < M) out[(size_t)M * H + threadIdx.x] = s_acc[M * H + threadIdx.x];
+}
+
+// 32 consecutive output elements per block; the 8 thread rows each sum every 8th partial (coalesced 128-byte reads,
+// independent chains), then meet in shared memory
+__global__ void __launch_bounds__(256)
+thin_wgrad_reduce_kernel(int parts, int M, int H, const float* __restrict__ partial, float* __restrict__ dW,
+                         float* __restrict__ db) {
+  __shared__ double s_sum[8][33];
+  const int n = M * H + M;
+  const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + x;
+  double s = 0.0;
+  if (i < n)
+    for (int c = y; c < parts; c += 8) s += (double)partial[(size_t)c * (M + 1) * H + i];
+  s_sum[y][x] = s;
+  __syncthreads();
+  if (y == 0 && i < n) {
+#pragma unroll
+    for (int k = 1; k < 8; k++) s += s_sum[k][x];
+    if (i < M * H) dW[i] = (float)s;
+    else if (db) db[i - M * H] = (float)s;
+  }
+}
+
 }  // namespace gsb
 
 using namespace gsb;
@@ -237,6 +360,49 @@ int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, 
   if (blocks > 148 * 16) blocks = 148 * 16;
   bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, G, ldg, dZ, lddz, Z, ldz, col_stats, gamma, eps, sums,
                                                         d_gamma, d_beta);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+int gsb_linear_thin_dx(int64_t rows, int32_t M, int32_t H, const float* G, int64_t ldg, const float* W, int64_t ldw,
+                       float* dX, int64_t ldx, void* stream) {
+  if (rows < 0 || M <= 0 || M > THIN_MAX_M || H <= 0 || (H & 3) || H > 1024) return GSB_EINVAL;
+  if (rows == 0) return GSB_OK;
+  if (!G || !W || !dX || ldg < M || ldw < H || ldx < H || (ldx & 3) || (reinterpret_cast<uintptr_t>(dX) & 15u)) return GSB_EINVAL;
+  const long long total = rows * (H >> 2);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  thin_dx_kernel<<<(unsigned)blocks, 256, (size_t)M * H * sizeof(float), reinterpret_cast<cudaStream_t>(stream)>>>(
+      rows, M, H, G, ldg, W, ldw, dX, ldx);
+  GSB_LAUNCH_CHECK();
+  return GSB_OK;
+}
+
+static int thin_wgrad_parts(int64_t rows) {
+  const int64_t want = (rows + THIN_WG_ROWS - 1) / THIN_WG_ROWS;
+  return (int)(want < 148 * 4 ? (want > 0 ? want : 1) : 148 * 4);
+}
+size_t gsb_linear_thin_wgrad_scratch_bytes(int32_t M, int32_t H) {
+  if (M <= 0 || H <= 0) return 0;
+  return (size_t)148 * 4 * (M + 1) * H * sizeof(float);
+}
+int gsb_linear_thin_wgrad(int64_t rows, int32_t M, int32_t H, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                          float* dW, float* db, void* scratch, void* stream) {
+  if (rows < 0 || M <= 0 || M > THIN_MAX_M || H < THIN_MAX_M || (H & 3) || H > 1024) return GSB_EINVAL;
+  if (!dW || !scratch) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (rows == 0) {
+    GSB_CUDA_CHECK(cudaMemsetAsync(dW, 0, (size_t)M * H * sizeof(float), st));
+    if (db) GSB_CUDA_CHECK(cudaMemsetAsync(db, 0, (size_t)M * sizeof(float), st));
+    return GSB_OK;
+  }
+  if (!G || !X || ldg < M || ldx < H || (ldx & 3) || (reinterpret_cast<uintptr_t>(X) & 15u)) return GSB_EINVAL;
+  const int parts = thin_wgrad_parts(rows);
+  thin_wgrad_kernel<<<parts, 256, ((size_t)M * H + THIN_MAX_M) * sizeof(float), st>>>(rows, M, H, G, ldg, X, ldx,
+                                                                                    reinterpret_cast<float*>(scratch));
+  GSB_LAUNCH_CHECK();
+  const int n = M * H + M;
+  thin_wgrad_reduce_kernel<<<(n + 31) / 32, 256, 0, st>>>(parts, M, H, reinterpret_cast<const float*>(scratch), dW, db);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }

@@ -15,16 +15,16 @@ Training: when gradients are enabled the forward runs inside ONE autograd node (
 activations (x, z1, a, z2 and the BatchNorm sums) and whose backward is built from the same pieces: dX = dY W on the
 forward GEMM with the transposed weight, dW = dY^T X on the MN-major tcgen05 weight-gradient kernel, and the two-pass
 BatchNorm / GELU adjoint (gsb_bn_gelu_backward).  With precise=True the input gradients run on the 3xTF32 layer and
-the weight gradients are FP32 products (torch.mm with TF32 off: a 3xTF32 form of the MN-major weight-gradient kernel
-would have to materialise hi / lo splits of both operands, which costs what the FP32 product costs); with
-precise=False both run in TF32 on the tcgen05 kernels.  The 7-wide output layer's two backward products stay on
-torch.mm: 7 is not a tensor-core tile, and they are 2% of the backward's bytes.
+the weight gradients on the 3xTF32 form of the weight-gradient kernel (both streamed operands split into hi / lo where
+they land in shared memory: gsb_linear_wgrad_tf32x3); with precise=False both run in plain TF32.  The 7-wide output
+layer's two backward products (7 is not a tensor-core tile) are FP32 streaming kernels (gsb_linear_thin_dx /
+gsb_linear_thin_wgrad).  No torch / cuBLAS matmul is left in the network.
 """
 import torch
 from torch import nn
 
 from . import _lib as L
-from .linear import linear, linear_wgrad
+from .linear import linear, linear_wgrad, thin_backward
 
 
 def positional_encoding(x, frequency_count, lo=None, span=None, out=None, col0=0):
@@ -176,20 +176,10 @@ class _DeformFn(torch.autograd.Function):
             return linear(g, w.detach().t().contiguous(), None, precise=precise)
 
         def dw(g, a):
-            if not precise:
-                return linear_wgrad(g, a)
-            prev = torch.backends.cuda.matmul.allow_tf32
-            torch.backends.cuda.matmul.allow_tf32 = False
-            try:
-                return g.t() @ a
-            finally:
-                torch.backends.cuda.matmul.allow_tf32 = prev
+            return linear_wgrad(g, a, precise=precise)
 
-        # output layer (7 columns): plain torch products
-        w_out = net.fc_out.weight.detach()
-        grads[net.fc_out.weight] = d_out.t() @ last
-        grads[net.fc_out.bias] = d_out.sum(0)
-        dh = d_out @ w_out
+        # output layer (7 columns, not a tensor-core tile): FP32 streaming kernels
+        dh, grads[net.fc_out.weight], grads[net.fc_out.bias] = thin_backward(d_out, net.fc_out.weight, last)
         for block, (identity, z1, st1, a, z2, st2) in zip(reversed(list(net.residual_blocks)), reversed(keep)):
             dz2, g2, dgam2, dbet2 = net._bn_bwd(dh, z2, st2, block.bn2, identity)
             grads[block.bn2.weight], grads[block.bn2.bias] = dgam2, dbet2

@@ -38,8 +38,9 @@ def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
     return y
 
 
-def linear_wgrad(grad_out, x, out=None, accumulate=False):
-    """dW [N, K] = grad_out[rows, N]^T @ x[rows, K] on the tcgen05 weight-gradient kernel (TF32)."""
+def linear_wgrad(grad_out, x, out=None, accumulate=False, precise=False):
+    """dW [N, K] = grad_out[rows, N]^T @ x[rows, K] on the tcgen05 weight-gradient kernel: TF32 multiplies, or the
+    3xTF32 operand split (precise=True: FP32-level accuracy, what the reference's FP32 autograd computes)."""
     L.require_cuda(x, "x")
     g = grad_out if (grad_out.dtype == torch.float32 and grad_out.stride(-1) == 1) else grad_out.float().contiguous()
     x = x if (x.dtype == torch.float32 and x.stride(-1) == 1) else x.float().contiguous()
@@ -59,7 +60,36 @@ def linear_wgrad(grad_out, x, out=None, accumulate=False):
     if key not in _scratch:
         _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
     with L.device_guard(x.device):
-        rc = L.lib().gsb_linear_wgrad_tf32(rows, n, k, L.ptr(g), g.stride(0), L.ptr(x), x.stride(0), L.ptr(dw),
-                                           1 if accumulate else 0, L.ptr(_scratch[key]), L.stream_ptr())
+        fn = L.lib().gsb_linear_wgrad_tf32x3 if precise else L.lib().gsb_linear_wgrad_tf32
+        rc = fn(rows, n, k, L.ptr(g), g.stride(0), L.ptr(x), x.stride(0), L.ptr(dw), 1 if accumulate else 0,
+                L.ptr(_scratch[key]), L.stream_ptr())
     L.check(rc, "gsb_linear_wgrad_tf32")
     return dw
+
+
+def thin_backward(grad_out, weight, x, parts="both"):
+    """The backward of a dense layer with at most 8 output columns (the network's 7-wide output layer,
+    train.py:80-110) in FP32: -> (dX [rows, H] = grad_out @ weight, dW [M, H] = grad_out^T @ x, db [M])."""
+    L.require_cuda(x, "x")
+    g = grad_out if (grad_out.dtype == torch.float32 and grad_out.stride(-1) == 1) else grad_out.float().contiguous()
+    x = x if (x.dtype == torch.float32 and x.stride(-1) == 1) else x.float().contiguous()
+    w = weight.detach().float().contiguous()
+    rows, m = g.shape
+    h = w.shape[1]
+    if w.shape[0] != m or x.shape != (rows, h):
+        raise RuntimeError("thin_backward: shapes differ")
+    dx = torch.empty((rows, h), dtype=torch.float32, device=x.device)
+    dw = torch.empty((m, h), dtype=torch.float32, device=x.device)
+    db = torch.empty((m,), dtype=torch.float32, device=x.device)
+    nbytes = L.lib().gsb_linear_thin_wgrad_scratch_bytes(m, h)
+    key = (x.device, "thin", nbytes)
+    if key not in _scratch:
+        _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    with L.device_guard(x.device):
+        if parts != "dw":   # (`parts` exists for the bench: one product alone)
+            L.check(L.lib().gsb_linear_thin_dx(rows, m, h, L.ptr(g), g.stride(0), L.ptr(w), h, L.ptr(dx), dx.stride(0),
+                                               L.stream_ptr()), "gsb_linear_thin_dx")
+        if parts != "dx":
+            L.check(L.lib().gsb_linear_thin_wgrad(rows, m, h, L.ptr(g), g.stride(0), L.ptr(x), x.stride(0), L.ptr(dw),
+                                                  L.ptr(db), L.ptr(_scratch[key]), L.stream_ptr()), "gsb_linear_thin_wgrad")
+    return dx, dw, db

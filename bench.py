@@ -892,6 +892,26 @@ def deformation_shaped(args, hidden=256, blocks=4, iters=10):
                           "bound": "hbm", "algorithmic_bytes": byts, "achieved": byts / (ms * 1e-3) / 1e9,
                           "peak": peak, "unit": "GB/s", "frac": (byts / (ms * 1e-3) / 1e9 / peak) if peak else None,
                           "tflops": 2.0 * n * 192 * hidden / (ms * 1e-3) / 1e12}
+    # weight gradient of a hidden layer, dW[H, H] = G^T A over the n rows: TF32 and 3xTF32 on the tcgen05 kernel against
+    # torch (cuBLAS) at the same precisions; and the 7-wide output layer's backward against its two torch products
+    from gsb200.linear import linear_wgrad, thin_backward
+    gmat, amat = torch.randn(n, hidden, device=dev), torch.randn(n, hidden, device=dev)
+    wg = {"what": f"dW[{hidden},{hidden}] = G^T A over {n} rows", "unit": "ms",
+          "ours_tf32": timed(lambda: linear_wgrad(gmat, amat)),
+          "ours_3xtf32": timed(lambda: linear_wgrad(gmat, amat, precise=True)),
+          "torch_fp32": timed(lambda: gmat.t() @ amat)}
+    torch.backends.cuda.matmul.allow_tf32 = True
+    wg["torch_tf32"] = timed(lambda: gmat.t() @ amat)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    wg["algorithmic_bytes"] = 2 * n * hidden * 4
+    wg["ours_3xtf32_gbs"] = wg["algorithmic_bytes"] / (wg["ours_3xtf32"] * 1e-3) / 1e9
+    res["hidden_layer_wgrad"] = wg
+    g7, w7 = torch.randn(n, 7, device=dev), torch.randn(7, hidden, device=dev)
+    res["output_layer_backward"] = {"what": f"dX = G W, dW = G^T A, db = sum G for the 7-wide output layer, {n} rows", "unit": "ms",
+                                    "ours": timed(lambda: thin_backward(g7, w7, amat)),
+                                    "ours_dx_only": timed(lambda: thin_backward(g7, w7, amat, parts="dx")),
+                                    "ours_wgrad_only": timed(lambda: thin_backward(g7, w7, amat, parts="dw")),
+                                    "torch_fp32": timed(lambda: (g7 @ w7, g7.t() @ amat, g7.sum(0)))}
     return res
 
 
@@ -947,7 +967,7 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
                    f"{views} of {args.cams} cameras {args.width}x{args.height}, rigidity K={neighbours}, Adam",
            "unit": "ms per step", "ours": timed(ours)}
     res["ours_steps_per_s"] = 1e3 / res["ours"]
-    res["network_matmuls"] = ("precise (default): 3xTF32 forward and input gradients, FP32 weight gradients -- compare with "
+    res["network_matmuls"] = ("precise (default): 3xTF32 forward, input and weight gradients (FP32-level accuracy) -- compare with "
                               "`stock` (torch FP32); ours_tf32: TF32 everywhere (opt-in fast mode)")
     torch.manual_seed(0)
     net = deform.DeformationNetwork(hidden, blocks, precise=False).to(dev)

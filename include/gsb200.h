@@ -395,6 +395,24 @@ size_t gsb_linear_wgrad_scratch_bytes(int32_t N, int32_t K);
 int gsb_linear_wgrad_tf32(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
                           float* dW, int32_t accumulate, void* scratch, void* stream);
 
+/* The same product with the 3xTF32 operand split: both streamed operands are split where they land in shared memory
+ * (hi = upper 19 bits, lo = x - hi) and Ghi Xhi + Ghi Xlo + Glo Xhi is accumulated -- FP32-level accuracy, what the
+ * reference's FP32 autograd matmuls compute (train.py:57-110).  Same constraints and scratch. */
+int gsb_linear_wgrad_tf32x3(int64_t rows, int32_t N, int32_t K, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                            float* dW, int32_t accumulate, void* scratch, void* stream);
+
+/* The two backward products of a THIN dense layer -- the network's 7-column output layer (train.py:80-110); autograd
+ * runs two cuBLAS SGEMMs in the reference -- as FP32 streaming kernels (7 is not a tensor-core tile), M <= 8:
+ *   gsb_linear_thin_dx:    dX[rows, H] = G[rows, M] . W[M, H]   (H % 4 == 0, H <= 1024, dX 16-byte aligned, ldx % 4 == 0)
+ *   gsb_linear_thin_wgrad: dW[M, H] (dense) = G^T . X[rows, H] and db[M] = column sums of G (optional);
+ *                          8 <= H <= 1024, H % 4 == 0, X 16-byte aligned, ldx % 4 == 0;
+ *                          scratch: gsb_linear_thin_wgrad_scratch_bytes(M, H) bytes (per-block partial sums). */
+int gsb_linear_thin_dx(int64_t rows, int32_t M, int32_t H, const float* G, int64_t ldg, const float* W, int64_t ldw,
+                       float* dX, int64_t ldx, void* stream);
+size_t gsb_linear_thin_wgrad_scratch_bytes(int32_t M, int32_t H);
+int gsb_linear_thin_wgrad(int64_t rows, int32_t M, int32_t H, const float* G, int64_t ldg, const float* X, int64_t ldx,
+                          float* dW, float* db, void* scratch, void* stream);
+
 /* BatchNorm1d in training mode (batch statistics; the reference never switches the network to eval) + optional
  * residual + exact (erf) GELU in one pass over Z [rows, N]: Y = act(gamma (Z - mean) / sqrt(var + eps) + beta
  * [+ residual]), mean / biased var from col_stats = the [2][N] sums gsb_linear_tf32 accumulated (train.py:57-78).
