@@ -15,21 +15,22 @@ namespace gsb {
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
 __global__ void __launch_bounds__(256)
-bn_gelu_kernel(long long rows, int N, const float* __restrict__ Z, long long ldz, const double* __restrict__ stats,
+bn_gelu_kernel(long long rows, long long batch_rows, int N, const float* __restrict__ Z, long long ldz, const double* __restrict__ stats,
                const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                const float* __restrict__ residual, long long ldr, float* __restrict__ Y, long long ldy,
                float* __restrict__ running_mean, float* __restrict__ running_var, float momentum, int apply_gelu) {
   __shared__ float s_scale[256], s_shift[256];
   for (int c = threadIdx.x; c < N; c += 256) {
-    const double mean = stats[c] / (double)rows;
-    double var = stats[N + c] / (double)rows - mean * mean;
+    // the statistics cover batch_rows rows (>= rows: the rows of all ranks when the batch is sharded by rows)
+    const double mean = stats[c] / (double)batch_rows;
+    double var = stats[N + c] / (double)batch_rows - mean * mean;
     var = var < 0.0 ? 0.0 : var;
     const float inv = (float)(1.0 / sqrt(var + (double)eps));
     const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
     s_scale[c] = g * inv;
     s_shift[c] = b - (float)mean * g * inv;
     if (blockIdx.x == 0 && running_mean) {
-      const double unbiased = rows > 1 ? var * (double)rows / (double)(rows - 1) : var;
+      const double unbiased = batch_rows > 1 ? var * (double)batch_rows / (double)(batch_rows - 1) : var;
       running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
       running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
     }
@@ -106,7 +107,7 @@ __device__ __forceinline__ BnCols bn_col(const double* stats, int N, int c, long
 }
 
 __global__ void __launch_bounds__(256)
-bn_act_bwd_reduce_kernel(long long rows, int N, const float* __restrict__ dY, long long ldd, const float* __restrict__ Z,
+bn_act_bwd_reduce_kernel(long long rows, long long batch_rows, int N, const float* __restrict__ dY, long long ldd, const float* __restrict__ Z,
                          long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma,
                          const float* __restrict__ beta, float eps, const float* __restrict__ residual, long long ldr,
                          int apply_gelu, float* __restrict__ G, long long ldg, double* __restrict__ sums) {
@@ -117,7 +118,7 @@ bn_act_bwd_reduce_kernel(long long rows, int N, const float* __restrict__ dY, lo
   const int c = cg << 2;
   BnCols b[4];
 #pragma unroll
-  for (int e = 0; e < 4; e++) b[e] = bn_col(stats, N, c + e, rows, gamma, beta, eps);
+  for (int e = 0; e < 4; e++) b[e] = bn_col(stats, N, c + e, batch_rows, gamma, beta, eps);
   float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
   for (long long r = (long long)blockIdx.x * row_lanes + rl; r < rows; r += (long long)gridDim.x * row_lanes) {
     const float4 z = *reinterpret_cast<const float4*>(Z + r * ldz + c);
@@ -150,13 +151,13 @@ bn_act_bwd_reduce_kernel(long long rows, int N, const float* __restrict__ dY, lo
 }
 
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(long long rows, int N, const float* G, long long ldg, float* dZ, long long lddz,
+bn_bwd_apply_kernel(long long rows, long long batch_rows, int N, const float* G, long long ldg, float* dZ, long long lddz,
                     const float* __restrict__ Z, long long ldz, const double* __restrict__ stats, const float* __restrict__ gamma, float eps,
                     const double* __restrict__ sums, float* __restrict__ d_gamma, float* __restrict__ d_beta) {
   __shared__ float s_k0[256], s_k1[256], s_k2[256];   // dz = k0 g + k1 + k2 z
   for (int c = threadIdx.x; c < N; c += 256) {
-    const BnCols b = bn_col(stats, N, c, rows, gamma, nullptr, eps);
-    const float db = (float)(sums[c] / (double)rows), dg = (float)(sums[N + c] / (double)rows);
+    const BnCols b = bn_col(stats, N, c, batch_rows, gamma, nullptr, eps);
+    const float db = (float)(sums[c] / (double)batch_rows), dg = (float)(sums[N + c] / (double)batch_rows);
     // dz = scale (g - db - xhat dg), xhat = (z - mean) inv_std
     s_k0[c] = b.scale;
     s_k2[c] = -b.scale * dg * b.inv_std;
@@ -311,10 +312,11 @@ using namespace gsb;
 
 extern "C" {
 
-int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const double* col_stats, const float* gamma,
-                const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
+int gsb_bn_gelu(int64_t rows, int64_t batch_rows, int32_t N, const float* Z, int64_t ldz, const double* col_stats,
+                const float* gamma, const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
                 float* running_mean, float* running_var, float momentum, int32_t apply_gelu, void* stream) {
-  if (rows < 0 || N <= 0 || N > 256 || (N & 3)) return GSB_EINVAL;
+  if (batch_rows == 0) batch_rows = rows;
+  if (rows < 0 || batch_rows < rows || N <= 0 || N > 256 || (N & 3)) return GSB_EINVAL;
   if (rows == 0) return GSB_OK;
   if (!Z || !col_stats || !Y || (ldz & 3) || (ldy & 3) || (residual && (ldr & 3))) return GSB_EINVAL;
   if ((running_mean == nullptr) != (running_var == nullptr)) return GSB_EINVAL;
@@ -322,7 +324,7 @@ int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const doub
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   bn_gelu_kernel<<<(unsigned)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      rows, N, Z, ldz, col_stats, gamma, beta, eps, residual, ldr, Y, ldy, running_mean, running_var, momentum,
+      rows, batch_rows, N, Z, ldz, col_stats, gamma, beta, eps, residual, ldr, Y, ldy, running_mean, running_var, momentum,
       apply_gelu);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
@@ -340,27 +342,36 @@ int gsb_positional_encoding(int64_t rows, int32_t D, int32_t F, const float* x, 
   return GSB_OK;
 }
 
-int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, const float* Z, int64_t ldz,
-                         const double* col_stats, const float* gamma, const float* beta, float eps,
-                         const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg, float* dZ,
-                         int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream) {
-  if (rows < 0 || N <= 0 || N > 256 || (N & 3)) return GSB_EINVAL;
-  if (rows == 0) return GSB_OK;
-  if (!dY || !Z || !col_stats || !G || !dZ || !sums) return GSB_EINVAL;
-  if ((ldd & 3) || (ldz & 3) || (ldg & 3) || (lddz & 3) || (residual && (ldr & 3))) return GSB_EINVAL;
+int gsb_bn_gelu_backward(int64_t rows, int64_t batch_rows, int32_t phase, int32_t N, const float* dY, int64_t ldd,
+                         const float* Z, int64_t ldz, const double* col_stats, const float* gamma, const float* beta,
+                         float eps, const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg,
+                         float* dZ, int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream) {
+  if (batch_rows == 0) batch_rows = rows;
+  if (rows < 0 || batch_rows < rows || phase < 0 || phase > 2 || N <= 0 || N > 256 || (N & 3)) return GSB_EINVAL;
+  if (!sums) return GSB_EINVAL;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  GSB_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * (size_t)N * sizeof(double), st));
+  if (phase != 2) GSB_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * (size_t)N * sizeof(double), st));
+  if (rows == 0 && batch_rows == 0) return GSB_OK;
+  if (rows > 0 && (!dY || !Z || !col_stats || !G || !dZ)) return GSB_EINVAL;
+  if ((ldd & 3) || (ldz & 3) || (ldg & 3) || (lddz & 3) || (residual && (ldr & 3))) return GSB_EINVAL;
   const int n4 = N >> 2;
   const int row_lanes = 256 / n4;
-  bn_act_bwd_reduce_kernel<<<148 * 4, n4 * row_lanes, 0, st>>>(rows, N, dY, ldd, Z, ldz, col_stats, gamma, beta, eps,
-                                                                residual, ldr, apply_gelu, G, ldg, sums);
-  GSB_LAUNCH_CHECK();
-  const long long total = rows * n4;
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, N, G, ldg, dZ, lddz, Z, ldz, col_stats, gamma, eps, sums,
-                                                        d_gamma, d_beta);
-  GSB_LAUNCH_CHECK();
+  if (phase != 2 && rows > 0) {
+    bn_act_bwd_reduce_kernel<<<148 * 4, n4 * row_lanes, 0, st>>>(rows, batch_rows, N, dY, ldd, Z, ldz, col_stats, gamma,
+                                                                  beta, eps, residual, ldr, apply_gelu, G, ldg, sums);
+    GSB_LAUNCH_CHECK();
+  }
+  if (phase != 1) {
+    // a rank without rows still runs one block: it writes d_gamma / d_beta from the (exchanged) sums
+    const long long total = rows * n4;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    if (!col_stats) return GSB_EINVAL;
+    bn_bwd_apply_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, batch_rows, N, G, ldg, dZ, lddz, Z, ldz, col_stats, gamma,
+                                                          eps, sums, d_gamma, d_beta);
+    GSB_LAUNCH_CHECK();
+  }
   return GSB_OK;
 }
 

@@ -19,12 +19,81 @@ the weight gradients on the 3xTF32 form of the weight-gradient kernel (both stre
 they land in shared memory: gsb_linear_wgrad_tf32x3); with precise=False both run in plain TF32.  The 7-wide output
 layer's two backward products (7 is not a tensor-core tile) are FP32 streaming kernels (gsb_linear_thin_dx /
 gsb_linear_thin_wgrad).  No torch / cuBLAS matmul is left in the network.
+
+Row sharding (multi-GPU; the reference has no distributed code): the network is a per-Gaussian function except for the
+BatchNorm batch statistics, so with `net.set_row_shard(group)` every rank runs it on its contiguous slice of the
+Gaussians only: the column sums behind every BatchNorm (forward: sum z, sum z^2; backward: sum g, sum g xhat -- 2 x 256
+doubles each) are added over the ranks, the [N, 7] output is all-gathered, and the parameter gradients (one flat
+buffer) are summed at the end of the backward.  The result equals the replicated network up to summation order, and
+replicas stay bit-identical because every rank receives the same reduced numbers.  update_gaussian_cloud_parameters
+uses it automatically when the network carries a shard.
 """
 import torch
 from torch import nn
 
+import torch.distributed as dist
+
 from . import _lib as L
 from .linear import linear, linear_wgrad, thin_backward
+
+
+class RowShard:
+    """This rank's contiguous slice of the Gaussians under row sharding, and the two collectives the network needs.
+    Works over NCCL (device tensors) and over gloo (tests: device tensors are staged through the host)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._via_host = dist.is_initialized() and dist.get_backend(group) == "gloo"
+
+    def bounds(self, n, rank=None):
+        """Rows [r0, r1) of rank `rank` (default: this rank): equal chunks of ceil(n / world) rows, the last ones shorter."""
+        rank = self.rank if rank is None else rank
+        chunk = (n + self.world - 1) // self.world
+        return min(rank * chunk, n), min((rank + 1) * chunk, n)
+
+    def all_reduce(self, t):
+        if self.world > 1:
+            if self._via_host and t.is_cuda:
+                h = t.cpu()
+                dist.all_reduce(h, group=self.group)
+                t.copy_(h)
+            else:
+                dist.all_reduce(t, group=self.group)
+        return t
+
+    def all_gather_rows(self, local, n):
+        """local [r1 - r0, k] of every rank -> [n, k] (rank order)."""
+        if self.world == 1:
+            return local
+        chunk = (n + self.world - 1) // self.world
+        pad = torch.zeros((chunk, local.shape[1]), dtype=local.dtype, device=local.device)
+        pad[:local.shape[0]] = local
+        if self._via_host and pad.is_cuda:
+            parts = [torch.empty(pad.shape, dtype=pad.dtype) for _ in range(self.world)]
+            dist.all_gather(parts, pad.cpu(), group=self.group)
+            out = torch.cat(parts, dim=0).to(local.device)
+        else:
+            out = torch.empty((self.world * chunk, local.shape[1]), dtype=local.dtype, device=local.device)
+            dist.all_gather_into_tensor(out, pad, group=self.group)
+        return out[:n]
+
+
+class _GatherRows(torch.autograd.Function):
+    """All-gather of the ranks' row slices.  Every rank goes on to evaluate the SAME loss on the gathered tensor (the
+    image term's gradient is already summed over the ranks by the step's exchange, the rigidity term is replicated),
+    so the adjoint is this rank's slice of the incoming gradient, not a reduce-scatter."""
+
+    @staticmethod
+    def forward(ctx, local, shard, n):
+        ctx.bounds = shard.bounds(n)
+        return shard.all_gather_rows(local, n)
+
+    @staticmethod
+    def backward(ctx, g):
+        r0, r1 = ctx.bounds
+        return g[r0:r1].contiguous(), None, None
 
 
 def positional_encoding(x, frequency_count, lo=None, span=None, out=None, col0=0):
@@ -81,12 +150,33 @@ class DeformationNetwork(nn.Module):
         self.residual_blocks = nn.Sequential(*(ResidualBlock(hidden_dimension) for _ in range(residual_block_count)))
         self.fc_out = nn.Linear(hidden_dimension, 7)
         self.precise = precise
+        self.shard = None          # RowShard: the network runs on this rank's slice of the rows (set_row_shard)
+        self._batch_rows = {}
+
+    def set_row_shard(self, group=None):
+        """Row-sharded mode over the ranks of `group` (see the module docstring); world size 1 leaves the network as it is."""
+        shard = RowShard(group)
+        self.shard = shard if shard.world > 1 else None
+        self._batch_rows = {}
+        return self
+
+    def _rows_of_batch(self, rows, device):
+        """Rows of the whole batch = sum of the ranks' rows (one tiny all-reduce per distinct local row count)."""
+        if self.shard is None:
+            return rows
+        if rows not in self._batch_rows:
+            t = torch.tensor([rows], dtype=torch.int64, device=device)
+            self._batch_rows[rows] = int(self.shard.all_reduce(t).item())
+        return self._batch_rows[rows]
 
     def _bn_act(self, z, stats, bn, residual, gelu=True):
         rows, n = z.shape
         y = torch.empty_like(z)
+        batch_rows = self._rows_of_batch(rows, z.device)
+        if self.shard is not None:
+            self.shard.all_reduce(stats)     # column sums of the whole batch
         with L.device_guard(z.device):
-            rc = L.lib().gsb_bn_gelu(rows, n, L.ptr(z), z.stride(0), L.ptr(stats), L.ptr(bn.weight.detach()),
+            rc = L.lib().gsb_bn_gelu(rows, batch_rows, n, L.ptr(z), z.stride(0), L.ptr(stats), L.ptr(bn.weight.detach()),
                                      L.ptr(bn.bias.detach()), float(bn.eps), L.ptr(residual),
                                      0 if residual is None else residual.stride(0), L.ptr(y), y.stride(0),
                                      L.ptr(bn.running_mean), L.ptr(bn.running_var),
@@ -103,13 +193,23 @@ class DeformationNetwork(nn.Module):
         sums = torch.empty((2, n), dtype=torch.float64, device=z.device)
         dgam, dbet = torch.empty(n, device=z.device), torch.empty(n, device=z.device)
         dy = dy.contiguous()
-        with L.device_guard(z.device):
-            rc = L.lib().gsb_bn_gelu_backward(rows, n, L.ptr(dy), dy.stride(0), L.ptr(z), z.stride(0), L.ptr(stats),
-                                              L.ptr(bn.weight.detach()), L.ptr(bn.bias.detach()), float(bn.eps),
-                                              L.ptr(residual), 0 if residual is None else residual.stride(0),
-                                              1 if gelu else 0, L.ptr(g), g.stride(0), L.ptr(dz), dz.stride(0), L.ptr(sums),
-                                              L.ptr(dgam), L.ptr(dbet), L.stream_ptr())
-        L.check(rc, "gsb_bn_gelu_backward")
+        batch_rows = self._rows_of_batch(rows, z.device)
+
+        def run(phase):
+            with L.device_guard(z.device):
+                rc = L.lib().gsb_bn_gelu_backward(rows, batch_rows, phase, n, L.ptr(dy), dy.stride(0), L.ptr(z), z.stride(0),
+                                                  L.ptr(stats), L.ptr(bn.weight.detach()), L.ptr(bn.bias.detach()),
+                                                  float(bn.eps), L.ptr(residual), 0 if residual is None else residual.stride(0),
+                                                  1 if gelu else 0, L.ptr(g), g.stride(0), L.ptr(dz), dz.stride(0), L.ptr(sums),
+                                                  L.ptr(dgam), L.ptr(dbet), L.stream_ptr())
+            L.check(rc, "gsb_bn_gelu_backward")
+
+        if self.shard is None:
+            run(0)
+        else:   # the two column sums of the adjoint cover the whole batch: add the ranks' sums between the passes
+            run(1)
+            self.shard.all_reduce(sums)
+            run(2)
         return dz, g, dgam, dbet
 
     def _forward_impl(self, x, keep):
@@ -194,6 +294,16 @@ class _DeformFn(torch.autograd.Function):
         grads[net.fc_in.bias] = dh.sum(0)
         ctx.keep = ctx.last = ctx.x = None
         plist = net._parameter_list()
+        if net.shard is not None:
+            # row-sharded: the dense layers' gradients are sums over this rank's rows -> ONE all-reduce of a flat buffer
+            # (the BatchNorm gradients come from the already exchanged column sums)
+            dense = [p for p in plist if p.dim() == 2 or p is net.fc_in.bias or p is net.fc_out.bias]
+            flat = torch.cat([grads[p].reshape(-1) for p in dense])
+            net.shard.all_reduce(flat)
+            o = 0
+            for p in dense:
+                grads[p] = flat[o:o + p.numel()].view_as(p)
+                o += p.numel()
         return (None, None, d_out) + tuple(grads[p] if p.requires_grad else None for p in plist)
 
 
@@ -205,12 +315,17 @@ def update_gaussian_cloud_parameters(deformation_network, initial_gaussian_cloud
     in place."""
     p = initial_gaussian_cloud_parameters
     n, dev = p["means"].shape[0], p["means"].device
-    x = torch.empty((n, 192), dtype=torch.float32, device=dev)
-    x[:, :92] = encoded_normalized_initial_means_and_rotations
-    x[:, 92:184] = encoded_normalized_previous_means_and_rotations
-    progress = torch.full((n, 1), timestep / timestep_count, dtype=torch.float32, device=dev)
+    shard = getattr(deformation_network, "shard", None)
+    r0, r1 = shard.bounds(n) if shard is not None else (0, n)   # row-sharded network: this rank's Gaussians only
+    x = torch.empty((r1 - r0, 192), dtype=torch.float32, device=dev)
+    x[:, :92] = encoded_normalized_initial_means_and_rotations[r0:r1]
+    x[:, 92:184] = encoded_normalized_previous_means_and_rotations[r0:r1]
+    progress = torch.full((r1 - r0, 1), timestep / timestep_count, dtype=torch.float32, device=dev)
     positional_encoding(progress, 4, out=x, col0=184)
-    delta = deformation_network(torch.cat((p["means"], p["rotation_quaternions"]), dim=1).detach(), network_input=x)
+    delta = deformation_network(torch.cat((p["means"][r0:r1], p["rotation_quaternions"][r0:r1]), dim=1).detach(),
+                                network_input=x)
+    if shard is not None:
+        delta = _GatherRows.apply(delta, shard, n)
     updated = dict(p)
     updated["means"] = p["means"].detach() + delta[:, :3] * 0.01
     updated["rotation_quaternions"] = p["rotation_quaternions"].detach() + delta[:, 3:] * 0.01

@@ -739,6 +739,8 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     enc_prev = enc0
     torch.manual_seed(0)
     net = deform.DeformationNetwork(256, 4, precise=True).to(dev)
+    if world > 1 and os.environ.get("GSB_BENCH_NET_SHARD", "1") != "0":
+        net.set_row_shard()     # every rank runs the network on its slice of the Gaussians (gsb200.deform row sharding)
     nopt = torch.optim.Adam(net.parameters(), lr=1e-4)
     ex = gd.Exchange(P1, dev)
     all_sc = scene.stack_cameras(cams, dev)
@@ -794,7 +796,8 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
                         "replicas_bit_identical": identical},
         "timesteps": {"count": timesteps, "ms_per_step_mean": float(np.mean(train_ms)), "ms_per_step_first": train_ms[0],
                       "steps_per_s": 1e3 / float(np.mean(train_ms)), "loss_first": losses[0], "loss_last": losses[-1],
-                      "knn_seconds": knn_s, "network": "replicated on every rank (precise mode: 3xTF32 forward / input gradients, FP32 weight gradients); views sharded"},
+                      "knn_seconds": knn_s, "network": ("row-sharded over the ranks (BatchNorm column sums, the [N, 7] output and the dense-layer gradients exchanged)"
+                                  if net.shard is not None else "one GPU") + "; precise mode (3xTF32 products); views sharded"},
         "peak_memory_bytes_per_gpu": int(peak.item()), "setup_seconds": setup_s,
     }
 

@@ -417,19 +417,24 @@ int gsb_linear_thin_wgrad(int64_t rows, int32_t M, int32_t H, const float* G, in
  * residual + exact (erf) GELU in one pass over Z [rows, N]: Y = act(gamma (Z - mean) / sqrt(var + eps) + beta
  * [+ residual]), mean / biased var from col_stats = the [2][N] sums gsb_linear_tf32 accumulated (train.py:57-78).
  * running_mean / running_var (both or neither) receive torch's momentum update with the unbiased variance.
- * N <= 256, N and all pitches multiples of 4. */
-int gsb_bn_gelu(int64_t rows, int32_t N, const float* Z, int64_t ldz, const double* col_stats, const float* gamma,
-                const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
+ * N <= 256, N and all pitches multiples of 4.  batch_rows: the number of rows col_stats was summed over -- 0 or rows
+ * for a whole batch; when the batch is sharded by rows over several GPUs (gsb200.deform row sharding) every rank passes
+ * its own rows, the column sums added over the ranks, and the batch's total row count here. */
+int gsb_bn_gelu(int64_t rows, int64_t batch_rows, int32_t N, const float* Z, int64_t ldz, const double* col_stats,
+                const float* gamma, const float* beta, float eps, const float* residual, int64_t ldr, float* Y, int64_t ldy,
                 float* running_mean, float* running_var, float momentum, int32_t apply_gelu, void* stream);
 
 /* Adjoint of gsb_bn_gelu (same arguments for the forward quantities): given dY it forms G = dY * act'(pre-activation)
  * (also the gradient of the residual input), the per-column sums (`sums`, DEVICE double[2][N], zeroed here) that are
  * d_beta = sum G and d_gamma = sum G xhat, and dZ = gamma inv_std (G - d_beta / rows - xhat d_gamma / rows).
- * dZ may alias G (in place) or be a separate buffer (G is then kept).  d_gamma / d_beta [N] optional. */
-int gsb_bn_gelu_backward(int64_t rows, int32_t N, const float* dY, int64_t ldd, const float* Z, int64_t ldz,
-                         const double* col_stats, const float* gamma, const float* beta, float eps,
-                         const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg, float* dZ,
-                         int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream);
+ * dZ may alias G (in place) or be a separate buffer (G is then kept).  d_gamma / d_beta [N] optional.
+ * batch_rows as in gsb_bn_gelu.  phase 0: the whole adjoint; phase 1: only the first pass (G and `sums` over this
+ * rank's rows); phase 2: only the second pass with `sums` as given -- a row-sharded batch adds the ranks' sums between
+ * the two. */
+int gsb_bn_gelu_backward(int64_t rows, int64_t batch_rows, int32_t phase, int32_t N, const float* dY, int64_t ldd,
+                         const float* Z, int64_t ldz, const double* col_stats, const float* gamma, const float* beta,
+                         float eps, const float* residual, int64_t ldr, int32_t apply_gelu, float* G, int64_t ldg,
+                         float* dZ, int64_t lddz, double* sums, float* d_gamma, float* d_beta, void* stream);
 
 /* PositionalEncoding (train.py:113-127) of x [rows, D] with F frequencies 2^k pi into out[:, col0 + j D + d],
  * j in [0, 2F): even j -> sin(f x), odd j -> cos(sin(f x)) (the reference's in-place quirk).  With lo / span [D]

@@ -159,3 +159,82 @@ def test_training_steps_follow_stock_torch():
             log.append(float(loss.detach()))
     assert lb[-1] < lb[0]
     assert max(abs(a - b) / a for a, b in zip(la, lb)) < 2e-2, (la, lb)
+
+
+def _row_shard_worker(rank, world, port, n, h, blocks, out_dir):
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "animating-gaussian-splats_b200")):
+        sys.path.insert(0, p)
+    import torch.distributed as dist
+    from gsb200 import deform
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = torch.device("cuda", rank % torch.cuda.device_count())
+    torch.cuda.set_device(dev)
+    case = torch.load(os.path.join(out_dir, "case.pt"))
+    net = deform.DeformationNetwork(h, blocks).to(dev)
+    net.load_state_dict(case["state"])
+    net.set_row_shard()
+    assert net.shard is not None and net.shard.world == world
+    p = {k: v.to(dev) for k, v in case["params"].items()}
+    enc0, encp = case["enc0"].to(dev), case["encp"].to(dev)
+    w = case["w"].to(dev)
+    outs = {}
+    for it in range(2):   # twice: the running statistics move, the cached batch row count is reused
+        net.zero_grad(set_to_none=True)
+        upd = deform.update_gaussian_cloud_parameters(net, p, enc0, encp, timestep=3, timestep_count=10)
+        full = torch.cat((upd["means"], upd["rotation_quaternions"]), dim=1)
+        assert full.shape == (n, 7)
+        (full * w).sum().backward()
+        outs[f"out{it}"] = full.detach().cpu()
+        for name, q in net.named_parameters():
+            outs[f"g{it}.{name}"] = q.grad.detach().cpu()
+    for name, b in net.named_buffers():
+        outs[f"buf.{name}"] = b.detach().cpu()
+    torch.save(outs, os.path.join(out_dir, f"r{rank}.pt"))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 20_001), (3, 4097)])
+def test_row_sharded_network_equals_replicated(tmp_path, world, n):
+    """The network on row slices (one process per slice; BatchNorm column sums, the [N, 7] output and the dense-layer
+    gradients exchanged) against the same network on all rows in this process: outputs, every parameter gradient and
+    the BatchNorm running statistics agree to summation order, and the ranks agree bit for bit."""
+    import os
+    import torch.multiprocessing as mp
+    from gsb200 import deform
+    h, blocks = 128, 2
+    torch.manual_seed(n)
+    ref = deform.DeformationNetwork(h, blocks).cuda()
+    with torch.no_grad():
+        for m in ref.modules():
+            if isinstance(m, nn.BatchNorm1d):
+                m.weight.uniform_(0.5, 1.5); m.bias.normal_(0, 0.3)
+    params = {"means": torch.randn(n, 3), "rotation_quaternions": torch.randn(n, 4), "colors": torch.rand(n, 3)}
+    enc0, encp, w = torch.randn(n, 92), torch.randn(n, 92), torch.randn(n, 7)
+    torch.save({"state": {k: v.cpu() for k, v in ref.state_dict().items()}, "params": params, "enc0": enc0, "encp": encp, "w": w},
+               tmp_path / "case.pt")
+    port = 29500 + (os.getpid() % 1500) + 10 + world
+    mp.spawn(_row_shard_worker, args=(world, port, n, h, blocks, str(tmp_path)), nprocs=world, join=True)
+    got = [torch.load(tmp_path / f"r{r}.pt") for r in range(world)]
+    p = {k: v.cuda() for k, v in params.items()}
+    want = {}
+    for it in range(2):
+        ref.zero_grad(set_to_none=True)
+        upd = deform.update_gaussian_cloud_parameters(ref, p, enc0.cuda(), encp.cuda(), timestep=3, timestep_count=10)
+        full = torch.cat((upd["means"], upd["rotation_quaternions"]), dim=1)
+        (full * w.cuda()).sum().backward()
+        want[f"out{it}"] = full.detach().cpu()
+        for name, q in ref.named_parameters():
+            want[f"g{it}.{name}"] = q.grad.detach().cpu()
+    for name, b in ref.named_buffers():
+        want[f"buf.{name}"] = b.detach().cpu()
+    assert set(want) == set(got[0])
+    for k, v in want.items():
+        for r in range(1, world):
+            assert torch.equal(got[r][k], got[0][k]), (k, r)            # replicas bit-identical
+        a, b = got[0][k].double(), v.double()
+        scale = b.pow(2).mean().sqrt().item() + 1e-12
+        assert (a - b).abs().max().item() / scale < 2e-4, (k, (a - b).abs().max().item() / scale)
