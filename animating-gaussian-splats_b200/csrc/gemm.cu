@@ -105,6 +105,8 @@ struct GemmParams {
   long long rows;
   int K, N, umma_n, stages, b_bytes;
   const float* bias;
+  const float* residual;   // optional [rows][N] tensor added to the output in the epilogue (row pitch ldr floats)
+  long long ldr;
   float* Y;
   long long ldy;
   double* col_stats;   // [2][N] column sums and sums of squares of Y over the rows (BatchNorm statistics), or NULL
@@ -250,11 +252,22 @@ linear_tf32_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
           __syncwarp();
           // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
           const int j = lane & 7;
+          float4 rq[8];
+          if (p.residual) {   // all eight loads in flight before the first store (Y may alias the residual element-wise)
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+              const long long grow = t * GM_BLOCK_M + q * 32 + i * 4 + (lane >> 3);
+              rq[i] = (grow < p.rows && c + 4 * j < p.N)
+                          ? __ldcs(reinterpret_cast<const float4*>(p.residual + grow * p.ldr + c + 4 * j))
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+          }
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const int r = i * 4 + (lane >> 3);
             const long long grow = t * GM_BLOCK_M + q * 32 + r;
-            const float4 o = *reinterpret_cast<const float4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
+            float4 o = *reinterpret_cast<const float4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
+            if (p.residual) { o.x += rq[i].x; o.y += rq[i].y; o.z += rq[i].z; o.w += rq[i].w; }
             if (grow < p.rows && c + 4 * j < p.N) *reinterpret_cast<float4*>(p.Y + grow * p.ldy + c + 4 * j) = o;
           }
           if (p.col_stats) {   // column `lane` of the chunk over this warp's valid rows (conflict-free: 32 consecutive floats)
@@ -579,8 +592,9 @@ static int sm_count() {
 template <bool SPLIT>
 static int launch_linear(long long rows, int K, int N, const float* X, long long ldx, const float* W, long long ldw,
                          const float* Wlo, const float* bias, float* Y, long long ldy, double* col_stats,
-                         cudaStream_t st) {
+                         cudaStream_t st, const float* residual = nullptr, long long ldr = 0) {
   GemmParams p;
+  p.residual = residual; p.ldr = ldr;
   p.col_stats = col_stats;
   p.rows = rows; p.K = K; p.N = N;
   p.umma_n = (N + 15) / 16 * 16;
@@ -589,6 +603,7 @@ static int launch_linear(long long rows, int K, int N, const float* X, long long
   const int stage_bytes = (GM_A_BYTES + p.b_bytes) * (SPLIT ? 2 : 1);
   p.tma_store = ((reinterpret_cast<uintptr_t>(Y) & 15u) == 0 && (ldy & 3) == 0 && (N & 3) == 0) ? 1 : 0;
   if (col_stats && !p.tma_store) return GSB_EINVAL;   // statistics come from the staged (vector) epilogue
+  if (residual && (!p.tma_store || (ldr & 3) || (reinterpret_cast<uintptr_t>(residual) & 15u))) return GSB_EINVAL;
   const int budget = 223 * 1024 - GM_EPI_BYTES;   // 227 KB per block minus static shared memory and alignment slack
   p.stages = budget / stage_bytes;
   if (p.stages > GM_MAX_STAGES) p.stages = GM_MAX_STAGES;
@@ -652,6 +667,23 @@ int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_
   split_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, W, hi, lo);
   GSB_LAUNCH_CHECK();
   return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, bias, Y, ldy, col_stats, st);
+}
+
+int gsb_linear_residual(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                        const float* residual, int64_t ldr, float* Y, int64_t ldy, int32_t precise, void* scratch,
+                        void* stream) {
+  if (rows == 0) return GSB_OK;
+  if (!linear_args_ok(rows, K, N, X, ldx, W, ldw, Y, ldy) || !residual || ldr < N) return GSB_EINVAL;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!precise)
+    return launch_linear<false>(rows, K, N, X, ldx, W, ldw, nullptr, nullptr, Y, ldy, nullptr, st, residual, ldr);
+  if (!scratch || ldw != K || (reinterpret_cast<uintptr_t>(scratch) & 15u)) return GSB_EINVAL;
+  float* hi = reinterpret_cast<float*>(scratch);
+  float* lo = hi + (size_t)N * K;
+  const long long n = (long long)N * K;
+  split_tf32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, W, hi, lo);
+  GSB_LAUNCH_CHECK();
+  return launch_linear<true>(rows, K, N, X, ldx, hi, K, lo, nullptr, Y, ldy, nullptr, st, residual, ldr);
 }
 
 size_t gsb_linear_wgrad_scratch_bytes(int32_t N, int32_t K) { return (size_t)148 * 2 * N * K * sizeof(float); }

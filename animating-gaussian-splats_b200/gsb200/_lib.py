@@ -128,6 +128,8 @@ SYMBOLS = {
     "gsb_linear_tf32x3_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_linear_tf32x3": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                     C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsb_linear_residual": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "gsb_linear_wgrad_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gsb_linear_wgrad_tf32": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                         C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),

@@ -272,8 +272,8 @@ class _DeformFn(torch.autograd.Function):
         # with allow_tf32) -- an opt-in fast mode
         precise = net.precise
 
-        def dx(g, w):
-            return linear(g, w.detach().t().contiguous(), None, precise=precise)
+        def dx(g, w, residual=None):
+            return linear(g, w.detach().t().contiguous(), None, precise=precise, residual=residual)
 
         def dw(g, a):
             return linear_wgrad(g, a, precise=precise)
@@ -288,8 +288,7 @@ class _DeformFn(torch.autograd.Function):
             dz1, _, dgam1, dbet1 = net._bn_bwd(da, z1, st1, block.bn1, None)
             grads[block.bn1.weight], grads[block.bn1.bias] = dgam1, dbet1
             grads[block.fc1.weight] = dw(dz1, identity)
-            dh = dx(dz1, block.fc1.weight)
-            dh += g2                                     # the residual branch
+            dh = dx(dz1, block.fc1.weight, residual=g2)   # + the residual branch's gradient, added in the GEMM epilogue
         grads[net.fc_in.weight] = dw(dh, x)
         grads[net.fc_in.bias] = dh.sum(0)
         ctx.keep = ctx.last = ctx.x = None

@@ -8,8 +8,9 @@ from . import _lib as L
 _scratch = {}
 
 
-def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
-    """col_stats: optional zeroed float64 [2, N] tensor receiving the column sums / sums of squares of the output."""
+def linear(x, weight, bias=None, precise=False, out=None, col_stats=None, residual=None):
+    """col_stats: optional zeroed float64 [2, N] tensor receiving the column sums / sums of squares of the output.
+    residual: optional [rows, N] tensor added to the output in the GEMM epilogue (no bias, no col_stats then)."""
     L.require_cuda(x, "x")
     x = x if (x.dtype == torch.float32 and x.stride(-1) == 1 and x.dim() == 2) else x.reshape(-1, x.shape[-1]).float().contiguous()
     w = weight.detach().float().contiguous()
@@ -23,6 +24,20 @@ def linear(x, weight, bias=None, precise=False, out=None, col_stats=None):
         if K % 4:
             raise RuntimeError("linear: K must be a multiple of 4 (TMA row pitch)")
     y = out if out is not None else torch.empty((rows, N), dtype=torch.float32, device=x.device)
+    if residual is not None:
+        if bias is not None or col_stats is not None:
+            raise RuntimeError("linear: residual excludes bias and col_stats")
+        r = residual if (residual.dtype == torch.float32 and residual.stride(-1) == 1) else residual.float().contiguous()
+        nbytes = L.lib().gsb_linear_tf32x3_scratch_bytes(K, N)
+        key = (x.device, nbytes)
+        if precise and key not in _scratch:
+            _scratch[key] = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+        with L.device_guard(x.device):
+            rc = L.lib().gsb_linear_residual(rows, K, N, L.ptr(x), x.stride(0), L.ptr(w), K, L.ptr(r), r.stride(0), L.ptr(y),
+                                             y.stride(0), 1 if precise else 0, L.ptr(_scratch[key]) if precise else None,
+                                             L.stream_ptr())
+        L.check(rc, "gsb_linear_residual")
+        return y
     with L.device_guard(x.device):
         if precise:
             nbytes = L.lib().gsb_linear_tf32x3_scratch_bytes(K, N)

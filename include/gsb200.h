@@ -386,6 +386,14 @@ size_t gsb_linear_tf32x3_scratch_bytes(int32_t K, int32_t N);
 int gsb_linear_tf32x3(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
                       const float* bias, float* Y, int64_t ldy, double* col_stats, void* scratch, void* stream);
 
+/* Y = X . W^T + residual[rows, N] (no bias): the dense layer with a second tensor added in the epilogue -- the input
+ * gradient of a residual block, dX = dZ1 . W1 + (gradient of the skip branch), without a separate pass over dX
+ * (train.py:57-78 under autograd).  precise != 0: the 3xTF32 form (scratch as for gsb_linear_tf32x3, ldw == K), else TF32
+ * (scratch ignored).  Y and residual 16-byte aligned, ldy, ldr and N multiples of 4; Y may alias residual. */
+int gsb_linear_residual(int64_t rows, int32_t K, int32_t N, const float* X, int64_t ldx, const float* W, int64_t ldw,
+                        const float* residual, int64_t ldr, float* Y, int64_t ldy, int32_t precise, void* scratch,
+                        void* stream);
+
 /* Weight gradient of the dense layer: dW[N, K] (dense, row pitch K) = G[rows, N]^T . X[rows, K] (+= when accumulate),
  * TF32 multiply / FP32 accumulate on tcgen05 with both operands MN-major (the reduction runs over the rows).
  * N, K multiples of 32 and <= 256; G, X 16-byte aligned with pitches multiples of 4; scratch: device buffer of

@@ -90,3 +90,18 @@ def test_thin_layer_backward_matches_float64(rows, M, H):
     assert ((dw.double() - want_dw).abs() / scale).max().item() < 4e-6
     want_db = go.double().sum(0)
     assert ((db.double() - want_db).abs().max() / (go.double().norm(dim=0).max() * rows ** 0.5 + 1e-30)).item() < 4e-6
+
+
+@pytest.mark.parametrize("precise", [False, True])
+@pytest.mark.parametrize("rows,K,N", [(1000, 192, 128), (300_001, 256, 256), (5, 64, 64)])
+def test_linear_with_residual_added_in_the_epilogue(rows, K, N, precise):
+    from gsb200.linear import linear
+    x, w, _, want, scale = _case(rows, K, N, seed=rows % 97, bias=False)
+    res = torch.randn(rows, N, generator=torch.Generator().manual_seed(1)).cuda()
+    y = linear(x, w, None, precise=precise, residual=res)
+    torch.cuda.synchronize()
+    err = ((y.double() - (want + res.double())).abs() / (scale + res.double().abs())).max().item()
+    assert err < (2e-6 if precise else 2e-3), err
+    inplace = res.clone()
+    linear(x, w, None, precise=precise, residual=inplace, out=inplace)     # Y may alias the residual
+    assert torch.equal(inplace, y)
