@@ -743,6 +743,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
         net.set_row_shard()     # every rank runs the network on its slice of the Gaussians (gsb200.deform row sharding)
     nopt = torch.optim.Adam(net.parameters(), lr=1e-4)
     ex = gd.Exchange(P1, dev)
+    varena = tt.ViewArena()      # host-free rendering: no read-back of the instance count inside the step
     all_sc = scene.stack_cameras(cams, dev)
     prng = random.Random(0)
     ts_list = [1 + (k * (T_total - 2)) // max(timesteps - 1, 1) for k in range(timesteps)]
@@ -764,7 +765,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
         e0.record()
         for _ in range(steps_per_timestep):
             loss, enc_t, fg_t = tt.train_step(net, nopt, init_p, enc0, enc_prev, fg_prev, ninfo, (sub, tgt), t, T_total,
-                                              exchange=ex, view_count=views_per_step)
+                                              exchange=ex, view_count=views_per_step, view_arena=varena)
         e1.record()
         torch.cuda.synchronize(dev)
         enc_prev, fg_prev = enc_t, fg_t
@@ -773,6 +774,7 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         train_ms.append(float(tm.item()))
         losses.append(float(loss))
+    varena.poll(wait=True)       # every step's status words: raises if a step's instances had not fit
     ex.close()
     peak = torch.tensor([float(torch.cuda.max_memory_allocated(dev))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -961,9 +963,10 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
     net = deform.DeformationNetwork(hidden, blocks, precise=True).to(dev)
     opt = torch.optim.Adam(net.parameters(), lr=1e-4)
     last = {}
+    varena = tt.ViewArena()   # host-free rendering (no read-back of the instance count inside the step)
 
     def ours(k):
-        loss, _, _ = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, sub(picks[k]), 7, 150)
+        loss, _, _ = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, sub(picks[k]), 7, 150, view_arena=varena)
         last["ours"] = loss
 
     res = {"what": f"one train.py step: DeformationNetwork ({hidden} x {blocks} blocks) over {args.gaussians} Gaussians, "
@@ -976,6 +979,7 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
     net = deform.DeformationNetwork(hidden, blocks, precise=False).to(dev)
     opt = torch.optim.Adam(net.parameters(), lr=1e-4)
     res["ours_tf32"] = timed(ours)
+    varena.poll(wait=True)
     ref = oracle_lib.load_reference_ext()
     if ref is None:
         return res

@@ -66,3 +66,39 @@ def test_train_steps_reduce_the_loss():
     assert all(torch.isfinite(torch.tensor(losses)))
     assert enc_next.shape == (4000, 92) and fg_next.offsets_to_neighbors.shape[1:] == (8, 3)
     assert sum(losses[-5:]) / 5 < 0.9 * sum(losses[:5]) / 5, losses
+
+
+def test_view_arena_renders_without_read_back_and_matches_the_blocking_path():
+    """ViewArena: the step through the capacity-guarded asynchronous forward equals the blocking path (same kernels),
+    over several steps with a changing number of views; a far too small arena is reported by poll() as ArenaOverflow."""
+    from gsb200 import raster, timestep_train as tt
+    raw, cams, stacked, settings = _scene(P=6000, n_cams=3)
+    keys = ("means", "rotation_quaternions", "colors", "opacity_logits", "log_scales")
+    gen = torch.Generator(device="cuda").manual_seed(4)
+    va = tt.ViewArena()
+    for n in (3, 2, 3, 3):
+        sub = {"viewmatrix": stacked["viewmatrix"][:n].contiguous(), "projmatrix": stacked["projmatrix"][:n].contiguous(),
+               "tanfovx": stacked["tanfovx"][:n], "tanfovy": stacked["tanfovy"][:n], "image_width": 96, "image_height": 64}
+        targets = torch.rand(n, 3, 64, 96, device="cuda", generator=gen)
+        a = {k: (raw[k].clone().requires_grad_(True) if k in keys else raw[k]) for k in raw}
+        b = {k: (raw[k].clone().requires_grad_(True) if k in keys else raw[k]) for k in raw}
+        la = tt.batched_image_loss(a, dict(sub), targets, view_arena=va)
+        la.backward()
+        lb = tt.batched_image_loss(b, dict(sub), targets)
+        lb.backward()
+        assert float(la.detach()) == float(lb.detach())
+        for k in keys:
+            bad, worst = helpers.grad_close(helpers.to_np(a[k].grad), helpers.to_np(b[k].grad), rel=1e-4, floor=2e-6)
+            assert bad == 0, (k, bad, worst)
+    va.poll(wait=True)
+    assert va.steps_monitored == 4 and len(va.arenas) == 2 and not va.pending
+    # an arena that cannot hold the instances: the step renders background, poll() reports it
+    key = next(k for k in va.arenas if k[1] == 3)
+    small = raster.RasterArena(raw["means"].device).reserve(6000, 3, 96, 64, 64)
+    va.arenas[key] = small
+    sub = {"viewmatrix": stacked["viewmatrix"], "projmatrix": stacked["projmatrix"], "tanfovx": stacked["tanfovx"],
+           "tanfovy": stacked["tanfovy"], "image_width": 96, "image_height": 64}
+    tt.batched_image_loss({k: v for k, v in raw.items()}, sub, torch.rand(3, 3, 64, 96, device="cuda", generator=gen), view_arena=va)
+    with pytest.raises(raster.ArenaOverflow):
+        va.poll(wait=True)
+    assert key not in va.arenas
