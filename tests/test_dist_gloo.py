@@ -84,3 +84,42 @@ def test_shard_cameras_cost_balanced():
         assert lpt <= rr + 1e-12
         assert lpt <= sum(costs) / world + max(costs)
     assert gd.shard_cameras(27, 3, 8) == list(range(3, 27, 8))
+
+
+def row_shard_worker(rank, world, port, n, out_dir):
+    sys.path.insert(0, os.path.join(ROOT, "animating-gaussian-splats_b200"))
+    from gsb200 import deform
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sh = deform.RowShard()
+    r0, r1 = sh.bounds(n)
+    full = torch.arange(n * 7, dtype=torch.float32).view(n, 7)
+    local = full[r0:r1].clone().requires_grad_(True)
+    gathered = deform._GatherRows.apply(local, sh, n)          # [n, 7] on every rank
+    w = torch.linspace(0.5, 1.5, n)[:, None]
+    (gathered * w).sum().backward()                           # every rank evaluates the same loss on the gathered rows
+    sums = torch.full((2, 4), float(rank + 1), dtype=torch.float64)
+    sh.all_reduce(sums)
+    np.savez(os.path.join(out_dir, f"shard{rank}.npz"), bounds=np.array([r0, r1]), gathered=gathered.detach().numpy(),
+             grad=local.grad.numpy(), sums=sums.numpy())
+    dist.destroy_process_group()
+
+
+def test_row_shard_collectives_three_ranks(tmp_path):
+    """gsb200.deform.RowShard on CPU tensors: contiguous row slices that cover [0, n) with a shorter last slice, the
+    all-gather of the slices and its adjoint (a rank's slice of the gradient), the column-sum all-reduce."""
+    world, n = 3, 100
+    port = 29500 + (os.getpid() % 2000) + 7
+    mp.spawn(row_shard_worker, args=(world, port, n, str(tmp_path)), nprocs=world, join=True)
+    got = [np.load(tmp_path / f"shard{r}.npz") for r in range(world)]
+    full = np.arange(n * 7, dtype=np.float32).reshape(n, 7)
+    w = np.linspace(0.5, 1.5, n, dtype=np.float32)[:, None]
+    edges = [tuple(g["bounds"]) for g in got]
+    assert edges[0][0] == 0 and edges[-1][1] == n and all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+    assert edges[0][1] - edges[0][0] == 34 and edges[2][1] - edges[2][0] == 32      # ceil(100 / 3) = 34, 34, 32
+    for r, g in enumerate(got):
+        assert np.array_equal(g["gathered"], full)
+        r0, r1 = edges[r]
+        assert np.allclose(g["grad"], np.broadcast_to(w[r0:r1], (r1 - r0, 7)))
+        assert np.array_equal(g["sums"], np.full((2, 4), 6.0))

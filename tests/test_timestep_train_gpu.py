@@ -102,3 +102,80 @@ def test_view_arena_renders_without_read_back_and_matches_the_blocking_path():
     with pytest.raises(raster.ArenaOverflow):
         va.poll(wait=True)
     assert key not in va.arenas
+
+
+def _sharded_case(dev):
+    """The same small training problem in every process: a cloud, 4 views, targets = the cloud moved by 3 cm."""
+    from gsb200 import deform, optim, raster, rigidity
+    torch.manual_seed(0)
+    raw, cams, stacked, settings = _scene(P=4000, n_cams=4, seed=1)
+    moved = dict(raw); moved["means"] = raw["means"] + torch.tensor([0.03, 0.0, 0.0], device=dev)
+    rot, opa, sca = optim.activate(moved)
+    with torch.no_grad():
+        targets, _, _, _ = raster.forward(moved["means"], moved["colors"], opa, sca, rot, None, torch.zeros(3, device=dev), 1.0,
+                                          stacked["viewmatrix"], stacked["projmatrix"], stacked["tanfovx"], stacked["tanfovy"],
+                                          64, 96, n_cams=4)
+    init = {k: v.clone() for k, v in raw.items()}
+    ninfo = rigidity.create_neighbor_info(init, k=8)
+    enc0 = deform.normalize_and_encode_means_and_rotations(init)
+    fg0 = rigidity.create_foreground_info(init, ninfo.indices)
+    torch.manual_seed(3)
+    net = deform.DeformationNetwork(64, 1, precise=True).to(dev)
+    return stacked, targets.clone(), init, ninfo, enc0, fg0, net
+
+
+def _sharded_train_worker(rank, world, port, steps, out_dir):
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "animating-gaussian-splats_b200"), os.path.join(root, "tests")):
+        sys.path.insert(0, p)
+    import torch.distributed as dist
+    from gsb200 import dist as gd, timestep_train as tt
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = torch.device("cuda", rank % torch.cuda.device_count())
+    torch.cuda.set_device(dev)
+    stacked, targets, init, ninfo, enc0, fg0, net = _sharded_case(dev)
+    net.set_row_shard()
+    opt = torch.optim.Adam(net.parameters(), lr=2e-3)
+    ex = gd.Exchange(init["means"].shape[0], dev)
+    va = tt.ViewArena()
+    mine = list(range(rank, 4, world))
+    sub = {"viewmatrix": stacked["viewmatrix"][mine].contiguous(), "projmatrix": stacked["projmatrix"][mine].contiguous(),
+           "tanfovx": [stacked["tanfovx"][i] for i in mine], "tanfovy": [stacked["tanfovy"][i] for i in mine],
+           "image_width": 96, "image_height": 64}
+    losses = []
+    for _ in range(steps):
+        loss, _, _ = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, (sub, targets[mine].contiguous()), 1, 1,
+                                   exchange=ex, view_count=4, view_arena=va)
+        losses.append(float(loss))
+    va.poll(wait=True)
+    torch.save({"losses": losses, "state": {k: v.cpu() for k, v in net.state_dict().items()}}, os.path.join(out_dir, f"t{rank}.pt"))
+    ex.close()
+    dist.destroy_process_group()
+
+
+def test_two_process_training_equals_one_process(tmp_path):
+    """train.py's step with the views sharded over two processes (one flat-record exchange per step), the network
+    row-sharded (BatchNorm sums, [N, 7] output, dense-layer gradients exchanged) and host-free rendering, against the same
+    steps in this process: the loss follows the same trajectory and both ranks hold bit-identical networks."""
+    import os
+    import torch.multiprocessing as mp
+    from gsb200 import timestep_train as tt
+    steps = 6
+    port = 29500 + (os.getpid() % 1500) + 20
+    mp.spawn(_sharded_train_worker, args=(2, port, steps, str(tmp_path)), nprocs=2, join=True)
+    got = [torch.load(tmp_path / f"t{r}.pt") for r in range(2)]
+    dev = torch.device("cuda")
+    stacked, targets, init, ninfo, enc0, fg0, net = _sharded_case(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=2e-3)
+    want = []
+    for _ in range(steps):
+        loss, _, _ = tt.train_step(net, opt, init, enc0, enc0, fg0, ninfo, (stacked, targets), 1, 1)
+        want.append(float(loss))
+    assert got[0]["losses"] == got[1]["losses"]
+    for k, v in got[0]["state"].items():
+        assert torch.equal(v, got[1]["state"][k]), k
+    for a, b in zip(got[0]["losses"], want):
+        assert abs(a - b) <= 2e-3 * abs(b), (got[0]["losses"], want)
