@@ -24,7 +24,12 @@ class ViewArena:
     blocking render with `slack` x the instances it needed, then every step renders through the capacity-guarded
     asynchronous forward.  The call's status words travel to pinned host memory behind the step (no wait); poll()
     reads the copies that have arrived, grows the arena when a step used more than `grow_at` of it, and raises
-    ArenaOverflow if a step did not fit (its images were background and its image gradients zero)."""
+    ArenaOverflow if a step did not fit (its images were background and its image gradients zero).
+
+    The arena is sized from the FIRST view set of a given size, so `slack` has to cover how much the instance count
+    differs between the view sets that follow: 1.5 is enough for 5 views sampled from a 27-camera rig (their sum varies
+    by ~10 %), NOT for a single camera that changes every timestep (one camera of that rig needs 1.5x the instances of
+    another) -- when the views are sharded so thinly, pass a larger slack or keep the blocking forward (view_arena=None)."""
 
     def __init__(self, slack=1.5, grow_at=0.8):
         self.slack, self.grow_at = float(slack), float(grow_at)

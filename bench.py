@@ -741,9 +741,13 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
     net = deform.DeformationNetwork(256, 4, precise=True).to(dev)
     if world > 1 and os.environ.get("GSB_BENCH_NET_SHARD", "1") != "0":
         net.set_row_shard()     # every rank runs the network on its slice of the Gaussians (gsb200.deform row sharding)
-    nopt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    nopt = goptim.FusedAdam(net.parameters(), lr=1e-4)   # torch.optim.Adam's update, every table in two launches
     ex = gd.Exchange(P1, dev)
-    varena = tt.ViewArena()      # host-free rendering: no read-back of the instance count inside the step
+    # host-free rendering (no read-back of the instance count inside the step) where a rank renders several of the
+    # step's views; with the views spread over several ranks a rank holds ONE camera that changes from timestep to
+    # timestep, and cameras differ by more than the arena's slack in instances (an 8-GPU run overflowed an arena sized
+    # from the first camera: 898 k instances against a capacity of 587 k), so those runs keep the blocking forward
+    varena = tt.ViewArena() if world == 1 else None
     all_sc = scene.stack_cameras(cams, dev)
     prng = random.Random(0)
     ts_list = [1 + (k * (T_total - 2)) // max(timesteps - 1, 1) for k in range(timesteps)]
@@ -774,7 +778,8 @@ def c5_sequence(args, world, rank, dev, P0=150_000, P_gt=600_000, steps_per_even
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         train_ms.append(float(tm.item()))
         losses.append(float(loss))
-    varena.poll(wait=True)       # every step's status words: raises if a step's instances had not fit
+    if varena is not None:
+        varena.poll(wait=True)   # every step's status words: raises if a step's instances had not fit
     ex.close()
     peak = torch.tensor([float(torch.cuda.max_memory_allocated(dev))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -931,7 +936,7 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
     import helpers
     import oracle_lib
     from torch import nn
-    from gsb200 import scene, deform, rigidity as R, timestep_train as tt
+    from gsb200 import scene, deform, optim as goptim, rigidity as R, timestep_train as tt
     dev = torch.device("cuda", torch.cuda.current_device())
     g_raw, tgt_raw, cams = build_workload(args)
     sc = scene.stack_cameras(cams, dev)
@@ -961,7 +966,7 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
 
     torch.manual_seed(0)
     net = deform.DeformationNetwork(hidden, blocks, precise=True).to(dev)
-    opt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    opt = goptim.FusedAdam(net.parameters(), lr=1e-4)   # torch.optim.Adam's update, every table in two launches
     last = {}
     varena = tt.ViewArena()   # host-free rendering (no read-back of the instance count inside the step)
 
@@ -977,7 +982,7 @@ def train_step_shaped(args, hidden=256, blocks=4, views=5, neighbours=20, iters=
                               "`stock` (torch FP32); ours_tf32: TF32 everywhere (opt-in fast mode)")
     torch.manual_seed(0)
     net = deform.DeformationNetwork(hidden, blocks, precise=False).to(dev)
-    opt = torch.optim.Adam(net.parameters(), lr=1e-4)
+    opt = goptim.FusedAdam(net.parameters(), lr=1e-4)
     res["ours_tf32"] = timed(ours)
     varena.poll(wait=True)
     ref = oracle_lib.load_reference_ext()
