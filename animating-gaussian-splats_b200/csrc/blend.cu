@@ -13,8 +13,6 @@
 // multi-value shuffle reduction (14 SHFL for 9 values) and only the per-warp sums go to global
 // atomics in one RED instruction (the reference issues 9 global atomics per pixel-Gaussian pair).
 // Warps skip list entries behind their deepest contributor, and whole batches behind the tile's.
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace gsb {
@@ -178,9 +176,6 @@ __device__ __forceinline__ TileCoord tile_coord(const uint32_t* __restrict__ ord
 
 #ifndef GSB_FWD_MINB
 #define GSB_FWD_MINB 6
-#endif
-#ifndef GSB_BWD_MINB
-#define GSB_BWD_MINB 4
 #endif
 // COUNT: the measurement variant behind gsb_raster_count_pairs -- the same walk, no image outputs; per camera it
 // adds up the walked pairs (sum of n_contrib) and the pairs actually composited (alpha >= 1/255 and not the
@@ -402,183 +397,12 @@ __device__ __forceinline__ void warp_reduce8(float (&v)[8], unsigned lane) {
   v[0] += __shfl_xor_sync(full, v[0], 1);
 }
 
-__global__ void __launch_bounds__(GSB_BLOCK_SIZE, GSB_BWD_MINB)
-render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int tiles_x, int tiles_pc,
-                  const uint32_t* __restrict__ point_list, int W, int H, int P,
-                  const float* __restrict__ bg, const float2* __restrict__ means2D,
-                  const float4* __restrict__ conic_opacity, const float* __restrict__ colors, int color_cam_stride,
-                  const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
-                  const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D,
-                  float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
-  __shared__ float4 s_a[GSB_BLOCK_SIZE];   // x, y, early-reject power threshold, bits(list position)
-  __shared__ float4 s_co[GSB_BLOCK_SIZE];  // conic a, b, c, opacity
-  __shared__ float4 s_ci[GSB_BLOCK_SIZE];  // r, g, b, bits(id)
-  __shared__ int s_wcnt[GSB_BLOCK_SIZE / 32];
-  __shared__ int s_block_last;
-  __shared__ int s_warp_last[GSB_BLOCK_SIZE / 32];
-
-  const TileCoord tc = tile_coord(order, tiles_x, tiles_pc);
-  const int cam = tc.cam;
-  const uint32_t tiles_per_cam = (uint32_t)tiles_pc;
-  const uint32_t tile = tc.tile;
-  const unsigned tid = threadIdx.y * GSB_BLOCK_X + threadIdx.x;
-  const unsigned lane = tid & 31u;
-  const uint32_t px = tc.bx * GSB_BLOCK_X + ((tid >> 5) & 1u) * 8u + (tid & 7u);   // 8x4 patch per warp
-  const uint32_t py = tc.by * GSB_BLOCK_Y + (tid >> 6) * 4u + ((tid >> 3) & 3u);
-  const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pfx = (float)px, pfy = (float)py;
-  const float tx0 = (float)(tc.bx * GSB_BLOCK_X), ty0 = (float)(tc.by * GSB_BLOCK_Y);
-  const size_t HW = (size_t)H * W;
-  const size_t pid = (size_t)py * W + px;
-
-  const uint2 range = ranges[(size_t)cam * tiles_per_cam + tile];
-  const size_t cam_off = (size_t)cam * P;
-  const float* col_tab = colors + (size_t)cam * color_cam_stride;
-  float* dcol_tab = dL_dcolor + (size_t)cam * color_cam_stride;
-
-  const float T_final = inside ? final_Ts[cam * HW + pid] : 0.f;
-  float T = T_final;
-  const int last_contributor = inside ? (int)n_contrib[cam * HW + pid] : 0;
-  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f;
-  if (inside) {
-    const float* dp = dL_dpixels + (size_t)cam * 3 * HW;
-    dpx0 = dp[pid]; dpx1 = dp[HW + pid]; dpx2 = dp[2 * HW + pid];
-  }
-  float bg_dot = 0.f;
-  bg_dot += bg[0] * dpx0; bg_dot += bg[1] * dpx1; bg_dot += bg[2] * dpx2;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // accum_rec
-  const float nTf_bg = -T_final * bg_dot;
-
-  // this lane's gradient slot: lanes 0,4,..,28 own the 8 reduced components, lane 1 the opacity gradient
-  float* lane_base;
-  unsigned lane_stride;
-  {
-    const unsigned comp = lane >> 2;
-    if (lane == 1) { lane_base = dL_dopacity; lane_stride = 1; }
-    else if (comp < 3) { lane_base = dcol_tab + comp; lane_stride = 3; }
-    else if (comp < 5) { lane_base = dL_dmean2D + 3 * cam_off + (comp - 3); lane_stride = 3; }
-    else { lane_base = dL_dconic + 4 * cam_off + (comp == 7 ? 3 : comp - 5); lane_stride = 4; }
-  }
-  const bool lane_writes = ((lane & 3u) == 0) || lane == 1;
-
-  // deepest contributor of the warp / of the tile: entries at list positions >= that are dead
-  int warp_last = last_contributor;
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, s));
-  if (tid == 0) s_block_last = 0;
-  __syncthreads();
-  if (lane == 0) {
-    s_warp_last[tid >> 5] = warp_last;
-    if (warp_last > 0) atomicMax(&s_block_last, warp_last);
-  }
-  __syncthreads();
-  const int block_last = s_block_last;   // list positions [0, block_last) matter
-  if (block_last == 0) return;
-
-  // walk positions block_last-1 ... 0 in batches of 256 (back to front)
-  const int rounds = (block_last + GSB_BLOCK_SIZE - 1) / GSB_BLOCK_SIZE;
-  for (int i = 0; i < rounds; i++) {
-    if (i > 0) __syncthreads();
-    const int pos_mine = block_last - 1 - i * GSB_BLOCK_SIZE - (int)tid;  // list position staged by this thread
-    bool keep = false;
-    uint32_t id = 0;
-    float2 xy = make_float2(0.f, 0.f);
-    float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
-    float thr = 0.f;
-    if (pos_mine >= 0) {
-      id = point_list[range.x + (uint32_t)pos_mine];
-      xy = means2D[cam_off + id];
-      co = conic_opacity[cam_off + id];
-      keep = tile_cull_keep<true>(xy.x, xy.y, co, tx0, ty0, thr);
-      if (keep) {
-        // fold "behind warp w's deepest contributor" into the patch mask, so the walk tests one bit per entry
-        unsigned m = __float_as_uint(thr) & 0xFFu;
-#pragma unroll
-        for (int w = 0; w < GSB_BLOCK_SIZE / 32; w++)
-          if (pos_mine >= s_warp_last[w]) m &= ~(1u << w);
-        thr = pack_thr(thr, m);
-        keep = m != 0;
-      }
-    }
-    int slot;
-    const int n = compact_slot(keep, tid, s_wcnt, slot);
-    if (keep) {
-      s_a[slot] = make_float4(xy.x, xy.y, thr, __int_as_float(pos_mine));
-      s_co[slot] = co;
-      s_ci[slot] = make_float4(col_tab[3 * (size_t)id], col_tab[3 * (size_t)id + 1], col_tab[3 * (size_t)id + 2],
-                               __uint_as_float(id));
-    }
-    __syncthreads();
-    for (int j = 0; j < n; j++) {
-      const float4 a = s_a[j];
-      const int pos = __float_as_int(a.w);
-      // warp-uniform: the entry cannot reach this warp's 8x4 patch, or lies behind its deepest contributor
-      if (!((__float_as_uint(a.z) >> (tid >> 5)) & 1u)) continue;
-      const float4 co2 = s_co[j];
-      const float dx = SUB(a.x, pfx), dy = SUB(a.y, pfy);
-      const float power = blend_power(dx, dy, co2.x, co2.y, co2.z);
-      const bool pre = (pos < last_contributor) && !(power > 0.0f) && !(power < a.z);
-      if (!__any_sync(0xffffffffu, pre)) continue;
-      const float G = expf(power);
-      const float alpha = fminf(0.99f, MUL(co2.w, G));
-      const bool valid = pre && !(alpha < 1.0f / 255.0f);
-      if (!__any_sync(0xffffffffu, valid)) continue;
-
-      float v[8];
-      float g_op = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; k++) v[k] = 0.f;
-      const float4 ci = s_ci[j];
-      if (valid) {
-        // 1 / (1 - alpha): MUFU.RCP + one Newton step (the reference divides twice, cr/backward.cu:503,534)
-        const float om = 1.f - alpha;
-        float rcp;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(om));
-        rcp = fmaf(rcp, fmaf(-om, rcp, 1.f), rcp);
-        T = T * rcp;
-        const float dchannel_dcolor = alpha * T;
-        // accum_rec of cr/backward.cu:515 is kept up to date eagerly: after this entry it becomes
-        // alpha c + (1 - alpha) accum_rec = accum_rec + alpha (c - accum_rec), the value the reference forms at the
-        // next contributing entry from last_alpha / last_color.
-        const float d0 = ci.x - ar0, d1 = ci.y - ar1, d2 = ci.z - ar2;
-        float dL_dalpha = d0 * dpx0;
-        dL_dalpha = fmaf(d1, dpx1, dL_dalpha);
-        dL_dalpha = fmaf(d2, dpx2, dL_dalpha);
-        ar0 = fmaf(alpha, d0, ar0);
-        ar1 = fmaf(alpha, d1, ar1);
-        ar2 = fmaf(alpha, d2, ar2);
-        v[0] = dchannel_dcolor * dpx0;
-        v[1] = dchannel_dcolor * dpx1;
-        v[2] = dchannel_dcolor * dpx2;
-        dL_dalpha = fmaf(dL_dalpha, T, nTf_bg * rcp);   // T (...) - T_final / (1 - alpha) * sum_c bg_c dL/dpix_c
-        // First and second moments of w = dL/dG * G over the pixels; the linear maps to dL/dmean2D
-        // (-ddelx_dx (A S1 + B S2), -ddely_dy (C S2 + B S1)) and dL/dconic (-0.5 q) are applied once per
-        // Gaussian in preprocess_bwd instead of once per pixel here (cr/backward.cu:536-548).
-        g_op = G * dL_dalpha;
-        const float wg = co2.w * g_op;
-        const float s1 = wg * dx, s2 = wg * dy;
-        v[3] = s1;
-        v[4] = s2;
-        v[5] = s1 * dx;
-        v[6] = s1 * dy;
-        v[7] = s2 * dy;
-      }
-      warp_reduce8(v, lane);
-#pragma unroll
-      for (int s = 16; s >= 1; s >>= 1) g_op += __shfl_xor_sync(0xffffffffu, g_op, s);
-
-      const uint32_t id2 = __float_as_uint(ci.w);
-      const float val = (lane == 1) ? g_op : v[0];
-      if (lane_writes && val != 0.f) atomicAdd(lane_base + id2 * lane_stride, val);   // 32-bit index: P * 4 < 2^32
-    }
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // Backward, two pixels per thread: 128 threads per tile, a warp owns an 8x8 block = two of the 8x4 patches
 // above (rows y and y + 4 of the same column), so one staged entry that touches both patches costs ONE
 // loop iteration, ONE 9-value warp reduction and ONE atomic instruction instead of two.  Per-pixel
-// arithmetic is the same as render_bwd_kernel's; only the order in which partial sums meet changes.
+// arithmetic is the reference's; only the order in which partial sums meet changes.  (A one-pixel-per-thread kernel,
+// 256 threads per tile, preceded this one: 2.64 vs 2.21 ms at C2; removed.)
 // ------------------------------------------------------------------------------------------------
 struct BwdPixel {
   float T, ar0, ar1, ar2, dpx0, dpx1, dpx2, nTf_bg, pfy;
@@ -861,8 +685,6 @@ int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const f
                       float* dL_dcolor2, float* dL_dmean2D_first) {
   const int tiles_pc = c.tiles_x * c.tiles_y, tiles_total = tiles_pc * a.n_cams;
   const uint32_t* order = use_tile_order(tiles_total) ? c.ranges + 2 * (size_t)tiles_total : nullptr;
-  dim3 block(GSB_BLOCK_X, GSB_BLOCK_Y);
-  static const int two_px = [] { const char* e = getenv("GSB_BWD_2PX"); return e ? atoi(e) : 1; }();
   if (dL_dpix2) {   // both images of a two-table forward in one walk
     if (!a.colors2 || !dL_dcolor2 || !dL_dmean2D_first || a.color_cam_stride != 0) return GSB_EINVAL;
     render_bwd2_kernel<true><<<tiles_total, 128, 0, st>>>(
@@ -874,21 +696,12 @@ int launch_render_bwd(const gsb_raster_args& a, const gsb_raster_ctx& c, const f
     GSB_LAUNCH_CHECK();
     return GSB_OK;
   }
-  if (two_px) {
-    render_bwd2_kernel<false><<<tiles_total, 128, 0, st>>>(
-        reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
-        a.background,
-        reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
-        a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, nullptr,
-        nullptr, nullptr, nullptr);
-    GSB_LAUNCH_CHECK();
-    return GSB_OK;
-  }
-  render_bwd_kernel<<<tiles_total, block, 0, st>>>(
+  render_bwd2_kernel<false><<<tiles_total, 128, 0, st>>>(
       reinterpret_cast<const uint2*>(c.ranges), order, c.tiles_x, tiles_pc, c.point_list, a.width, a.height, a.P,
       a.background,
       reinterpret_cast<const float2*>(c.means2D), reinterpret_cast<const float4*>(c.conic_opacity), a.colors,
-      a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+      a.color_cam_stride, c.final_T, c.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, nullptr,
+      nullptr, nullptr, nullptr);
   GSB_LAUNCH_CHECK();
   return GSB_OK;
 }
