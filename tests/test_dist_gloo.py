@@ -123,3 +123,49 @@ def test_row_shard_collectives_three_ranks(tmp_path):
         r0, r1 = edges[r]
         assert np.allclose(g["grad"], np.broadcast_to(w[r0:r1], (r1 - r0, 7)))
         assert np.array_equal(g["sums"], np.full((2, 4), 6.0))
+
+
+def test_shard_bands_partition_properties():
+    """Tile-band sharding host logic (gsb200.dist.shard_bands / band_tables / flat_width) on random cost tables: the
+    bands tile every (camera, tile row) exactly once in order, a rank holds at most two partial cameras, exactly the
+    cameras held by more than one rank get a split slot, the loads stay within one row's cost of the ideal share, and the
+    entry / row tables carry one halo tile row per open edge with visibility counted by the band that holds row 0."""
+    sys.path.insert(0, os.path.join(ROOT, "animating-gaussian-splats_b200"))
+    import random
+    from gsb200 import dist as gd
+    rng = random.Random(5)
+    for trial in range(60):
+        n_cams, gy, world = rng.randint(1, 9), rng.randint(1, 23), rng.randint(1, 8)
+        costs = [[rng.uniform(0.1, 3.0) for _ in range(gy)] for _ in range(n_cams)]
+        bands, slots = gd.shard_bands(costs, world)
+        assert len(bands) == world
+        seen = []
+        for mine in bands:
+            partial = 0
+            for cam, r0, r1 in mine:
+                assert 0 <= r0 < r1 <= gy
+                partial += (r1 - r0) < gy
+                seen += [(cam, r) for r in range(r0, r1)]
+            assert partial <= 2
+        assert seen == [(c, r) for c in range(n_cams) for r in range(gy)]           # exactly once, in order
+        owners = {}
+        for rk, mine in enumerate(bands):
+            for cam, _, _ in mine:
+                owners.setdefault(cam, set()).add(rk)
+        split = sorted(c for c, o in owners.items() if len(o) > 1)
+        assert sorted(slots) == split and sorted(slots.values()) == list(range(len(split)))
+        total = sum(map(sum, costs))
+        biggest = max(map(max, costs))
+        for mine in bands:
+            load = sum(costs[cam][r] for cam, r0, r1 in mine for r in range(r0, r1))
+            assert load <= total / world + biggest + 1e-9
+        assert gd.flat_width(len(split)) % 4 == 0 and gd.flat_width(len(split)) >= gd.WIDTH + 2 * len(split)
+        height = 16 * gy - rng.randint(0, 15)
+        for mine in bands:
+            if not mine:
+                continue
+            ent, rows = gd.band_tables(mine, slots, gy, height, "cpu")
+            for (cam, r0, r1), e, rw in zip(mine, ent.tolist(), rows.tolist()):
+                assert e[0] == max(r0 - 1, 0) and e[1] == min(r1 + 1, gy)
+                assert e[2] == slots.get(cam, -1) and e[3] == (1 if r0 == 0 else 0)
+                assert rw == [16 * r0, min(16 * r1, height), 16 * e[0], min(16 * e[1], height)]
